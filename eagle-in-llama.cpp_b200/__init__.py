@@ -1,0 +1,413 @@
+"""eagle_b200 — host-side mirror of the reference's operator / decode interface for the EAGLE
+speculative-step hot path, over the C-ABI of libeagle_b200.so (include/eagle_b200.h).
+
+Names follow the reference: ggml ops (mul_mat, flash_attn_ext, rms_norm, rope, get_rows, top_k …,
+R/ggml/include/ggml.h) and the llama.cpp decode surface (a model with GGUF tensors, a session
+with KV caches, forward over a tree-shaped batch, one speculative round).  Everything runs on
+the GPU through the shared library; there is NO CPU fallback — importing works anywhere, but
+any compute call raises if the library or an sm_100 device is missing.
+
+The directory name contains '-' and '.', so import it through `load_package()` in
+__graft_entry__.py / tests/conftest.py, which registers it as module `eagle_b200`.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libeagle_b200.so")
+
+F32, F16, Q4_0, Q8_0, Q4_K, Q6_K = 0, 1, 2, 8, 12, 14
+BLOCK = {F32: (1, 4), F16: (1, 2), Q4_0: (32, 18), Q8_0: (32, 34), Q4_K: (256, 144), Q6_K: (256, 210)}
+T_TOK_EMBD, T_OUTPUT_NORM, T_OUTPUT, T_FC, T_FC_BIAS = range(5)
+L_ATTN_NORM, L_WQ, L_WK, L_WV, L_WO, L_FFN_NORM, L_GATE, L_UP, L_DOWN = range(9)
+
+
+class EagleB200Error(RuntimeError):
+    pass
+
+
+class SessionParams(C.Structure):
+    _fields_ = [("n_ctx", C.c_int), ("max_nodes", C.c_int), ("n_branch", C.c_int), ("n_draft", C.c_int),
+                ("max_depth", C.c_int), ("top_k", C.c_int), ("p_split", C.c_float), ("fixed_accept", C.c_int),
+                ("use_graph", C.c_int)]
+
+
+class RoundResult(C.Structure):
+    _fields_ = [("n_nodes", C.c_int), ("n_accept", C.c_int), ("bonus", C.c_int32), ("tokens", C.c_int32 * 128),
+                ("parent", C.c_int32 * 128), ("path", C.c_int32 * 128), ("gpu_ms", C.c_float)]
+
+
+_lib = None
+
+
+def lib():
+    """Load libeagle_b200.so (built by `make` / __graft_entry__.build()).  Fails loudly."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise EagleB200Error(f"{LIB_PATH} is missing: run `make` (or __graft_entry__.build()); there is no CPU fallback")
+    L = C.CDLL(LIB_PATH)
+    vp, i32, i64, f32, sz = C.c_void_p, C.c_int, C.c_int64, C.c_float, C.c_size_t
+    sig = {
+        "eb_last_error": ([], C.c_char_p), "eb_version": ([], i32), "eb_device_init": ([i32], i32),
+        "eb_device_sm_count": ([], i32), "eb_row_size": ([i32, i64], sz),
+        "eb_malloc": ([C.POINTER(vp), sz], i32), "eb_free": ([vp], i32), "eb_memset": ([vp, i32, sz, vp], i32),
+        "eb_upload": ([vp, vp, sz, vp], i32), "eb_download": ([vp, vp, sz, vp], i32), "eb_synchronize": ([vp], i32),
+        "eb_repack": ([i32, vp, vp, i64, vp], i32), "eb_unpack": ([i32, vp, vp, i64, vp], i32),
+        "eb_quantize_act_planes": ([i32, vp, i64, i32, vp, vp, vp, vp], i32),
+        "eb_dequantize": ([i32, vp, vp, i64, vp], i32),
+        "eb_mul_mat_ws_size": ([i32, i64, i64, i64], sz),
+        "eb_mul_mat": ([i32, vp, i64, i64, vp, i64, vp, vp, vp], i32),
+        "eb_rms_norm": ([vp, vp, vp, i64, i64, f32, vp], i32),
+        "eb_rope_norm": ([vp, vp, i32, i32, i32, f32, vp], i32),
+        "eb_get_rows_n": ([i32, vp, i64, i64, vp, i32, vp, vp], i32),
+        "eb_add": ([vp, vp, vp, i64, i64, vp], i32), "eb_mul": ([vp, vp, vp, i64, i64, vp], i32),
+        "eb_silu": ([vp, vp, i64, vp], i32), "eb_relu": ([vp, vp, i64, vp], i32),
+        "eb_cpy_f32_f16": ([vp, vp, i64, vp], i32),
+        "eb_flash_attn_ws_size": ([i32, i32, i32, i32], sz),
+        "eb_flash_attn": ([vp, vp, vp, i64, vp, i64, vp, i32, i32, i32, i32, i32, f32, vp, vp, vp], i32),
+        "eb_top_k": ([vp, i32, i32, i32, vp, vp, vp, vp], i32), "eb_argmax": ([vp, i32, i32, vp, vp], i32),
+        "eb_model_create": ([i32, i32, i32, i32, i32, f32, f32, i32], vp), "eb_model_free": ([vp], None),
+        "eb_model_set_tensor": ([vp, i32, i32, i32, vp], i32),
+        "eb_model_synth_tensor": ([vp, i32, i32, i32, C.c_uint64, f32], i32),
+        "eb_model_get_tensor": ([vp, i32, i32, vp, sz], i32),
+        "eb_model_share_lm_head": ([vp, vp], i32), "eb_model_weight_bytes": ([vp], sz),
+        "eb_session_create": ([vp, vp, C.POINTER(SessionParams)], vp), "eb_session_free": ([vp], None),
+        "eb_session_forward": ([vp, i32, vp, vp, vp, vp, i32, vp, vp], i32),
+        "eb_session_commit": ([vp, i32, i32], i32), "eb_session_n_past": ([vp, i32], i32),
+        "eb_session_synth_kv": ([vp, i32, C.c_uint64], i32), "eb_session_set_root": ([vp, C.c_int32, vp], i32),
+        "eb_session_round": ([vp, C.POINTER(RoundResult)], i32),
+        "eb_session_verify_only": ([vp, i32, C.POINTER(f32)], i32),
+        "eb_bench_mul_mat_kernel": ([i32, i64, i64, i32, i32, i32, C.POINTER(f32)], i32),
+        "eb_launch_count": ([i32], C.c_long),
+    }
+    for name, (args, res) in sig.items():
+        fn = getattr(L, name)
+        fn.argtypes, fn.restype = args, res
+    _lib = L
+    return L
+
+
+EXPORTS = None  # filled by tests: every symbol declared in include/eagle_b200.h
+
+
+def _ck(rc):
+    if rc != 0:
+        raise EagleB200Error(f"eagle_b200 error {rc}: {lib().eb_last_error().decode()}")
+
+
+def init(device=0):
+    _ck(lib().eb_device_init(device))
+
+
+def row_size(t, k):
+    be, bb = BLOCK[t]
+    assert k % be == 0, (t, k)
+    return k // be * bb
+
+
+def _hp(a):
+    if a is None:
+        return None
+    assert isinstance(a, np.ndarray) and a.flags["C_CONTIGUOUS"]
+    return a.ctypes.data_as(C.c_void_p)
+
+
+class DeviceBuffer:
+    """A device allocation (ggml_backend_buffer: alloc / set_tensor / get_tensor)."""
+
+    def __init__(self, nbytes):
+        self.ptr = C.c_void_p()
+        self.nbytes = int(nbytes)
+        _ck(lib().eb_malloc(C.byref(self.ptr), self.nbytes))
+
+    @classmethod
+    def from_host(cls, arr):
+        arr = np.ascontiguousarray(arr)
+        b = cls(max(arr.nbytes, 1))
+        if arr.nbytes:
+            _ck(lib().eb_upload(b.ptr, _hp(arr), arr.nbytes, None))
+        return b
+
+    def to_host(self, dtype, shape):
+        out = np.empty(shape, dtype)
+        assert out.nbytes <= self.nbytes
+        if out.nbytes:
+            _ck(lib().eb_download(_hp(out), self.ptr, out.nbytes, None))
+        return out
+
+    def free(self):
+        if self.ptr:
+            lib().eb_free(self.ptr)
+            self.ptr = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+
+def upload_weights(t, raw, n_elems):
+    """GGUF block bytes (host) -> device layout buffer (set_tensor)."""
+    src = DeviceBuffer.from_host(np.ascontiguousarray(raw).view(np.uint8))
+    if t in (Q4_0, Q8_0, Q6_K):
+        dst = DeviceBuffer(src.nbytes)
+        _ck(lib().eb_repack(t, src.ptr, dst.ptr, n_elems, None))
+        _ck(lib().eb_synchronize(None))
+        src.free()
+        return dst
+    return src
+
+
+def download_weights(t, buf, n_elems):
+    """device layout buffer -> GGUF block bytes (get_tensor)."""
+    nbytes = row_size(t, n_elems)
+    if t in (Q4_0, Q8_0, Q6_K):
+        tmp = DeviceBuffer(nbytes)
+        _ck(lib().eb_unpack(t, buf.ptr, tmp.ptr, n_elems, None))
+        return tmp.to_host(np.uint8, nbytes)
+    return buf.to_host(np.uint8, nbytes)
+
+
+# ---- ggml ops over host buffers (each call: H2D, kernel(s), D2H) -------------------------------
+def dequantize(t, raw, n_elems):
+    w = upload_weights(t, raw, n_elems)
+    out = DeviceBuffer(n_elems * 4)
+    _ck(lib().eb_dequantize(t, w.ptr, out.ptr, n_elems, None))
+    return out.to_host(np.float32, n_elems)
+
+
+def quantize_act(kq, x):
+    """-> (qs int8 [T][K], d f32 [T][K/B], bsum f32 [T][K/16] or None)"""
+    x = np.ascontiguousarray(x, np.float32)
+    T, K = x.shape
+    B = 256 if kq else 32
+    dx = DeviceBuffer.from_host(x)
+    qs, d = DeviceBuffer(T * K), DeviceBuffer(T * (K // B) * 4)
+    bs = DeviceBuffer(T * (K // 16) * 2) if kq else None
+    _ck(lib().eb_quantize_act_planes(int(kq), dx.ptr, K, T, qs.ptr, d.ptr, bs.ptr if bs else None, None))
+    return (qs.to_host(np.int8, (T, K)), d.to_host(np.float32, (T, K // B)),
+            bs.to_host(np.float16, (T, K // 16)).astype(np.float32) if bs else None)
+
+
+class Weights:
+    """A quantised matrix resident on the device (rows = output features)."""
+
+    def __init__(self, t, raw, N, K):
+        self.t, self.N, self.K = t, N, K
+        self.buf = upload_weights(t, raw, N * K)
+
+
+def mul_mat(w, x):
+    """GGML_OP_MUL_MAT: w Weights [N][K], x f32 [T][K] -> f32 [T][N]"""
+    x = np.ascontiguousarray(x, np.float32).reshape(-1, w.K)
+    T = x.shape[0]
+    dx, dy = DeviceBuffer.from_host(x), DeviceBuffer(T * w.N * 4)
+    ws = DeviceBuffer(lib().eb_mul_mat_ws_size(w.t, w.N, w.K, min(T, 128)))
+    _ck(lib().eb_mul_mat(w.t, w.buf.ptr, w.N, w.K, dx.ptr, T, dy.ptr, ws.ptr, None))
+    return dy.to_host(np.float32, (T, w.N))
+
+
+def rms_norm(x, eps, weight=None):
+    x = np.ascontiguousarray(x, np.float32)
+    n = x.shape[-1]
+    dx, dy = DeviceBuffer.from_host(x), DeviceBuffer(x.nbytes)
+    dw = DeviceBuffer.from_host(np.ascontiguousarray(weight, np.float32)) if weight is not None else None
+    _ck(lib().eb_rms_norm(dx.ptr, dw.ptr if dw else None, dy.ptr, n, x.size // n, eps, None))
+    return dy.to_host(np.float32, x.shape)
+
+
+def rope_norm(x, pos, freq_base):
+    x = np.ascontiguousarray(x, np.float32)
+    T, H, D = x.shape
+    dx, dp = DeviceBuffer.from_host(x), DeviceBuffer.from_host(np.ascontiguousarray(pos, np.int32))
+    _ck(lib().eb_rope_norm(dx.ptr, dp.ptr, D, H, T, freq_base, None))
+    return dx.to_host(np.float32, x.shape)
+
+
+def get_rows(w, ids):
+    ids = np.ascontiguousarray(ids, np.int32)
+    di, out = DeviceBuffer.from_host(ids), DeviceBuffer(ids.size * w.K * 4)
+    _ck(lib().eb_get_rows_n(w.t, w.buf.ptr, w.N, w.K, di.ptr, ids.size, out.ptr, None))
+    return out.to_host(np.float32, (ids.size, w.K))
+
+
+def _binary(fn, a, b):
+    a = np.ascontiguousarray(a, np.float32); b = np.ascontiguousarray(b, np.float32)
+    da, db, dy = DeviceBuffer.from_host(a), DeviceBuffer.from_host(b), DeviceBuffer(a.nbytes)
+    _ck(fn(da.ptr, db.ptr, dy.ptr, a.size, b.size, None))
+    return dy.to_host(np.float32, a.shape)
+
+
+def add(a, b):
+    return _binary(lib().eb_add, a, b)
+
+
+def mul(a, b):
+    return _binary(lib().eb_mul, a, b)
+
+
+def _unary(fn, x):
+    x = np.ascontiguousarray(x, np.float32)
+    dx, dy = DeviceBuffer.from_host(x), DeviceBuffer(x.nbytes)
+    _ck(fn(dx.ptr, dy.ptr, x.size, None))
+    return dy.to_host(np.float32, x.shape)
+
+
+def silu(x):
+    return _unary(lib().eb_silu, x)
+
+
+def relu(x):
+    return _unary(lib().eb_relu, x)
+
+
+def tree_bits_from_parent(parent):
+    """ancestor-or-self sets, 128 bits per row (the compact tree mask)"""
+    T = len(parent)
+    bits = np.zeros((T, 4), np.uint32)
+    for t in range(T):
+        if parent[t] >= 0:
+            bits[t] = bits[parent[t]]
+        bits[t, t >> 5] |= np.uint32(1 << (t & 31))
+    return bits
+
+
+def flash_attn_ext(q, k, v, scale, mask_f16=None, tree_bits=None, n_prefix=0):
+    """GGML_OP_FLASH_ATTN_EXT.  q f32 [T][H][D]; k, v f16 [n_kv][H][D]; mask_f16 [T_pad][n_kv]
+    (0 / -inf) or the compact tree form (tree_bits [T][4] u32 + n_prefix)."""
+    q = np.ascontiguousarray(q, np.float32)
+    T, H, D = q.shape
+    k = np.ascontiguousarray(k).view(np.uint16); v = np.ascontiguousarray(v).view(np.uint16)
+    n_kv = k.shape[0]
+    dq, dk, dv, do = DeviceBuffer.from_host(q), DeviceBuffer.from_host(k), DeviceBuffer.from_host(v), DeviceBuffer(q.nbytes)
+    ws = DeviceBuffer(lib().eb_flash_attn_ws_size(T, H, D, n_kv))
+    dm = db = None
+    stride = 0
+    if mask_f16 is not None:
+        m = np.ascontiguousarray(mask_f16, np.float16)
+        stride = m.shape[1]
+        dm = DeviceBuffer.from_host(m.view(np.uint16))
+    else:
+        db = DeviceBuffer.from_host(np.ascontiguousarray(tree_bits, np.uint32))
+    _ck(lib().eb_flash_attn(dq.ptr, dk.ptr, dv.ptr, H * D, dm.ptr if dm else None, stride, db.ptr if db else None,
+                            n_prefix, T, H, D, n_kv, scale, do.ptr, ws.ptr, None))
+    return do.to_host(np.float32, q.shape)
+
+
+def top_k(logits, k):
+    logits = np.ascontiguousarray(logits, np.float32)
+    rows, V = logits.shape
+    dl = DeviceBuffer.from_host(logits)
+    di, dv, dp = DeviceBuffer(rows * k * 4), DeviceBuffer(rows * k * 4), DeviceBuffer(rows * k * 4)
+    _ck(lib().eb_top_k(dl.ptr, rows, V, k, di.ptr, dv.ptr, dp.ptr, None))
+    return di.to_host(np.int32, (rows, k)), dv.to_host(np.float32, (rows, k)), dp.to_host(np.float32, (rows, k))
+
+
+def argmax(logits):
+    logits = np.ascontiguousarray(logits, np.float32)
+    rows, V = logits.shape
+    dl, di = DeviceBuffer.from_host(logits), DeviceBuffer(rows * 4)
+    _ck(lib().eb_argmax(dl.ptr, rows, V, di.ptr, None))
+    return di.to_host(np.int32, rows)
+
+
+# ---- engine ---------------------------------------------------------------------------------
+class Model:
+    """Weights of one GGUF model in HBM (llama target or eagle head)."""
+
+    def __init__(self, E, H, F, V, L, eps=1e-5, freq_base=10000.0, is_eagle=False):
+        self.E, self.H, self.F, self.V, self.L, self.is_eagle = E, H, F, V, L, bool(is_eagle)
+        self.eps, self.freq_base = eps, freq_base
+        self.h = lib().eb_model_create(E, H, F, V, L, eps, freq_base, int(is_eagle))
+        if not self.h:
+            raise EagleB200Error(lib().eb_last_error().decode())
+
+    def set_tensor(self, layer, which, t, raw):
+        raw = np.ascontiguousarray(raw)
+        _ck(lib().eb_model_set_tensor(self.h, layer, which, t, _hp(raw)))
+
+    def synth_tensor(self, layer, which, t, seed, scale=0.02):
+        _ck(lib().eb_model_synth_tensor(self.h, layer, which, t, seed, scale))
+
+    def get_tensor(self, layer, which, nbytes):
+        out = np.empty(nbytes, np.uint8)
+        _ck(lib().eb_model_get_tensor(self.h, layer, which, _hp(out), nbytes))
+        return out
+
+    def share_lm_head(self, target):
+        _ck(lib().eb_model_share_lm_head(self.h, target.h))
+
+    def weight_bytes(self):
+        return int(lib().eb_model_weight_bytes(self.h))
+
+    def free(self):
+        if self.h:
+            lib().eb_model_free(self.h)
+            self.h = None
+
+
+class Session:
+    """One decoding stream: target + draft head + both KV caches + device-side tree state."""
+
+    def __init__(self, target, head=None, n_ctx=4096, max_nodes=65, n_branch=8, n_draft=64, max_depth=8, top_k=10,
+                 p_split=0.1, fixed_accept=-1, use_graph=True):
+        self.target, self.head = target, head
+        self.params = SessionParams(n_ctx, max_nodes, n_branch, n_draft, max_depth, top_k, p_split, fixed_accept, int(use_graph))
+        self.h = lib().eb_session_create(target.h, head.h if head else None, C.byref(self.params))
+        if not self.h:
+            raise EagleB200Error(lib().eb_last_error().decode())
+
+    def forward(self, model, tokens, pos, parent=None, hidden=None, want_logits=True):
+        """llama_decode over a tree-shaped batch (host buffers in, host buffers out)."""
+        tokens = np.ascontiguousarray(tokens, np.int32); pos = np.ascontiguousarray(pos, np.int32)
+        T = tokens.size
+        m = self.head if model else self.target
+        par = None if parent is None else np.ascontiguousarray(parent, np.int32)
+        hid = None if hidden is None else np.ascontiguousarray(hidden, np.float32)
+        logits = np.empty((T, m.V), np.float32) if want_logits else None
+        feat = np.empty((T, m.E), np.float32)
+        _ck(lib().eb_session_forward(self.h, model, _hp(tokens), _hp(pos), _hp(par), _hp(hid), T, _hp(logits), _hp(feat)))
+        return logits, feat
+
+    def commit(self, model, n):
+        _ck(lib().eb_session_commit(self.h, model, n))
+
+    def n_past(self):
+        return lib().eb_session_n_past(self.h, 0)
+
+    def synth_kv(self, n_past, seed=1):
+        _ck(lib().eb_session_synth_kv(self.h, n_past, seed))
+
+    def set_root(self, id_last, feat=None):
+        f = None if feat is None else np.ascontiguousarray(feat, np.float32)
+        _ck(lib().eb_session_set_root(self.h, int(id_last), _hp(f)))
+
+    def round(self):
+        r = RoundResult()
+        _ck(lib().eb_session_round(self.h, C.byref(r)))
+        return r
+
+    def verify_only(self, T):
+        ms = C.c_float()
+        _ck(lib().eb_session_verify_only(self.h, T, C.byref(ms)))
+        return ms.value
+
+    def free(self):
+        if self.h:
+            lib().eb_session_free(self.h)
+            self.h = None
+
+
+def bench_mul_mat_kernel(t, N, K, T, n_bufs=8, iters=50):
+    ms = C.c_float()
+    _ck(lib().eb_bench_mul_mat_kernel(t, N, K, T, n_bufs, iters, C.byref(ms)))
+    return ms.value
+
+
+def launch_count(reset=False):
+    return int(lib().eb_launch_count(int(reset)))

@@ -1,0 +1,176 @@
+// capi.cu — the operator-layer C-ABI (include/eagle_b200.h) over the kernels, plus device
+// bring-up, error reporting and launch accounting.
+#include "engine.cuh"
+#include <atomic>
+#include <cstdarg>
+#include <vector>
+
+thread_local std::string g_eb_err;
+static std::atomic<long> g_launches{0};
+static int g_sm_count = 0;
+static int g_device = -1;
+
+int eb_set_err(int code, const char *fmt, ...) {
+    char buf[1024]; va_list ap; va_start(ap, fmt); vsnprintf(buf, sizeof(buf), fmt, ap); va_end(ap);
+    g_eb_err = buf;
+    return code;
+}
+void eb_count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
+int eb_sm_count() { return g_sm_count > 0 ? g_sm_count : 148; }
+
+extern "C" {
+
+const char *eb_last_error(void) { return g_eb_err.c_str(); }
+int eb_version(void) { return 100; }
+long eb_launch_count(int reset) { return reset ? g_launches.exchange(0) : g_launches.load(); }
+
+int eb_device_init(int device) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess || n == 0) { cudaGetLastError(); return eb_set_err(EB_ERR_CUDA, "no CUDA device: this library has no CPU fallback"); }
+    if (device < 0 || device >= n) return eb_set_err(EB_ERR_ARG, "device %d of %d", device, n);
+    cudaDeviceProp prop;
+    EB_CUDA(cudaGetDeviceProperties(&prop, device));
+    if (prop.major != 10) return eb_set_err(EB_ERR_UNSUPPORTED, "device %d is sm_%d%d; this library is built for sm_100a only", device, prop.major, prop.minor);
+    EB_CUDA(cudaSetDevice(device));
+    g_sm_count = prop.multiProcessorCount; g_device = device;
+    int rc;
+    if ((rc = eb_mmq_init()) || (rc = eb_fattn_init()) || (rc = eb_spec_init())) return rc;
+    return EB_OK;
+}
+int eb_device_sm_count(void) { return g_sm_count; }
+
+size_t eb_row_size(int type, int64_t k) {
+    switch (type) {
+        case EB_F32: return (size_t)k * 4;
+        case EB_F16: return (size_t)k * 2;
+        case EB_Q4_0: return k % 32 ? 0 : (size_t)(k / 32) * 18;
+        case EB_Q8_0: return k % 32 ? 0 : (size_t)(k / 32) * 34;
+        case EB_Q4_K: return k % 256 ? 0 : (size_t)(k / 256) * 144;
+        case EB_Q6_K: return k % 256 ? 0 : (size_t)(k / 256) * 210;
+    }
+    return 0;
+}
+
+#define NEED_DEV() do { if (g_device < 0) { int rc_ = eb_device_init(0); if (rc_) return rc_; } } while (0)
+static inline cudaStream_t S(void *s) { return (cudaStream_t)s; }
+
+int eb_malloc(void **p, size_t bytes) { NEED_DEV(); if (cudaMalloc(p, bytes ? bytes : 1) != cudaSuccess) { cudaGetLastError(); return eb_set_err(EB_ERR_OOM, "cudaMalloc(%zu)", bytes); } return EB_OK; }
+int eb_free(void *p) { EB_CUDA(cudaFree(p)); return EB_OK; }
+int eb_memset(void *p, int v, size_t bytes, void *st) { EB_CUDA(cudaMemsetAsync(p, v, bytes, S(st))); return EB_OK; }
+int eb_upload(void *d, const void *h, size_t bytes, void *st) { NEED_DEV(); EB_CUDA(cudaMemcpyAsync(d, h, bytes, cudaMemcpyHostToDevice, S(st))); EB_CUDA(cudaStreamSynchronize(S(st))); return EB_OK; }
+int eb_download(void *h, const void *d, size_t bytes, void *st) { EB_CUDA(cudaMemcpyAsync(h, d, bytes, cudaMemcpyDeviceToHost, S(st))); EB_CUDA(cudaStreamSynchronize(S(st))); return EB_OK; }
+int eb_synchronize(void *st) { EB_CUDA(cudaStreamSynchronize(S(st))); return EB_OK; }
+
+// GGUF block layout <-> device layout (aligned planes), see common.cuh WPlanes
+int eb_repack(int type, const void *d_gguf, void *d_dev, int64_t n_elems, void *st) {
+    NEED_DEV();
+    if (type == EB_Q4_0 || type == EB_Q8_0 || type == EB_Q6_K) return eb_repack_impl(type, const_cast<void *>(d_gguf), d_dev, n_elems / (type == EB_Q6_K ? 256 : 32), 0, S(st));
+    EB_CUDA(cudaMemcpyAsync(d_dev, d_gguf, eb_row_size(type, n_elems), cudaMemcpyDeviceToDevice, S(st)));
+    return EB_OK;
+}
+int eb_unpack(int type, const void *d_dev, void *d_gguf, int64_t n_elems, void *st) {
+    NEED_DEV();
+    if (type == EB_Q4_0 || type == EB_Q8_0 || type == EB_Q6_K) return eb_repack_impl(type, d_gguf, const_cast<void *>(d_dev), n_elems / (type == EB_Q6_K ? 256 : 32), 1, S(st));
+    EB_CUDA(cudaMemcpyAsync(d_gguf, d_dev, eb_row_size(type, n_elems), cudaMemcpyDeviceToDevice, S(st)));
+    return EB_OK;
+}
+
+int eb_dequantize(int type, const void *d_src, float *d_dst, int64_t n_elems, void *st) {
+    NEED_DEV();
+    const int be = (type == EB_Q4_K || type == EB_Q6_K) ? 256 : (type == EB_Q4_0 || type == EB_Q8_0) ? 32 : 1;
+    return eb_dequantize_impl(type, d_src, n_elems / be, 0, d_dst, n_elems, S(st));
+}
+
+size_t eb_mul_mat_ws_size(int type, int64_t N, int64_t K, int64_t T) {
+    (void)type;
+    return 2 * eb_actq_bytes(1, K, (int)T) + (size_t)8 * T * N * 4 + 1024;
+}
+int eb_mul_mat(int type, const void *d_W, int64_t N, int64_t K, const float *d_x, int64_t T, float *d_y, void *d_ws, void *st) {
+    NEED_DEV();
+    if (T < 1) return EB_OK;
+    if (!d_ws) return eb_set_err(EB_ERR_ARG, "mul_mat: workspace required");
+    const size_t aq = 2 * eb_actq_bytes(1, K, (int)T);
+    // batches beyond one verify tile are processed in column chunks of 128
+    for (int64_t t0 = 0; t0 < T; t0 += 128) {
+        const int tc = (int)std::min<int64_t>(128, T - t0);
+        int rc = eb_mul_mat_impl(type, d_W, N, K, d_x + t0 * K, tc, d_y + t0 * N, d_ws, (float *)((char *)d_ws + ((aq + 255) & ~(size_t)255)), S(st));
+        if (rc) return rc;
+    }
+    return EB_OK;
+}
+// activation quantiser exposed for the parity tests: planes as documented in common.cuh
+int eb_quantize_act_planes(int kq, const float *d_x, int64_t K, int T, int8_t *d_qs, float *d_d, void *d_bsum_f16, void *st) {
+    NEED_DEV();
+    ActQ a; a.qs = d_qs; a.d = d_d; a.bsum = (__half *)d_bsum_f16; a.K = K; a.T = T; a.kq = kq;
+    return eb_quantize_act(d_x, a, S(st));
+}
+
+int eb_rms_norm(const float *x, const float *w, float *y, int64_t n, int64_t rows, float eps, void *st) { NEED_DEV(); return eb_rms_norm_impl(x, w, y, n, rows, eps, S(st)); }
+int eb_rope_norm(float *x, const int32_t *pos, int D, int n_head, int T, float freq_base, void *st) { NEED_DEV(); return eb_rope_norm_impl(x, pos, D, n_head, T, freq_base, S(st)); }
+int eb_get_rows_n(int type, const void *W, int64_t n_rows, int64_t K, const int32_t *ids, int n, float *out, void *st) { NEED_DEV(); return eb_get_rows_dev(type, W, n_rows, K, ids, n, out, S(st)); }
+int eb_add(const float *a, const float *b, float *y, int64_t n, int64_t nb, void *st) { NEED_DEV(); return eb_add_impl(a, b, y, n, nb, S(st)); }
+int eb_mul(const float *a, const float *b, float *y, int64_t n, int64_t nb, void *st) { NEED_DEV(); return eb_mul_impl(a, b, y, n, nb, S(st)); }
+int eb_silu(const float *x, float *y, int64_t n, void *st) { NEED_DEV(); return eb_silu_impl(x, y, n, S(st)); }
+int eb_relu(const float *x, float *y, int64_t n, void *st) { NEED_DEV(); return eb_relu_impl(x, y, n, S(st)); }
+int eb_cpy_f32_f16(const float *x, void *y, int64_t n, void *st) { NEED_DEV(); return eb_cpy_f32_f16_impl(x, y, n, S(st)); }
+
+size_t eb_flash_attn_ws_size(int T, int H, int D, int n_kv) { return eb_flash_attn_ws_size_impl(T, H, D, n_kv); }
+int eb_flash_attn(const float *q, const void *k, const void *v, int64_t kv_stride, const void *mask, int64_t mask_stride,
+                  const uint32_t *tree_bits, int n_prefix, int T, int H, int D, int n_kv, float scale, float *out, void *ws, void *st) {
+    NEED_DEV();
+    return eb_flash_attn_impl(q, k, v, kv_stride, mask, mask_stride, tree_bits, n_prefix, T, H, D, n_kv, scale, out, ws, S(st));
+}
+int eb_top_k(const float *logits, int rows, int V, int k, int32_t *ids, float *vals, float *probs, void *st) { NEED_DEV(); return eb_top_k_impl(logits, rows, V, k, ids, vals, probs, S(st)); }
+int eb_argmax(const float *logits, int rows, int V, int32_t *ids, void *st) { NEED_DEV(); return eb_argmax_impl(logits, rows, V, ids, S(st)); }
+
+
+// Micro-bench of ONE hot kernel launch class, timed with CUDA events on the launching stream:
+// the GEMM (T > 8) or matvec (T <= 8) over `n_bufs` distinct weight buffers in rotation (so that
+// weights always come from HBM, not L2).  Activations are pre-quantised outside the timed region.
+// Returns the average milliseconds per launch in *ms_per_launch.
+int eb_bench_mul_mat_kernel(int type, int64_t N, int64_t K, int T, int n_bufs, int iters, float *ms_per_launch) {
+    NEED_DEV();
+    if (n_bufs < 1 || iters < 1 || T < 1 || T > 128) return eb_set_err(EB_ERR_ARG, "bench: bad arguments");
+    const size_t wbytes = eb_row_size(type, K) * N;
+    if (!wbytes) return eb_set_err(EB_ERR_ARG, "bench: type/K");
+    std::vector<void *> w(n_bufs, nullptr);
+    float *x = nullptr, *y = nullptr, *partial = nullptr; void *aq = nullptr;
+    cudaStream_t st; cudaEvent_t e0, e1;
+    EB_CUDA(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking)); EB_CUDA(cudaEventCreate(&e0)); EB_CUDA(cudaEventCreate(&e1));
+    int rc = EB_OK;
+    const int kq = (type == EB_Q4_K || type == EB_Q6_K);
+    for (int i = 0; i < n_bufs && !rc; i++) {
+        if (cudaMalloc(&w[i], wbytes + 256) != cudaSuccess) { rc = eb_set_err(EB_ERR_OOM, "bench: weights"); break; }
+        void *tmp = w[i];
+        if (type == EB_Q6_K || type == EB_Q4_0 || type == EB_Q8_0) {     // synth writes GGUF order; planes need a repack
+            if (cudaMalloc(&tmp, wbytes) != cudaSuccess) { rc = eb_set_err(EB_ERR_OOM, "bench: tmp"); break; }
+        }
+        rc = eb_synth_impl(type, tmp, N * K, 1234 + i, 0.02f, 0, st);
+        if (!rc && tmp != w[i]) { rc = eb_repack_impl(type, tmp, w[i], N * K / (kq ? 256 : 32), 0, st); cudaStreamSynchronize(st); cudaFree(tmp); }
+    }
+    if (!rc && (cudaMalloc((void **)&x, (size_t)T * K * 4) || cudaMalloc((void **)&y, (size_t)T * N * 4) ||
+                cudaMalloc((void **)&partial, (size_t)8 * T * N * 4) || cudaMalloc(&aq, eb_actq_bytes(kq, K, T) + 256)))
+        rc = eb_set_err(EB_ERR_OOM, "bench: activations");
+    if (!rc) rc = eb_synth_impl(EB_F32, x, (int64_t)T * K, 99, 1.0f, 0, st);
+    ActQ a = eb_actq_carve(aq, kq, K, T);
+    if (!rc) rc = eb_quantize_act(x, a, st);
+    const bool use_mmq = eb_mmq_supported(type, N, K, T);
+    const int ks = use_mmq ? eb_mmq_pick_ksplit(type, N, K, T) : 1;
+    auto one = [&](int i) { return use_mmq ? eb_mmq(type, w[i % n_bufs], N, K, a, y, partial, ks, st) : eb_mmvq(type, w[i % n_bufs], N, K, a, y, st); };
+    for (int i = 0; i < 3 && !rc; i++) rc = one(i);
+    if (!rc) {
+        cudaStreamSynchronize(st);
+        cudaEventRecord(e0, st);
+        for (int i = 0; i < iters && !rc; i++) rc = one(i);
+        cudaEventRecord(e1, st);
+        if (cudaStreamSynchronize(st) != cudaSuccess) rc = eb_set_err(EB_ERR_CUDA, "bench: %s", cudaGetErrorString(cudaGetLastError()));
+        float ms = 0; cudaEventElapsedTime(&ms, e0, e1);
+        if (ms_per_launch) *ms_per_launch = ms / iters;
+    }
+    for (void *p : w) cudaFree(p);
+    cudaFree(x); cudaFree(y); cudaFree(partial); cudaFree(aq);
+    cudaEventDestroy(e0); cudaEventDestroy(e1); cudaStreamDestroy(st);
+    return rc;
+}
+
+}  // extern "C"

@@ -1,0 +1,443 @@
+// engine.cu — the speculative-step engine: weights resident in HBM, tree-verify forward of the
+// target (build_llama, R/src/llama.cpp:1647-1811), draft-head forward (build_eagle, :1839-2019),
+// device-side tree expansion / accept walk / KV compaction, the whole round replayed as one CUDA
+// graph.  No ggml graph rebuild, no host-side mask build, no logits download per step.
+#include "engine.cuh"
+#include <cmath>
+#include <cstring>
+
+static int tensor_shape(const eb_model *m, int layer, int which, int64_t &rows, int64_t &cols) {
+    const int64_t E = m->E, F = m->F, V = m->V;
+    if (layer < 0) {
+        switch (which) {
+            case EB_T_TOK_EMBD: rows = V; cols = E; return 0;
+            case EB_T_OUTPUT_NORM: rows = 1; cols = E; return 0;
+            case EB_T_OUTPUT: rows = V; cols = E; return 0;
+            case EB_T_FC: rows = E; cols = 2 * E; return 0;
+            case EB_T_FC_BIAS: rows = 1; cols = E; return 0;
+        }
+        return -1;
+    }
+    switch (which) {
+        case EB_L_ATTN_NORM: case EB_L_FFN_NORM: rows = 1; cols = E; return 0;
+        case EB_L_WQ: case EB_L_WK: case EB_L_WV: case EB_L_WO: rows = E; cols = E; return 0;
+        case EB_L_GATE: case EB_L_UP: rows = F; cols = E; return 0;
+        case EB_L_DOWN: rows = E; cols = F; return 0;
+    }
+    return -1;
+}
+static DTensor *slot(eb_model *m, int layer, int which) {
+    if (layer < 0) return (which >= 0 && which < EB_T_GLOBAL_COUNT) ? &m->g[which] : nullptr;
+    if (layer >= m->L || which < 0 || which >= EB_L_COUNT) return nullptr;
+    return &m->layers[layer][which];
+}
+static bool is_planar(int type) { return type == EB_Q4_0 || type == EB_Q8_0 || type == EB_Q6_K; }
+static int block_elems(int type) { return (type == EB_Q4_K || type == EB_Q6_K) ? 256 : (type == EB_Q4_0 || type == EB_Q8_0) ? 32 : 1; }
+
+extern "C" eb_model *eb_model_create(int E, int H, int F, int V, int L, float eps, float freq_base, int is_eagle) {
+    if (E <= 0 || H <= 0 || E % H || E % 256 || F % 256 || L <= 0) { eb_set_err(EB_ERR_ARG, "model_create: E=%d H=%d F=%d L=%d (E,F must be multiples of 256)", E, H, F, L); return nullptr; }
+    eb_model *m = new eb_model();
+    m->E = E; m->H = H; m->F = F; m->V = V; m->L = L; m->eps = eps; m->freq_base = freq_base; m->is_eagle = is_eagle;
+    m->layers.assign(L, std::vector<DTensor>(EB_L_COUNT));
+    return m;
+}
+extern "C" void eb_model_free(eb_model *m) {
+    if (!m) return;
+    for (auto &t : m->g) if (t.owned) cudaFree(t.data);
+    for (auto &l : m->layers) for (auto &t : l) if (t.owned) cudaFree(t.data);
+    delete m;
+}
+static int alloc_tensor(eb_model *m, int layer, int which, int type, DTensor **out) {
+    DTensor *t = slot(m, layer, which);
+    int64_t rows, cols;
+    if (!t || tensor_shape(m, layer, which, rows, cols)) return eb_set_err(EB_ERR_ARG, "bad tensor slot %d/%d", layer, which);
+    if (cols % block_elems(type)) return eb_set_err(EB_ERR_ARG, "tensor %d/%d: cols %lld not a multiple of the block size", layer, which, (long long)cols);
+    const size_t bytes = eb_row_size(type, cols) * rows;
+    if (bytes == 0) return eb_set_err(EB_ERR_UNSUPPORTED, "tensor type %d", type);
+    if (t->owned) cudaFree(t->data);
+    *t = DTensor();
+    EB_CUDA(cudaMalloc(&t->data, bytes + 256));
+    t->type = type; t->rows = rows; t->cols = cols; t->bytes = bytes; t->owned = true;
+    *out = t;
+    return EB_OK;
+}
+extern "C" int eb_model_set_tensor(eb_model *m, int layer, int which, int type, const void *h_data) {
+    DTensor *t; int rc = alloc_tensor(m, layer, which, type, &t); if (rc) return rc;
+    if (is_planar(type)) {
+        void *tmp; EB_CUDA(cudaMalloc(&tmp, t->bytes));
+        EB_CUDA(cudaMemcpy(tmp, h_data, t->bytes, cudaMemcpyHostToDevice));
+        rc = eb_repack_impl(type, tmp, t->data, t->rows * t->cols / block_elems(type), 0, 0);
+        EB_CUDA(cudaDeviceSynchronize()); cudaFree(tmp);
+        return rc;
+    }
+    EB_CUDA(cudaMemcpy(t->data, h_data, t->bytes, cudaMemcpyHostToDevice));
+    return EB_OK;
+}
+extern "C" int eb_model_synth_tensor(eb_model *m, int layer, int which, int type, uint64_t seed, float scale) {
+    DTensor *t; int rc = alloc_tensor(m, layer, which, type, &t); if (rc) return rc;
+    const bool norm = (layer < 0 && which == EB_T_OUTPUT_NORM) || (layer >= 0 && (which == EB_L_ATTN_NORM || which == EB_L_FFN_NORM));
+    if (is_planar(type)) {
+        void *tmp; EB_CUDA(cudaMalloc(&tmp, t->bytes));
+        rc = eb_synth_impl(type, tmp, t->rows * t->cols, seed, scale, 0, 0);
+        if (!rc) rc = eb_repack_impl(type, tmp, t->data, t->rows * t->cols / block_elems(type), 0, 0);
+        EB_CUDA(cudaDeviceSynchronize()); cudaFree(tmp);
+        return rc;
+    }
+    rc = eb_synth_impl(type, t->data, t->rows * t->cols, seed, scale, norm, 0);
+    EB_CUDA(cudaDeviceSynchronize());
+    return rc;
+}
+extern "C" int eb_model_get_tensor(const eb_model *m, int layer, int which, void *h_data, size_t bytes) {
+    const DTensor *t = slot(const_cast<eb_model *>(m), layer, which);
+    if (!t || !t->data) return eb_set_err(EB_ERR_ARG, "get_tensor: empty slot %d/%d", layer, which);
+    if (bytes != t->bytes) return eb_set_err(EB_ERR_ARG, "get_tensor: size %zu != %zu", bytes, t->bytes);
+    if (is_planar(t->type)) {
+        void *tmp; EB_CUDA(cudaMalloc(&tmp, t->bytes));
+        int rc = eb_repack_impl(t->type, tmp, t->data, t->rows * t->cols / block_elems(t->type), 1, 0);
+        if (!rc) EB_CUDA(cudaMemcpy(h_data, tmp, bytes, cudaMemcpyDeviceToHost));
+        cudaFree(tmp);
+        return rc;
+    }
+    EB_CUDA(cudaMemcpy(h_data, t->data, bytes, cudaMemcpyDeviceToHost));
+    return EB_OK;
+}
+extern "C" int eb_model_share_lm_head(eb_model *head, const eb_model *target) {
+    if (!head || !target || !target->g[EB_T_OUTPUT].data) return eb_set_err(EB_ERR_ARG, "share_lm_head: target has no output tensor");
+    if (head->g[EB_T_OUTPUT].owned) cudaFree(head->g[EB_T_OUTPUT].data);
+    head->g[EB_T_OUTPUT] = target->g[EB_T_OUTPUT]; head->g[EB_T_OUTPUT].owned = false;
+    return EB_OK;
+}
+extern "C" size_t eb_model_weight_bytes(const eb_model *m) {
+    size_t b = 0;
+    for (int i = 0; i < EB_T_GLOBAL_COUNT; i++) if (i != EB_T_TOK_EMBD) b += m->g[i].bytes;   // embeddings: T rows only
+    for (auto &l : m->layers) for (auto &t : l) b += t.bytes;
+    return b;
+}
+
+// ------------------------------------------------------------------ mul_mat dispatch
+// T <= 8: dequant-dot matvec (K1); T > 8: int8 tensor-core GEMM (K2) for K-quants, else K1 in
+// column chunks.  actq_ws holds the quantised activations.
+int eb_mul_mat_impl(int type, const void *W, int64_t N, int64_t K, const float *x, int T, float *y, void *actq_ws, float *partial, cudaStream_t st) {
+    const int kq = (type == EB_Q4_K || type == EB_Q6_K);
+    if (!kq && type != EB_Q4_0 && type != EB_Q8_0) return eb_set_err(EB_ERR_UNSUPPORTED, "mul_mat: weight type %d", type);
+    ActQ a = eb_actq_carve(actq_ws, kq, K, T);
+    int rc = eb_quantize_act(x, a, st); if (rc) return rc;
+    if (eb_mmq_supported(type, N, K, T)) return eb_mmq(type, W, N, K, a, y, partial, eb_mmq_pick_ksplit(type, N, K, T), st);
+    return eb_mmvq(type, W, N, K, a, y, st);
+}
+// same activations for several weight matrices (wq/wk/wv, gate/up): quantise once
+static int mul_mat_preq(const DTensor &w, const ActQ &a, float *y, float *partial, cudaStream_t st) {
+    if (eb_mmq_supported(w.type, w.rows, w.cols, a.T)) return eb_mmq(w.type, w.data, w.rows, w.cols, a, y, partial, eb_mmq_pick_ksplit(w.type, w.rows, w.cols, a.T), st);
+    return eb_mmvq(w.type, w.data, w.rows, w.cols, a, y, st);
+}
+static int kq_of(const DTensor &w) { return w.type == EB_Q4_K || w.type == EB_Q6_K; }
+
+// ------------------------------------------------------------------ session
+static int ws_alloc(Workspace &w, const eb_model *m, int Tmax, int n_ctx) {
+    const size_t E = m->E, F = m->F, V = m->V, T = Tmax;
+    w.Tmax = Tmax;
+    auto fa = [&](float **p, size_t n) { return cudaMalloc((void **)p, n * sizeof(float)); };
+    EB_CUDA(fa(&w.x, T * E)); EB_CUDA(fa(&w.cur, T * E)); EB_CUDA(fa(&w.q, T * E)); EB_CUDA(fa(&w.k, T * E)); EB_CUDA(fa(&w.v, T * E));
+    EB_CUDA(fa(&w.att, T * E)); EB_CUDA(fa(&w.gate, T * F)); EB_CUDA(fa(&w.up, T * F)); EB_CUDA(fa(&w.cat, T * 2 * E));
+    EB_CUDA(fa(&w.hidden, T * E)); EB_CUDA(fa(&w.feat, T * E)); EB_CUDA(fa(&w.logits, T * V));
+    const size_t Kmax = std::max<size_t>(2 * E, F), Nmax = std::max<size_t>(std::max<size_t>(F, V), E);
+    w.actq_bytes = 2 * eb_actq_bytes(1, Kmax, Tmax) + 1024;   // generous: either grid
+    EB_CUDA(cudaMalloc(&w.actq, w.actq_bytes));
+    w.partial_bytes = (size_t)8 * T * Nmax * 4;
+    EB_CUDA(cudaMalloc((void **)&w.partial, w.partial_bytes));
+    w.fa_bytes = eb_flash_attn_ws_size_impl(Tmax, m->H, m->E / m->H, n_ctx);
+    EB_CUDA(cudaMalloc(&w.fa_ws, w.fa_bytes));
+    EB_CUDA(cudaMalloc((void **)&w.tokens, T * 4)); EB_CUDA(cudaMalloc((void **)&w.pos, T * 4));
+    EB_CUDA(cudaMalloc((void **)&w.bits, T * 16)); EB_CUDA(cudaMalloc((void **)&w.ctl, sizeof(FwdCtl)));
+    return EB_OK;
+}
+static void ws_free(Workspace &w) {
+    for (void *p : {(void *)w.x, (void *)w.cur, (void *)w.q, (void *)w.k, (void *)w.v, (void *)w.att, (void *)w.gate, (void *)w.up, (void *)w.cat,
+                    (void *)w.hidden, (void *)w.feat, (void *)w.logits, (void *)w.partial, w.actq, w.fa_ws, (void *)w.tokens, (void *)w.pos, (void *)w.bits, (void *)w.ctl})
+        cudaFree(p);
+}
+static int kv_alloc(KVCache &kv, const eb_model *m, int n_ctx) {
+    kv.L = m->L; kv.E = m->E; kv.n_ctx = n_ctx; kv.layer_stride = (int64_t)n_ctx * m->E;
+    const size_t bytes = (size_t)kv.L * kv.layer_stride * 2;
+    EB_CUDA(cudaMalloc((void **)&kv.k, bytes)); EB_CUDA(cudaMalloc((void **)&kv.v, bytes));
+    EB_CUDA(cudaMemset(kv.k, 0, bytes)); EB_CUDA(cudaMemset(kv.v, 0, bytes));
+    return EB_OK;
+}
+
+extern "C" eb_session *eb_session_create(eb_model *target, eb_model *head, const eb_session_params *p) {
+    if (!target || !p || p->max_nodes < 1 || p->max_nodes > 128 || p->n_branch < 1 || p->n_branch > 16 || p->top_k < 1 || p->top_k > 16) {
+        eb_set_err(EB_ERR_ARG, "session_create: bad parameters"); return nullptr;
+    }
+    if (head && (head->E != target->E || head->V != target->V)) { eb_set_err(EB_ERR_ARG, "session_create: head/target shape mismatch"); return nullptr; }
+    eb_session *s = new eb_session();
+    s->tgt = target; s->head = head; s->p = *p;
+    s->cfg = SpecCfg{p->max_nodes, p->n_branch, p->n_draft, p->max_depth, p->top_k, p->fixed_accept, p->p_split};
+    const int E = target->E;
+    auto fail = [&]() { eb_session_free(s); return (eb_session *)nullptr; };
+    if (cudaStreamCreateWithFlags(&s->st, cudaStreamNonBlocking) != cudaSuccess) { eb_set_err(EB_ERR_CUDA, "stream"); delete s; return nullptr; }
+    cudaEventCreate(&s->ev0); cudaEventCreate(&s->ev1);
+    if (kv_alloc(s->kv_t, target, p->n_ctx) || ws_alloc(s->ws_t, target, 128, p->n_ctx)) return fail();
+    if (head && (kv_alloc(s->kv_h, head, p->n_ctx) || ws_alloc(s->ws_h, head, 128, p->n_ctx))) return fail();
+    s->max_acc = std::min(p->max_nodes, p->max_depth + 2);
+    const size_t Lmax = std::max(target->L, head ? head->L : 0);
+    if (cudaMalloc((void **)&s->state, sizeof(SpecState)) || cudaMemset(s->state, 0, sizeof(SpecState)) ||
+        cudaMalloc((void **)&s->root_feat, E * 4) || cudaMemset(s->root_feat, 0, E * 4) ||
+        cudaMalloc((void **)&s->node_feat, (size_t)128 * E * 4) ||
+        cudaMalloc((void **)&s->cand_ids, 16 * 16 * 4) || cudaMalloc((void **)&s->cand_vals, 16 * 16 * 4) || cudaMalloc((void **)&s->cand_p, 16 * 16 * 4) ||
+        cudaMalloc((void **)&s->best, 128 * 4) ||
+        cudaMalloc((void **)&s->stage, Lmax * s->max_acc * 2 * (size_t)E * 2) ||
+        cudaMalloc((void **)&s->d_res, sizeof(eb_round_result)) || cudaMallocHost((void **)&s->h_res, sizeof(eb_round_result))) {
+        eb_set_err(EB_ERR_OOM, "session_create: %s", cudaGetErrorString(cudaGetLastError())); return fail();
+    }
+    return s;
+}
+extern "C" void eb_session_free(eb_session *s) {
+    if (!s) return;
+    cudaDeviceSynchronize();
+    if (s->graph_round) cudaGraphExecDestroy(s->graph_round);
+    if (s->graph_verify) cudaGraphExecDestroy(s->graph_verify);
+    ws_free(s->ws_t); cudaFree(s->kv_t.k); cudaFree(s->kv_t.v);
+    if (s->head) { ws_free(s->ws_h); cudaFree(s->kv_h.k); cudaFree(s->kv_h.v); }
+    for (void *p : {(void *)s->state, (void *)s->root_feat, (void *)s->node_feat, (void *)s->cand_ids, (void *)s->cand_vals, (void *)s->cand_p, (void *)s->best, (void *)s->stage, (void *)s->d_res})
+        cudaFree(p);
+    if (s->h_res) cudaFreeHost(s->h_res);
+    cudaEventDestroy(s->ev0); cudaEventDestroy(s->ev1); cudaStreamDestroy(s->st);
+    delete s;
+}
+
+// ------------------------------------------------------------------ forward
+// All inputs are device-resident: tokens/pos/bits [T], hidden [T][E] (head), ctl (n_prefix,
+// node_base, n_tree).  K/V rows go to cells n_prefix + node_base + t.
+static int forward_dev(const eb_model *m, KVCache &kv, Workspace &w, const int32_t *tokens, const int32_t *pos, const uint32_t *bits,
+                       const float *hidden, const FwdCtl *ctl, int T, bool want_logits, cudaStream_t st) {
+    const int E = m->E, H = m->H, F = m->F, D = E / H;
+    const int64_t TE = (int64_t)T * E;
+    int rc;
+#define RC(x) do { rc = (x); if (rc) return rc; } while (0)
+    const DTensor &emb = m->g[EB_T_TOK_EMBD];
+    RC(eb_get_rows_dev(emb.type, emb.data, emb.rows, E, tokens, T, w.x, st));
+    if (m->is_eagle) {
+        RC(eb_concat2_impl(w.x, hidden, w.cat, E, T, st));
+        const DTensor &fc = m->g[EB_T_FC];
+        RC(eb_mul_mat_impl(fc.type, fc.data, E, 2 * E, w.cat, T, w.cur, w.actq, w.partial, st));
+        RC(eb_bias_relu_impl(w.cur, (const float *)m->g[EB_T_FC_BIAS].data, w.x, TE, E, st));
+    }
+    for (int l = 0; l < m->L; l++) {
+        const std::vector<DTensor> &t = m->layers[l];
+        RC(eb_rms_norm_impl(w.x, (const float *)t[EB_L_ATTN_NORM].data, w.cur, E, T, m->eps, st));
+        if (kq_of(t[EB_L_WQ]) == kq_of(t[EB_L_WK]) && kq_of(t[EB_L_WQ]) == kq_of(t[EB_L_WV])) {
+            ActQ a = eb_actq_carve(w.actq, kq_of(t[EB_L_WQ]), E, T);
+            RC(eb_quantize_act(w.cur, a, st));
+            RC(mul_mat_preq(t[EB_L_WQ], a, w.q, w.partial, st)); RC(mul_mat_preq(t[EB_L_WK], a, w.k, w.partial, st)); RC(mul_mat_preq(t[EB_L_WV], a, w.v, w.partial, st));
+        } else {
+            RC(eb_mul_mat_impl(t[EB_L_WQ].type, t[EB_L_WQ].data, E, E, w.cur, T, w.q, w.actq, w.partial, st));
+            RC(eb_mul_mat_impl(t[EB_L_WK].type, t[EB_L_WK].data, E, E, w.cur, T, w.k, w.actq, w.partial, st));
+            RC(eb_mul_mat_impl(t[EB_L_WV].type, t[EB_L_WV].data, E, E, w.cur, T, w.v, w.actq, w.partial, st));
+        }
+        __half *kc = kv.k + (int64_t)l * kv.layer_stride, *vc = kv.v + (int64_t)l * kv.layer_stride;
+        RC(eb_rope_kv_store_ctl(w.q, w.k, w.v, pos, kc, vc, ctl, D, H, T, m->freq_base, st));
+        RC(eb_flash_attn_ctl(w.q, kc, vc, E, bits, ctl, T, H, D, kv.n_ctx, 1.0f / sqrtf((float)D), w.att, w.fa_ws, st));
+        RC(eb_mul_mat_impl(t[EB_L_WO].type, t[EB_L_WO].data, E, E, w.att, T, w.cur, w.actq, w.partial, st));
+        RC(eb_add_impl(w.cur, w.x, w.x, TE, TE, st));                      // ffn_inp = cur + inpSA
+        RC(eb_rms_norm_impl(w.x, (const float *)t[EB_L_FFN_NORM].data, w.cur, E, T, m->eps, st));
+        if (kq_of(t[EB_L_UP]) == kq_of(t[EB_L_GATE])) {
+            ActQ a = eb_actq_carve(w.actq, kq_of(t[EB_L_UP]), E, T);
+            RC(eb_quantize_act(w.cur, a, st));
+            RC(mul_mat_preq(t[EB_L_UP], a, w.up, w.partial, st)); RC(mul_mat_preq(t[EB_L_GATE], a, w.gate, w.partial, st));
+        } else {
+            RC(eb_mul_mat_impl(t[EB_L_UP].type, t[EB_L_UP].data, F, E, w.cur, T, w.up, w.actq, w.partial, st));
+            RC(eb_mul_mat_impl(t[EB_L_GATE].type, t[EB_L_GATE].data, F, E, w.cur, T, w.gate, w.actq, w.partial, st));
+        }
+        RC(eb_swiglu_impl(w.gate, w.up, w.gate, (int64_t)T * F, st));
+        RC(eb_mul_mat_impl(t[EB_L_DOWN].type, t[EB_L_DOWN].data, E, F, w.gate, T, w.cur, w.actq, w.partial, st));
+        RC(eb_add_impl(w.cur, w.x, w.x, TE, TE, st));
+    }
+    RC(eb_rms_norm_impl(w.x, (const float *)m->g[EB_T_OUTPUT_NORM].data, w.feat, E, T, m->eps, st));   // result_norm
+    if (want_logits) {
+        const DTensor &o = m->g[EB_T_OUTPUT];
+        RC(eb_mul_mat_impl(o.type, o.data, m->V, E, w.feat, T, w.logits, w.actq, w.partial, st));
+    }
+#undef RC
+    return EB_OK;
+}
+
+static int check_model(const eb_model *m) {
+    for (int i = 0; i < EB_T_GLOBAL_COUNT; i++) {
+        const bool need = (i == EB_T_TOK_EMBD || i == EB_T_OUTPUT) || (m->is_eagle && i == EB_T_FC) || (!m->is_eagle && i == EB_T_OUTPUT_NORM);
+        if (need && !m->g[i].data) return eb_set_err(EB_ERR_ARG, "model: global tensor %d missing", i);
+    }
+    for (int l = 0; l < m->L; l++) for (int i = 0; i < EB_L_COUNT; i++) {
+        const bool need = !(i == EB_L_ATTN_NORM && m->is_eagle);
+        if (need && !m->layers[l][i].data) return eb_set_err(EB_ERR_ARG, "model: layer %d tensor %d missing", l, i);
+    }
+    return EB_OK;
+}
+
+extern "C" int eb_session_n_past(const eb_session *s, int model) {
+    (void)model; int n = -1;
+    if (cudaMemcpy(&n, &s->state->n_past, 4, cudaMemcpyDeviceToHost) != cudaSuccess) return -1;
+    return n;
+}
+
+extern "C" int eb_session_forward(eb_session *s, int model, const int32_t *h_tokens, const int32_t *h_pos, const int32_t *h_parent,
+                                  const float *h_hidden, int T, float *h_logits, float *h_feat) {
+    eb_model *m = model ? s->head : s->tgt;
+    if (!m) return eb_set_err(EB_ERR_ARG, "forward: no such model");
+    if (T < 1 || T > 128) return eb_set_err(EB_ERR_ARG, "forward: T=%d", T);
+    int rc = check_model(m); if (rc) return rc;
+    KVCache &kv = model ? s->kv_h : s->kv_t; Workspace &w = model ? s->ws_h : s->ws_t;
+    const int n_past = eb_session_n_past(s, model);
+    if (n_past + T > kv.n_ctx) return eb_set_err(EB_ERR_ARG, "forward: KV cache full (%d + %d > %d)", n_past, T, kv.n_ctx);
+    uint32_t bits[128 * 4]; memset(bits, 0, sizeof(bits));
+    for (int t = 0; t < T; t++) {
+        const int par = h_parent ? h_parent[t] : t - 1;
+        if (par >= t) return eb_set_err(EB_ERR_ARG, "forward: parent[%d]=%d", t, par);
+        if (par >= 0) memcpy(bits + t * 4, bits + par * 4, 16);
+        bits[t * 4 + (t >> 5)] |= 1u << (t & 31);
+    }
+    FwdCtl ctl{n_past, 0, T};
+    EB_CUDA(cudaMemcpyAsync(w.tokens, h_tokens, T * 4, cudaMemcpyHostToDevice, s->st));
+    EB_CUDA(cudaMemcpyAsync(w.pos, h_pos, T * 4, cudaMemcpyHostToDevice, s->st));
+    EB_CUDA(cudaMemcpyAsync(w.bits, bits, T * 16, cudaMemcpyHostToDevice, s->st));
+    EB_CUDA(cudaMemcpyAsync(w.ctl, &ctl, sizeof(ctl), cudaMemcpyHostToDevice, s->st));
+    if (m->is_eagle) {
+        if (!h_hidden) return eb_set_err(EB_ERR_ARG, "forward: the head needs hidden input");
+        EB_CUDA(cudaMemcpyAsync(w.hidden, h_hidden, (size_t)T * m->E * 4, cudaMemcpyHostToDevice, s->st));
+    }
+    rc = forward_dev(m, kv, w, w.tokens, w.pos, w.bits, w.hidden, w.ctl, T, h_logits != nullptr, s->st); if (rc) return rc;
+    if (h_logits) EB_CUDA(cudaMemcpyAsync(h_logits, w.logits, (size_t)T * m->V * 4, cudaMemcpyDeviceToHost, s->st));
+    if (h_feat) EB_CUDA(cudaMemcpyAsync(h_feat, w.feat, (size_t)T * m->E * 4, cudaMemcpyDeviceToHost, s->st));
+    EB_CUDA(cudaStreamSynchronize(s->st));
+    s->last_T[model ? 1 : 0] = T;
+    return EB_OK;
+}
+
+__global__ void set_n_past_kernel(SpecState *s, int n) { s->n_past = n; }
+__global__ void set_root_kernel(SpecState *s, int tok) { s->root_token = tok; }
+
+extern "C" int eb_session_commit(eb_session *s, int model, int n) {
+    // chain prefill: the first n rows of the last forward become committed cells.  Both caches
+    // share n_past, so commit once after forwarding the same tokens through both models.
+    if (n < 0 || n > s->last_T[model ? 1 : 0]) return eb_set_err(EB_ERR_ARG, "commit: n=%d", n);
+    const int n_past = eb_session_n_past(s, model);
+    set_n_past_kernel<<<1, 1, 0, s->st>>>(s->state, n_past + n); EB_CHECK_LAUNCH();
+    EB_CUDA(cudaStreamSynchronize(s->st));
+    return EB_OK;
+}
+extern "C" int eb_session_set_root(eb_session *s, int32_t id_last, const float *h_feat) {
+    set_root_kernel<<<1, 1, 0, s->st>>>(s->state, id_last); EB_CHECK_LAUNCH();
+    if (h_feat) EB_CUDA(cudaMemcpyAsync(s->root_feat, h_feat, (size_t)s->tgt->E * 4, cudaMemcpyHostToDevice, s->st));
+    EB_CUDA(cudaStreamSynchronize(s->st));
+    return EB_OK;
+}
+extern "C" int eb_session_synth_kv(eb_session *s, int n_past, uint64_t seed) {
+    if (n_past < 0 || n_past + s->p.max_nodes + s->p.n_branch > s->p.n_ctx) return eb_set_err(EB_ERR_ARG, "synth_kv: n_past=%d does not leave room for a tree", n_past);
+    for (int mi = 0; mi < 2; mi++) {
+        KVCache &kv = mi ? s->kv_h : s->kv_t;
+        if (mi && !s->head) break;
+        for (int l = 0; l < kv.L; l++) {
+            int rc = eb_synth_impl(EB_F16, kv.k + l * kv.layer_stride, (int64_t)n_past * kv.E, seed + 2 * l + 1000 * mi, 1.0f, 0, s->st); if (rc) return rc;
+            rc = eb_synth_impl(EB_F16, kv.v + l * kv.layer_stride, (int64_t)n_past * kv.E, seed + 2 * l + 1 + 1000 * mi, 1.0f, 0, s->st); if (rc) return rc;
+        }
+    }
+    set_n_past_kernel<<<1, 1, 0, s->st>>>(s->state, n_past); EB_CHECK_LAUNCH();
+    int rc = eb_synth_impl(EB_F32, s->root_feat, s->tgt->E, seed + 77, 1.0f, 0, s->st); if (rc) return rc;
+    EB_CUDA(cudaStreamSynchronize(s->st));
+    return EB_OK;
+}
+
+// ------------------------------------------------------------------ the round
+static int verify_dev(eb_session *s, int T, cudaStream_t st) {
+    SpecState *d = s->state;
+    return forward_dev(s->tgt, s->kv_t, s->ws_t, d->tokens, d->pos, d->tree_bits, nullptr, &d->ctl_tgt, T, true, st);
+}
+static int round_dev(eb_session *s, cudaStream_t st) {
+    SpecState *d = s->state; const SpecCfg &c = s->cfg; const int E = s->tgt->E, V = s->tgt->V;
+    int rc;
+#define RC(x) do { rc = (x); if (rc) return rc; } while (0)
+    RC(eb_spec_round_begin(d, c, st));
+    for (int depth = 0; depth <= c.max_depth; depth++) {
+        // head forward over the nodes created at this depth (depth 0: the root)
+        RC(eb_spec_gather_hidden(d, s->root_feat, s->node_feat, s->ws_h.hidden, E, c.n_branch, st));
+        const bool last = depth == c.max_depth;
+        RC(forward_dev(s->head, s->kv_h, s->ws_h, d->dft_tokens, d->dft_pos, d->dft_bits, s->ws_h.hidden, &d->ctl_head, c.n_branch, !last, st));
+        RC(eb_spec_scatter_feat(d, s->ws_h.feat, s->node_feat, E, c.n_branch, st));
+        if (last) break;
+        RC(eb_top_k_impl(s->ws_h.logits, c.n_branch, V, c.top_k, s->cand_ids, s->cand_vals, s->cand_p, st));
+        RC(eb_spec_expand(d, c, s->cand_ids, s->cand_p, st));
+    }
+    RC(verify_dev(s, c.max_nodes, st));
+    RC(eb_argmax_impl(s->ws_t.logits, c.max_nodes, V, s->best, st));
+    RC(eb_spec_accept(d, c, s->best, st));
+    RC(eb_spec_compact(d, s->kv_t.k, s->kv_t.v, s->stage, s->kv_t.layer_stride, E, s->tgt->L, s->max_acc, st));
+    RC(eb_spec_compact(d, s->kv_h.k, s->kv_h.v, s->stage, s->kv_h.layer_stride, E, s->head->L, s->max_acc, st));
+    RC(eb_spec_round_end(d, s->ws_t.feat, s->root_feat, E, s->d_res, st));
+#undef RC
+    return EB_OK;
+}
+
+static int capture(eb_session *s, cudaGraphExec_t *exec, int (*fn)(eb_session *, int, cudaStream_t), int arg) {
+    cudaGraph_t g;
+    EB_CUDA(cudaStreamBeginCapture(s->st, cudaStreamCaptureModeThreadLocal));
+    const int rc = fn(s, arg, s->st);
+    const cudaError_t e = cudaStreamEndCapture(s->st, &g);
+    if (rc) { if (e == cudaSuccess) cudaGraphDestroy(g); return rc; }
+    if (e != cudaSuccess) return eb_set_err(EB_ERR_CUDA, "graph capture: %s", cudaGetErrorString(e));
+    const cudaError_t e2 = cudaGraphInstantiate(exec, g, 0);
+    cudaGraphDestroy(g);
+    if (e2 != cudaSuccess) return eb_set_err(EB_ERR_CUDA, "graph instantiate: %s", cudaGetErrorString(e2));
+    return EB_OK;
+}
+static int round_fn(eb_session *s, int, cudaStream_t st) { return round_dev(s, st); }
+static int verify_fn(eb_session *s, int T, cudaStream_t st) { return verify_dev(s, T, st); }
+
+extern "C" int eb_session_round(eb_session *s, eb_round_result *h_out) {
+    if (!s->head) return eb_set_err(EB_ERR_ARG, "round: session has no draft head");
+    int rc = check_model(s->tgt); if (rc) return rc;
+    rc = check_model(s->head); if (rc) return rc;
+    const int n_past = eb_session_n_past(s, 0);
+    if (n_past + s->p.max_nodes + s->p.n_branch > s->p.n_ctx) return eb_set_err(EB_ERR_ARG, "round: KV cache full (n_past=%d)", n_past);
+    if (s->p.use_graph && !s->graph_round) {                    // capture only records; the first launch below is the first round
+        rc = capture(s, &s->graph_round, round_fn, 0); if (rc) return rc;
+    }
+    EB_CUDA(cudaEventRecord(s->ev0, s->st));
+    if (s->graph_round) EB_CUDA(cudaGraphLaunch(s->graph_round, s->st));
+    else { rc = round_dev(s, s->st); if (rc) return rc; }
+    EB_CUDA(cudaEventRecord(s->ev1, s->st));
+    EB_CUDA(cudaMemcpyAsync(s->h_res, s->d_res, sizeof(eb_round_result), cudaMemcpyDeviceToHost, s->st));
+    EB_CUDA(cudaStreamSynchronize(s->st));
+    float ms = 0; EB_CUDA(cudaEventElapsedTime(&ms, s->ev0, s->ev1));
+    s->h_res->gpu_ms = ms;
+    if (h_out) *h_out = *s->h_res;
+    return EB_OK;
+}
+
+__global__ void verify_setup_kernel(SpecState *s, int T) {      // chain-shaped dummy tree of T nodes for the micro-bench
+    if (threadIdx.x || blockIdx.x) return;
+    for (int i = 0; i < T; i++) {
+        s->tokens[i] = (i * 7919 + 13) % 1000; s->parent[i] = i - 1; s->pos[i] = s->n_past + i;
+        uint32_t *b = s->tree_bits + i * 4; b[0] = b[1] = b[2] = b[3] = 0;
+        for (int j = 0; j <= i; j++) b[j >> 5] |= 1u << (j & 31);
+    }
+    s->n_nodes = T; s->ctl_tgt.n_prefix = s->n_past; s->ctl_tgt.node_base = 0; s->ctl_tgt.n_tree = T;
+}
+extern "C" int eb_session_verify_only(eb_session *s, int T, float *gpu_ms) {
+    if (T < 1 || T > 128) return eb_set_err(EB_ERR_ARG, "verify_only: T=%d", T);
+    int rc = check_model(s->tgt); if (rc) return rc;
+    verify_setup_kernel<<<1, 32, 0, s->st>>>(s->state, T); EB_CHECK_LAUNCH();
+    if (s->p.use_graph && (!s->graph_verify || s->graph_verify_T != T)) {
+        if (s->graph_verify) { cudaGraphExecDestroy(s->graph_verify); s->graph_verify = nullptr; }
+        rc = verify_dev(s, T, s->st); if (rc) return rc;
+        EB_CUDA(cudaStreamSynchronize(s->st));
+        rc = capture(s, &s->graph_verify, verify_fn, T); if (rc) return rc;
+        s->graph_verify_T = T;
+    }
+    EB_CUDA(cudaEventRecord(s->ev0, s->st));
+    if (s->graph_verify) EB_CUDA(cudaGraphLaunch(s->graph_verify, s->st));
+    else { rc = verify_dev(s, T, s->st); if (rc) return rc; }
+    EB_CUDA(cudaEventRecord(s->ev1, s->st));
+    EB_CUDA(cudaStreamSynchronize(s->st));
+    float ms = 0; EB_CUDA(cudaEventElapsedTime(&ms, s->ev0, s->ev1));
+    if (gpu_ms) *gpu_ms = ms;
+    return EB_OK;
+}

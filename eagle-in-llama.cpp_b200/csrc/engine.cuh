@@ -1,0 +1,56 @@
+// engine.cuh — model / session containers of the speculative-step engine.
+#pragma once
+#include <vector>
+#include "common.cuh"
+#include "spec.cuh"
+
+struct DTensor { int type = -1; void *data = nullptr; int64_t rows = 0, cols = 0; size_t bytes = 0; bool owned = false; };
+
+struct eb_model {
+    int E, H, F, V, L, is_eagle; float eps, freq_base;
+    DTensor g[EB_T_GLOBAL_COUNT];
+    std::vector<std::vector<DTensor>> layers;
+};
+
+struct KVCache { __half *k = nullptr, *v = nullptr; int64_t layer_stride = 0; int L = 0, E = 0, n_ctx = 0; };
+
+// activation buffers for one forward of up to Tmax rows
+struct Workspace {
+    int Tmax = 0;
+    float *x, *cur, *q, *k, *v, *att, *gate, *up, *cat, *hidden, *feat, *logits, *partial;
+    void *actq; size_t actq_bytes; void *fa_ws; size_t fa_bytes; size_t partial_bytes;
+    int32_t *tokens, *pos; uint32_t *bits; FwdCtl *ctl;
+};
+
+struct eb_session {
+    eb_model *tgt, *head; eb_session_params p; SpecCfg cfg;
+    KVCache kv_t, kv_h; Workspace ws_t, ws_h;
+    SpecState *state; float *root_feat, *node_feat; int32_t *cand_ids; float *cand_vals, *cand_p; int32_t *best;
+    __half *stage; int max_acc;
+    eb_round_result *d_res, *h_res;
+    cudaStream_t st; cudaEvent_t ev0, ev1;
+    cudaGraphExec_t graph_round = nullptr, graph_verify = nullptr; int graph_verify_T = 0;
+    int last_T[2] = {0, 0};
+};
+
+// ops implemented in the other translation units
+int eb_rms_norm_impl(const float *x, const float *w, float *y, int64_t n, int64_t rows, float eps, cudaStream_t st);
+int eb_rope_norm_impl(float *x, const int32_t *pos, int D, int n_head, int T, float freq_base, cudaStream_t st);
+int eb_add_impl(const float *a, const float *b, float *y, int64_t n, int64_t nb, cudaStream_t st);
+int eb_mul_impl(const float *a, const float *b, float *y, int64_t n, int64_t nb, cudaStream_t st);
+int eb_silu_impl(const float *x, float *y, int64_t n, cudaStream_t st);
+int eb_relu_impl(const float *x, float *y, int64_t n, cudaStream_t st);
+int eb_bias_relu_impl(const float *x, const float *b, float *y, int64_t n, int nb, cudaStream_t st);
+int eb_cpy_f32_f16_impl(const float *x, void *y, int64_t n, cudaStream_t st);
+int eb_concat2_impl(const float *a, const float *b, float *y, int E, int T, cudaStream_t st);
+int eb_swiglu_impl(const float *gate, const float *up, float *y, int64_t n, cudaStream_t st);
+int eb_get_rows_dev(int type, const void *W, int64_t n_rows, int64_t K, const int32_t *d_ids, int n, float *out, cudaStream_t st);
+size_t eb_flash_attn_ws_size_impl(int T, int H, int D, int n_kv);
+int eb_flash_attn_impl(const float *q, const void *k, const void *v, int64_t kv_stride, const void *mask, int64_t mask_stride,
+                       const uint32_t *tree_bits, int n_prefix, int T, int H, int D, int n_kv, float scale, float *out, void *ws, cudaStream_t st);
+// engine forms: cell base / prefix length are read from device memory (CUDA-graph friendly)
+int eb_rope_kv_store_ctl(float *q, const float *k, const float *v, const int32_t *pos, void *kc, void *vc, const FwdCtl *ctl,
+                         int D, int n_head, int T, float freq_base, cudaStream_t st);
+int eb_flash_attn_ctl(const float *q, const void *k, const void *v, int64_t kv_stride, const uint32_t *tree_bits, const FwdCtl *ctl,
+                      int T, int H, int D, int n_ctx, float scale, float *out, void *ws, cudaStream_t st);
+int eb_mul_mat_impl(int type, const void *W, int64_t N, int64_t K, const float *x, int T, float *y, void *actq_ws, float *partial, cudaStream_t st);

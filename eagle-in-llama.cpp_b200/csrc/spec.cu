@@ -1,0 +1,278 @@
+// spec.cu — K11 + the fused device-side speculative-step kernels: top-k / argmax over the
+// vocabulary, draft-tree expansion, greedy accept walk, KV compaction, feature hand-off.
+// Nothing here returns to the host inside a round (the reference does a 32000-float D2H and a
+// host partial_sort per node: R/src/llama.cpp:9637, R/src/llama-sampling.cpp:228-302).
+#include "common.cuh"
+#include "spec.cuh"
+
+// ------------------------------------------------------------------ top-k / argmax
+// One CTA (1024 threads) per logits row.  k rounds of block arg-max over a shared copy of the
+// row; ties resolve to the lower token id.  probs = softmax over the k kept logits
+// (llama_sampler_softmax_impl, R/src/llama-sampling.cpp:130-150).
+__global__ void __launch_bounds__(1024) top_k_kernel(const float *__restrict__ logits, int V, int k,
+                                                     int32_t *__restrict__ ids, float *__restrict__ vals, float *__restrict__ probs) {
+    extern __shared__ float row[];
+    __shared__ float wv[32]; __shared__ int wi[32];
+    __shared__ float kv[16]; __shared__ int ki[16];
+    const int r = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const float *x = logits + (int64_t)r * V;
+    for (int i = tid; i < V; i += 1024) row[i] = x[i];
+    __syncthreads();
+    for (int j = 0; j < k; j++) {
+        float bv = -INFINITY; int bi = 0x7fffffff;
+        for (int i = tid; i < V; i += 1024) { const float v = row[i]; if (v > bv) { bv = v; bi = i; } }   // ascending i: first max kept
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const float ov = __shfl_xor_sync(0xffffffffu, bv, o); const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+            if (ov > bv || (ov == bv && oi < bi)) { bv = ov; bi = oi; }
+        }
+        if (lane == 0) { wv[warp] = bv; wi[warp] = bi; }
+        __syncthreads();
+        if (warp == 0) {
+            bv = wv[lane]; bi = wi[lane];
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                const float ov = __shfl_xor_sync(0xffffffffu, bv, o); const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+                if (ov > bv || (ov == bv && oi < bi)) { bv = ov; bi = oi; }
+            }
+            if (lane == 0) { kv[j] = bv; ki[j] = bi; if (bi < V) row[bi] = -INFINITY; }
+        }
+        __syncthreads();
+    }
+    if (tid == 0) {
+        const float mx = kv[0]; float sum = 0.f; float pr[16];
+        for (int j = 0; j < k; j++) { pr[j] = expf(kv[j] - mx); sum += pr[j]; }
+        for (int j = 0; j < k; j++) {
+            ids[r * k + j] = ki[j]; vals[r * k + j] = kv[j];
+            if (probs) probs[r * k + j] = pr[j] / sum;
+        }
+    }
+}
+int eb_top_k_impl(const float *logits, int rows, int V, int k, int32_t *ids, float *vals, float *probs, cudaStream_t st) {
+    if (k < 1 || k > 16 || V > 56000) return eb_set_err(EB_ERR_ARG, "top_k: k=%d V=%d", k, V);
+    if (rows == 0) return EB_OK;
+    top_k_kernel<<<rows, 1024, (size_t)V * 4, st>>>(logits, V, k, ids, vals, probs);
+    EB_CHECK_LAUNCH();
+    return EB_OK;
+}
+
+__global__ void __launch_bounds__(1024) argmax_kernel(const float *__restrict__ logits, int V, int32_t *__restrict__ ids) {
+    __shared__ float wv[32]; __shared__ int wi[32];
+    const int r = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const float *x = logits + (int64_t)r * V;
+    float bv = -INFINITY; int bi = 0x7fffffff;
+    for (int i = tid; i < V; i += 1024) { const float v = x[i]; if (v > bv) { bv = v; bi = i; } }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const float ov = __shfl_xor_sync(0xffffffffu, bv, o); const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+        if (ov > bv || (ov == bv && oi < bi)) { bv = ov; bi = oi; }
+    }
+    if (lane == 0) { wv[warp] = bv; wi[warp] = bi; }
+    __syncthreads();
+    if (warp == 0) {
+        bv = wv[lane]; bi = wi[lane];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const float ov = __shfl_xor_sync(0xffffffffu, bv, o); const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+            if (ov > bv || (ov == bv && oi < bi)) { bv = ov; bi = oi; }
+        }
+        if (lane == 0) ids[r] = bi == 0x7fffffff ? 0 : bi;
+    }
+}
+int eb_argmax_impl(const float *logits, int rows, int V, int32_t *ids, cudaStream_t st) {
+    if (rows == 0) return EB_OK;
+    argmax_kernel<<<rows, 1024, 0, st>>>(logits, V, ids);
+    EB_CHECK_LAUNCH();
+    return EB_OK;
+}
+
+// ------------------------------------------------------------------ tree state kernels
+__device__ void set_bits_from_parent(SpecState *s, int node) {
+    uint32_t *b = s->tree_bits + node * 4;
+    const int par = s->parent[node];
+    if (par >= 0) { const uint32_t *pb = s->tree_bits + par * 4; b[0] = pb[0]; b[1] = pb[1]; b[2] = pb[2]; b[3] = pb[3]; }
+    else { b[0] = b[1] = b[2] = b[3] = 0; }
+    b[node >> 5] |= 1u << (node & 31);
+}
+
+// Start of a round: node 0 = last accepted token (R/examples/speculative/speculative-eagle.cpp:516-517),
+// branch 0 drafting, first draft batch = {root} with the target's feature as hidden input.
+__global__ void round_begin_kernel(SpecState *s, SpecCfg c) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    for (int i = 0; i < c.max_nodes; i++) {            // dummy rows: attend only themselves
+        s->tokens[i] = 0; s->parent[i] = -1; s->pos[i] = s->n_past; s->depth[i] = 0;
+        uint32_t *b = s->tree_bits + i * 4; b[0] = b[1] = b[2] = b[3] = 0; b[i >> 5] = 1u << (i & 31);
+    }
+    s->tokens[0] = s->root_token; s->n_nodes = 1; s->n_seq_cur = 1; s->cur_depth = 0; s->done = 0;
+    for (int b = 0; b < 16; b++) { s->br_drafting[b] = 0; s->br_last_node[b] = 0; s->br_row[b] = 0; }
+    s->br_drafting[0] = 1;
+    s->dft_n = 1; s->dft_node_base = 0;
+    for (int r = 0; r < c.n_branch; r++) {
+        s->dft_tokens[r] = r == 0 ? s->root_token : 0; s->dft_pos[r] = s->n_past; s->dft_src[r] = -1;
+        uint32_t *b = s->dft_bits + r * 4; b[0] = b[1] = b[2] = b[3] = 0; b[r >> 5] = 1u << (r & 31);   // bit of cell node_base + r
+    }
+    s->ctl_head.n_prefix = s->n_past; s->ctl_head.node_base = 0; s->ctl_head.n_tree = c.n_branch;
+    s->ctl_tgt.n_prefix = s->n_past; s->ctl_tgt.node_base = 0; s->ctl_tgt.n_tree = c.max_nodes;
+}
+
+// hidden input rows of the draft batch: root <- target feature, others <- the head's own
+// result_norm of the parent node (F5: R/src/llama.cpp:10170, R/src/llama-context.cpp:83-88)
+__global__ void gather_hidden_kernel(const SpecState *s, const float *root_feat, const float *node_feat, float *hidden, int E, int n_branch) {
+    const int r = blockIdx.y; const int i = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
+    if (i >= E || r >= n_branch) return;
+    const int src = s->dft_src[r];
+    const float *p = src < 0 ? root_feat : node_feat + (int64_t)src * E;
+    *(float4 *)(hidden + (int64_t)r * E + i) = *(const float4 *)(p + i);
+}
+// after a head forward: feat rows -> per-node feature store
+__global__ void scatter_feat_kernel(const SpecState *s, const float *feat, float *node_feat, int E, int n_branch) {
+    const int r = blockIdx.y; const int i = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
+    if (i >= E || r >= s->dft_n) return;
+    const int node = s->dft_node_base + r;
+    *(float4 *)(node_feat + (int64_t)node * E + i) = *(const float4 *)(feat + (int64_t)r * E + i);
+}
+
+// One depth level of the reference's tree expansion (speculative-eagle.cpp:527-642), on device.
+// cand_ids/cand_p: [n_branch][top_k] sorted candidates of the rows of the last draft batch.
+__global__ void tree_expand_kernel(SpecState *s, SpecCfg c, const int32_t *cand_ids, const float *cand_p) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    if (s->done) {                                     // nothing left to draft: park the dummy rows behind the real nodes
+        const int base = s->n_nodes;
+        s->dft_n = 0; s->dft_node_base = base;
+        for (int r = 0; r < c.n_branch; r++) {
+            s->dft_tokens[r] = 0; s->dft_pos[r] = s->n_past; s->dft_src[r] = -1;
+            uint32_t *b = s->dft_bits + r * 4; b[0] = b[1] = b[2] = b[3] = 0;
+            const int cell = base + r; if (cell < 128) b[cell >> 5] = 1u << (cell & 31);
+        }
+        s->ctl_head.node_base = base; s->ctl_head.n_tree = min(128, base + c.n_branch);
+        return;
+    }
+    const int n_seq_dft = c.n_branch;
+    int skip[16];
+    for (int b = 0; b < 16; b++) skip[b] = 0;
+    const int first_new = s->n_nodes;
+    int n_new = 0;
+    int new_tok[16], new_src[16], new_br[16];
+    for (int b = 0; b < n_seq_dft; b++) {
+        if (!s->br_drafting[b] || skip[b]) continue;
+        const int32_t *ids = cand_ids + s->br_row[b] * c.top_k; const float *pr = cand_p + s->br_row[b] * c.top_k;
+        int sa[16]; int nsa = 0; sa[nsa++] = b;
+        for (int f = 1; f < 8 && f < c.top_k; f++) {                                  // :556-597
+            if (s->n_seq_cur < n_seq_dft && pr[f] > c.p_split) {
+                const int nb = s->n_seq_cur++;
+                s->br_drafting[nb] = 1; skip[nb] = 1; s->br_last_node[nb] = s->br_last_node[b]; s->br_row[nb] = s->br_row[b];
+                sa[nsa++] = nb;
+            } else break;
+        }
+        for (int is = 0; is < nsa; is++) {                                            // :599-625
+            const int br = sa[is];
+            if (s->n_nodes + n_new >= c.max_nodes) { s->br_drafting[br] = 0; continue; }   // capacity guard (not in the reference)
+            new_tok[n_new] = ids[is]; new_src[n_new] = s->br_last_node[br]; new_br[n_new] = br; n_new++;
+            if (s->n_nodes + n_new > c.n_draft) s->br_drafting[br] = 0;               // batch_tgt.n_tokens > n_draft
+        }
+    }
+    for (int i = 0; i < n_new; i++) {
+        const int node = first_new + i, par = new_src[i];
+        s->tokens[node] = new_tok[i]; s->parent[node] = par; s->depth[node] = s->depth[par] + 1; s->pos[node] = s->n_past + s->depth[node];
+        set_bits_from_parent(s, node);
+        s->br_last_node[new_br[i]] = node; s->br_row[new_br[i]] = i;
+    }
+    s->n_nodes = first_new + n_new;
+    s->cur_depth++;
+    // next draft batch = the new nodes (every node is run through the head so that it owns a KV cell)
+    s->dft_n = n_new; s->dft_node_base = first_new;
+    for (int r = 0; r < c.n_branch; r++) {
+        const bool live = r < n_new; const int node = first_new + r;
+        s->dft_tokens[r] = live ? new_tok[r] : 0;
+        s->dft_pos[r] = live ? s->pos[node] : s->n_past;
+        s->dft_src[r] = live ? new_src[r] : -1;
+        uint32_t *b = s->dft_bits + r * 4;
+        if (live) { const uint32_t *nb = s->tree_bits + node * 4; b[0] = nb[0]; b[1] = nb[1]; b[2] = nb[2]; b[3] = nb[3]; }
+        else { b[0] = b[1] = b[2] = b[3] = 0; const int cell = first_new + r; if (cell < 128) b[cell >> 5] = 1u << (cell & 31); }
+    }
+    s->ctl_head.node_base = first_new; s->ctl_head.n_tree = min(128, first_new + c.n_branch);
+    int any = 0;
+    for (int b = 0; b < n_seq_dft; b++) any |= s->br_drafting[b];
+    if (n_new == 0 || !any || s->n_nodes > c.n_draft) s->done = 1;                    // :627-641
+}
+
+// Greedy accept walk (speculative-eagle.cpp:395-449) + state update.  best[t] = target argmax at
+// node t.  fixed_accept >= 0: accept exactly that many draft nodes down first children (bench).
+__global__ void accept_kernel(SpecState *s, SpecCfg c, const int32_t *best) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    int cur = 0, n = 0;
+    s->path[n++] = 0;
+    for (;;) {
+        int next = -1;
+        for (int ch = cur + 1; ch < s->n_nodes; ch++) {
+            if (s->parent[ch] != cur) continue;
+            if (c.fixed_accept >= 0 ? true : s->tokens[ch] == best[cur]) { next = ch; break; }
+        }
+        if (next < 0 || (c.fixed_accept >= 0 && n - 1 >= c.fixed_accept)) break;
+        cur = next; s->path[n++] = cur;
+    }
+    s->n_accept = n; s->bonus = best[cur]; s->last_node = cur;
+}
+
+// KV compaction, phase 1: gather accepted cells to a staging buffer; phase 2: write them back at
+// the contiguous tail.  (Reference: metadata-only seq_keep/seq_cp + lazy defrag,
+// R/src/llama-kv-cache.cpp:368-499, R/src/llama.cpp:1384-1450; here the rows move immediately.)
+__global__ void kv_gather_kernel(const SpecState *s, const __half *kc, const __half *vc, __half *stage, int64_t layer_stride, int E, int max_acc) {
+    const int i = blockIdx.y, l = blockIdx.z;
+    if (i >= s->n_accept || s->path[i] == i) return;
+    const int64_t src = (int64_t)l * layer_stride + (int64_t)(s->n_past + s->path[i]) * E;
+    const int64_t dst = (((int64_t)l * max_acc + i) * 2) * E;
+    for (int e = (blockIdx.x * blockDim.x + threadIdx.x) * 8; e < E; e += gridDim.x * blockDim.x * 8) {
+        *(int4 *)(stage + dst + e) = *(const int4 *)(kc + src + e);
+        *(int4 *)(stage + dst + E + e) = *(const int4 *)(vc + src + e);
+    }
+}
+__global__ void kv_scatter_kernel(const SpecState *s, __half *kc, __half *vc, const __half *stage, int64_t layer_stride, int E, int max_acc) {
+    const int i = blockIdx.y, l = blockIdx.z;
+    if (i >= s->n_accept || s->path[i] == i) return;
+    const int64_t dstc = (int64_t)l * layer_stride + (int64_t)(s->n_past + i) * E;
+    const int64_t src = (((int64_t)l * max_acc + i) * 2) * E;
+    for (int e = (blockIdx.x * blockDim.x + threadIdx.x) * 8; e < E; e += gridDim.x * blockDim.x * 8) {
+        *(int4 *)(kc + dstc + e) = *(const int4 *)(stage + src + e);
+        *(int4 *)(vc + dstc + e) = *(const int4 *)(stage + src + E + e);
+    }
+}
+// end of round: commit, hand the target feature of the last accepted node to the head, fill the
+// host-visible result record
+__global__ void round_end_kernel(SpecState *s, const float *tgt_feat, float *root_feat, int E, eb_round_result *res) {
+    const int last = s->last_node;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < E; i += gridDim.x * blockDim.x) root_feat[i] = tgt_feat[(int64_t)last * E + i];
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        res->n_nodes = s->n_nodes; res->n_accept = s->n_accept; res->bonus = s->bonus;
+        for (int i = 0; i < 128; i++) { res->tokens[i] = s->tokens[i]; res->parent[i] = s->parent[i]; res->path[i] = i < s->n_accept ? s->path[i] : -1; }
+    }
+}
+__global__ void round_commit_kernel(SpecState *s) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    s->n_past += s->n_accept; s->root_token = s->bonus;
+}
+
+int eb_spec_round_begin(SpecState *s, const SpecCfg &c, cudaStream_t st) { round_begin_kernel<<<1, 32, 0, st>>>(s, c); EB_CHECK_LAUNCH(); return EB_OK; }
+int eb_spec_gather_hidden(const SpecState *s, const float *root_feat, const float *node_feat, float *hidden, int E, int n_branch, cudaStream_t st) {
+    gather_hidden_kernel<<<dim3((unsigned)cdiv(E / 4, 256), n_branch), 256, 0, st>>>(s, root_feat, node_feat, hidden, E, n_branch); EB_CHECK_LAUNCH(); return EB_OK;
+}
+int eb_spec_scatter_feat(const SpecState *s, const float *feat, float *node_feat, int E, int n_branch, cudaStream_t st) {
+    scatter_feat_kernel<<<dim3((unsigned)cdiv(E / 4, 256), n_branch), 256, 0, st>>>(s, feat, node_feat, E, n_branch); EB_CHECK_LAUNCH(); return EB_OK;
+}
+int eb_spec_expand(SpecState *s, const SpecCfg &c, const int32_t *cand_ids, const float *cand_p, cudaStream_t st) {
+    tree_expand_kernel<<<1, 32, 0, st>>>(s, c, cand_ids, cand_p); EB_CHECK_LAUNCH(); return EB_OK;
+}
+int eb_spec_accept(SpecState *s, const SpecCfg &c, const int32_t *best, cudaStream_t st) { accept_kernel<<<1, 32, 0, st>>>(s, c, best); EB_CHECK_LAUNCH(); return EB_OK; }
+int eb_spec_compact(SpecState *s, void *kc, void *vc, void *stage, int64_t layer_stride, int E, int L, int max_acc, cudaStream_t st) {
+    const dim3 grid(2, max_acc, L);
+    kv_gather_kernel<<<grid, 256, 0, st>>>(s, (const __half *)kc, (const __half *)vc, (__half *)stage, layer_stride, E, max_acc); EB_CHECK_LAUNCH();
+    kv_scatter_kernel<<<grid, 256, 0, st>>>(s, (__half *)kc, (__half *)vc, (const __half *)stage, layer_stride, E, max_acc); EB_CHECK_LAUNCH();
+    return EB_OK;
+}
+int eb_spec_round_end(SpecState *s, const float *tgt_feat, float *root_feat, int E, eb_round_result *res, cudaStream_t st) {
+    round_end_kernel<<<4, 256, 0, st>>>(s, tgt_feat, root_feat, E, res); EB_CHECK_LAUNCH();
+    round_commit_kernel<<<1, 32, 0, st>>>(s); EB_CHECK_LAUNCH();
+    return EB_OK;
+}
+
+int eb_spec_init() { EB_CUDA(cudaFuncSetAttribute(top_k_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 56000 * 4)); return EB_OK; }

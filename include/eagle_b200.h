@@ -1,0 +1,189 @@
+/*
+ * eagle_b200.h — C-ABI of libeagle_b200.so: the B200 (sm_100a) implementation of the EAGLE
+ * speculative-decoding hot path of mkjsym/EAGLE-in-llama.cpp.
+ *
+ * Plain pointers and sizes only; no torch / ggml types.  Two layers:
+ *   (1) operator entry points — one per ggml op on the path (what a ggml backend's
+ *       graph_compute dispatches to; eagle-in-llama.cpp_b200/ggml_backend/ggml-b200.cpp binds
+ *       them behind the reference's ggml_backend_i vtable);
+ *   (2) the fused speculative-step engine (model upload, tree-verify forward, draft-head
+ *       forward + tree expansion, accept walk, KV compaction) with no host round trip inside
+ *       a round.
+ * Pointers named d_* are device pointers, h_* are host pointers.  `stream` is a cudaStream_t
+ * passed as void* (NULL = the library's own stream).  Every function returns 0 on success or a
+ * negative eb_status; eb_last_error() gives the message.  There is no CPU fallback: every entry
+ * point fails with EB_ERR_CUDA when no sm_100 device is usable.
+ *
+ * R = /root/reference/llama.cpp/ in the citations below.
+ */
+#ifndef EAGLE_B200_H
+#define EAGLE_B200_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define EB_API __attribute__((visibility("default")))
+
+typedef enum { EB_OK = 0, EB_ERR_ARG = -1, EB_ERR_CUDA = -2, EB_ERR_UNSUPPORTED = -3, EB_ERR_OOM = -4 } eb_status;
+
+/* numeric values of enum ggml_type, R/ggml/include/ggml.h:351-390 */
+typedef enum { EB_F32 = 0, EB_F16 = 1, EB_Q4_0 = 2, EB_Q8_0 = 8, EB_Q4_K = 12, EB_Q6_K = 14 } eb_type;
+
+EB_API const char *eb_last_error(void);
+EB_API int  eb_version(void);
+EB_API int  eb_device_init(int device);                 /* selects the device, checks sm_100 */
+EB_API int  eb_device_sm_count(void);
+EB_API size_t eb_row_size(int type, int64_t k);         /* ggml_row_size, R/ggml/src/ggml.c:1183 */
+
+/* ---- device memory (ggml_backend_buffer_i alloc/set/get, R/ggml/src/ggml-backend-impl.h:41-72) */
+EB_API int eb_malloc(void **d_ptr, size_t bytes);
+EB_API int eb_free(void *d_ptr);
+EB_API int eb_memset(void *d_ptr, int value, size_t bytes, void *stream);
+EB_API int eb_upload(void *d_dst, const void *h_src, size_t bytes, void *stream);    /* set_tensor */
+EB_API int eb_download(void *h_dst, const void *d_src, size_t bytes, void *stream);  /* get_tensor */
+EB_API int eb_synchronize(void *stream);
+
+/* ---- operator layer ------------------------------------------------------------------ */
+/* Device layout of quantised weights.  Q4_K blocks (16-byte aligned) stay in GGUF order; the
+ * 2-byte-aligned GGUF formats (Q4_0 18 B, Q8_0 34 B, Q6_K 210 B blocks, R/ggml/src/ggml-common.h:
+ * 161-327) are split into aligned planes over the whole tensor so that every kernel load is a
+ * full-width aligned vector load.  Same byte count, lossless; eb_unpack restores the GGUF bytes
+ * (this is what a backend's set_tensor / get_tensor do: R/ggml/src/ggml-backend-impl.h:50-52).
+ * All operator entry points below take weights in DEVICE layout. */
+EB_API int eb_repack(int type, const void *d_gguf, void *d_dev, int64_t n_elems, void *stream);
+EB_API int eb_unpack(int type, const void *d_dev, void *d_gguf, int64_t n_elems, void *stream);
+/* from_float of the CPU mul_mat (quantize_row_q8_K R/ggml/src/ggml-quants.c:2479 when kq = 1,
+ * quantize_row_q8_0 R/ggml/src/ggml-cpu/ggml-cpu-quants.c:738 when kq = 0), output as planes:
+ * qs int8 [T][K]; d f32 [T][K/256 | K/32]; bsum f16 [T][K/16] (kq = 1 only).  Replaces
+ * quantize_q8_1 R/ggml/src/ggml-cuda/quantize.cu:4. */
+EB_API int eb_quantize_act_planes(int kq, const float *d_x, int64_t K, int T, int8_t *d_qs, float *d_d,
+                                  void *d_bsum_f16, void *stream);
+/* to_float of a quantised tensor: replaces dequantize_block_* R/ggml/src/ggml-cuda/convert.cu:71,190,255
+ * (CPU: dequantize_row_* R/ggml/src/ggml-quants.c:255,349,1280,1690).  Bit-exact. */
+EB_API int eb_dequantize(int type, const void *d_src, float *d_dst, int64_t n_elems, void *stream);
+
+/* GGML_OP_MUL_MAT: d_y[t*N + n] = sum_k W[n][k] * d_x[t*K + k].  Replaces mul_mat_vec_q
+ * (R/ggml/src/ggml-cuda/mmvq.cu:49-200, T <= 8) and mul_mat_q (R/ggml/src/ggml-cuda/mmq.cuh:2502-2822,
+ * T > 8).  Activations are quantised on the CPU backend's grid (Q8_K for K-quants, Q8_0 for
+ * Q4_0/Q8_0: R/ggml/src/ggml-cpu/ggml-cpu.c:254-419,7588-7623) so integer dots equal the oracle's.
+ * d_ws: scratch of at least eb_mul_mat_ws_size() bytes. */
+EB_API size_t eb_mul_mat_ws_size(int type, int64_t N, int64_t K, int64_t T);
+EB_API int eb_mul_mat(int type, const void *d_W, int64_t N, int64_t K, const float *d_x, int64_t T,
+                      float *d_y, void *d_ws, void *stream);
+
+/* GGML_OP_RMS_NORM (+ optional GGML_OP_MUL by a weight row): R/ggml/src/ggml-cuda/norm.cu:108 */
+EB_API int eb_rms_norm(const float *d_x, const float *d_weight_or_null, float *d_y, int64_t n,
+                       int64_t rows, float eps, void *stream);
+/* GGML_OP_ROPE, mode NORM, in place on [T][n_head][D]: R/ggml/src/ggml-cuda/rope.cu:41 */
+EB_API int eb_rope_norm(float *d_x, const int32_t *d_pos, int D, int n_head, int T, float freq_base, void *stream);
+/* GGML_OP_GET_ROWS with dequantisation: R/ggml/src/ggml-cuda/getrows.cu:5-148 */
+EB_API int eb_get_rows_n(int type, const void *d_W, int64_t n_rows, int64_t K, const int32_t *d_ids, int n, float *d_out, void *stream);
+/* elementwise: R/ggml/src/ggml-cuda/binbcast.cu:26, unary.cu:45,201.  b is broadcast over rows
+ * when nb < n (nb must divide n). */
+EB_API int eb_add(const float *d_a, const float *d_b, float *d_y, int64_t n, int64_t nb, void *stream);
+EB_API int eb_mul(const float *d_a, const float *d_b, float *d_y, int64_t n, int64_t nb, void *stream);
+EB_API int eb_silu(const float *d_x, float *d_y, int64_t n, void *stream);
+EB_API int eb_relu(const float *d_x, float *d_y, int64_t n, void *stream);
+/* GGML_OP_CPY f32 -> f16 (KV store), R/ggml/src/ggml-cuda/cpy.cu:35 */
+EB_API int eb_cpy_f32_f16(const float *d_x, void *d_y_f16, int64_t n, void *stream);
+
+/* GGML_OP_FLASH_ATTN_EXT: replaces flash_attn_ext_f16 R/ggml/src/ggml-cuda/fattn-mma-f16.cuh:806
+ * (CPU: R/ggml/src/ggml-cpu/ggml-cpu.c:10999).  q f32 [T][H][D]; k, v f16 cells, row stride
+ * kv_stride elements between cells, head h at offset h*D; out f32 [T][H][D].  D must be 128.
+ * Mask, one of:  d_mask_f16 [T_pad][n_kv] (ggml layout, R/ggml/include/ggml.h:1778-1793), or
+ * the compact tree form: cells [0,n_prefix) visible to all rows, cell n_prefix+j visible to row t
+ * iff bit j of d_tree_bits[t*4 .. t*4+3] (128 bits per row) is set; other cells invisible. */
+EB_API size_t eb_flash_attn_ws_size(int T, int H, int D, int n_kv);
+EB_API int eb_flash_attn(const float *d_q, const void *d_k, const void *d_v, int64_t kv_stride,
+                         const void *d_mask_f16, int64_t mask_stride,
+                         const uint32_t *d_tree_bits, int n_prefix,
+                         int T, int H, int D, int n_kv, float scale, float *d_out, void *d_ws, void *stream);
+
+/* GGML_OP_ARGMAX / top-k (R/ggml/src/ggml-cuda/argmax.cu:8, argsort.cu:11; host sampler
+ * R/src/llama-sampling.cpp:228-302): per row top-k by logit, ties to the lower id; probs =
+ * softmax over the k kept logits. k <= 16. */
+EB_API int eb_top_k(const float *d_logits, int rows, int V, int k, int32_t *d_ids, float *d_vals, float *d_probs, void *stream);
+EB_API int eb_argmax(const float *d_logits, int rows, int V, int32_t *d_ids, void *stream);
+
+/* ---- engine layer -------------------------------------------------------------------- */
+typedef struct eb_model eb_model;      /* weights of one GGUF model resident in HBM */
+typedef struct eb_session eb_session;  /* target + head + both KV caches + tree state */
+
+/* tensor slots (R/src/llama-arch.cpp:1301-1326 names in comments) */
+enum { EB_T_TOK_EMBD = 0 /*token_embd*/, EB_T_OUTPUT_NORM /*output_norm*/, EB_T_OUTPUT /*output*/,
+       EB_T_FC /*fc.weight*/, EB_T_FC_BIAS /*fc.bias*/, EB_T_GLOBAL_COUNT };
+enum { EB_L_ATTN_NORM = 0, EB_L_WQ, EB_L_WK, EB_L_WV, EB_L_WO, EB_L_FFN_NORM, EB_L_GATE, EB_L_UP,
+       EB_L_DOWN, EB_L_COUNT };
+
+/* hparams: R/src/llama-model.cpp:410-487.  is_eagle selects build_eagle (R/src/llama.cpp:1839). */
+EB_API eb_model *eb_model_create(int E, int H, int F, int V, int L, float eps, float freq_base, int is_eagle);
+EB_API void      eb_model_free(eb_model *m);
+/* upload one tensor in its GGUF block layout (host pointer); layer = -1 for globals */
+EB_API int eb_model_set_tensor(eb_model *m, int layer, int which, int type, const void *h_data);
+/* fill one tensor with synthetic random blocks directly on the device (bench fixtures) */
+EB_API int eb_model_synth_tensor(eb_model *m, int layer, int which, int type, uint64_t seed, float scale);
+/* read a tensor back in GGUF block layout (get_tensor) */
+EB_API int eb_model_get_tensor(const eb_model *m, int layer, int which, void *h_data, size_t bytes);
+EB_API int eb_model_share_lm_head(eb_model *head, const eb_model *target);   /* R/src/llama.cpp:2016 */
+EB_API size_t eb_model_weight_bytes(const eb_model *m);   /* bytes one forward streams */
+
+typedef struct {
+    int n_ctx;          /* KV cells per cache */
+    int max_nodes;      /* verify batch capacity incl. root (<= 128) */
+    int n_branch;       /* -np: max simultaneous draft branches (<= 16) */
+    int n_draft;        /* --draft-max: stop a branch once the verify batch exceeds it */
+    int max_depth;      /* draft levels captured in the graph */
+    int top_k;          /* draft candidates per node (reference: 10, R/common/speculative.cpp:47) */
+    float p_split;      /* --draft-p-split, R/common/common.h:183 */
+    int fixed_accept;   /* >= 0: accept exactly this many draft nodes per round (bench mode) */
+    int use_graph;      /* capture the round in a CUDA graph */
+} eb_session_params;
+
+EB_API eb_session *eb_session_create(eb_model *target, eb_model *head, const eb_session_params *p);
+EB_API void        eb_session_free(eb_session *s);
+
+/* One forward of `model` (0 = target, 1 = head) over T tokens with tree structure parent[]
+ * (parent[i] < i, -1 = attends the committed prefix only), appended at the cache tail without
+ * committing.  Host in / host out; used by parity tests and by prefill.  h_hidden [T][E] only
+ * for the head.  h_logits [T][V] / h_feat [T][E] may be NULL. */
+EB_API int eb_session_forward(eb_session *s, int model, const int32_t *h_tokens, const int32_t *h_pos,
+                              const int32_t *h_parent, const float *h_hidden, int T,
+                              float *h_logits, float *h_feat);
+/* commit the first n of the T tokens of the last forward of `model` (chain prefill) */
+EB_API int eb_session_commit(eb_session *s, int model, int n);
+EB_API int eb_session_n_past(const eb_session *s, int model);
+/* fill both KV caches with n_past cells of synthetic N(0,1) K/V (bench: 4K context) */
+EB_API int eb_session_synth_kv(eb_session *s, int n_past, uint64_t seed);
+/* start decoding: last committed token id + the target feature (result_norm) that produced it */
+EB_API int eb_session_set_root(eb_session *s, int32_t id_last, const float *h_feat_or_null);
+
+typedef struct {
+    int n_nodes;        /* verify batch size incl. root */
+    int n_accept;       /* accepted nodes incl. root */
+    int32_t bonus;      /* target argmax at the last accepted node = next round's root */
+    int32_t tokens[128];   /* tree tokens (node order) */
+    int32_t parent[128];
+    int32_t path[128];     /* accepted node ids */
+    float   gpu_ms;        /* device time of the round (CUDA events) */
+} eb_round_result;
+
+/* One speculative round entirely on the device: draft-head forward(s) + top-k tree expansion,
+ * tree-verify forward of the target, greedy accept walk, KV compaction of both caches, feature
+ * hand-off.  Only h_out crosses the bus (one small D2H). */
+EB_API int eb_session_round(eb_session *s, eb_round_result *h_out);
+/* verify forward alone on the current tree (micro-bench: device time in *gpu_ms) */
+EB_API int eb_session_verify_only(eb_session *s, int T, float *gpu_ms);
+/* micro-bench of one hot kernel class (GEMM for T > 8, matvec for T <= 8): average device ms per
+ * launch over `iters` launches cycling through n_bufs distinct weight buffers (HBM-resident,
+ * larger than L2 in total), CUDA events on the launching stream */
+EB_API int eb_bench_mul_mat_kernel(int type, int64_t N, int64_t K, int T, int n_bufs, int iters, float *ms_per_launch);
+/* launches of this library's kernels since the last call (bench "gpu_launches") */
+EB_API long eb_launch_count(int reset);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,142 @@
+"""Synthetic model fixtures shared by the CPU and GPU tests (random-init weights, fixed seeds).
+
+Weights are N(0, 0.02^2) (norm weights 1 + N(0, 0.02^2)) quantised with the reference's own
+quantiser when oracle/_ref is present (ggml_quantize_chunk, what llama-quantize calls); without
+it, well-formed random blocks are generated instead — any block bytes are a valid tensor for
+both the oracle and the GPU path.
+"""
+import numpy as np
+
+import pyoracle as po
+
+QTYPES = (po.Q4_0, po.Q8_0, po.Q4_K, po.Q6_K)
+
+
+def random_blocks(t, n_elems, rng, scale=0.02):
+    be, bb = po.BLOCK[t]
+    nb = n_elems // be
+    raw = rng.integers(0, 256, (nb, bb), dtype=np.uint8)
+    d = (scale * (2.2 + 0.6 * rng.random(nb))).astype(np.float32)
+    if t == po.Q4_K:
+        raw[:, 0:2] = (d / (7.5 * 48)).astype(np.float16).view(np.uint8).reshape(nb, 2)
+        raw[:, 2:4] = (d / 48).astype(np.float16).view(np.uint8).reshape(nb, 2)
+    elif t == po.Q6_K:
+        raw[:, 208:210] = (d / (32 * 96)).astype(np.float16).view(np.uint8).reshape(nb, 2)
+    elif t == po.Q4_0:
+        raw[:, 0:2] = (d / 8).astype(np.float16).view(np.uint8).reshape(nb, 2)
+    elif t == po.Q8_0:
+        raw[:, 0:2] = (d / 127).astype(np.float16).view(np.uint8).reshape(nb, 2)
+    return raw.reshape(-1)
+
+
+def quantize(t, w, rng=None):
+    """f32 [rows][cols] -> GGUF block bytes"""
+    w = np.ascontiguousarray(w, np.float32)
+    if t == po.F32:
+        return w.view(np.uint8).reshape(-1).copy()
+    if t == po.F16:
+        return w.astype(np.float16).view(np.uint8).reshape(-1).copy()
+    rows, cols = w.shape
+    if po.have_ref():
+        raw = np.empty(rows * po.row_size(t, cols), np.uint8)
+        po.ref()._g("quantize")(t, po._ptr(w), po._ptr(raw), rows, cols)
+        return raw
+    return random_blocks(t, rows * cols, rng or np.random.default_rng(0))
+
+
+def q4_k_m_type(which, layer, n_layer):
+    """llama-quantize's Q4_K_M mixture (R/src/llama-quant.cpp:129-338): Q6_K for `output` and for
+    attn_v / ffn_down in the use_more_bits layers, Q4_K elsewhere."""
+    more = layer < n_layer // 8 or layer >= 7 * n_layer // 8 or (layer - n_layer // 8) % 3 == 2
+    if which in (po.L_WV, po.L_DOWN) and more:
+        return po.Q6_K
+    return po.Q4_K
+
+
+def make_model(E, H, F, V, L, ftype, seed, is_eagle=False, std=0.02):
+    """-> dict: {'hparams':..., 'globals': {which: (type, raw)}, 'layers': [{which: (type, raw)}]}
+    ftype: one of Q4_0 / Q8_0 / 'q4_k_m'"""
+    rng = np.random.default_rng(seed)
+
+    def mat(rows, cols, t):
+        return (t, quantize(t, rng.normal(0, std, (rows, cols)).astype(np.float32), rng))
+
+    def vec(n):
+        return (po.F32, (1 + rng.normal(0, std, n)).astype(np.float32).view(np.uint8).reshape(-1).copy())
+
+    def lt(which, l):
+        if ftype == "q4_k_m":
+            return q4_k_m_type(which, l, L)
+        return ftype
+
+    base = po.Q4_K if ftype == "q4_k_m" else ftype
+    out_t = po.Q6_K if ftype in ("q4_k_m", po.Q4_0) else ftype      # `output` is Q6_K for Q4_0 and Q4_K_M files
+    g = {po.T_TOK_EMBD: mat(V, E, base)}
+    if is_eagle:
+        g[po.T_FC] = mat(E, 2 * E, base)
+        g[po.T_FC_BIAS] = (po.F32, rng.normal(0, std, E).astype(np.float32).view(np.uint8).reshape(-1).copy())
+    else:
+        g[po.T_OUTPUT_NORM] = vec(E)
+        g[po.T_OUTPUT] = mat(V, E, out_t)
+    layers = []
+    for l in range(L):
+        d = {}
+        if not is_eagle:
+            d[po.L_ATTN_NORM] = vec(E)
+        d[po.L_WQ] = mat(E, E, lt(po.L_WQ, l)); d[po.L_WK] = mat(E, E, lt(po.L_WK, l)); d[po.L_WV] = mat(E, E, lt(po.L_WV, l))
+        d[po.L_WO] = mat(E, E, lt(po.L_WO, l)); d[po.L_FFN_NORM] = vec(E)
+        d[po.L_GATE] = mat(F, E, lt(po.L_GATE, l)); d[po.L_UP] = mat(F, E, lt(po.L_UP, l)); d[po.L_DOWN] = mat(E, F, lt(po.L_DOWN, l))
+        layers.append(d)
+    return {"hparams": dict(E=E, H=H, F=F, V=V, L=L, eps=1e-5, freq_base=10000.0, is_eagle=is_eagle), "globals": g, "layers": layers}
+
+
+def to_cpu_model(path, fx, target=None):
+    """instantiate the fixture in a CPU path (oracle or ref); keeps the raw buffers alive"""
+    hp = fx["hparams"]
+    m = path.model_new(hp["E"], hp["H"], hp["F"], hp["V"], hp["L"], hp["eps"], hp["freq_base"], hp["is_eagle"])
+    for which, (t, raw) in fx["globals"].items():
+        path._g("model_set_global")(m, which, t, po._ptr(raw))
+    for l, d in enumerate(fx["layers"]):
+        for which, (t, raw) in d.items():
+            path._g("model_set_layer")(m, l, which, t, po._ptr(raw))
+    if target is not None:
+        path._g("model_set_lm_head_from")(m, target)
+    return m
+
+
+def to_gpu_model(eb, fx, target=None):
+    hp = fx["hparams"]
+    m = eb.Model(hp["E"], hp["H"], hp["F"], hp["V"], hp["L"], hp["eps"], hp["freq_base"], hp["is_eagle"])
+    for which, (t, raw) in fx["globals"].items():
+        m.set_tensor(-1, which, t, raw)
+    for l, d in enumerate(fx["layers"]):
+        for which, (t, raw) in d.items():
+            m.set_tensor(l, which, t, raw)
+    if target is not None:
+        m.share_lm_head(target)
+    return m
+
+
+def tree_parents(T, rng, n_branch=4):
+    """random tree in creation order: parent[i] < i"""
+    par = np.full(T, -1, np.int32)
+    for i in range(1, T):
+        par[i] = rng.integers(max(0, i - n_branch), i)
+    return par
+
+
+def tree_depths(par):
+    d = np.zeros(len(par), np.int32)
+    for i in range(1, len(par)):
+        d[i] = d[par[i]] + 1
+    return d
+
+
+def vis_matrix(par, n_past, n_kv):
+    """[T][n_kv] visibility: committed prefix + ancestors-or-self (cells n_past + node)"""
+    tv = po.tree_vis(par)
+    T = len(par)
+    vis = np.zeros((T, n_kv), np.uint8)
+    vis[:, :n_past] = 1
+    vis[:, n_past:n_past + T] = tv
+    return vis
