@@ -148,15 +148,21 @@ __global__ void __launch_bounds__(256) fattn_kernel(FaParams p) {
         const float corr0 = exp2f(m0 - base0), corr1 = exp2f(m1 - base1);   // m = -inf -> 0
         m0 = mn0; m1 = mn1;
         float rs0 = 0.f, rs1 = 0.f;
-        uint32_t pa[4][4];
+        // P is split into an f16 head and an f16 residual (two MMAs per tile) so that P.V carries
+        // ~22 bits of P: activation quantisation downstream amplifies 1e-4 errors into logit noise
+        uint32_t pa[4][4], pl[4][4];
 #pragma unroll
         for (int nt = 0; nt < 8; nt++) {
             const float p0 = exp2f(s[nt][0] - base0), p1 = exp2f(s[nt][1] - base0);
             const float p2 = exp2f(s[nt][2] - base1), p3 = exp2f(s[nt][3] - base1);
             rs0 += p0 + p1; rs1 += p2 + p3;
             const __half2 h01 = __floats2half2_rn(p0, p1), h23 = __floats2half2_rn(p2, p3);
+            const __half2 l01 = __floats2half2_rn(p0 - __low2float(h01), p1 - __high2float(h01));
+            const __half2 l23 = __floats2half2_rn(p2 - __low2float(h23), p3 - __high2float(h23));
             pa[nt >> 1][(nt & 1) * 2 + 0] = *(const uint32_t *)&h01;
             pa[nt >> 1][(nt & 1) * 2 + 1] = *(const uint32_t *)&h23;
+            pl[nt >> 1][(nt & 1) * 2 + 0] = *(const uint32_t *)&l01;
+            pl[nt >> 1][(nt & 1) * 2 + 1] = *(const uint32_t *)&l23;
         }
         l0 = l0 * corr0 + rs0; l1 = l1 * corr1 + rs1;      // per-lane partial sums (reduced over t at the end)
 #pragma unroll
@@ -171,6 +177,8 @@ __global__ void __launch_bounds__(256) fattn_kernel(FaParams p) {
                 ldsm4t(b, sv + fa_off(cell, chunk));
                 fa_mma(o[nd], pa[kk], b[0], b[1]);
                 fa_mma(o[nd + 1], pa[kk], b[2], b[3]);
+                fa_mma(o[nd], pl[kk], b[0], b[1]);
+                fa_mma(o[nd + 1], pl[kk], b[2], b[3]);
             }
         }
         }

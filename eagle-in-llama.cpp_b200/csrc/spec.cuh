@@ -12,13 +12,13 @@ struct SpecState {
     int n_past; int root_token;
     // tree of the current round (node 0 = root)
     int n_nodes; int tokens[128]; int parent[128]; int pos[128]; int depth[128];
-    uint32_t tree_bits[128 * 4];          // ancestor-or-self sets
+    alignas(16) uint32_t tree_bits[128 * 4];   // ancestor-or-self sets (read as uint4)
     // branches (the reference's drafts[s], speculative-eagle.cpp:21-33)
     int n_seq_cur; int br_drafting[16]; int br_last_node[16]; int br_row[16];
     int cur_depth; int done;
     // draft batch for the next head forward
     int dft_n; int dft_node_base; int dft_tokens[16]; int dft_pos[16]; int dft_src[16];
-    uint32_t dft_bits[16 * 4];
+    alignas(16) uint32_t dft_bits[16 * 4];
     // accept
     int n_accept; int bonus; int last_node; int path[128];
     FwdCtl ctl_head, ctl_tgt;

@@ -364,8 +364,40 @@ void eo_get_rows(int type, const void *W, int64_t K, const int32_t *ids, int n, 
 
 /* ggml-cpu.c:10999-11212 with K,V f16: Q row -> f16, s = dot(K,Q) in f32, online softmax with an
  * f16 VKQ accumulator (ggml_vec_scale_f16 / ggml_vec_mad_f16 round to f16 after every op). */
+static int g_fa_acc_f32 = 0;
+/* 0 (default): the reference's f16 VKQ accumulator.  1: f32 accumulator — NOT the reference's
+ * arithmetic; it is the checker for the GPU kernel's documented deviation:
+ * everything else in the forward stays the reference's. */
+void eo_set_fattn_acc_f32(int on) { g_fa_acc_f32 = on; }
+
+static void flash_attn_f32acc(const float *q, const uint16_t *k, const uint16_t *v, const uint8_t *vis,
+                              int T, int H, int D, int n_kv, float scale, float *out) {
+    #pragma omp parallel for collapse(2) schedule(static)
+    for (int t = 0; t < T; t++) for (int h = 0; h < H; h++) {
+        float qf[512], acc[512];
+        const float *pq = q + ((size_t)t * H + h) * D;
+        for (int d = 0; d < D; d++) { qf[d] = eo_f16_to_f32(eo_f32_to_f16(pq[d])); acc[d] = 0; }
+        float S = 0.0f, M = -INFINITY;
+        for (int ic = 0; ic < n_kv; ic++) {
+            if (!vis[(size_t)t * n_kv + ic]) continue;
+            const uint16_t *kr = k + ((size_t)ic * H + h) * D, *vr = v + ((size_t)ic * H + h) * D;
+            float s = 0; for (int d = 0; d < D; d++) s += eo_f16_to_f32(kr[d]) * qf[d];
+            s = s * scale;
+            const float Mold = M; float ms = 1.0f, vs = 1.0f;
+            if (s > M) { M = s; ms = expf(Mold - M); for (int d = 0; d < D; d++) acc[d] *= ms; }
+            else vs = expf(s - M);
+            for (int d = 0; d < D; d++) acc[d] += eo_f16_to_f32(vr[d]) * vs;
+            S = S * ms + vs;
+        }
+        const float S_inv = 1.0f / S;
+        float *po = out + ((size_t)t * H + h) * D;
+        for (int d = 0; d < D; d++) po[d] = acc[d] * S_inv;
+    }
+}
+
 void eo_flash_attn(const float *q, const uint16_t *k, const uint16_t *v, const uint8_t *vis,
                    int T, int H, int D, int n_kv, float scale, float *out) {
+    if (g_fa_acc_f32) { flash_attn_f32acc(q, k, v, vis, T, H, D, n_kv, scale, out); return; }
     #pragma omp parallel for collapse(2) schedule(static)
     for (int t = 0; t < T; t++) for (int h = 0; h < H; h++) {
         float qf[512]; uint16_t acc[512];

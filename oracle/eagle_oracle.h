@@ -59,6 +59,10 @@ void eo_get_rows(int type, const void *W, int64_t K, const int32_t *ids, int n, 
 void eo_flash_attn(const float *q, const uint16_t *k, const uint16_t *v, const uint8_t *vis,
                    int T, int H, int D, int n_kv, float scale, float *out);
 
+/* checker switch for the GPU kernel's documented deviation: 1 = keep the V accumulator in f32
+ * instead of the reference's f16 (default 0 = reference arithmetic) */
+void eo_set_fattn_acc_f32(int on);
+
 /* KQ mask rule of R/src/llama-context.cpp:161-193: cell i visible to query j iff the cell holds
  * the query's first seq id and cell_pos[i] <= pos[j].  seq sets are 64-bit bitsets. */
 void eo_build_kq_mask(const int32_t *cell_pos, const uint64_t *cell_seq, int n_kv,

@@ -204,6 +204,19 @@ def ref():
     return _cache["ref"]
 
 
+def set_fattn_acc_f32(on):
+    """oracle only: f32 V accumulator in flash attention (checker for the GPU deviation)"""
+    oracle().lib.eo_set_fattn_acc_f32(int(on))
+
+
+class fattn_acc_f32:
+    def __enter__(self):
+        set_fattn_acc_f32(1)
+
+    def __exit__(self, *a):
+        set_fattn_acc_f32(0)
+
+
 # ---- oracle-only helpers (speculative-step pieces)
 def top_k(logits, k):
     o = oracle()
