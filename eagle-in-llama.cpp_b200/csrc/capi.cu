@@ -16,6 +16,8 @@ int eb_set_err(int code, const char *fmt, ...) {
     return code;
 }
 void eb_count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
+long eb_launches_now() { return g_launches.load(); }
+void eb_launches_add(long n) { g_launches.fetch_add(n); }
 int eb_sm_count() { return g_sm_count > 0 ? g_sm_count : 148; }
 
 extern "C" {
@@ -34,7 +36,7 @@ int eb_device_init(int device) {
     EB_CUDA(cudaSetDevice(device));
     g_sm_count = prop.multiProcessorCount; g_device = device;
     int rc;
-    if ((rc = eb_mmq_init()) || (rc = eb_fattn_init()) || (rc = eb_spec_init())) return rc;
+    if ((rc = eb_mmq_init()) || (rc = eb_fattn_init()) || (rc = eb_spec_init()) || (rc = eb_fused_init())) return rc;
     return EB_OK;
 }
 int eb_device_sm_count(void) { return g_sm_count; }

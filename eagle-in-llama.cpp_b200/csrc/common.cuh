@@ -55,6 +55,7 @@ int eb_set_err(int code, const char *fmt, ...);
 #define EB_CHECK_LAUNCH() do { eb_count_launch(); cudaError_t e_ = cudaGetLastError(); if (e_ != cudaSuccess) \
     return eb_set_err(EB_ERR_CUDA, "%s:%d launch: %s", __FILE__, __LINE__, cudaGetErrorString(e_)); } while (0)
 void eb_count_launch();
+long eb_launches_now(); void eb_launches_add(long n);   // kernels recorded in a CUDA graph are counted per replay
 int eb_sm_count();
 int eb_mmq_init(); int eb_fattn_init(); int eb_spec_init();
 
@@ -91,5 +92,7 @@ int eb_repack_impl(int type, void *gguf, void *dev, int64_t nb, int dir, cudaStr
 int eb_synth_impl(int type, void *dst, int64_t n_elems, uint64_t seed, float scale, int norm_weight, cudaStream_t st);
 int eb_mmvq(int type, const void *W, int64_t N, int64_t K, const ActQ &a, float *y, cudaStream_t st);   // mmvq.cu
 int eb_mmq(int type, const void *W, int64_t N, int64_t K, const ActQ &a, float *y, float *partial, int ksplit, cudaStream_t st); // mmq.cu
+int eb_mmq_parts(int type, const void *W, int64_t N, int64_t K, const ActQ &a, float *planes, int *ks_out, cudaStream_t st);
+int eb_fused_init();
 int eb_mmq_supported(int type, int64_t N, int64_t K, int T);
 int eb_mmq_pick_ksplit(int type, int64_t N, int64_t K, int T);

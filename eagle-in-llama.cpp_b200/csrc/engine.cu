@@ -140,9 +140,11 @@ static int ws_alloc(Workspace &w, const eb_model *m, int Tmax, int n_ctx) {
     EB_CUDA(fa(&w.x, T * E)); EB_CUDA(fa(&w.cur, T * E)); EB_CUDA(fa(&w.q, T * E)); EB_CUDA(fa(&w.k, T * E)); EB_CUDA(fa(&w.v, T * E));
     EB_CUDA(fa(&w.att, T * E)); EB_CUDA(fa(&w.gate, T * F)); EB_CUDA(fa(&w.up, T * F)); EB_CUDA(fa(&w.cat, T * 2 * E));
     EB_CUDA(fa(&w.hidden, T * E)); EB_CUDA(fa(&w.feat, T * E)); EB_CUDA(fa(&w.logits, T * V));
+    EB_CUDA(fa(&w.pq, 8 * T * E)); EB_CUDA(fa(&w.pk, 8 * T * E)); EB_CUDA(fa(&w.pv, 8 * T * E)); EB_CUDA(fa(&w.po, 8 * T * E));
+    EB_CUDA(fa(&w.pgate, 8 * T * F)); EB_CUDA(fa(&w.pup, 8 * T * F));
     const size_t Kmax = std::max<size_t>(2 * E, F), Nmax = std::max<size_t>(std::max<size_t>(F, V), E);
     w.actq_bytes = 2 * eb_actq_bytes(1, Kmax, Tmax) + 1024;   // generous: either grid
-    EB_CUDA(cudaMalloc(&w.actq, w.actq_bytes));
+    EB_CUDA(cudaMalloc(&w.actq, w.actq_bytes)); EB_CUDA(cudaMalloc(&w.actq2, w.actq_bytes));
     w.partial_bytes = (size_t)8 * T * Nmax * 4;
     EB_CUDA(cudaMalloc((void **)&w.partial, w.partial_bytes));
     w.fa_bytes = eb_flash_attn_ws_size_impl(Tmax, m->H, m->E / m->H, n_ctx);
@@ -153,7 +155,7 @@ static int ws_alloc(Workspace &w, const eb_model *m, int Tmax, int n_ctx) {
 }
 static void ws_free(Workspace &w) {
     for (void *p : {(void *)w.x, (void *)w.cur, (void *)w.q, (void *)w.k, (void *)w.v, (void *)w.att, (void *)w.gate, (void *)w.up, (void *)w.cat,
-                    (void *)w.hidden, (void *)w.feat, (void *)w.logits, (void *)w.partial, w.actq, w.fa_ws, (void *)w.tokens, (void *)w.pos, (void *)w.bits, (void *)w.ctl})
+                    (void *)w.hidden, (void *)w.feat, (void *)w.logits, (void *)w.partial, w.actq, w.actq2, (void *)w.pq, (void *)w.pk, (void *)w.pv, (void *)w.po, (void *)w.pgate, (void *)w.pup, w.fa_ws, (void *)w.tokens, (void *)w.pos, (void *)w.bits, (void *)w.ctl})
         cudaFree(p);
 }
 static int kv_alloc(KVCache &kv, const eb_model *m, int n_ctx) {
@@ -208,6 +210,14 @@ extern "C" void eb_session_free(eb_session *s) {
 // ------------------------------------------------------------------ forward
 // All inputs are device-resident: tokens/pos/bits [T], hidden [T][E] (head), ctl (n_prefix,
 // node_base, n_tree).  K/V rows go to cells n_prefix + node_base + t.
+// GEMM into split-K planes (T > 8, K-quants) or a single plane (matvec path)
+static int mm_parts(const DTensor &w, const ActQ &a, float *planes, int *ks, cudaStream_t st) {
+    if (eb_mmq_supported(w.type, w.rows, w.cols, a.T)) return eb_mmq_parts(w.type, w.data, w.rows, w.cols, a, planes, ks, st);
+    *ks = 1;
+    return eb_mmvq(w.type, w.data, w.rows, w.cols, a, planes, st);
+}
+static int grid_of(const DTensor &w) { return w.type == EB_Q4_K || w.type == EB_Q6_K; }
+
 static int forward_dev(const eb_model *m, KVCache &kv, Workspace &w, const int32_t *tokens, const int32_t *pos, const uint32_t *bits,
                        const float *hidden, const FwdCtl *ctl, int T, bool want_logits, cudaStream_t st) {
     const int E = m->E, H = m->H, F = m->F, D = E / H;
@@ -222,40 +232,50 @@ static int forward_dev(const eb_model *m, KVCache &kv, Workspace &w, const int32
         RC(eb_mul_mat_impl(fc.type, fc.data, E, 2 * E, w.cat, T, w.cur, w.actq, w.partial, st));
         RC(eb_bias_relu_impl(w.cur, (const float *)m->g[EB_T_FC_BIAS].data, w.x, TE, E, st));
     }
+    const float *pend = nullptr; int pend_ks = 0;          // down-projection planes not yet added to x
     for (int l = 0; l < m->L; l++) {
         const std::vector<DTensor> &t = m->layers[l];
-        RC(eb_rms_norm_impl(w.x, (const float *)t[EB_L_ATTN_NORM].data, w.cur, E, T, m->eps, st));
-        if (kq_of(t[EB_L_WQ]) == kq_of(t[EB_L_WK]) && kq_of(t[EB_L_WQ]) == kq_of(t[EB_L_WV])) {
-            ActQ a = eb_actq_carve(w.actq, kq_of(t[EB_L_WQ]), E, T);
-            RC(eb_quantize_act(w.cur, a, st));
-            RC(mul_mat_preq(t[EB_L_WQ], a, w.q, w.partial, st)); RC(mul_mat_preq(t[EB_L_WK], a, w.k, w.partial, st)); RC(mul_mat_preq(t[EB_L_WV], a, w.v, w.partial, st));
-        } else {
-            RC(eb_mul_mat_impl(t[EB_L_WQ].type, t[EB_L_WQ].data, E, E, w.cur, T, w.q, w.actq, w.partial, st));
-            RC(eb_mul_mat_impl(t[EB_L_WK].type, t[EB_L_WK].data, E, E, w.cur, T, w.k, w.actq, w.partial, st));
-            RC(eb_mul_mat_impl(t[EB_L_WV].type, t[EB_L_WV].data, E, E, w.cur, T, w.v, w.actq, w.partial, st));
-        }
+        // x += pending; cur = rms_norm(x) * attn_norm -> activation grid of wq
+        const int gq = grid_of(t[EB_L_WQ]);
+        ActQ a = eb_actq_carve(w.actq, gq, E, T);
+        RC(eb_resid_norm_quant(w.x, pend, pend_ks, (const float *)t[EB_L_ATTN_NORM].data, m->eps, E, T, a, nullptr, st));
+        int kq_, kk_, kv_;
+        RC(mm_parts(t[EB_L_WQ], a, w.pq, &kq_, st));
+        ActQ ak = a, av = a;
+        if (grid_of(t[EB_L_WK]) != gq || grid_of(t[EB_L_WV]) != gq) return eb_set_err(EB_ERR_UNSUPPORTED, "layer %d: wq/wk/wv mix K-quant and 32-block formats", l);
+        RC(mm_parts(t[EB_L_WK], ak, w.pk, &kk_, st));
+        RC(mm_parts(t[EB_L_WV], av, w.pv, &kv_, st));
         __half *kc = kv.k + (int64_t)l * kv.layer_stride, *vc = kv.v + (int64_t)l * kv.layer_stride;
-        RC(eb_rope_kv_store_ctl(w.q, w.k, w.v, pos, kc, vc, ctl, D, H, T, m->freq_base, st));
+        RC(eb_rope_kv_store_fused(w.pq, kq_, w.pk, kk_, w.pv, kv_, w.q, pos, kc, vc, ctl, D, H, T, m->freq_base, st));
         RC(eb_flash_attn_ctl(w.q, kc, vc, E, bits, ctl, T, H, D, kv.n_ctx, 1.0f / sqrtf((float)D), w.att, w.fa_ws, st));
-        RC(eb_mul_mat_impl(t[EB_L_WO].type, t[EB_L_WO].data, E, E, w.att, T, w.cur, w.actq, w.partial, st));
-        RC(eb_add_impl(w.cur, w.x, w.x, TE, TE, st));                      // ffn_inp = cur + inpSA
-        RC(eb_rms_norm_impl(w.x, (const float *)t[EB_L_FFN_NORM].data, w.cur, E, T, m->eps, st));
-        if (kq_of(t[EB_L_UP]) == kq_of(t[EB_L_GATE])) {
-            ActQ a = eb_actq_carve(w.actq, kq_of(t[EB_L_UP]), E, T);
-            RC(eb_quantize_act(w.cur, a, st));
-            RC(mul_mat_preq(t[EB_L_UP], a, w.up, w.partial, st)); RC(mul_mat_preq(t[EB_L_GATE], a, w.gate, w.partial, st));
-        } else {
-            RC(eb_mul_mat_impl(t[EB_L_UP].type, t[EB_L_UP].data, F, E, w.cur, T, w.up, w.actq, w.partial, st));
-            RC(eb_mul_mat_impl(t[EB_L_GATE].type, t[EB_L_GATE].data, F, E, w.cur, T, w.gate, w.actq, w.partial, st));
-        }
-        RC(eb_swiglu_impl(w.gate, w.up, w.gate, (int64_t)T * F, st));
-        RC(eb_mul_mat_impl(t[EB_L_DOWN].type, t[EB_L_DOWN].data, E, F, w.gate, T, w.cur, w.actq, w.partial, st));
-        RC(eb_add_impl(w.cur, w.x, w.x, TE, TE, st));
+        ActQ ao = eb_actq_carve(w.actq, grid_of(t[EB_L_WO]), E, T);
+        RC(eb_quantize_act(w.att, ao, st));
+        int ko_;
+        RC(mm_parts(t[EB_L_WO], ao, w.po, &ko_, st));
+        // ffn_inp = wo.att + x ; cur = rms_norm(ffn_inp) * ffn_norm -> grid of up/gate
+        const int gu = grid_of(t[EB_L_UP]);
+        if (grid_of(t[EB_L_GATE]) != gu) return eb_set_err(EB_ERR_UNSUPPORTED, "layer %d: ffn_up/ffn_gate mix formats", l);
+        ActQ af = eb_actq_carve(w.actq, gu, E, T);
+        RC(eb_resid_norm_quant(w.x, w.po, ko_, (const float *)t[EB_L_FFN_NORM].data, m->eps, E, T, af, nullptr, st));
+        int ku_, kg_;
+        RC(mm_parts(t[EB_L_UP], af, w.pup, &ku_, st));
+        RC(mm_parts(t[EB_L_GATE], af, w.pgate, &kg_, st));
+        ActQ ad = eb_actq_carve(w.actq2, grid_of(t[EB_L_DOWN]), F, T);
+        RC(eb_swiglu_quant(w.pgate, kg_, w.pup, ku_, F, T, ad, st));
+        RC(mm_parts(t[EB_L_DOWN], ad, w.pq, &pend_ks, st));       // pq is free again: holds the down planes
+        pend = w.pq;
     }
-    RC(eb_rms_norm_impl(w.x, (const float *)m->g[EB_T_OUTPUT_NORM].data, w.feat, E, T, m->eps, st));   // result_norm
+    // x += pending; result_norm = rms_norm(x) * output_norm  (-> feat, and the lm_head's grid)
+    const DTensor &o = m->g[EB_T_OUTPUT];
+    ActQ al = eb_actq_carve(w.actq, grid_of(o), E, T);
+    if (!want_logits) al.qs = nullptr;
+    RC(eb_resid_norm_quant(w.x, pend, pend_ks, (const float *)m->g[EB_T_OUTPUT_NORM].data, m->eps, E, T, al, w.feat, st));
     if (want_logits) {
-        const DTensor &o = m->g[EB_T_OUTPUT];
-        RC(eb_mul_mat_impl(o.type, o.data, m->V, E, w.feat, T, w.logits, w.actq, w.partial, st));
+        int kl_;
+        if (eb_mmq_supported(o.type, o.rows, o.cols, T) && eb_mmq_pick_ksplit(o.type, o.rows, o.cols, T) > 1)
+            RC(eb_mmq(o.type, o.data, o.rows, o.cols, al, w.logits, w.partial, eb_mmq_pick_ksplit(o.type, o.rows, o.cols, T), st));
+        else
+            RC(mm_parts(o, al, w.logits, &kl_, st));
     }
 #undef RC
     return EB_OK;
@@ -376,11 +396,13 @@ static int round_dev(eb_session *s, cudaStream_t st) {
     return EB_OK;
 }
 
-static int capture(eb_session *s, cudaGraphExec_t *exec, int (*fn)(eb_session *, int, cudaStream_t), int arg) {
+static int capture(eb_session *s, cudaGraphExec_t *exec, int (*fn)(eb_session *, int, cudaStream_t), int arg, long *n_kernels) {
     cudaGraph_t g;
+    const long before = eb_launches_now();
     EB_CUDA(cudaStreamBeginCapture(s->st, cudaStreamCaptureModeThreadLocal));
     const int rc = fn(s, arg, s->st);
     const cudaError_t e = cudaStreamEndCapture(s->st, &g);
+    *n_kernels = eb_launches_now() - before; eb_launches_add(-*n_kernels);      // recorded, not executed
     if (rc) { if (e == cudaSuccess) cudaGraphDestroy(g); return rc; }
     if (e != cudaSuccess) return eb_set_err(EB_ERR_CUDA, "graph capture: %s", cudaGetErrorString(e));
     const cudaError_t e2 = cudaGraphInstantiate(exec, g, 0);
@@ -398,10 +420,10 @@ extern "C" int eb_session_round(eb_session *s, eb_round_result *h_out) {
     const int n_past = eb_session_n_past(s, 0);
     if (n_past + s->p.max_nodes + s->p.n_branch > s->p.n_ctx) return eb_set_err(EB_ERR_ARG, "round: KV cache full (n_past=%d)", n_past);
     if (s->p.use_graph && !s->graph_round) {                    // capture only records; the first launch below is the first round
-        rc = capture(s, &s->graph_round, round_fn, 0); if (rc) return rc;
+        rc = capture(s, &s->graph_round, round_fn, 0, &s->graph_round_kernels); if (rc) return rc;
     }
     EB_CUDA(cudaEventRecord(s->ev0, s->st));
-    if (s->graph_round) EB_CUDA(cudaGraphLaunch(s->graph_round, s->st));
+    if (s->graph_round) { EB_CUDA(cudaGraphLaunch(s->graph_round, s->st)); eb_launches_add(s->graph_round_kernels); }
     else { rc = round_dev(s, s->st); if (rc) return rc; }
     EB_CUDA(cudaEventRecord(s->ev1, s->st));
     EB_CUDA(cudaMemcpyAsync(s->h_res, s->d_res, sizeof(eb_round_result), cudaMemcpyDeviceToHost, s->st));
@@ -429,11 +451,11 @@ extern "C" int eb_session_verify_only(eb_session *s, int T, float *gpu_ms) {
         if (s->graph_verify) { cudaGraphExecDestroy(s->graph_verify); s->graph_verify = nullptr; }
         rc = verify_dev(s, T, s->st); if (rc) return rc;
         EB_CUDA(cudaStreamSynchronize(s->st));
-        rc = capture(s, &s->graph_verify, verify_fn, T); if (rc) return rc;
+        rc = capture(s, &s->graph_verify, verify_fn, T, &s->graph_verify_kernels); if (rc) return rc;
         s->graph_verify_T = T;
     }
     EB_CUDA(cudaEventRecord(s->ev0, s->st));
-    if (s->graph_verify) EB_CUDA(cudaGraphLaunch(s->graph_verify, s->st));
+    if (s->graph_verify) { EB_CUDA(cudaGraphLaunch(s->graph_verify, s->st)); eb_launches_add(s->graph_verify_kernels); }
     else { rc = verify_dev(s, T, s->st); if (rc) return rc; }
     EB_CUDA(cudaEventRecord(s->ev1, s->st));
     EB_CUDA(cudaStreamSynchronize(s->st));

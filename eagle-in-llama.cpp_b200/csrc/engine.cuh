@@ -18,6 +18,8 @@ struct KVCache { __half *k = nullptr, *v = nullptr; int64_t layer_stride = 0; in
 struct Workspace {
     int Tmax = 0;
     float *x, *cur, *q, *k, *v, *att, *gate, *up, *cat, *hidden, *feat, *logits, *partial;
+    float *pq, *pk, *pv, *po, *pgate, *pup;      // split-K planes [<=8][T][N], summed by the consumer kernel
+    void *actq2;                                  // second activation-grid buffer
     void *actq; size_t actq_bytes; void *fa_ws; size_t fa_bytes; size_t partial_bytes;
     int32_t *tokens, *pos; uint32_t *bits; FwdCtl *ctl;
 };
@@ -30,6 +32,7 @@ struct eb_session {
     eb_round_result *d_res, *h_res;
     cudaStream_t st; cudaEvent_t ev0, ev1;
     cudaGraphExec_t graph_round = nullptr, graph_verify = nullptr; int graph_verify_T = 0;
+    long graph_round_kernels = 0, graph_verify_kernels = 0;
     int last_T[2] = {0, 0};
 };
 
@@ -53,4 +56,8 @@ int eb_rope_kv_store_ctl(float *q, const float *k, const float *v, const int32_t
                          int D, int n_head, int T, float freq_base, cudaStream_t st);
 int eb_flash_attn_ctl(const float *q, const void *k, const void *v, int64_t kv_stride, const uint32_t *tree_bits, const FwdCtl *ctl,
                       int T, int H, int D, int n_ctx, float scale, float *out, void *ws, cudaStream_t st);
+int eb_resid_norm_quant(float *x, const float *part, int ks, const float *w, float eps, int n, int T, const ActQ &aq, float *feat, cudaStream_t st);
+int eb_rope_kv_store_fused(const float *qp, int qks, const float *kp, int kks, const float *vp, int vks, float *q, const int32_t *pos, void *kc, void *vc,
+                           const FwdCtl *ctl, int D, int n_head, int T, float freq_base, cudaStream_t st);
+int eb_swiglu_quant(const float *gate, int gks, const float *up, int uks, int n, int T, const ActQ &aq, cudaStream_t st);
 int eb_mul_mat_impl(int type, const void *W, int64_t N, int64_t K, const float *x, int T, float *y, void *actq_ws, float *partial, cudaStream_t st);

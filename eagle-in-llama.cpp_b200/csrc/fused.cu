@@ -1,0 +1,138 @@
+// fused.cu — engine-only fusions of the glue between the GEMMs and attention.  Every kernel reads
+// the split-K partial planes of the producing GEMM directly (fixed summation order -> results
+// are deterministic), so no stand-alone reduce / add / norm / quantise launches remain:
+//   resid_norm_quant : x += sum_s part[s];  cur = rms_norm(x) * w;  cur -> activation grid
+//                      (ADD -> RMS_NORM -> MUL -> from_float of R/src/llama.cpp:1763-1790)
+//   rope_kv_store    : q,k,v = sum_s part[s]; RoPE(q,k); K,V -> f16 cache rows (:1710-1757, :228-270)
+//   swiglu_quant     : silu(sum gate) * sum up -> activation grid (llm_build_ffn :456-581)
+// All are one pass over [T][E|F] f32 data that lives in L2; coalesced float4 accesses.
+#include "common.cuh"
+#include "quant_dev.cuh"
+#include "spec.cuh"
+
+struct Parts { const float *p; int ks; int64_t plane; };   // plane = T*N elements between split planes
+
+__device__ __forceinline__ float4 sum_parts(const Parts &s, int64_t off) {
+    float4 a = *(const float4 *)(s.p + off);
+    for (int k = 1; k < s.ks; k++) { const float4 b = *(const float4 *)(s.p + (int64_t)k * s.plane + off); a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w; }
+    return a;
+}
+
+// one CTA (256 threads) per token row
+__global__ void __launch_bounds__(256) resid_norm_quant_kernel(float *__restrict__ x, Parts add, const float *__restrict__ w, float eps,
+                                                              int n, ActQ aq, float *__restrict__ feat) {
+    extern __shared__ float row[];
+    __shared__ double red[8];
+    __shared__ float s_scale;
+    const int r = blockIdx.x, tid = threadIdx.x;
+    float *xr = x + (int64_t)r * n;
+    double acc = 0.0;
+    for (int i = tid * 4; i < n; i += 1024) {
+        float4 v = *(const float4 *)(xr + i);
+        if (add.p) {                                       // ffn_inp = cur + inpSA (ggml_add(cur, inpSA))
+            const float4 c = sum_parts(add, (int64_t)r * n + i);
+            v.x = __fadd_rn(c.x, v.x); v.y = __fadd_rn(c.y, v.y); v.z = __fadd_rn(c.z, v.z); v.w = __fadd_rn(c.w, v.w);
+            *(float4 *)(xr + i) = v;
+        }
+        *(float4 *)(row + i) = v;
+        acc += (double)(v.x * v.x); acc += (double)(v.y * v.y); acc += (double)(v.z * v.z); acc += (double)(v.w * v.w);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    if ((tid & 31) == 0) red[tid >> 5] = acc;
+    __syncthreads();
+    if (tid == 0) {
+        double s = 0; for (int i = 0; i < 8; i++) s += red[i];
+        s_scale = 1.0f / sqrtf((float)(s / n) + eps);
+    }
+    __syncthreads();
+    const float sc = s_scale;
+    for (int i = tid * 4; i < n; i += 1024) {
+        float4 v = *(float4 *)(row + i);
+        v.x = __fmul_rn(v.x, sc); v.y = __fmul_rn(v.y, sc); v.z = __fmul_rn(v.z, sc); v.w = __fmul_rn(v.w, sc);
+        if (w) { const float4 g = *(const float4 *)(w + i); v.x = __fmul_rn(v.x, g.x); v.y = __fmul_rn(v.y, g.y); v.z = __fmul_rn(v.z, g.z); v.w = __fmul_rn(v.w, g.w); }
+        *(float4 *)(row + i) = v;
+        if (feat) *(float4 *)(feat + (int64_t)r * n + i) = v;
+    }
+    __syncthreads();
+    if (aq.qs) quant_row_smem(row, aq, r, tid, 256);
+}
+
+// grid (T, heads/8): thread = (head-in-group, pair).  cos/sin are computed once per (token, pair)
+// by the first 64 threads with the reference's sequential theta recurrence and shared via smem.
+__global__ void __launch_bounds__(512) rope_kv_store_fused_kernel(Parts qp, Parts kp, Parts vp, float *__restrict__ q,
+                                                                 const int32_t *__restrict__ pos, __half *__restrict__ kc, __half *__restrict__ vc,
+                                                                 const FwdCtl *__restrict__ ctl, int D, int n_head, float theta_scale) {
+    __shared__ float cs[128], sn[128];
+    const int t = blockIdx.x, tid = threadIdx.x, half = D / 2;
+    if (tid < half) {
+        float theta = (float)pos[t];
+        for (int j = 0; j < tid; j++) theta = __fmul_rn(theta, theta_scale);
+        cs[tid] = cosf(theta); sn[tid] = sinf(theta);
+    }
+    __syncthreads();
+    const int64_t cell0 = ctl ? (int64_t)(ctl->n_prefix + ctl->node_base) * n_head * D : 0;
+    const int E = n_head * D;
+    // float4 = two rotation pairs
+    for (int e = (blockIdx.y * blockDim.x + tid) * 4; e < E; e += gridDim.y * blockDim.x * 4) {
+        const int i = (e % D) / 2;
+        const float c0 = cs[i], s0 = sn[i], c1 = cs[i + 1], s1 = sn[i + 1];
+        const int64_t o = (int64_t)t * E + e;
+        const float4 a = sum_parts(qp, o), b = sum_parts(kp, o), v = sum_parts(vp, o);
+        *(float4 *)(q + o) = make_float4(__fsub_rn(__fmul_rn(a.x, c0), __fmul_rn(a.y, s0)), __fadd_rn(__fmul_rn(a.x, s0), __fmul_rn(a.y, c0)),
+                                         __fsub_rn(__fmul_rn(a.z, c1), __fmul_rn(a.w, s1)), __fadd_rn(__fmul_rn(a.z, s1), __fmul_rn(a.w, c1)));
+        const __half2 k0 = __floats2half2_rn(__fsub_rn(__fmul_rn(b.x, c0), __fmul_rn(b.y, s0)), __fadd_rn(__fmul_rn(b.x, s0), __fmul_rn(b.y, c0)));
+        const __half2 k1 = __floats2half2_rn(__fsub_rn(__fmul_rn(b.z, c1), __fmul_rn(b.w, s1)), __fadd_rn(__fmul_rn(b.z, s1), __fmul_rn(b.w, c1)));
+        const __half2 v0 = __floats2half2_rn(v.x, v.y), v1 = __floats2half2_rn(v.z, v.w);
+        *(uint2 *)(kc + cell0 + o) = make_uint2(*(const uint32_t *)&k0, *(const uint32_t *)&k1);
+        *(uint2 *)(vc + cell0 + o) = make_uint2(*(const uint32_t *)&v0, *(const uint32_t *)&v1);
+    }
+}
+
+__device__ __forceinline__ float silu_ref(float x) { return x / (1.0f + expf(-x)); }   // ggml_silu_f32
+// one CTA per token row; row staged in smem (F floats) then quantised
+__global__ void __launch_bounds__(512) swiglu_quant_kernel(Parts gate, Parts up, int n, ActQ aq) {
+    extern __shared__ float row[];
+    const int r = blockIdx.x, tid = threadIdx.x;
+    for (int i = tid * 4; i < n; i += 2048) {
+        const float4 g = sum_parts(gate, (int64_t)r * n + i), u = sum_parts(up, (int64_t)r * n + i);
+        *(float4 *)(row + i) = make_float4(__fmul_rn(silu_ref(g.x), u.x), __fmul_rn(silu_ref(g.y), u.y), __fmul_rn(silu_ref(g.z), u.z), __fmul_rn(silu_ref(g.w), u.w));
+    }
+    __syncthreads();
+    quant_row_smem(row, aq, r, tid, 512);
+}
+
+// plain row quantisation of an f32 [T][K] tensor that is already final (attention output)
+int eb_resid_norm_quant(float *x, const float *part, int ks, const float *w, float eps, int n, int T, const ActQ &aq, float *feat, cudaStream_t st) {
+    if (n % 4 || n > 16384) return eb_set_err(EB_ERR_ARG, "resid_norm_quant: n=%d", n);
+    if (T == 0) return EB_OK;
+    Parts p{part, ks, (int64_t)T * n};
+    resid_norm_quant_kernel<<<T, 256, (size_t)n * 4, st>>>(x, p, w, eps, n, aq, feat);
+    EB_CHECK_LAUNCH();
+    return EB_OK;
+}
+int eb_rope_kv_store_fused(const float *qp, int qks, const float *kp, int kks, const float *vp, int vks, float *q, const int32_t *pos, void *kc, void *vc,
+                           const FwdCtl *ctl, int D, int n_head, int T, float freq_base, cudaStream_t st) {
+    if (T == 0) return EB_OK;
+    if (D > 256 || D % 4) return eb_set_err(EB_ERR_ARG, "rope: D=%d", D);
+    const int64_t plane = (int64_t)T * n_head * D;
+    const int E = n_head * D;
+    const int threads = 512, gy = (int)cdiv(E / 4, threads);
+    rope_kv_store_fused_kernel<<<dim3(T, gy), threads, 0, st>>>(Parts{qp, qks, plane}, Parts{kp, kks, plane}, Parts{vp, vks, plane}, q, pos,
+                                                                 (__half *)kc, (__half *)vc, ctl, D, n_head, powf(freq_base, -2.0f / D));
+    EB_CHECK_LAUNCH();
+    return EB_OK;
+}
+int eb_swiglu_quant(const float *gate, int gks, const float *up, int uks, int n, int T, const ActQ &aq, cudaStream_t st) {
+    if (T == 0) return EB_OK;
+    if (n % 4) return eb_set_err(EB_ERR_ARG, "swiglu: n");
+    const int64_t plane = (int64_t)T * n;
+    swiglu_quant_kernel<<<T, 512, (size_t)n * 4, st>>>(Parts{gate, gks, plane}, Parts{up, uks, plane}, n, aq);
+    EB_CHECK_LAUNCH();
+    return EB_OK;
+}
+int eb_fused_init() {
+    EB_CUDA(cudaFuncSetAttribute(resid_norm_quant_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 65536));
+    EB_CUDA(cudaFuncSetAttribute(swiglu_quant_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 131072));
+    return EB_OK;
+}

@@ -257,7 +257,7 @@ __global__ void splitk_reduce_kernel(const float *__restrict__ partial, float *_
 }
 
 int eb_mmq_supported(int type, int64_t N, int64_t K, int T) {
-    return (type == EB_Q4_K || type == EB_Q6_K) && N % 16 == 0 && K % 256 == 0 && T > 8 && T <= 128;
+    return (type == EB_Q4_K || type == EB_Q6_K) && N % 16 == 0 && K % 256 == 0 && T > 1 && T <= 128;
 }
 
 int eb_mmq_pick_ksplit(int type, int64_t N, int64_t K, int T) {
@@ -288,6 +288,24 @@ static int launch(int type, const void *W, int64_t N, int nbr, const ActQ &a, fl
     return EB_OK;
 }
 
+// engine form: leave the split-K planes unreduced in `planes` ([ks][T][N]); the consumer kernel sums them
+int eb_mmq_parts(int type, const void *W, int64_t N, int64_t K, const ActQ &a, float *planes, int *ks_out, cudaStream_t st) {
+    if (!eb_mmq_supported(type, N, K, a.T)) return eb_set_err(EB_ERR_UNSUPPORTED, "mmq: type %d N %lld K %lld T %d", type, (long long)N, (long long)K, a.T);
+    const int nbr = (int)(K / 256);
+    int ksplit = eb_mmq_pick_ksplit(type, N, K, a.T);
+    if (ksplit > nbr) ksplit = nbr;
+    ksplit = (int)cdiv(nbr, cdiv(nbr, ksplit));
+    *ks_out = ksplit;
+    const int nt = (a.T + 7) / 8;
+    if (nt <= 1) return launch<1>(type, W, N, nbr, a, planes, ksplit, st);
+    if (nt <= 2) return launch<2>(type, W, N, nbr, a, planes, ksplit, st);
+    if (nt <= 4) return launch<4>(type, W, N, nbr, a, planes, ksplit, st);
+    if (nt <= 6) return launch<6>(type, W, N, nbr, a, planes, ksplit, st);
+    if (nt <= 9) return launch<9>(type, W, N, nbr, a, planes, ksplit, st);
+    if (nt <= 12) return launch<12>(type, W, N, nbr, a, planes, ksplit, st);
+    return launch<16>(type, W, N, nbr, a, planes, ksplit, st);
+}
+
 // y [T][N]; partial: scratch of ksplit*T*N floats (only used when ksplit > 1)
 int eb_mmq(int type, const void *W, int64_t N, int64_t K, const ActQ &a, float *y, float *partial, int ksplit, cudaStream_t st) {
     if (!eb_mmq_supported(type, N, K, a.T)) return eb_set_err(EB_ERR_UNSUPPORTED, "mmq: type %d N %lld K %lld T %d", type, (long long)N, (long long)K, a.T);
@@ -298,7 +316,8 @@ int eb_mmq(int type, const void *W, int64_t N, int64_t K, const ActQ &a, float *
     float *out = ksplit > 1 ? partial : y;
     const int nt = (a.T + 7) / 8;
     int rc;
-    if (nt <= 2) rc = launch<2>(type, W, N, nbr, a, out, ksplit, st);
+    if (nt <= 1) rc = launch<1>(type, W, N, nbr, a, out, ksplit, st);
+    else if (nt <= 2) rc = launch<2>(type, W, N, nbr, a, out, ksplit, st);
     else if (nt <= 4) rc = launch<4>(type, W, N, nbr, a, out, ksplit, st);
     else if (nt <= 6) rc = launch<6>(type, W, N, nbr, a, out, ksplit, st);
     else if (nt <= 9) rc = launch<9>(type, W, N, nbr, a, out, ksplit, st);
@@ -320,6 +339,6 @@ template <int NT> static int init_nt() {
 }
 int eb_mmq_init() {   // dynamic-smem opt-in for every instantiation, once per process (never inside a graph capture)
     int rc;
-    if ((rc = init_nt<2>()) || (rc = init_nt<4>()) || (rc = init_nt<6>()) || (rc = init_nt<9>()) || (rc = init_nt<12>()) || (rc = init_nt<16>())) return rc;
+    if ((rc = init_nt<1>()) || (rc = init_nt<2>()) || (rc = init_nt<4>()) || (rc = init_nt<6>()) || (rc = init_nt<9>()) || (rc = init_nt<12>()) || (rc = init_nt<16>())) return rc;
     return EB_OK;
 }
