@@ -42,9 +42,13 @@ struct WPlanes {
 //   qs    int8  [T][K]
 //   d     f32   [T][K/B]      B = 256 (Q8_K grid) or 32 (Q8_0 grid; value is f16-rounded)
 //   bsum  f16   [T][K/16]     Q8_K only: sums of 16 quants (|sum| <= 2032 is exact in f16)
+//   h16   f16   [T][K]        Q8_K only: the same quants as f16 (exact) = UMMA B operand (mmq_tc.cu)
+//   dT    f32   [K/256][80]   Q8_K only: d transposed (super-block major) for the GEMM epilogue
+#define EB_DT_PITCH 80
 struct ActQ {
     int8_t *qs; float *d; __half *bsum;
     int64_t K; int T; int kq;   // kq = 1: Q8_K grid, 0: Q8_0 grid
+    __half *h16 = nullptr; float *dT = nullptr;
 };
 
 // ---- error handling
@@ -94,5 +98,9 @@ int eb_mmvq(int type, const void *W, int64_t N, int64_t K, const ActQ &a, float 
 int eb_mmq(int type, const void *W, int64_t N, int64_t K, const ActQ &a, float *y, float *partial, int ksplit, cudaStream_t st); // mmq.cu
 int eb_mmq_parts(int type, const void *W, int64_t N, int64_t K, const ActQ &a, float *planes, int *ks_out, cudaStream_t st);
 int eb_fused_init();
+int eb_mmq_tc_init();                                                                  // mmq_tc.cu (tcgen05 path)
+int eb_mmq_tc_supported(int type, int64_t N, int64_t K, int T);
+int eb_mmq_tc_parts(int type, const void *W, int64_t N, int64_t K, const ActQ &a, float *planes, int *ks_out, cudaStream_t st);
+int eb_splitk_reduce(const float *partial, float *y, int64_t n, int ksplit, cudaStream_t st);
 int eb_mmq_supported(int type, int64_t N, int64_t K, int T);
 int eb_mmq_pick_ksplit(int type, int64_t N, int64_t K, int T);

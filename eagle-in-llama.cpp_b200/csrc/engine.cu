@@ -122,6 +122,11 @@ int eb_mul_mat_impl(int type, const void *W, int64_t N, int64_t K, const float *
     if (!kq && type != EB_Q4_0 && type != EB_Q8_0) return eb_set_err(EB_ERR_UNSUPPORTED, "mul_mat: weight type %d", type);
     ActQ a = eb_actq_carve(actq_ws, kq, K, T);
     int rc = eb_quantize_act(x, a, st); if (rc) return rc;
+    if (eb_mmq_tc_supported(type, N, K, T)) {
+        int ks = 1;
+        rc = eb_mmq_tc_parts(type, W, N, K, a, partial, &ks, st); if (rc) return rc;
+        return eb_splitk_reduce(partial, y, (int64_t)T * N, ks, st);
+    }
     if (eb_mmq_supported(type, N, K, T)) return eb_mmq(type, W, N, K, a, y, partial, eb_mmq_pick_ksplit(type, N, K, T), st);
     return eb_mmvq(type, W, N, K, a, y, st);
 }
@@ -212,6 +217,7 @@ extern "C" void eb_session_free(eb_session *s) {
 // node_base, n_tree).  K/V rows go to cells n_prefix + node_base + t.
 // GEMM into split-K planes (T > 8, K-quants) or a single plane (matvec path)
 static int mm_parts(const DTensor &w, const ActQ &a, float *planes, int *ks, cudaStream_t st) {
+    if (eb_mmq_tc_supported(w.type, w.rows, w.cols, a.T)) return eb_mmq_tc_parts(w.type, w.data, w.rows, w.cols, a, planes, ks, st);
     if (eb_mmq_supported(w.type, w.rows, w.cols, a.T)) return eb_mmq_parts(w.type, w.data, w.rows, w.cols, a, planes, ks, st);
     *ks = 1;
     return eb_mmvq(w.type, w.data, w.rows, w.cols, a, planes, st);

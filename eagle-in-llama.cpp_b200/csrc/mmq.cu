@@ -256,6 +256,13 @@ __global__ void splitk_reduce_kernel(const float *__restrict__ partial, float *_
     *(float4 *)(y + i) = s;
 }
 
+int eb_splitk_reduce(const float *partial, float *y, int64_t n, int ksplit, cudaStream_t st) {
+    if (n % 4) return eb_set_err(EB_ERR_ARG, "splitk_reduce: n %% 4");
+    splitk_reduce_kernel<<<(unsigned)cdiv(n / 4, 256), 256, 0, st>>>(partial, y, n, ksplit);
+    EB_CHECK_LAUNCH();
+    return EB_OK;
+}
+
 int eb_mmq_supported(int type, int64_t N, int64_t K, int T) {
     return (type == EB_Q4_K || type == EB_Q6_K) && N % 16 == 0 && K % 256 == 0 && T > 1 && T <= 128;
 }

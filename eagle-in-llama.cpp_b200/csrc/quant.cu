@@ -107,7 +107,9 @@ __global__ void quant_act_kernel(const float *__restrict__ x, ActQ a) {
     if (a.kq) {
         const int64_t nb = a.K / 256, total = nb * a.T;
         if (warp >= total) return;
-        quant_block_q8K(x + warp * 256, a.qs + warp * 256, a.d + warp, a.bsum + warp * 16, lane);
+        const int64_t t = warp / nb, b = warp % nb;
+        quant_block_q8K(x + warp * 256, a.qs + warp * 256, a.d + warp, a.bsum + warp * 16, lane,
+                        a.h16 ? a.h16 + warp * 256 : nullptr, (a.dT && t < EB_DT_PITCH) ? a.dT + b * EB_DT_PITCH + t : nullptr);
     } else {
         const int64_t total = a.K / 128 * a.T;
         if (warp >= total) return;
@@ -117,15 +119,18 @@ __global__ void quant_act_kernel(const float *__restrict__ x, ActQ a) {
 
 size_t eb_actq_bytes(int kq, int64_t K, int T) {
     size_t qs = (size_t)T * K, d = (size_t)T * (K / (kq ? 256 : 32)) * 4, bs = kq ? (size_t)T * (K / 16) * 2 : 0;
+    size_t h16 = kq ? (size_t)T * K * 2 : 0, dT = kq ? (size_t)(K / 256) * EB_DT_PITCH * 4 : 0;
     auto al = [](size_t v) { return (v + 255) & ~(size_t)255; };
-    return al(qs) + al(d) + al(bs);
+    return al(qs) + al(d) + al(bs) + al(h16) + al(dT);
 }
 ActQ eb_actq_carve(void *ws, int kq, int64_t K, int T) {
     auto al = [](size_t v) { return (v + 255) & ~(size_t)255; };
     ActQ a; char *p = (char *)ws;
     a.qs = (int8_t *)p; p += al((size_t)T * K);
     a.d = (float *)p; p += al((size_t)T * (K / (kq ? 256 : 32)) * 4);
-    a.bsum = kq ? (__half *)p : nullptr;
+    a.bsum = kq ? (__half *)p : nullptr; if (kq) p += al((size_t)T * (K / 16) * 2);
+    a.h16 = kq ? (__half *)p : nullptr; if (kq) p += al((size_t)T * K * 2);
+    a.dT = kq ? (float *)p : nullptr;
     a.K = K; a.T = T; a.kq = kq;
     return a;
 }

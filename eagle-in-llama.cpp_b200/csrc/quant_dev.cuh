@@ -8,7 +8,8 @@
 // lane l owns elements 8l..8l+7.  "max" is the signed value of the FIRST element reaching the
 // largest |x| (strict > in the reference scan), so ties resolve to the lowest index.
 __device__ __forceinline__ void quant_regs_q8K(const float (&v)[8], int8_t *__restrict__ qs,
-                                               float *__restrict__ dout, __half *__restrict__ bsum, int lane) {
+                                               float *__restrict__ dout, __half *__restrict__ bsum, int lane,
+                                               __half *__restrict__ h16 = nullptr, float *__restrict__ dT = nullptr) {
     float amax = 0.f, mx = 0.f; int idx = 0;
 #pragma unroll
     for (int j = 0; j < 8; j++) { const float ax = fabsf(v[j]); if (ax > amax) { amax = ax; mx = v[j]; idx = lane * 8 + j; } }
@@ -23,12 +24,17 @@ __device__ __forceinline__ void quant_regs_q8K(const float (&v)[8], int8_t *__re
     if (amax == 0.f) {
 #pragma unroll
         for (int j = 0; j < 8; j++) q[j] = 0;
-        if (lane == 0) *dout = 0.f;
+        if (lane == 0) { *dout = 0.f; if (dT) *dT = 0.f; }
     } else {
         const float iscale = __fdiv_rn(-127.f, mx);
 #pragma unroll
         for (int j = 0; j < 8; j++) q[j] = min(127, __float2int_rn(__fmul_rn(iscale, v[j])));
-        if (lane == 0) *dout = __fdiv_rn(1.f, iscale);
+        if (lane == 0) { const float dd = __fdiv_rn(1.f, iscale); *dout = dd; if (dT) *dT = dd; }
+    }
+    if (h16) {                                                // exact: |q| <= 127
+        const __half2 a = __floats2half2_rn((float)q[0], (float)q[1]), b = __floats2half2_rn((float)q[2], (float)q[3]);
+        const __half2 c = __floats2half2_rn((float)q[4], (float)q[5]), e = __floats2half2_rn((float)q[6], (float)q[7]);
+        ((uint4 *)h16)[lane] = make_uint4(*(const uint32_t *)&a, *(const uint32_t *)&b, *(const uint32_t *)&c, *(const uint32_t *)&e);
     }
     uint32_t w0 = (q[0] & 0xff) | ((q[1] & 0xff) << 8) | ((q[2] & 0xff) << 16) | ((uint32_t)(q[3] & 0xff) << 24);
     uint32_t w1 = (q[4] & 0xff) | ((q[5] & 0xff) << 8) | ((q[6] & 0xff) << 16) | ((uint32_t)(q[7] & 0xff) << 24);
@@ -54,11 +60,12 @@ __device__ __forceinline__ void quant_regs_q8_0x4(const float4 a, int8_t *__rest
 
 
 __device__ __forceinline__ void quant_block_q8K(const float *__restrict__ x, int8_t *__restrict__ qs,
-                                                float *__restrict__ dout, __half *__restrict__ bsum, int lane) {
+                                                float *__restrict__ dout, __half *__restrict__ bsum, int lane,
+                                                __half *__restrict__ h16 = nullptr, float *__restrict__ dT = nullptr) {
     float v[8];
     const float4 a = ((const float4 *)x)[lane * 2], b = ((const float4 *)x)[lane * 2 + 1];
     v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
-    quant_regs_q8K(v, qs, dout, bsum, lane);
+    quant_regs_q8K(v, qs, dout, bsum, lane, h16, dT);
 }
 __device__ __forceinline__ void quant_block_q8_0x4(const float *__restrict__ x, int8_t *__restrict__ qs,
                                                    float *__restrict__ dout, int lane) {
@@ -70,7 +77,8 @@ __device__ __forceinline__ void quant_row_smem(const float *row, const ActQ &a, 
     if (a.kq) {
         const int nb = (int)(a.K / 256);
         for (int b = warp; b < nb; b += nw)
-            quant_block_q8K(row + b * 256, a.qs + (int64_t)t * a.K + b * 256, a.d + (int64_t)t * nb + b, a.bsum + ((int64_t)t * nb + b) * 16, lane);
+            quant_block_q8K(row + b * 256, a.qs + (int64_t)t * a.K + b * 256, a.d + (int64_t)t * nb + b, a.bsum + ((int64_t)t * nb + b) * 16, lane,
+                            a.h16 ? a.h16 + (int64_t)t * a.K + b * 256 : nullptr, (a.dT && t < EB_DT_PITCH) ? a.dT + (int64_t)b * EB_DT_PITCH + t : nullptr);
     } else {
         const int ng = (int)(a.K / 128);
         for (int g = warp; g < ng; g += nw)
