@@ -1,8 +1,8 @@
-// mmq_tc.cu — K2 on 5th-generation tensor cores: tree-batched (T = 9..80) verify GEMM on Q4_K / Q6_K
+// mmq_tc.cu — K2 on 5th-generation tensor cores: tree-batched (T = 9..80) verify GEMM on Q4_K
 // weights with tcgen05.mma (kind::f16, accumulators in TMEM), weights streamed from HBM exactly once
 // by TMA.  Replaces mul_mat_q (R/ggml/src/ggml-cuda/mmq.cuh:2502-2822); results follow
-// ggml_vec_dot_q4_K_q8_K / q6_K_q8_K (R/ggml/src/ggml-cpu/ggml-cpu-quants.c:6266,7903): all integer
-// sums are exact, only the order of the f32 additions over super-blocks differs.
+// ggml_vec_dot_q4_K_q8_K (R/ggml/src/ggml-cpu/ggml-cpu-quants.c:6266): all integer sums are exact,
+// only the order of the f32 additions over super-blocks differs.
 //
 // Exact integers on an f16 tensor pipe.  Per super-block (K = 256) and weight row r, column c:
 //     y[r,c] += d[r]*dx[c] * SUM_k (sc[r,k/32]*q[r,k]) * a[c,k]  -  dmin[r]*dx[c] * SUM_j m[r,j]*bsum16[c,2j..2j+1]
@@ -13,11 +13,15 @@
 //
 // CTA = 128 weight rows, persistent over (row block, K split) items.  Warp roles (20 warps):
 //   0      TMA producer of raw weight tiles  (128 rows x one super-block, 6-stage ring)
-//   1      tcgen05.mma issuer (one thread)
+//   1      tcgen05.mma issuer (warp-uniform loop, one elected lane issues 8-9 MMAs per asm block)
 //   2      TMA producer of the activation tiles (f16 quants, 16-sums)
 //   3      TMEM allocator
 //   4-11   dequant: smem raw blocks -> exact f16 integers -> TMEM A operand (lane = weight row)
 //   12-19  epilogue: TMEM accumulators -> f32 registers (d*dx scaling), final store of the split-K plane
+// Measured on B200 (tools/ubench*.cu, profiles/): tcgen05.mma costs ~165 clk each when issued from a divergent
+// single-thread loop (R2UR traffic) and 40 clk (the N = 80 floor) when several are issued back to back from
+// uniform registers; every mbarrier hand-off costs 100-300 clk of latency, so stages are coarse (half a
+// super-block of A, a whole super-block of D) and the TMEM stores overlap the next group's arithmetic.
 #include "common.cuh"
 #include "tc.cuh"
 #include <cstdlib>
@@ -34,18 +38,30 @@ constexpr int OFF_W = 0;
 constexpr int OFF_B = OFF_W + S_W * W_STAGE;    // 110592
 constexpr int OFF_BS = OFF_B + 2 * B_STAGE;     // 192512
 constexpr int OFF_HDR = OFF_BS + 2 * B_BOX;     // 212992
-constexpr int OFF_BAR = OFF_HDR + 4 * 128 * 8;  // 217088
+constexpr int OFF_DX = OFF_HDR + 4 * 128 * 8;   // 217088: per epilogue warp 2 x 40 floats
+constexpr int OFF_BAR = OFF_DX + 8 * 80 * 4;    // 219648
 constexpr int SMEM_BYTES = OFF_BAR + 512 + 1024;   // + barriers + alignment slack
-// TMEM columns
+// TMEM columns: D stage s at s*160 (main 80 | min 80), A half-super-block h at 320 + 64h, mins operand at 448 + 8*(i&1)
 constexpr int D_STRIDE = 160, D_MIN = 80, A_OFF = 320, AM_OFF = 448;
 // barrier indices
-enum { W_FULL = 0, W_EMPTY = 6, B_FULL = 12, B_EMPTY = 14, BS_FULL = 16, BS_EMPTY = 18, A_FULL = 20, A_EMPTY = 24,
-       D_FULL = 28, D_EMPTY = 30, HDR_FULL = 32, N_BARS = 36 };
+enum { W_FULL = 0, W_EMPTY = 6, B_FULL = 12, B_EMPTY = 14, BS_FULL = 16, BS_EMPTY = 18, A_FULL = 20, A_EMPTY = 22,
+       D_FULL = 24, D_EMPTY = 26, HDR_FULL = 28, N_BARS = 32 };
 
 struct TcArgs {
-    const float *dT; float *out; int64_t N; int nbr, T, npad, n_rb, n_items, spp;
+    const float *dT; float *out; int64_t N; int nbr, T, npad, n_rb, n_items, spp; long long *prof;
+    uint32_t k_lo, k_hi, k_magic;    // 0x000f000f, 0x00f000f0, 0x64006400 passed as data: kept in registers so that (x & m) | c is ONE LOP3
 };
 
+// optional in-kernel profile (EB_TC_PROF=1): cycles each role of CTA 0 spends waiting on its barriers
+#define TCP_WAIT(slot, barrier, parity) do { if (PROF) { const long long t_ = clock64(); tc::mbar_wait(barrier, parity); pw[slot] += clock64() - t_; } else tc::mbar_wait(barrier, parity); } while (0)
+
+__device__ __forceinline__ uint32_t and_or(uint32_t x, uint32_t m, uint32_t c) {
+    uint32_t r; asm("lop3.b32 %0, %1, %2, %3, 0xEA;" : "=r"(r) : "r"(x), "r"(m), "r"(c)); return r;
+}
+// packed f32x2 arithmetic (sm_100): one issue slot for two FMAs
+__device__ __forceinline__ unsigned long long pk2(float x, float y) { unsigned long long r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(x), "f"(y)); return r; }
+__device__ __forceinline__ unsigned long long mul2(unsigned long long a, unsigned long long b) { unsigned long long r; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ unsigned long long fma2(unsigned long long a, unsigned long long b, unsigned long long c) { unsigned long long r; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c)); return r; }
 __device__ __forceinline__ uint32_t h2u(__half2 h) { return *reinterpret_cast<uint32_t *>(&h); }
 __device__ __forceinline__ __half2 u2h(uint32_t u) { return *reinterpret_cast<__half2 *>(&u); }
 // byte b (0..3) of word w as half2 (v, v), v in [0,255] exact
@@ -54,6 +70,175 @@ __device__ __forceinline__ __half2 byte_to_h2(uint32_t w, int b) {
     return __hsub2(u2h(v | (v << 16) | 0x64006400u), u2h(0x64006400u));
 }
 
+// one 64-element group (32 bytes: low nibbles = sub-block 2g, high nibbles = sub-block 2g+1) -> 32 TMEM columns
+// of exact f16 integers sc*q.  Column 2w+e of a sub-block holds elements (4w+e, 4w+e+2): the activation plane
+// h16 uses the same (0,2,1,3) order inside every group of four (quant_dev.cuh).
+__device__ __forceinline__ void dequant_group(uint32_t (&r)[32], const uint4 &q0, const uint4 &q1, __half2 s_lo, __half2 s_hi,
+                                              uint32_t k_lo, uint32_t k_hi, uint32_t k_magic) {
+    const __half2 mul_lo = s_lo, add_lo = __hmul2(s_lo, __float2half2_rn(-1024.f));                       // (1024+q)*sc - 1024*sc
+    const __half2 mul_hi = __hmul2(s_hi, __float2half2_rn(0.0625f)), add_hi = __hmul2(s_hi, __float2half2_rn(-64.f));   // (1024+16q)*sc/16 - 64*sc
+    const uint32_t xs[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
+#pragma unroll
+    for (int w = 0; w < 8; w++) {
+        const uint32_t x = xs[w], z = x >> 8;                     // bytes (1,3) under the same masks as bytes (0,2)
+        r[2 * w]          = h2u(__hfma2(u2h(and_or(x, k_lo, k_magic)), mul_lo, add_lo));
+        r[2 * w + 1]      = h2u(__hfma2(u2h(and_or(z, k_lo, k_magic)), mul_lo, add_lo));
+        r[16 + 2 * w]     = h2u(__hfma2(u2h(and_or(x, k_hi, k_magic)), mul_hi, add_hi));
+        r[16 + 2 * w + 1] = h2u(__hfma2(u2h(and_or(z, k_hi, k_magic)), mul_hi, add_hi));
+    }
+}
+
+// dequant role: raw Q4_K rows in smem -> TMEM A operand (lane = weight row).  MEMBER 0 handles groups 0 and 2
+// (+ the header and the mins operand), MEMBER 1 groups 1 and 3; half-super-block h = groups 2h, 2h+1.
+template <int MEMBER, bool PROF>
+__device__ __forceinline__ void dequant_q4_K(const TcArgs &p, uint8_t *smem, uint32_t bar0, uint32_t tmem, int q, int lane) {
+    auto bar = [&](int i) { return bar0 + 8u * i; };
+    const int row = 32 * q + lane;
+    const uint32_t lane_base = tmem + ((uint32_t)(32 * q) << 16);
+    float2 *hdr_sm = (float2 *)(smem + OFF_HDR);
+    const uint32_t k_lo = p.k_lo, k_hi = p.k_hi, k_magic = p.k_magic;
+    uint32_t i = 0;
+    long long pw[4] = {0, 0, 0, 0}; const long long pt0 = PROF ? clock64() : 0;
+    for (int item = blockIdx.x; item < p.n_items; item += gridDim.x) {
+        const int ks = item / p.n_rb;
+        const int sb0 = ks * p.spp, sb1 = min(p.nbr, sb0 + p.spp);
+        for (int sb = sb0; sb < sb1; sb++, i++) {
+            const uint32_t s = i % S_W;
+            TCP_WAIT(0, bar(W_FULL + s), (i / S_W) & 1);
+            const uint8_t *rp = smem + OFF_W + s * W_STAGE + row * 144;
+            const uint4 hd = *(const uint4 *)rp;
+            const uint4 qa0 = *(const uint4 *)(rp + 16 + 32 * MEMBER), qa1 = *(const uint4 *)(rp + 32 + 32 * MEMBER);
+            const uint4 qb0 = *(const uint4 *)(rp + 16 + 32 * (MEMBER + 2)), qb1 = *(const uint4 *)(rp + 32 + 32 * (MEMBER + 2));
+            __syncwarp();
+            if (lane == 0) tc::mbar_arrive(bar(W_EMPTY + s));
+            // 6-bit scales / mins (get_scale_min_k4, R/ggml/src/ggml-quants.c:631) as bytes of u0..u1 / u2..u3
+            const uint32_t u0 = hd.y & 0x3f3f3f3fu, u1 = (hd.w & 0x0f0f0f0fu) | (((hd.y >> 6) & 0x03030303u) << 4);
+            uint32_t r[32];
+            // ---- first half-super-block (group MEMBER)
+            dequant_group(r, qa0, qa1, byte_to_h2(u0, 2 * MEMBER), byte_to_h2(u0, 2 * MEMBER + 1), k_lo, k_hi, k_magic);
+            TCP_WAIT(1, bar(A_EMPTY + 0), (i & 1) ^ 1);
+            tc::fence_after();
+            if (MEMBER == 0) {                                          // header + mins operand, once per super-block
+                const uint32_t u2 = hd.z & 0x3f3f3f3fu, u3 = ((hd.w >> 4) & 0x0f0f0f0fu) | (((hd.z >> 6) & 0x03030303u) << 4);
+                const __half2 dm = u2h(hd.x);
+                hdr_sm[(i & 3) * 128 + row] = make_float2(__low2float(dm), __high2float(dm));
+                uint32_t mr[8];
+#pragma unroll
+                for (int j = 0; j < 8; j++) mr[j] = h2u(byte_to_h2(j < 4 ? u2 : u3, j & 3));
+                tc::tmem_st8(lane_base + AM_OFF + 8 * (i & 1), mr);
+            }
+            tc::tmem_st32(lane_base + A_OFF + 32 * MEMBER, r);
+            // ---- second half (group MEMBER + 2): its arithmetic overlaps the TMEM store above
+            uint32_t r2[32];
+            dequant_group(r2, qb0, qb1, byte_to_h2(u1, 2 * MEMBER), byte_to_h2(u1, 2 * MEMBER + 1), k_lo, k_hi, k_magic);
+            tc::wait_st();
+            tc::fence_before();
+            __syncwarp();
+            if (lane == 0) {
+                tc::mbar_arrive(bar(A_FULL + 0));
+                if (MEMBER == 0) tc::mbar_arrive(bar(HDR_FULL + (i & 3)));
+            }
+            TCP_WAIT(2, bar(A_EMPTY + 1), (i & 1) ^ 1);
+            tc::fence_after();
+            tc::tmem_st32(lane_base + A_OFF + 64 + 32 * MEMBER, r2);
+            tc::wait_st();
+            tc::fence_before();
+            __syncwarp();
+            if (lane == 0) tc::mbar_arrive(bar(A_FULL + 1));
+        }
+    }
+    if (PROF && blockIdx.x == 0 && q == 0 && lane == 0) {
+        long long *o = p.prof + 16 + 8 * MEMBER;
+        o[0] = clock64() - pt0; o[1] = pw[0]; o[2] = pw[1]; o[3] = pw[2]; o[4] = pw[3]; o[5] = i;
+    }
+}
+
+// epilogue role: 8 warps; warp (q, hf) owns TMEM lanes 32q..32q+31 (weight rows) and columns [40hf, 40hf+40)
+template <bool PROF>
+__device__ __forceinline__ void epilogue_role(const TcArgs &p, uint8_t *smem, uint32_t bar0, uint32_t tmem, int warp, int lane) {
+    auto bar = [&](int i) { return bar0 + 8u * i; };
+    const int q = warp & 3, hf = (warp - 12) >> 2, row = 32 * q + lane, c_base = 40 * hf;
+    const uint32_t lane_base = tmem + ((uint32_t)(32 * q) << 16);
+    const float2 *hdr_sm = (const float2 *)(smem + OFF_HDR);
+    float *dx_sm = (float *)(smem + OFF_DX) + (warp - 12) * 80;
+    const bool tail = c_base + 32 < p.T;                                // columns [32,40) of this warp hold tokens
+    uint32_t i = 0;
+    long long pw[3] = {0, 0, 0}; const long long pt0 = PROF ? clock64() : 0;
+    for (int item = blockIdx.x; item < p.n_items; item += gridDim.x) {
+        const int ks = item / p.n_rb, rb = item % p.n_rb;
+        const int sb0 = ks * p.spp, sb1 = min(p.nbr, sb0 + p.spp);
+        unsigned long long acc2[20];                                    // 40 columns as f32 pairs
+#pragma unroll
+        for (int c = 0; c < 20; c++) acc2[c] = 0ull;
+        // dx (activation scales) of a super-block: 40 columns, fetched one super-block ahead into two registers per
+        // lane, staged through a per-warp smem strip and read back as broadcast float4
+        const bool va = c_base + lane < p.T, vb = lane < 8 && c_base + 32 + lane < p.T;
+        float dxa = va ? __ldg(p.dT + (int64_t)sb0 * EB_DT_PITCH + c_base + lane) : 0.f;
+        float dxb = vb ? __ldg(p.dT + (int64_t)sb0 * EB_DT_PITCH + c_base + 32 + lane) : 0.f;
+        for (int sb = sb0; sb < sb1; sb++, i++) {
+            float *dxs = dx_sm + (i & 1) * 40;
+            dxs[lane] = dxa;
+            if (lane < 8) dxs[32 + lane] = dxb;
+            if (sb + 1 < sb1) {
+                if (va) dxa = __ldg(p.dT + (int64_t)(sb + 1) * EB_DT_PITCH + c_base + lane);
+                if (vb) dxb = __ldg(p.dT + (int64_t)(sb + 1) * EB_DT_PITCH + c_base + 32 + lane);
+            }
+            TCP_WAIT(0, bar(HDR_FULL + (i & 3)), (i >> 2) & 1);
+            const float2 h = hdr_sm[(i & 3) * 128 + row];
+            const unsigned long long hd2 = pk2(h.x, h.x), hm2 = pk2(-h.y, -h.y);
+            const uint32_t s = i & 1;
+            TCP_WAIT(1, bar(D_FULL + s), (i >> 1) & 1);
+            tc::fence_after();
+            const long long te_ = PROF ? clock64() : 0;
+            __syncwarp();
+            const uint32_t t_main = lane_base + s * D_STRIDE + c_base, t_min = t_main + D_MIN;
+            // two passes keep the live registers under the 120 granted by setmaxnreg: columns [0,16) then [16,40)
+            auto fold4 = [&](const uint32_t *vm, const uint32_t *vn, int col0, int n4) {
+#pragma unroll
+                for (int e4 = 0; e4 < n4; e4++) {
+                    const ulonglong2 dx = *(const ulonglong2 *)(dxs + col0 + 4 * e4);
+                    const int k = 4 * e4, a = (col0 >> 1) + 2 * e4;
+                    unsigned long long t0 = mul2(hd2, pk2(__uint_as_float(vm[k]), __uint_as_float(vm[k + 1])));
+                    unsigned long long t1 = mul2(hd2, pk2(__uint_as_float(vm[k + 2]), __uint_as_float(vm[k + 3])));
+                    t0 = fma2(hm2, pk2(__uint_as_float(vn[k]), __uint_as_float(vn[k + 1])), t0);
+                    t1 = fma2(hm2, pk2(__uint_as_float(vn[k + 2]), __uint_as_float(vn[k + 3])), t1);
+                    acc2[a] = fma2(dx.x, t0, acc2[a]);
+                    acc2[a + 1] = fma2(dx.y, t1, acc2[a + 1]);
+                }
+            };
+            {
+                uint32_t vm[16], vn[16];
+                tc::tmem_ld16(t_main, vm); tc::tmem_ld16(t_min, vn);
+                tc::wait_ld();
+                fold4(vm, vn, 0, 4);
+            }
+            {
+                uint32_t vm[16], vn[16], wm[8], wn[8];
+                tc::tmem_ld16(t_main + 16, vm); tc::tmem_ld16(t_min + 16, vn);
+                if (tail) { tc::tmem_ld8(t_main + 32, wm); tc::tmem_ld8(t_min + 32, wn); }
+                tc::wait_ld();
+                tc::fence_before();
+                __syncwarp();
+                if (lane == 0) tc::mbar_arrive(bar(D_EMPTY + s));       // accumulators are in registers: hand the stage back
+                fold4(vm, vn, 16, 4);
+                if (tail) fold4(wm, wn, 32, 2);
+            }
+            if (PROF) pw[2] += clock64() - te_;
+        }
+        const int64_t grow = (int64_t)rb * 128 + row;
+        if (grow < p.N) {
+            float *o = p.out + (int64_t)ks * p.T * p.N + grow;
+#pragma unroll
+            for (int c = 0; c < 40; c++) {
+                const uint32_t bits = (c & 1) ? (uint32_t)(acc2[c >> 1] >> 32) : (uint32_t)acc2[c >> 1];
+                if (c_base + c < p.T) o[(int64_t)(c_base + c) * p.N] = __uint_as_float(bits);
+            }
+        }
+    }
+    if (PROF && blockIdx.x == 0 && warp == 12 && lane == 0) { long long *o = p.prof + 32; o[0] = clock64() - pt0; o[1] = pw[0]; o[2] = pw[1]; o[3] = pw[2]; }
+}
+
+template <bool PROF>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 mmq_tc_q4_K(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmB, const __grid_constant__ CUtensorMap tmBS, TcArgs p) {
     extern __shared__ uint8_t smem_raw[];
@@ -69,9 +254,10 @@ mmq_tc_q4_K(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUt
         for (int i = 0; i < 2; i++) {
             tc::mbar_init(bar(B_FULL + i), 1); tc::mbar_init(bar(B_EMPTY + i), 1);
             tc::mbar_init(bar(BS_FULL + i), 1); tc::mbar_init(bar(BS_EMPTY + i), 1);
+            tc::mbar_init(bar(A_FULL + i), 8); tc::mbar_init(bar(A_EMPTY + i), 1);
             tc::mbar_init(bar(D_FULL + i), 1); tc::mbar_init(bar(D_EMPTY + i), 8);
         }
-        for (int i = 0; i < 4; i++) { tc::mbar_init(bar(A_FULL + i), 4); tc::mbar_init(bar(A_EMPTY + i), 1); tc::mbar_init(bar(HDR_FULL + i), 4); }
+        for (int i = 0; i < 4; i++) tc::mbar_init(bar(HDR_FULL + i), 4);
         tc::fence_barrier_init();
         tc::tma_prefetch_desc(&tmW); tc::tma_prefetch_desc(&tmB); tc::tma_prefetch_desc(&tmBS);
     }
@@ -81,202 +267,102 @@ mmq_tc_q4_K(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUt
     tc::fence_after();
     const uint32_t tmem = *tmem_slot;
 
-    if (warp == 0) {
-        // ---------------------------------------------------------------- weight producer
-        if (lane == 0) {
-            uint32_t i = 0;
-            for (int item = blockIdx.x; item < p.n_items; item += gridDim.x) {
-                const int ks = item / p.n_rb, rb = item % p.n_rb;
-                const int sb0 = ks * p.spp, sb1 = min(p.nbr, sb0 + p.spp);
-                for (int sb = sb0; sb < sb1; sb++, i++) {
-                    const uint32_t s = i % S_W, ph = (i / S_W) & 1;
-                    tc::mbar_wait(bar(W_EMPTY + s), ph ^ 1);
-                    tc::mbar_expect_tx(bar(W_FULL + s), W_STAGE);
-                    tc::tma_load_2d(sbase + OFF_W + s * W_STAGE, &tmW, sb * 144, rb * 128, bar(W_FULL + s));
-                }
-            }
-        }
-        __syncwarp();
-    } else if (warp == 2) {
-        // ---------------------------------------------------------------- activation producer
-        if (lane == 0) {
-            uint32_t i = 0, nbx = 0;
-            const uint32_t box_bytes = (uint32_t)p.npad * 128u;
-            for (int item = blockIdx.x; item < p.n_items; item += gridDim.x) {
-                const int ks = item / p.n_rb;
-                const int sb0 = ks * p.spp, sb1 = min(p.nbr, sb0 + p.spp);
-                for (int sb = sb0; sb < sb1; sb++, i++) {
-                    if (sb == sb0 || (sb & 3) == 0) {
-                        const uint32_t s2 = nbx & 1, ph2 = (nbx >> 1) & 1;
-                        tc::mbar_wait(bar(BS_EMPTY + s2), ph2 ^ 1);
-                        tc::mbar_expect_tx(bar(BS_FULL + s2), box_bytes);
-                        tc::tma_load_2d(sbase + OFF_BS + s2 * B_BOX, &tmBS, 64 * (sb >> 2), 0, bar(BS_FULL + s2));
-                        nbx++;
+    if (warp < 4) {
+        tc::setmaxnreg_dec<40>();                   // hand registers to the epilogue warps
+        if (warp == 0) {
+            // ------------------------------------------------------------ weight producer
+            if (lane == 0) {
+                uint32_t i = 0;
+                long long pw[1] = {0}; const long long pt0 = PROF ? clock64() : 0;
+                for (int item = blockIdx.x; item < p.n_items; item += gridDim.x) {
+                    const int ks = item / p.n_rb, rb = item % p.n_rb;
+                    const int sb0 = ks * p.spp, sb1 = min(p.nbr, sb0 + p.spp);
+                    for (int sb = sb0; sb < sb1; sb++, i++) {
+                        const uint32_t s = i % S_W, ph = (i / S_W) & 1;
+                        TCP_WAIT(0, bar(W_EMPTY + s), ph ^ 1);
+                        tc::mbar_expect_tx(bar(W_FULL + s), W_STAGE);
+                        tc::tma_load_2d(sbase + OFF_W + s * W_STAGE, &tmW, sb * 144, rb * 128, bar(W_FULL + s));
                     }
-                    const uint32_t s = i & 1, ph = (i >> 1) & 1;
-                    tc::mbar_wait(bar(B_EMPTY + s), ph ^ 1);
-                    tc::mbar_expect_tx(bar(B_FULL + s), 4 * box_bytes);
+                }
+                if (PROF && blockIdx.x == 0) { p.prof[0] = clock64() - pt0; p.prof[1] = pw[0]; }
+            }
+        } else if (warp == 2) {
+            // ------------------------------------------------------------ activation producer
+            if (lane == 0) {
+                uint32_t i = 0, nbx = 0;
+                const uint32_t box_bytes = (uint32_t)p.npad * 128u;
+                for (int item = blockIdx.x; item < p.n_items; item += gridDim.x) {
+                    const int ks = item / p.n_rb;
+                    const int sb0 = ks * p.spp, sb1 = min(p.nbr, sb0 + p.spp);
+                    for (int sb = sb0; sb < sb1; sb++, i++) {
+                        if (sb == sb0 || (sb & 3) == 0) {
+                            const uint32_t s2 = nbx & 1, ph2 = (nbx >> 1) & 1;
+                            tc::mbar_wait(bar(BS_EMPTY + s2), ph2 ^ 1);
+                            tc::mbar_expect_tx(bar(BS_FULL + s2), box_bytes);
+                            tc::tma_load_2d(sbase + OFF_BS + s2 * B_BOX, &tmBS, 64 * (sb >> 2), 0, bar(BS_FULL + s2));
+                            nbx++;
+                        }
+                        const uint32_t s = i & 1, ph = (i >> 1) & 1;
+                        tc::mbar_wait(bar(B_EMPTY + s), ph ^ 1);
+                        tc::mbar_expect_tx(bar(B_FULL + s), 4 * box_bytes);
 #pragma unroll
-                    for (int g = 0; g < 4; g++)
-                        tc::tma_load_2d(sbase + OFF_B + s * B_STAGE + g * B_BOX, &tmB, sb * 256 + 64 * g, 0, bar(B_FULL + s));
+                        for (int g = 0; g < 4; g++)
+                            tc::tma_load_2d(sbase + OFF_B + s * B_STAGE + g * B_BOX, &tmB, sb * 256 + 64 * g, 0, bar(B_FULL + s));
+                    }
                 }
             }
-        }
-        __syncwarp();
-    } else if (warp == 1) {
-        // ---------------------------------------------------------------- MMA issuer
-        if (lane == 0) {
+        } else if (warp == 1) {
+            // ------------------------------------------------------------ MMA issuer
+            // The whole warp runs the loop so that every address stays in uniform registers; one elected lane issues.
+            const bool leader = tc::elect_one();
             const uint32_t idesc = tc::idesc_f16_m128(p.npad);
             uint32_t i = 0, nbx = 0; int cur_bs = -1;
+            long long pw[4] = {0, 0, 0, 0}; const long long pt0 = PROF ? clock64() : 0;
             for (int item = blockIdx.x; item < p.n_items; item += gridDim.x) {
                 const int ks = item / p.n_rb;
                 const int sb0 = ks * p.spp, sb1 = min(p.nbr, sb0 + p.spp);
                 for (int sb = sb0; sb < sb1; sb++, i++) {
                     if (sb == sb0 || (sb & 3) == 0) {
-                        if (cur_bs >= 0) tc::mma_commit(bar(BS_EMPTY + (cur_bs & 1)));
+                        if (cur_bs >= 0 && leader) tc::mma_commit(bar(BS_EMPTY + (cur_bs & 1)));
                         cur_bs = (int)nbx;
-                        tc::mbar_wait(bar(BS_FULL + (nbx & 1)), (nbx >> 1) & 1);
+                        TCP_WAIT(0, bar(BS_FULL + (nbx & 1)), (nbx >> 1) & 1);
                         nbx++;
                     }
                     const uint32_t s = i & 1, ph = (i >> 1) & 1;
-                    tc::mbar_wait(bar(B_FULL + s), ph);
-                    tc::mbar_wait(bar(D_EMPTY + s), ph ^ 1);
-                    tc::fence_after();
+                    TCP_WAIT(1, bar(B_FULL + s), ph);
+                    TCP_WAIT(2, bar(D_EMPTY + s), ph ^ 1);
                     const uint32_t d_main = tmem + s * D_STRIDE, d_min = d_main + D_MIN;
+                    const uint64_t bdesc = tc::smem_desc_sw128(sbase + OFF_B + s * B_STAGE);
+                    const uint64_t mdesc = tc::smem_desc_sw128(sbase + OFF_BS + (cur_bs & 1) * B_BOX + 32 * (sb & 3));
 #pragma unroll
-                    for (int g = 0; g < 4; g++) {
-                        tc::mbar_wait(bar(A_FULL + g), i & 1);
+                    for (int h = 0; h < 2; h++) {
+                        TCP_WAIT(3, bar(A_FULL + h), i & 1);
                         tc::fence_after();
-                        const uint32_t bsm = sbase + OFF_B + s * B_STAGE + g * B_BOX;
-#pragma unroll
-                        for (int j = 0; j < 4; j++)
-                            tc::mma_f16_ts(d_main, tmem + A_OFF + 32 * g + 8 * j, tc::smem_desc_sw128(bsm + 32 * j), idesc, (g | j) != 0);
-                        if (g == 0)
-                            tc::mma_f16_ts(d_min, tmem + AM_OFF + 8 * (i & 1), tc::smem_desc_sw128(sbase + OFF_BS + (cur_bs & 1) * B_BOX + 32 * (sb & 3)), idesc, 0);
-                        tc::mma_commit(bar(A_EMPTY + g));
+                        if (leader) {
+                            tc::mma_f16_ts_x8(d_main, tmem + A_OFF + 64 * h, bdesc + (uint64_t)((2 * h) * (B_BOX >> 4)),
+                                              bdesc + (uint64_t)((2 * h + 1) * (B_BOX >> 4)), idesc, h != 0);
+                            if (h == 0) tc::mma_f16_ts(d_min, tmem + AM_OFF + 8 * (i & 1), mdesc, idesc, 0);
+                            tc::mma_commit(bar(A_EMPTY + h));
+                            if (h == 1) { tc::mma_commit(bar(B_EMPTY + s)); tc::mma_commit(bar(D_FULL + s)); }
+                        }
+                        __syncwarp();
                     }
-                    tc::mma_commit(bar(B_EMPTY + s));
-                    tc::mma_commit(bar(D_FULL + s));
                 }
             }
+            if (PROF && blockIdx.x == 0 && lane == 0) { long long *o = p.prof + 8; o[0] = clock64() - pt0; o[1] = pw[0]; o[2] = pw[1]; o[3] = pw[2]; o[4] = pw[3]; }
         }
         __syncwarp();
-    } else if (warp >= 4 && warp < 12) {
-        // ---------------------------------------------------------------- dequant: raw Q4_K -> f16 integers in TMEM
-        const int q = warp & 3, member = (warp - 4) >> 2, row = 32 * q + lane;
-        const uint32_t lane_base = tmem + ((uint32_t)(32 * q) << 16);
-        float2 *hdr_sm = (float2 *)(smem + OFF_HDR);
-        uint32_t i = 0;
-        for (int item = blockIdx.x; item < p.n_items; item += gridDim.x) {
-            const int ks = item / p.n_rb;
-            const int sb0 = ks * p.spp, sb1 = min(p.nbr, sb0 + p.spp);
-            for (int sb = sb0; sb < sb1; sb++, i++) {
-                const uint32_t s = i % S_W;
-                tc::mbar_wait(bar(W_FULL + s), (i / S_W) & 1);
-                const uint8_t *rp = smem + OFF_W + s * W_STAGE + row * 144;
-                const uint4 hd = *(const uint4 *)rp;
-                uint4 qv[2][2];
-#pragma unroll
-                for (int h = 0; h < 2; h++) {
-                    qv[h][0] = *(const uint4 *)(rp + 16 + 32 * (member + 2 * h));
-                    qv[h][1] = *(const uint4 *)(rp + 32 + 32 * (member + 2 * h));
-                }
-                __syncwarp();
-                if (lane == 0) tc::mbar_arrive(bar(W_EMPTY + s));
-                // 6-bit scales / mins (get_scale_min_k4, R/ggml/src/ggml-quants.c:631) as bytes of u[0..1] / u[2..3]
-                uint32_t u[4];
-                u[0] = hd.y & 0x3f3f3f3fu; u[1] = (hd.w & 0x0f0f0f0fu) | (((hd.y >> 6) & 0x03030303u) << 4);
-                u[2] = hd.z & 0x3f3f3f3fu; u[3] = ((hd.w >> 4) & 0x0f0f0f0fu) | (((hd.z >> 6) & 0x03030303u) << 4);
-#pragma unroll
-                for (int h = 0; h < 2; h++) {
-                    const int g = member + 2 * h;                       // 64-element group: sub-blocks 2g (low nibbles), 2g+1 (high)
-                    const __half2 s_lo = byte_to_h2(u[g >> 1], (2 * g) & 3), s_hi = byte_to_h2(u[g >> 1], (2 * g + 1) & 3);
-                    const __half2 mul_lo = s_lo, add_lo = __hmul2(s_lo, __float2half2_rn(-1024.f));
-                    const __half2 mul_hi = __hmul2(s_hi, __float2half2_rn(0.0625f)), add_hi = __hmul2(s_hi, __float2half2_rn(-64.f));
-                    uint32_t r[32];
-                    const uint32_t xs[8] = {qv[h][0].x, qv[h][0].y, qv[h][0].z, qv[h][0].w, qv[h][1].x, qv[h][1].y, qv[h][1].z, qv[h][1].w};
-#pragma unroll
-                    for (int w = 0; w < 8; w++) {
-                        const uint32_t y = __byte_perm(xs[w], 0, 0x4140), z = __byte_perm(xs[w], 0, 0x4342);
-                        r[2 * w]          = h2u(__hfma2(u2h((y & 0x000f000fu) | 0x64006400u), mul_lo, add_lo));
-                        r[2 * w + 1]      = h2u(__hfma2(u2h((z & 0x000f000fu) | 0x64006400u), mul_lo, add_lo));
-                        r[16 + 2 * w]     = h2u(__hfma2(u2h((y & 0x00f000f0u) | 0x64006400u), mul_hi, add_hi));
-                        r[16 + 2 * w + 1] = h2u(__hfma2(u2h((z & 0x00f000f0u) | 0x64006400u), mul_hi, add_hi));
-                    }
-                    tc::mbar_wait(bar(A_EMPTY + g), (i & 1) ^ 1);
-                    tc::fence_after();
-                    if (g == 0) {                                        // member 0, first group: header + mins operand
-                        const __half2 dm = u2h(hd.x);
-                        hdr_sm[(i & 3) * 128 + row] = make_float2(__low2float(dm), __high2float(dm));
-                        uint32_t mr[8];
-#pragma unroll
-                        for (int j = 0; j < 8; j++) mr[j] = h2u(byte_to_h2(u[2 + (j >> 2)], j & 3));
-                        tc::tmem_st8(lane_base + AM_OFF + 8 * (i & 1), mr);
-                    }
-                    tc::tmem_st32(lane_base + A_OFF + 32 * g, r);
-                    tc::wait_st();
-                    tc::fence_before();
-                    __syncwarp();
-                    if (lane == 0) {
-                        tc::mbar_arrive(bar(A_FULL + g));
-                        if (g == 0) tc::mbar_arrive(bar(HDR_FULL + (i & 3)));
-                    }
-                }
-            }
-        }
-    } else if (warp >= 12) {
-        // ---------------------------------------------------------------- epilogue
-        const int q = warp & 3, hf = (warp - 12) >> 2, row = 32 * q + lane, c_base = 40 * hf;
-        const uint32_t lane_base = tmem + ((uint32_t)(32 * q) << 16);
-        const float2 *hdr_sm = (const float2 *)(smem + OFF_HDR);
-        uint32_t i = 0;
-        for (int item = blockIdx.x; item < p.n_items; item += gridDim.x) {
-            const int ks = item / p.n_rb, rb = item % p.n_rb;
-            const int sb0 = ks * p.spp, sb1 = min(p.nbr, sb0 + p.spp);
-            float acc[40];
-#pragma unroll
-            for (int c = 0; c < 40; c++) acc[c] = 0.f;
-            for (int sb = sb0; sb < sb1; sb++, i++) {
-                const float dxa = (c_base + lane < p.T) ? __ldg(p.dT + (int64_t)sb * EB_DT_PITCH + c_base + lane) : 0.f;
-                const float dxb = (lane < 8 && c_base + 32 + lane < p.T) ? __ldg(p.dT + (int64_t)sb * EB_DT_PITCH + c_base + 32 + lane) : 0.f;
-                tc::mbar_wait(bar(HDR_FULL + (i & 3)), (i >> 2) & 1);
-                const float2 h = hdr_sm[(i & 3) * 128 + row];
-                const uint32_t s = i & 1;
-                tc::mbar_wait(bar(D_FULL + s), (i >> 1) & 1);
-                tc::fence_after();
-#pragma unroll
-                for (int ch = 0; ch < 5; ch++) {
-                    if (c_base + 8 * ch < p.npad) {
-                        uint32_t vm[8], vn[8];
-                        tc::tmem_ld8(lane_base + s * D_STRIDE + c_base + 8 * ch, vm);
-                        tc::tmem_ld8(lane_base + s * D_STRIDE + D_MIN + c_base + 8 * ch, vn);
-                        tc::wait_ld();
-#pragma unroll
-                        for (int e = 0; e < 8; e++) {
-                            const int idx = 8 * ch + e;
-                            const float dx = __shfl_sync(0xffffffffu, idx < 32 ? dxa : dxb, idx & 31);
-                            acc[idx] += (h.x * dx) * __uint_as_float(vm[e]) - (h.y * dx) * __uint_as_float(vn[e]);
-                        }
-                    }
-                }
-                tc::fence_before();
-                __syncwarp();
-                if (lane == 0) tc::mbar_arrive(bar(D_EMPTY + s));
-            }
-            const int64_t grow = (int64_t)rb * 128 + row;
-            if (grow < p.N) {
-                float *o = p.out + (int64_t)ks * p.T * p.N + grow;
-#pragma unroll
-                for (int c = 0; c < 40; c++)
-                    if (c_base + c < p.T) o[(int64_t)(c_base + c) * p.N] = acc[c];
-            }
-        }
+    } else if (warp < 12) {
+        if (warp < 8) dequant_q4_K<0, PROF>(p, smem, bar0, tmem, warp & 3, lane);
+        else dequant_q4_K<1, PROF>(p, smem, bar0, tmem, warp & 3, lane);
+    } else {
+        tc::setmaxnreg_inc<120>();   // CTA pool: 128*40 + 256*96 + 256*120 = 60416 <= 640*96
+        epilogue_role<PROF>(p, smem, bar0, tmem, warp, lane);
     }
     tc::fence_before();
     __syncthreads();
     if (warp == 3) tc::tmem_dealloc(tmem, 512);
 }
-
 // ------------------------------------------------------------------ host side
 typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
                                   const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
@@ -306,7 +392,8 @@ int eb_mmq_tc_init() {
         }
         g_encode = (EncodeTiledFn)fn;
     }
-    EB_CUDA(cudaFuncSetAttribute(mmq_tc_q4_K, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+    EB_CUDA(cudaFuncSetAttribute(mmq_tc_q4_K<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+    EB_CUDA(cudaFuncSetAttribute(mmq_tc_q4_K<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
     return EB_OK;
 }
 
@@ -338,15 +425,27 @@ int eb_mmq_tc_parts(int type, const void *W, int64_t N, int64_t K, const ActQ &a
     const int ks = tc_pick_ksplit(N, nbr);
     TcArgs p;
     p.dT = a.dT; p.out = planes; p.N = N; p.nbr = nbr; p.T = a.T; p.npad = (a.T + 15) / 16 * 16;
+    p.k_lo = 0x000f000fu; p.k_hi = 0x00f000f0u; p.k_magic = 0x64006400u;
     p.n_rb = (int)cdiv(N, 128); p.spp = (int)cdiv(nbr, ks); p.n_items = p.n_rb * ks;
     CUtensorMap tmW, tmB, tmBS;
     int rc;
     if ((rc = make_map_2d(&tmW, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, W, (uint64_t)nbr * 144, (uint64_t)N, (uint64_t)nbr * 144, 144, 128, CU_TENSOR_MAP_SWIZZLE_NONE))) return rc;
     if ((rc = make_map_2d(&tmB, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, a.h16, (uint64_t)K, (uint64_t)a.T, (uint64_t)K * 2, 64, (uint32_t)p.npad, CU_TENSOR_MAP_SWIZZLE_128B))) return rc;
     if ((rc = make_map_2d(&tmBS, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, a.bsum, (uint64_t)K / 16, (uint64_t)a.T, (uint64_t)K / 16 * 2, 64, (uint32_t)p.npad, CU_TENSOR_MAP_SWIZZLE_128B))) return rc;
+    static long long *prof_buf = nullptr; static const int want_prof = getenv("EB_TC_PROF") ? 1 : 0;
+    if (want_prof && !prof_buf) { cudaMalloc((void **)&prof_buf, 512 * 8); cudaMemset(prof_buf, 0, 512 * 8); }
+    p.prof = want_prof ? prof_buf : nullptr;
     const int grid = std::min(p.n_items, eb_sm_count());
-    mmq_tc_q4_K<<<grid, TC_THREADS, SMEM_BYTES, st>>>(tmW, tmB, tmBS, p);
+    if (want_prof) mmq_tc_q4_K<true><<<grid, TC_THREADS, SMEM_BYTES, st>>>(tmW, tmB, tmBS, p);
+    else mmq_tc_q4_K<false><<<grid, TC_THREADS, SMEM_BYTES, st>>>(tmW, tmB, tmBS, p);
     EB_CHECK_LAUNCH();
     *ks_out = ks;
+    if (want_prof) {
+        long long h[512]; cudaStreamSynchronize(st); cudaMemcpy(h, prof_buf, sizeof(h), cudaMemcpyDeviceToHost);
+        fprintf(stderr, "[tc prof] N=%lld K=%lld T=%d ks=%d items=%d grid=%d | Wprod total %lld wait %lld | MMA total %lld bs %lld b %lld d_empty %lld a_full %lld | "
+                "DQ0 total %lld w_full %lld a_empty0 %lld a_empty1 %lld - %lld n=%lld | DQ1 total %lld w_full %lld a_e0 %lld a_e1 %lld - %lld | EPI total %lld hdr %lld d_full %lld work %lld\n",
+                (long long)N, (long long)K, a.T, ks, p.n_items, grid, h[0], h[1], h[8], h[9], h[10], h[11], h[12], h[16], h[17], h[18], h[19], h[20], h[21],
+                h[24], h[25], h[26], h[27], h[28], h[32], h[33], h[34], h[35]);
+    }
     return EB_OK;
 }

@@ -31,9 +31,10 @@ __device__ __forceinline__ void quant_regs_q8K(const float (&v)[8], int8_t *__re
         for (int j = 0; j < 8; j++) q[j] = min(127, __float2int_rn(__fmul_rn(iscale, v[j])));
         if (lane == 0) { const float dd = __fdiv_rn(1.f, iscale); *dout = dd; if (dT) *dT = dd; }
     }
-    if (h16) {                                                // exact: |q| <= 127
-        const __half2 a = __floats2half2_rn((float)q[0], (float)q[1]), b = __floats2half2_rn((float)q[2], (float)q[3]);
-        const __half2 c = __floats2half2_rn((float)q[4], (float)q[5]), e = __floats2half2_rn((float)q[6], (float)q[7]);
+    if (h16) {                                                // exact: |q| <= 127.  K order inside each group of 4 is
+        // (0,2,1,3): the tc GEMM's dequant extracts nibbles of bytes (0,2) and (1,3) of a word with one mask each
+        const __half2 a = __floats2half2_rn((float)q[0], (float)q[2]), b = __floats2half2_rn((float)q[1], (float)q[3]);
+        const __half2 c = __floats2half2_rn((float)q[4], (float)q[6]), e = __floats2half2_rn((float)q[5], (float)q[7]);
         ((uint4 *)h16)[lane] = make_uint4(*(const uint32_t *)&a, *(const uint32_t *)&b, *(const uint32_t *)&c, *(const uint32_t *)&e);
     }
     uint32_t w0 = (q[0] & 0xff) | ((q[1] & 0xff) << 8) | ((q[2] & 0xff) << 16) | ((uint32_t)(q[3] & 0xff) << 24);

@@ -60,6 +60,45 @@ __device__ __forceinline__ void mma_f16_ts(uint32_t d_tmem, uint32_t a_tmem, uin
                  "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
                  ::"r"(d_tmem), "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(accumulate) : "memory");
 }
+// four K = 16 steps issued back to back (one asm block: the issue slot is ~40 clk/MMA only when
+// nothing sits between consecutive tcgen05.mma — measured in tools/ubench_mma.cu): A columns
+// a_tmem + 8j, B descriptor b_desc + 32j bytes.  The first step overwrites D when acc_first == 0.
+__device__ __forceinline__ void mma_f16_ts_x4(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t idesc, uint32_t acc_first) {
+    asm volatile("{\n\t.reg .pred p, q;\n\t.reg .b32 a1, a2, a3;\n\t.reg .b64 b1, b2, b3;\n\t"
+                 "setp.ne.b32 p, %4, 0;\n\tsetp.eq.b32 q, 0, 0;\n\t"
+                 "add.u32 a1, %1, 8;\n\tadd.u32 a2, %1, 16;\n\tadd.u32 a3, %1, 24;\n\t"
+                 "add.u64 b1, %2, 2;\n\tadd.u64 b2, %2, 4;\n\tadd.u64 b3, %2, 6;\n\t"
+                 "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t"
+                 "tcgen05.mma.cta_group::1.kind::f16 [%0], [a1], b1, %3, q;\n\t"
+                 "tcgen05.mma.cta_group::1.kind::f16 [%0], [a2], b2, %3, q;\n\t"
+                 "tcgen05.mma.cta_group::1.kind::f16 [%0], [a3], b3, %3, q;\n\t}"
+                 ::"r"(d_tmem), "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(acc_first) : "memory");
+}
+// eight K = 16 steps (two 64-element groups): A columns a_tmem + 8j, B = b_lo + 32j bytes (j < 4), b_hi + 32(j-4) bytes
+__device__ __forceinline__ void mma_f16_ts_x8(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_lo, uint64_t b_hi, uint32_t idesc, uint32_t acc_first) {
+    asm volatile("{\n\t.reg .pred p, q;\n\t.reg .b32 a1, a2, a3, a4, a5, a6, a7;\n\t.reg .b64 b1, b2, b3, b5, b6, b7;\n\t"
+                 "setp.ne.b32 p, %5, 0;\n\tsetp.eq.b32 q, 0, 0;\n\t"
+                 "add.u32 a1, %1, 8;\n\tadd.u32 a2, %1, 16;\n\tadd.u32 a3, %1, 24;\n\tadd.u32 a4, %1, 32;\n\t"
+                 "add.u32 a5, %1, 40;\n\tadd.u32 a6, %1, 48;\n\tadd.u32 a7, %1, 56;\n\t"
+                 "add.u64 b1, %2, 2;\n\tadd.u64 b2, %2, 4;\n\tadd.u64 b3, %2, 6;\n\t"
+                 "add.u64 b5, %3, 2;\n\tadd.u64 b6, %3, 4;\n\tadd.u64 b7, %3, 6;\n\t"
+                 "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %4, p;\n\t"
+                 "tcgen05.mma.cta_group::1.kind::f16 [%0], [a1], b1, %4, q;\n\t"
+                 "tcgen05.mma.cta_group::1.kind::f16 [%0], [a2], b2, %4, q;\n\t"
+                 "tcgen05.mma.cta_group::1.kind::f16 [%0], [a3], b3, %4, q;\n\t"
+                 "tcgen05.mma.cta_group::1.kind::f16 [%0], [a4], %3, %4, q;\n\t"
+                 "tcgen05.mma.cta_group::1.kind::f16 [%0], [a5], b5, %4, q;\n\t"
+                 "tcgen05.mma.cta_group::1.kind::f16 [%0], [a6], b6, %4, q;\n\t"
+                 "tcgen05.mma.cta_group::1.kind::f16 [%0], [a7], b7, %4, q;\n\t}"
+                 ::"r"(d_tmem), "r"(a_tmem), "l"(b_lo), "l"(b_hi), "r"(idesc), "r"(acc_first) : "memory");
+}
+template <int N> __device__ __forceinline__ void setmaxnreg_inc() { asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(N)); }
+template <int N> __device__ __forceinline__ void setmaxnreg_dec() { asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(N)); }
+__device__ __forceinline__ bool elect_one() {
+    uint32_t e;
+    asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(e));
+    return e != 0;
+}
 // arrive on an mbarrier once all previously issued tcgen05.mma of this thread have completed
 __device__ __forceinline__ void mma_commit(uint32_t bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
@@ -95,6 +134,21 @@ __device__ __forceinline__ void tmem_st8(uint32_t taddr, const uint32_t (&r)[8])
 __device__ __forceinline__ void tmem_ld8(uint32_t taddr, uint32_t (&r)[8]) {
     asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
                  : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]) : "r"(taddr) : "memory");
+}
+
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&r)[16]) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+                   "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]) : "r"(taddr) : "memory");
+}
+
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,"
+                 "%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+                   "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+                   "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+                   "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31]) : "r"(taddr) : "memory");
 }
 
 }  // namespace tc
