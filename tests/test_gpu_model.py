@@ -77,6 +77,32 @@ def test_tiny_model_vs_golden(eb):
     s.free()
 
 
+def test_independent_rows_rounding_flips(eb):
+    """A batch of INDEPENDENT first tokens (parent = -1) is a pure GEMM chain per row: no attention mixing, so the
+    only source of deviation from the oracle is an activation-quantisation rounding flip (an f32 value within 1 ulp of
+    a .5 boundary of the Q8_K grid rounds the other way because the f32 summation ORDER differs).  Measured on B200:
+    ~5-6 % of rows flip, identically for the mma.sync and the tcgen05 GEMM; a flipped row deviates ~1e-2, all other
+    rows agree to f32 rounding.  Bound the flip rate and the unflipped error."""
+    hp = dict(E=512, H=4, F=1024, V=2048, L=3)
+    tgt = fx.make_model(**hp, ftype="q4_k_m", seed=21)
+    o = po.oracle(); n_ctx = 256
+    mo = fx.to_cpu_model(o, tgt); mg = fx.to_gpu_model(eb, tgt)
+    P, clean, total = 40, 0, 0
+    po.set_fattn_acc_f32(1)
+    for seed in range(4):
+        kv = o._g("kv_new")(hp["L"], hp["E"], n_ctx)
+        s = eb.Session(mg, None, n_ctx=n_ctx, max_nodes=65, use_graph=False)
+        prompt = np.random.default_rng(1000 + seed).integers(3, hp["V"], P).astype(np.int32)
+        vis = np.zeros((P, n_ctx), np.uint8); vis[np.arange(P), np.arange(P)] = 1
+        lo, _ = o.forward(mo, kv, prompt, np.zeros(P, np.int32), None, 0, n_ctx, vis, hp["E"], hp["V"])
+        lg, _ = s.forward(0, prompt, np.zeros(P, np.int32), parent=np.full(P, -1, np.int32))
+        err = np.abs(lg - lo).max(1) / np.abs(lo).max()
+        assert err.max() < MODEL_REL
+        clean += int((err < 1e-5).sum()); total += P
+        s.free()
+    assert clean >= 0.8 * total, (clean, total)
+
+
 @pytest.mark.parametrize("ftype", ["q4_k_m", po.Q4_0, po.Q8_0])
 @pytest.mark.parametrize("T", [1, 16, 27, 65])
 def test_forward_vs_oracle(eb, ftype, T):
@@ -95,7 +121,6 @@ def test_forward_vs_oracle(eb, ftype, T):
     lo, fo = o.forward(mo, kv, prompt, np.arange(P), None, 0, n_ctx, vis, hp["E"], hp["V"])
     lg, fg = s.forward(0, prompt, np.arange(P))
     assert rel_max(lg, lo) < MODEL_REL and nmse(lg, lo) < MODEL_NMSE
-    assert np.abs(lg[0] - lo[0]).max() < 1e-4 * np.abs(lo[0]).max()      # first token: no attention mixing yet, few flips
     s.commit(0, P)
     par = fx.tree_parents(T, rng, 6)
     toks = rng.integers(3, hp["V"], T).astype(np.int32); pos = (P + fx.tree_depths(par)).astype(np.int32)
