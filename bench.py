@@ -101,6 +101,28 @@ def algorithmic_bytes(tgt_bytes, n_kv, T):
     return tgt_bytes + kv_read + kv_write
 
 
+def max_over_ranks(dist, times_ms, device):
+    """Replicas share nothing on the data path; the only exchange is this MAX of the per-rank
+    timings (the job is as slow as its slowest replica).  dist=None -> single process."""
+    if dist is None:
+        return list(times_ms)
+    import torch
+    tt = torch.tensor(list(times_ms), device=device, dtype=torch.float64)
+    dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    dist.barrier()
+    return tt.tolist()
+
+
+def job_tokens(steps, world):
+    """whole-job tokens: every replica commits fixed_accept drafted tokens + the bonus token per round"""
+    return (FIXED_ACCEPT + 1) * steps * world
+
+
+def replica_seed(rank):
+    """each replica fills its KV prefix from its own seed (independent sequences, weak scaling)"""
+    return 3 + rank
+
+
 def run_gpu(args, rank, world, local_rank):
     from __graft_entry__ import load_package
     eb = load_package()
@@ -113,14 +135,14 @@ def run_gpu(args, rank, world, local_rank):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     tgt, head = build_gpu_models(eb)
     s = eb.Session(tgt, head, n_ctx=4096 + 256, fixed_accept=FIXED_ACCEPT, use_graph=True, **TREE)
-    s.synth_kv(N_PAST0, seed=3 + rank)
+    s.synth_kv(N_PAST0, seed=replica_seed(rank))
     s.set_root(1)
     tok = 1
     res = None
     for _ in range(max(args.warmup, 3)):
         s.set_root(tok); res = s.round(); tok = res.bonus
     # rewind the KV length so that the timed rounds sit around the 4K mark
-    s.synth_kv(N_PAST0, seed=3 + rank); s.set_root(tok)
+    s.synth_kv(N_PAST0, seed=replica_seed(rank)); s.set_root(tok)
 
     def barrier():
         if dist is not None:
@@ -141,14 +163,9 @@ def run_gpu(args, rank, world, local_rank):
     t1 = time.perf_counter()
     launches = eb.launch_count()
     wall_ms = (t1 - t0) * 1e3
-    if dist is not None:
-        import torch
-        tt = torch.tensor([wall_ms, gpu_ms], device="cuda", dtype=torch.float64)
-        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-        wall_ms, gpu_ms = tt.tolist()
-        dist.barrier()
+    wall_ms, gpu_ms = max_over_ranks(dist, [wall_ms, gpu_ms], "cuda")
     clocks = sampler.summary()
-    tokens = (FIXED_ACCEPT + 1) * args.steps * world
+    tokens = job_tokens(args.steps, world)
     out = None
     if rank == 0:
         hbm, peak_src = peaks()
@@ -176,7 +193,7 @@ def run_gpu(args, rank, world, local_rank):
             "verify_step_us": verify_us,
             "verify_step_hbm_frac": step_bytes / (verify_us * 1e-6) / 1e9 / hbm,
             "verify_step_bytes": step_bytes,
-            "roofline": {"kernel": "mmq_q4_K<9> (Q4_K x Q8_K int8-MMA GEMM, N=11008 K=4096 T=65)", "bound": "hbm", "achieved": achieved, "peak": hbm,
+            "roofline": {"kernel": "mmq_tc_q4_K (Q4_K x Q8_K tcgen05 kind::f16 exact-integer GEMM, A in TMEM, TMA weight ring; N=11008 K=4096 T=65)", "bound": "hbm", "achieved": achieved, "peak": hbm,
                          "unit": "GB/s", "frac": achieved / hbm, "traffic": None, "peak_source": peak_src, "ms_per_launch": k_ms,
                          "matvec_T1_gbs": k_bytes / (mv_ms * 1e-3) / 1e9},
             "clocks": clocks,

@@ -4,8 +4,8 @@
  *
  * Plain pointers and sizes only; no torch / ggml types.  Two layers:
  *   (1) operator entry points — one per ggml op on the path (what a ggml backend's
- *       graph_compute dispatches to; eagle-in-llama.cpp_b200/ggml_backend/ggml-b200.cpp binds
- *       them behind the reference's ggml_backend_i vtable, see INTEGRATION.md);
+ *       graph_compute dispatches to; INTEGRATION.md shows the reference-side stub that binds
+ *       them behind the reference's ggml_backend_i vtable);
  *   (2) the fused speculative-step engine (model upload, tree-verify forward, draft-head
  *       forward + tree expansion, accept walk, KV compaction) with no host round trip inside
  *       a round.
