@@ -36,7 +36,7 @@ int eb_device_init(int device) {
     EB_CUDA(cudaSetDevice(device));
     g_sm_count = prop.multiProcessorCount; g_device = device;
     int rc;
-    if ((rc = eb_mmq_init()) || (rc = eb_mmq_tc_init()) || (rc = eb_fattn_init()) || (rc = eb_spec_init()) || (rc = eb_fused_init())) return rc;
+    if ((rc = eb_mmq_init()) || (rc = eb_mmq_tc_init()) || (rc = eb_fattn_tc_init()) || (rc = eb_fattn_init()) || (rc = eb_spec_init()) || (rc = eb_fused_init())) return rc;
     return EB_OK;
 }
 int eb_device_sm_count(void) { return g_sm_count; }
@@ -116,10 +116,12 @@ int eb_silu(const float *x, float *y, int64_t n, void *st) { NEED_DEV(); return 
 int eb_relu(const float *x, float *y, int64_t n, void *st) { NEED_DEV(); return eb_relu_impl(x, y, n, S(st)); }
 int eb_cpy_f32_f16(const float *x, void *y, int64_t n, void *st) { NEED_DEV(); return eb_cpy_f32_f16_impl(x, y, n, S(st)); }
 
-size_t eb_flash_attn_ws_size(int T, int H, int D, int n_kv) { return eb_flash_attn_ws_size_impl(T, H, D, n_kv); }
+size_t eb_flash_attn_ws_size(int T, int H, int D, int n_kv) { return std::max(eb_flash_attn_ws_size_impl(T, H, D, n_kv), eb_fattn_tc_ws_size(T, H, n_kv)); }
 int eb_flash_attn(const float *q, const void *k, const void *v, int64_t kv_stride, const void *mask, int64_t mask_stride,
                   const uint32_t *tree_bits, int n_prefix, int T, int H, int D, int n_kv, float scale, float *out, void *ws, void *st) {
     NEED_DEV();
+    if (!mask && tree_bits && eb_fattn_tc_supported(T, D) && kv_stride % 8 == 0)      // compact tree mask: tcgen05 kernel
+        return eb_fattn_tc_f32q(q, k, v, kv_stride, tree_bits, n_prefix, n_kv, T, H, scale, out, ws, S(st));
     return eb_flash_attn_impl(q, k, v, kv_stride, mask, mask_stride, tree_bits, n_prefix, T, H, D, n_kv, scale, out, ws, S(st));
 }
 int eb_top_k(const float *logits, int rows, int V, int k, int32_t *ids, float *vals, float *probs, void *st) { NEED_DEV(); return eb_top_k_impl(logits, rows, V, k, ids, vals, probs, S(st)); }

@@ -152,7 +152,8 @@ static int ws_alloc(Workspace &w, const eb_model *m, int Tmax, int n_ctx) {
     EB_CUDA(cudaMalloc(&w.actq, w.actq_bytes)); EB_CUDA(cudaMalloc(&w.actq2, w.actq_bytes));
     w.partial_bytes = (size_t)8 * T * Nmax * 4;
     EB_CUDA(cudaMalloc((void **)&w.partial, w.partial_bytes));
-    w.fa_bytes = eb_flash_attn_ws_size_impl(Tmax, m->H, m->E / m->H, n_ctx);
+    w.fa_bytes = std::max(eb_flash_attn_ws_size_impl(Tmax, m->H, m->E / m->H, n_ctx), eb_fattn_tc_ws_size(Tmax, m->H, n_ctx));
+    EB_CUDA(cudaMalloc((void **)&w.q16, T * E * 2)); EB_CUDA(cudaMemset(w.q16, 0, T * E * 2));
     EB_CUDA(cudaMalloc(&w.fa_ws, w.fa_bytes));
     EB_CUDA(cudaMalloc((void **)&w.tokens, T * 4)); EB_CUDA(cudaMalloc((void **)&w.pos, T * 4));
     EB_CUDA(cudaMalloc((void **)&w.bits, T * 16)); EB_CUDA(cudaMalloc((void **)&w.ctl, sizeof(FwdCtl)));
@@ -160,7 +161,7 @@ static int ws_alloc(Workspace &w, const eb_model *m, int Tmax, int n_ctx) {
 }
 static void ws_free(Workspace &w) {
     for (void *p : {(void *)w.x, (void *)w.cur, (void *)w.q, (void *)w.k, (void *)w.v, (void *)w.att, (void *)w.gate, (void *)w.up, (void *)w.cat,
-                    (void *)w.hidden, (void *)w.feat, (void *)w.logits, (void *)w.partial, w.actq, w.actq2, (void *)w.pq, (void *)w.pk, (void *)w.pv, (void *)w.po, (void *)w.pgate, (void *)w.pup, w.fa_ws, (void *)w.tokens, (void *)w.pos, (void *)w.bits, (void *)w.ctl})
+                    (void *)w.hidden, (void *)w.feat, (void *)w.logits, (void *)w.partial, w.actq, w.actq2, (void *)w.pq, (void *)w.pk, (void *)w.pv, (void *)w.po, (void *)w.pgate, (void *)w.pup, w.fa_ws, (void *)w.tokens, (void *)w.pos, (void *)w.bits, (void *)w.ctl, (void *)w.q16})
         cudaFree(p);
 }
 static int kv_alloc(KVCache &kv, const eb_model *m, int n_ctx) {
@@ -252,8 +253,10 @@ static int forward_dev(const eb_model *m, KVCache &kv, Workspace &w, const int32
         RC(mm_parts(t[EB_L_WK], ak, w.pk, &kk_, st));
         RC(mm_parts(t[EB_L_WV], av, w.pv, &kv_, st));
         __half *kc = kv.k + (int64_t)l * kv.layer_stride, *vc = kv.v + (int64_t)l * kv.layer_stride;
-        RC(eb_rope_kv_store_fused(w.pq, kq_, w.pk, kk_, w.pv, kv_, w.q, pos, kc, vc, ctl, D, H, T, m->freq_base, st));
-        RC(eb_flash_attn_ctl(w.q, kc, vc, E, bits, ctl, T, H, D, kv.n_ctx, 1.0f / sqrtf((float)D), w.att, w.fa_ws, st));
+        const bool fa_tc = eb_fattn_tc_supported(T, D);
+        RC(eb_rope_kv_store_fused(w.pq, kq_, w.pk, kk_, w.pv, kv_, w.q, fa_tc ? w.q16 : nullptr, pos, kc, vc, ctl, D, H, T, m->freq_base, st));
+        if (fa_tc) RC(eb_fattn_tc(w.q16, kc, vc, E, kv.n_ctx, bits, ctl, 0, 0, T, H, 1.0f / sqrtf((float)D), w.att, w.fa_ws, st));
+        else RC(eb_flash_attn_ctl(w.q, kc, vc, E, bits, ctl, T, H, D, kv.n_ctx, 1.0f / sqrtf((float)D), w.att, w.fa_ws, st));
         ActQ ao = eb_actq_carve(w.actq, grid_of(t[EB_L_WO]), E, T);
         RC(eb_quantize_act(w.att, ao, st));
         int ko_;

@@ -22,6 +22,7 @@ struct Workspace {
     void *actq2;                                  // second activation-grid buffer
     void *actq; size_t actq_bytes; void *fa_ws; size_t fa_bytes; size_t partial_bytes;
     int32_t *tokens, *pos; uint32_t *bits; FwdCtl *ctl;
+    __half *q16;                                  // f16 copy of the rotated queries (TMA source of the tcgen05 attention)
 };
 
 struct eb_session {
@@ -57,7 +58,13 @@ int eb_rope_kv_store_ctl(float *q, const float *k, const float *v, const int32_t
 int eb_flash_attn_ctl(const float *q, const void *k, const void *v, int64_t kv_stride, const uint32_t *tree_bits, const FwdCtl *ctl,
                       int T, int H, int D, int n_ctx, float scale, float *out, void *ws, cudaStream_t st);
 int eb_resid_norm_quant(float *x, const float *part, int ks, const float *w, float eps, int n, int T, const ActQ &aq, float *feat, cudaStream_t st);
-int eb_rope_kv_store_fused(const float *qp, int qks, const float *kp, int kks, const float *vp, int vks, float *q, const int32_t *pos, void *kc, void *vc,
+int eb_rope_kv_store_fused(const float *qp, int qks, const float *kp, int kks, const float *vp, int vks, float *q, void *q16, const int32_t *pos, void *kc, void *vc,
                            const FwdCtl *ctl, int D, int n_head, int T, float freq_base, cudaStream_t st);
+// fattn_tc.cu: tcgen05 tree attention
+int eb_fattn_tc_init(); int eb_fattn_tc_supported(int T, int D); size_t eb_fattn_tc_ws_size(int T, int H, int n_kv);
+int eb_fattn_tc(const __half *q16, const void *k, const void *v, int64_t kv_stride, int64_t n_cells, const uint32_t *tree_bits, const FwdCtl *ctl,
+                int n_prefix, int n_kv, int T, int H, float scale, float *out, void *ws, cudaStream_t st);
+int eb_fattn_tc_f32q(const float *q, const void *k, const void *v, int64_t kv_stride, const uint32_t *tree_bits, int n_prefix, int n_kv,
+                     int T, int H, float scale, float *out, void *ws, cudaStream_t st);
 int eb_swiglu_quant(const float *gate, int gks, const float *up, int uks, int n, int T, const ActQ &aq, cudaStream_t st);
 int eb_mul_mat_impl(int type, const void *W, int64_t N, int64_t K, const float *x, int T, float *y, void *actq_ws, float *partial, cudaStream_t st);

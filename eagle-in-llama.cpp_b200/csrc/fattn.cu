@@ -226,6 +226,9 @@ __global__ void fattn_combine_kernel(const float *__restrict__ part_o, const flo
     *(float4 *)(out + ((int64_t)r * H + h) * FA_D + lane * 4) = make_float4(acc.x * inv, acc.y * inv, acc.z * inv, acc.w * inv);
 }
 
+void eb_fattn_combine(const float *part_o, const float *part_ml, float *out, int T, int H, int nsplit, cudaStream_t st) {
+    fattn_combine_kernel<<<(unsigned)cdiv((int64_t)T * H, 8), 256, 0, st>>>(part_o, part_ml, out, T, H, nsplit);
+}
 static int fa_pick_split(int H, int n_tiles) {
     int ns = (int)cdiv(2 * eb_sm_count(), H);
     if (ns > n_tiles) ns = n_tiles;

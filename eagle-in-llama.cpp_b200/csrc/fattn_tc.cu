@@ -1,0 +1,302 @@
+// fattn_tc.cu — tree-masked flash attention on the 5th-gen tensor cores (tcgen05, accumulators in TMEM, K/V tiles by TMA).
+// Same contract as fattn.cu (replaces flash_attn_ext_f16, R/ggml/src/ggml-cuda/fattn-mma-f16.cuh:806; CPU
+// ggml_compute_forward_flash_attn_ext_f16, R/ggml/src/ggml-cpu/ggml-cpu.c:10999-11212) for the compact tree mask.
+//
+// One CTA = one head x one KV split; all T <= 128 query rows ride in the M = 128 dimension of the MMA, so every K/V byte
+// is read from HBM exactly once per layer.  Per 128-cell tile:
+//     S = Q K^T    tcgen05.mma SS   (Q, K K-major 128B-swizzled smem)           -> TMEM S[b]  (128 lanes x 128 f32 columns)
+//     softmax      one thread per query row: tcgen05.ld S row -> registers, mask, running max (rescale of O only when the
+//                  max grows by more than 2^8), P = exp2 -> f16 pairs -> tcgen05.st over the first 64 columns of S[b]
+//     O += P V     tcgen05.mma TS   (P from TMEM, V MN-major smem: the cache layout [cell][dim] needs no transpose)
+// S is double-buffered so QK^T of tile i+2 and PV of tile i run on the tensor pipe while the softmax warps work on tile i+1.
+// Roles: warp 0 TMA producer (3-stage K ring + 3-stage V ring, 32 KB tiles), warp 1 MMA issuer, warp 2 TMEM allocator,
+// warps 4-7 softmax / correction / epilogue (warp 4+q owns TMEM lanes 32q..32q+31 = query rows).
+#include "common.cuh"
+#include "spec.cuh"
+#include "tc.cuh"
+
+namespace {
+using namespace tc;
+
+constexpr int FT_TILE = 128;
+constexpr int FT_STAGES = 3;
+constexpr uint32_t FT_BOX = 16384;                      // 128 rows x 64 f16
+constexpr uint32_t FT_OFF_Q = 0;                        // 2 boxes
+constexpr uint32_t FT_STAGE = 2 * FT_BOX;               // one K (or V) tile: dims 0-63 | dims 64-127
+constexpr uint32_t FT_OFF_K = 2 * FT_BOX;               // K ring and V ring are independent: K(i) is free once S(i) is done,
+constexpr uint32_t FT_OFF_V = FT_OFF_K + FT_STAGES * FT_STAGE;   // V(i) only after PV(i), so K runs further ahead
+constexpr uint32_t FT_OFF_BAR = FT_OFF_V + FT_STAGES * FT_STAGE;
+constexpr uint32_t FT_SMEM = FT_OFF_BAR + 256 + 1024;   // + alignment slack
+enum { FB_Q = 0, FB_K_FULL = 1, FB_K_EMPTY = 4, FB_V_FULL = 7, FB_V_EMPTY = 10, FB_S_FULL = 13, FB_P_READY = 15, FB_O_DONE = 17, FB_COUNT = 18 };
+constexpr uint32_t FT_COL_O = 256;                      // TMEM: S[0] 0..127, S[1] 128..255, O 256..383
+
+struct FtArgs {
+    const uint32_t *tree_bits; const FwdCtl *ctl;
+    int n_prefix, n_kv, n_ctx;
+    int T, H, nsplit;
+    float scale_log2;
+    float *out, *part_o, *part_ml;
+};
+
+__device__ __forceinline__ float ex2(float x) { float y; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
+__device__ __forceinline__ uint32_t pack_h2(float a, float b) { const __half2 h = __floats2half2_rn(a, b); return *(const uint32_t *)&h; }
+
+// visibility of the 32 cells [cb, cb+32) for one row: committed prefix = all visible, tree cell j = bit j of tb
+__device__ __forceinline__ uint32_t vis_word(int cb, int n_prefix, const uint32_t (&tb)[4]) {
+    const int lo = cb - n_prefix;
+    if (lo <= -32) return 0xffffffffu;
+    if (lo < 0) return ((1u << (-lo)) - 1u) | (tb[0] << (-lo));
+    const int w = lo >> 5, s = lo & 31;
+    const uint32_t a = w == 0 ? tb[0] : w == 1 ? tb[1] : w == 2 ? tb[2] : w == 3 ? tb[3] : 0u;
+    const uint32_t b = w == 0 ? tb[1] : w == 1 ? tb[2] : w == 2 ? tb[3] : 0u;
+    return __funnelshift_r(a, b, s);
+}
+
+__global__ void __launch_bounds__(256, 1)
+fattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK, const __grid_constant__ CUtensorMap tmV, FtArgs p) {
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t sbase = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    const uint32_t bars = sbase + FT_OFF_BAR, slot = bars + FB_COUNT * 8;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int h = blockIdx.x, split = blockIdx.y;
+    int n_prefix = p.n_prefix, n_kv = p.n_kv;
+    if (p.ctl) { n_prefix = p.ctl->n_prefix; n_kv = min(p.n_ctx, n_prefix + p.ctl->n_tree); }
+    const int n_tiles = (n_kv + FT_TILE - 1) / FT_TILE, tps = (n_tiles + p.nsplit - 1) / p.nsplit;
+    const int t0 = split * tps, n = max(0, min(n_tiles, t0 + tps) - t0);
+    const int nsw = (p.T + 31) >> 5;                                         // softmax warps with at least one live row
+
+    if (threadIdx.x == 0) {
+        mbar_init(bars + FB_Q * 8, 1);
+        for (int s = 0; s < FT_STAGES; s++) {
+            mbar_init(bars + (FB_K_FULL + s) * 8, 1); mbar_init(bars + (FB_K_EMPTY + s) * 8, 1);
+            mbar_init(bars + (FB_V_FULL + s) * 8, 1); mbar_init(bars + (FB_V_EMPTY + s) * 8, 1);
+        }
+        for (int b = 0; b < 2; b++) { mbar_init(bars + (FB_S_FULL + b) * 8, 1); mbar_init(bars + (FB_P_READY + b) * 8, nsw); }
+        mbar_init(bars + FB_O_DONE * 8, 1);
+        fence_barrier_init();
+        tma_prefetch_desc(&tmQ); tma_prefetch_desc(&tmK); tma_prefetch_desc(&tmV);
+    }
+    if (warp == 2) tmem_alloc(slot, 512);
+    fence_before();
+    __syncthreads();
+    fence_after();
+    uint32_t tmem;
+    asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem) : "r"(slot));
+
+    if (warp == 0) {
+        // ------------------------------------------------------------------ TMA producer
+        if (n > 0 && elect_one()) {
+            mbar_expect_tx(bars + FB_Q * 8, 2 * FT_BOX);
+            tma_load_2d(sbase + FT_OFF_Q, &tmQ, h * 128, 0, bars + FB_Q * 8);
+            tma_load_2d(sbase + FT_OFF_Q + FT_BOX, &tmQ, h * 128 + 64, 0, bars + FB_Q * 8);
+            for (int i = 0; i < n; i++) {
+                const int s = i % FT_STAGES, u = i / FT_STAGES;
+                const int cell0 = (t0 + i) * FT_TILE;
+                if (u > 0) mbar_wait(bars + (FB_K_EMPTY + s) * 8, (u - 1) & 1);
+                const uint32_t kf = bars + (FB_K_FULL + s) * 8, kd = sbase + FT_OFF_K + s * FT_STAGE;
+                mbar_expect_tx(kf, FT_STAGE);
+                tma_load_2d(kd, &tmK, h * 128, cell0, kf);
+                tma_load_2d(kd + FT_BOX, &tmK, h * 128 + 64, cell0, kf);
+                if (u > 0) mbar_wait(bars + (FB_V_EMPTY + s) * 8, (u - 1) & 1);
+                const uint32_t vf = bars + (FB_V_FULL + s) * 8, vd = sbase + FT_OFF_V + s * FT_STAGE;
+                mbar_expect_tx(vf, FT_STAGE);
+                tma_load_2d(vd, &tmV, h * 128, cell0, vf);
+                tma_load_2d(vd + FT_BOX, &tmV, h * 128 + 64, cell0, vf);
+            }
+        }
+    } else if (warp == 1) {
+        // ------------------------------------------------------------------ MMA issuer (warp-uniform loop, one elected lane issues)
+        const uint32_t id_s = idesc_f16_m128(128), id_o = id_s | TC_IDESC_B_MN;
+        const uint64_t q_lo = smem_desc_sw128(sbase + FT_OFF_Q), q_hi = smem_desc_sw128(sbase + FT_OFF_Q + FT_BOX);
+        auto issue_s = [&](int i) {
+            const int s = i % FT_STAGES;
+            mbar_wait(bars + (FB_K_FULL + s) * 8, (i / FT_STAGES) & 1);
+            fence_after();
+            const uint32_t kb = sbase + FT_OFF_K + s * FT_STAGE;
+            if (elect_one()) {
+                mma_f16_ss_x8(tmem + (i & 1) * 128, q_lo, q_hi, smem_desc_sw128(kb), smem_desc_sw128(kb + FT_BOX), id_s, 0);
+                mma_commit(bars + (FB_K_EMPTY + s) * 8);
+                mma_commit(bars + (FB_S_FULL + (i & 1)) * 8);
+            }
+            __syncwarp();
+        };
+        if (n > 0) {
+            mbar_wait(bars + FB_Q * 8, 0);
+            issue_s(0);
+            if (n > 1) issue_s(1);
+            for (int i = 0; i < n; i++) {
+                const int b = i & 1, s = i % FT_STAGES;
+                mbar_wait(bars + (FB_V_FULL + s) * 8, (i / FT_STAGES) & 1);
+                mbar_wait(bars + (FB_P_READY + b) * 8, (i >> 1) & 1);
+                fence_after();
+                const uint32_t vb = sbase + FT_OFF_V + s * FT_STAGE;
+                if (elect_one()) {
+                    mma_f16_ts_x8_rows(tmem + FT_COL_O, tmem + b * 128, smem_desc_sw128_mn(vb, FT_BOX), id_o, i > 0);
+                    mma_commit(bars + (FB_V_EMPTY + s) * 8);
+                    mma_commit(bars + FB_O_DONE * 8);
+                }
+                __syncwarp();
+                if (i + 2 < n) issue_s(i + 2);       // overwrites S[b] = P(i): tcgen05.mma of one thread execute in issue order
+            }
+        }
+    } else if (warp >= 4 && (warp - 4) * 32 < p.T) {
+        // ------------------------------------------------------------------ softmax / correction / epilogue: one thread per query row
+        const int q = warp - 4, row = q * 32 + lane;
+        const bool live = row < p.T;
+        const uint32_t lane_base = tmem + ((uint32_t)(q * 32) << 16);
+        uint32_t tb[4] = {0, 0, 0, 0};
+        if (live) { const uint4 w = *(const uint4 *)(p.tree_bits + row * 4); tb[0] = w.x; tb[1] = w.y; tb[2] = w.z; tb[3] = w.w; }
+        const float c = p.scale_log2;
+        float m = -INFINITY, l = 0.f;                                       // m in raw score units (before the scale)
+        for (int i = 0; i < n; i++) {
+            const int b = i & 1;
+            mbar_wait(bars + (FB_S_FULL + b) * 8, (i >> 1) & 1);
+            fence_after();
+            const uint32_t ts = lane_base + b * 128;
+            uint32_t sr[4][32];
+            tmem_ld32(ts, sr[0]); tmem_ld32(ts + 32, sr[1]); tmem_ld32(ts + 64, sr[2]); tmem_ld32(ts + 96, sr[3]);
+            wait_ld();
+            const int cb0 = (t0 + i) * FT_TILE;
+            if (cb0 + FT_TILE > n_prefix) {                                  // tile touches the tree cells (or the cache tail)
+#pragma unroll
+                for (int ch = 0; ch < 4; ch++) {
+                    const uint32_t vw = vis_word(cb0 + ch * 32, n_prefix, tb);
+#pragma unroll
+                    for (int k = 0; k < 32; k++) if (!((vw >> k) & 1u)) sr[ch][k] = 0xff800000u;   // -inf
+                }
+            }
+            float tm = -INFINITY;
+#pragma unroll
+            for (int ch = 0; ch < 4; ch++)
+#pragma unroll
+                for (int k = 0; k < 32; k++) tm = fmaxf(tm, __uint_as_float(sr[ch][k]));
+            // running max: O is rescaled only when the max moves by more than 2^8 (P stays within f16 range, the row sum is f32)
+            const bool grow = m != -INFINITY && (tm - m) * c > 8.f;
+            if (i > 0 && __any_sync(0xffffffffu, grow)) {
+                mbar_wait(bars + FB_O_DONE * 8, (i - 1) & 1);
+                fence_after();
+                const float mn = fmaxf(m, tm);
+                const float f = m == -INFINITY ? 1.f : ex2((m - mn) * c);
+#pragma unroll
+                for (int ch = 0; ch < 4; ch++) {
+                    uint32_t o[32];
+                    tmem_ld32(lane_base + FT_COL_O + ch * 32, o);
+                    wait_ld();
+#pragma unroll
+                    for (int k = 0; k < 32; k++) o[k] = __float_as_uint(__uint_as_float(o[k]) * f);
+                    tmem_st32(lane_base + FT_COL_O + ch * 32, o);
+                }
+                l *= f; m = mn;
+            } else if (m == -INFINITY) {
+                m = tm;
+            }
+            const float base = m == -INFINITY ? 0.f : m * c;
+            float rs = 0.f;
+            uint32_t pk[2][32];
+#pragma unroll
+            for (int ch = 0; ch < 4; ch++)
+#pragma unroll
+                for (int k = 0; k < 32; k += 2) {
+                    const float p0 = ex2(fmaf(__uint_as_float(sr[ch][k]), c, -base)), p1 = ex2(fmaf(__uint_as_float(sr[ch][k + 1]), c, -base));
+                    rs += p0 + p1;
+                    pk[ch >> 1][(ch & 1) * 16 + (k >> 1)] = pack_h2(p0, p1);
+                }
+            l += rs;
+            tmem_st32(ts, pk[0]); tmem_st32(ts + 32, pk[1]);
+            wait_st();
+            fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bars + (FB_P_READY + b) * 8);
+        }
+        // epilogue: O / l -> output (or the split's partial + (max, sum) in the log2 domain)
+        float *dst = nullptr;
+        if (live) {
+            if (p.nsplit == 1) dst = p.out + ((int64_t)row * p.H + h) * 128;
+            else {
+                const int64_t pb = ((int64_t)h * p.nsplit + split) * p.T + row;
+                dst = p.part_o + pb * 128;
+                p.part_ml[pb * 2] = m == -INFINITY ? -INFINITY : m * c; p.part_ml[pb * 2 + 1] = l;
+            }
+        }
+        if (n > 0) { mbar_wait(bars + FB_O_DONE * 8, (n - 1) & 1); fence_after(); }
+        const float inv = l > 0.f ? 1.f / l : 0.f;
+#pragma unroll
+        for (int ch = 0; ch < 4; ch++) {
+            uint32_t o[32];
+            if (n > 0) { tmem_ld32(lane_base + FT_COL_O + ch * 32, o); wait_ld(); }
+#pragma unroll
+            for (int k = 0; k < 32; k += 4) {
+                float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (n > 0) v = make_float4(__uint_as_float(o[k]) * inv, __uint_as_float(o[k + 1]) * inv, __uint_as_float(o[k + 2]) * inv, __uint_as_float(o[k + 3]) * inv);
+                if (live) *(float4 *)(dst + ch * 32 + k) = v;
+            }
+        }
+    }
+    fence_before();
+    __syncthreads();
+    if (warp == 2) tmem_dealloc(tmem, 512);
+}
+
+__global__ void q_to_f16_kernel(const float *__restrict__ q, __half *__restrict__ q16, int64_t n) {
+    const int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+    if (i >= n) return;
+    const float4 v = *(const float4 *)(q + i);
+    const __half2 a = __floats2half2_rn(v.x, v.y), b = __floats2half2_rn(v.z, v.w);
+    *(uint2 *)(q16 + i) = make_uint2(*(const uint32_t *)&a, *(const uint32_t *)&b);
+}
+
+}  // namespace
+
+// number of KV splits: one CTA per SM at most (the CTA owns the whole shared memory)
+int eb_fattn_tc_nsplit(int H, int n_tiles) {
+    int ns = std::max(1, eb_sm_count() / H);
+    if (ns > n_tiles) ns = std::max(1, n_tiles);
+    return ns;
+}
+int eb_fattn_tc_supported(int T, int D) {
+    static const int off = getenv("EB_NO_TC_FA") ? 1 : 0;
+    return !off && eb_tc_ready() && D == 128 && T >= 1 && T <= 128;
+}
+size_t eb_fattn_tc_ws_size(int T, int H, int n_kv) {
+    const int ns = eb_fattn_tc_nsplit(H, (int)cdiv(n_kv, FT_TILE));
+    return (size_t)H * ns * T * (128 + 2) * 4 + (size_t)T * H * 128 * 2 + 512;
+}
+void eb_fattn_combine(const float *part_o, const float *part_ml, float *out, int T, int H, int nsplit, cudaStream_t st);
+
+// q16: f16 copy of the (rotated) queries [T][H*128]; k, v: f16 cells with kv_stride elements between cells.
+// ctl != null: lengths are read on the device (engine); otherwise n_prefix / n_kv are used.
+int eb_fattn_tc(const __half *q16, const void *k, const void *v, int64_t kv_stride, int64_t n_cells, const uint32_t *tree_bits, const FwdCtl *ctl,
+                int n_prefix, int n_kv, int T, int H, float scale, float *out, void *ws, cudaStream_t st) {
+    FtArgs p;
+    p.tree_bits = tree_bits; p.ctl = ctl; p.n_prefix = n_prefix; p.n_kv = n_kv; p.n_ctx = (int)n_cells;
+    p.T = T; p.H = H; p.scale_log2 = scale * 1.44269504f;
+    const int n_tiles_max = (int)cdiv(n_cells, FT_TILE);     // the split count depends on the buffer size only (workspace bound)
+    p.nsplit = eb_fattn_tc_nsplit(H, n_tiles_max);
+    p.out = out; p.part_o = (float *)ws; p.part_ml = p.part_o + (size_t)H * p.nsplit * T * 128;
+    if (p.nsplit > 1 && !ws) return eb_set_err(EB_ERR_ARG, "flash_attn: workspace required");
+    CUtensorMap tmQ, tmK, tmV;
+    int rc;
+    if ((rc = eb_tc_map_2d_f16(&tmQ, q16, (uint64_t)H * 128, (uint64_t)T, (uint64_t)H * 128 * 2, 64, 128))) return rc;
+    if ((rc = eb_tc_map_2d_f16(&tmK, k, (uint64_t)H * 128, (uint64_t)n_cells, (uint64_t)kv_stride * 2, 64, 128))) return rc;
+    if ((rc = eb_tc_map_2d_f16(&tmV, v, (uint64_t)H * 128, (uint64_t)n_cells, (uint64_t)kv_stride * 2, 64, 128))) return rc;
+    fattn_tc_kernel<<<dim3(H, p.nsplit), 256, FT_SMEM, st>>>(tmQ, tmK, tmV, p);
+    EB_CHECK_LAUNCH();
+    if (p.nsplit > 1) eb_fattn_combine(p.part_o, p.part_ml, out, T, H, p.nsplit, st);
+    EB_CHECK_LAUNCH();
+    return EB_OK;
+}
+// operator-layer entry: f32 queries are rounded to f16 first (GGML_FP32_TO_FP16 of ggml-cpu.c:11115), staged behind the partials in ws
+int eb_fattn_tc_f32q(const float *q, const void *k, const void *v, int64_t kv_stride, const uint32_t *tree_bits, int n_prefix, int n_kv,
+                     int T, int H, float scale, float *out, void *ws, cudaStream_t st) {
+    if (!ws) return eb_set_err(EB_ERR_ARG, "flash_attn: workspace required");
+    const int ns = eb_fattn_tc_nsplit(H, (int)cdiv(n_kv, FT_TILE));
+    __half *q16 = (__half *)((uint8_t *)ws + (((size_t)H * ns * T * (128 + 2) * 4 + 255) & ~(size_t)255));
+    const int64_t nq = (int64_t)T * H * 128;
+    q_to_f16_kernel<<<(unsigned)cdiv(nq / 4, 256), 256, 0, st>>>(q, q16, nq);
+    EB_CHECK_LAUNCH();
+    return eb_fattn_tc(q16, k, v, kv_stride, n_kv, tree_bits, nullptr, n_prefix, std::min(n_kv, n_prefix + T), T, H, scale, out, ws, st);
+}
+int eb_fattn_tc_init() {
+    EB_CUDA(cudaFuncSetAttribute(fattn_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FT_SMEM));
+    return EB_OK;
+}

@@ -58,9 +58,48 @@ __global__ void __launch_bounds__(256) resid_norm_quant_kernel(float *__restrict
     if (aq.qs) quant_row_smem(row, aq, r, tid, 256);
 }
 
+// Q8_K-grid rows of n = 8 * blockDim.x <= 8192 values: thread t owns elements 8t..8t+7 in registers for the whole kernel
+// (warp w = quantisation block w), one __syncthreads for the row sum, no shared-memory staging of the row
+__global__ void __launch_bounds__(1024) resid_norm_quant_regs_kernel(float *__restrict__ x, Parts add, const float *__restrict__ w, float eps,
+                                                                    int n, ActQ a, float *__restrict__ feat) {
+    __shared__ double red[32];
+    const int r = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nw = blockDim.x >> 5;
+    const int64_t off = (int64_t)r * n + tid * 8;
+    float4 v0 = *(const float4 *)(x + off), v1 = *(const float4 *)(x + off + 4);
+    if (add.p) {
+        const float4 c0 = sum_parts(add, off), c1 = sum_parts(add, off + 4);
+        v0.x = __fadd_rn(c0.x, v0.x); v0.y = __fadd_rn(c0.y, v0.y); v0.z = __fadd_rn(c0.z, v0.z); v0.w = __fadd_rn(c0.w, v0.w);
+        v1.x = __fadd_rn(c1.x, v1.x); v1.y = __fadd_rn(c1.y, v1.y); v1.z = __fadd_rn(c1.z, v1.z); v1.w = __fadd_rn(c1.w, v1.w);
+        *(float4 *)(x + off) = v0; *(float4 *)(x + off + 4) = v1;
+    }
+    float4 g0 = make_float4(1.f, 1.f, 1.f, 1.f), g1 = g0;
+    if (w) { g0 = *(const float4 *)(w + tid * 8); g1 = *(const float4 *)(w + tid * 8 + 4); }
+    double acc = (double)(v0.x * v0.x); acc += (double)(v0.y * v0.y); acc += (double)(v0.z * v0.z); acc += (double)(v0.w * v0.w);
+    acc += (double)(v1.x * v1.x); acc += (double)(v1.y * v1.y); acc += (double)(v1.z * v1.z); acc += (double)(v1.w * v1.w);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    if (lane == 0) red[warp] = acc;
+    __syncthreads();
+    double s = 0;
+    for (int i = 0; i < nw; i++) s += red[i];
+    const float sc = 1.0f / sqrtf((float)(s / n) + eps);
+    float v[8] = {__fmul_rn(v0.x, sc), __fmul_rn(v0.y, sc), __fmul_rn(v0.z, sc), __fmul_rn(v0.w, sc),
+                  __fmul_rn(v1.x, sc), __fmul_rn(v1.y, sc), __fmul_rn(v1.z, sc), __fmul_rn(v1.w, sc)};
+    if (w) {
+        v[0] = __fmul_rn(v[0], g0.x); v[1] = __fmul_rn(v[1], g0.y); v[2] = __fmul_rn(v[2], g0.z); v[3] = __fmul_rn(v[3], g0.w);
+        v[4] = __fmul_rn(v[4], g1.x); v[5] = __fmul_rn(v[5], g1.y); v[6] = __fmul_rn(v[6], g1.z); v[7] = __fmul_rn(v[7], g1.w);
+    }
+    if (feat) { *(float4 *)(feat + off) = make_float4(v[0], v[1], v[2], v[3]); *(float4 *)(feat + off + 4) = make_float4(v[4], v[5], v[6], v[7]); }
+    if (a.qs) {
+        const int nb = n / 256;
+        quant_regs_q8K(v, a.qs + (int64_t)r * n + warp * 256, a.d + (int64_t)r * nb + warp, a.bsum + ((int64_t)r * nb + warp) * 16, lane,
+                       a.h16 ? a.h16 + (int64_t)r * n + warp * 256 : nullptr, (a.dT && r < EB_DT_PITCH) ? a.dT + (int64_t)warp * EB_DT_PITCH + r : nullptr);
+    }
+}
+
 // grid (T, heads/8): thread = (head-in-group, pair).  cos/sin are computed once per (token, pair)
 // by the first 64 threads with the reference's sequential theta recurrence and shared via smem.
-__global__ void __launch_bounds__(512) rope_kv_store_fused_kernel(Parts qp, Parts kp, Parts vp, float *__restrict__ q,
+__global__ void __launch_bounds__(512) rope_kv_store_fused_kernel(Parts qp, Parts kp, Parts vp, float *__restrict__ q, __half *__restrict__ q16,
                                                                  const int32_t *__restrict__ pos, __half *__restrict__ kc, __half *__restrict__ vc,
                                                                  const FwdCtl *__restrict__ ctl, int D, int n_head, float theta_scale) {
     __shared__ float cs[128], sn[128];
@@ -79,8 +118,13 @@ __global__ void __launch_bounds__(512) rope_kv_store_fused_kernel(Parts qp, Part
         const float c0 = cs[i], s0 = sn[i], c1 = cs[i + 1], s1 = sn[i + 1];
         const int64_t o = (int64_t)t * E + e;
         const float4 a = sum_parts(qp, o), b = sum_parts(kp, o), v = sum_parts(vp, o);
-        *(float4 *)(q + o) = make_float4(__fsub_rn(__fmul_rn(a.x, c0), __fmul_rn(a.y, s0)), __fadd_rn(__fmul_rn(a.x, s0), __fmul_rn(a.y, c0)),
-                                         __fsub_rn(__fmul_rn(a.z, c1), __fmul_rn(a.w, s1)), __fadd_rn(__fmul_rn(a.z, s1), __fmul_rn(a.w, c1)));
+        const float4 qr = make_float4(__fsub_rn(__fmul_rn(a.x, c0), __fmul_rn(a.y, s0)), __fadd_rn(__fmul_rn(a.x, s0), __fmul_rn(a.y, c0)),
+                                      __fsub_rn(__fmul_rn(a.z, c1), __fmul_rn(a.w, s1)), __fadd_rn(__fmul_rn(a.z, s1), __fmul_rn(a.w, c1)));
+        *(float4 *)(q + o) = qr;
+        if (q16) {                                          // the attention kernel's f16 queries (GGML_FP32_TO_FP16 of ggml-cpu.c:11115)
+            const __half2 q0 = __floats2half2_rn(qr.x, qr.y), q1 = __floats2half2_rn(qr.z, qr.w);
+            *(uint2 *)(q16 + o) = make_uint2(*(const uint32_t *)&q0, *(const uint32_t *)&q1);
+        }
         const __half2 k0 = __floats2half2_rn(__fsub_rn(__fmul_rn(b.x, c0), __fmul_rn(b.y, s0)), __fadd_rn(__fmul_rn(b.x, s0), __fmul_rn(b.y, c0)));
         const __half2 k1 = __floats2half2_rn(__fsub_rn(__fmul_rn(b.z, c1), __fmul_rn(b.w, s1)), __fadd_rn(__fmul_rn(b.z, s1), __fmul_rn(b.w, c1)));
         const __half2 v0 = __floats2half2_rn(v.x, v.y), v1 = __floats2half2_rn(v.z, v.w);
@@ -90,16 +134,27 @@ __global__ void __launch_bounds__(512) rope_kv_store_fused_kernel(Parts qp, Part
 }
 
 __device__ __forceinline__ float silu_ref(float x) { return x / (1.0f + expf(-x)); }   // ggml_silu_f32
-// one CTA per token row; row staged in smem (F floats) then quantised
-__global__ void __launch_bounds__(512) swiglu_quant_kernel(Parts gate, Parts up, int n, ActQ aq) {
-    extern __shared__ float row[];
-    const int r = blockIdx.x, tid = threadIdx.x;
-    for (int i = tid * 4; i < n; i += 2048) {
-        const float4 g = sum_parts(gate, (int64_t)r * n + i), u = sum_parts(up, (int64_t)r * n + i);
-        *(float4 *)(row + i) = make_float4(__fmul_rn(silu_ref(g.x), u.x), __fmul_rn(silu_ref(g.y), u.y), __fmul_rn(silu_ref(g.z), u.z), __fmul_rn(silu_ref(g.w), u.w));
+// one warp per quantisation block (256 values on the Q8_K grid, 4 x 32 on the Q8_0 grid): the blocks of a row are
+// independent, so the grid is (blocks, T) instead of one CTA per row — 65 x 43 warps for the 7B ffn instead of 65 CTAs
+__device__ __forceinline__ float4 swiglu4(const Parts &gate, const Parts &up, int64_t off) {
+    const float4 g = sum_parts(gate, off), u = sum_parts(up, off);
+    return make_float4(__fmul_rn(silu_ref(g.x), u.x), __fmul_rn(silu_ref(g.y), u.y), __fmul_rn(silu_ref(g.z), u.z), __fmul_rn(silu_ref(g.w), u.w));
+}
+__global__ void __launch_bounds__(256) swiglu_quant_kernel(Parts gate, Parts up, int n, ActQ a) {
+    const int r = blockIdx.y, lane = threadIdx.x & 31, b = blockIdx.x * 8 + (threadIdx.x >> 5);
+    const int64_t row0 = (int64_t)r * n;
+    if (a.kq) {
+        const int nb = n / 256;
+        if (b >= nb) return;
+        const float4 x = swiglu4(gate, up, row0 + b * 256 + lane * 8), y = swiglu4(gate, up, row0 + b * 256 + lane * 8 + 4);
+        const float v[8] = {x.x, x.y, x.z, x.w, y.x, y.y, y.z, y.w};
+        quant_regs_q8K(v, a.qs + row0 + b * 256, a.d + (int64_t)r * nb + b, a.bsum + ((int64_t)r * nb + b) * 16, lane,
+                       a.h16 ? a.h16 + row0 + b * 256 : nullptr, (a.dT && r < EB_DT_PITCH) ? a.dT + (int64_t)b * EB_DT_PITCH + r : nullptr);
+    } else {
+        const int ng = n / 128;
+        if (b >= ng) return;
+        quant_regs_q8_0x4(swiglu4(gate, up, row0 + b * 128 + lane * 4), a.qs + row0 + b * 128, a.d + (int64_t)r * (n / 32) + b * 4, lane);
     }
-    __syncthreads();
-    quant_row_smem(row, aq, r, tid, 512);
 }
 
 // plain row quantisation of an f32 [T][K] tensor that is already final (attention output)
@@ -107,32 +162,35 @@ int eb_resid_norm_quant(float *x, const float *part, int ks, const float *w, flo
     if (n % 4 || n > 16384) return eb_set_err(EB_ERR_ARG, "resid_norm_quant: n=%d", n);
     if (T == 0) return EB_OK;
     Parts p{part, ks, (int64_t)T * n};
-    resid_norm_quant_kernel<<<T, 256, (size_t)n * 4, st>>>(x, p, w, eps, n, aq, feat);
+    if (n % 256 == 0 && n <= 8192 && (!aq.qs || (aq.kq && aq.K == n)))
+        resid_norm_quant_regs_kernel<<<T, n / 8, 0, st>>>(x, p, w, eps, n, aq, feat);
+    else
+        resid_norm_quant_kernel<<<T, 256, (size_t)n * 4, st>>>(x, p, w, eps, n, aq, feat);
     EB_CHECK_LAUNCH();
     return EB_OK;
 }
-int eb_rope_kv_store_fused(const float *qp, int qks, const float *kp, int kks, const float *vp, int vks, float *q, const int32_t *pos, void *kc, void *vc,
+int eb_rope_kv_store_fused(const float *qp, int qks, const float *kp, int kks, const float *vp, int vks, float *q, void *q16, const int32_t *pos, void *kc, void *vc,
                            const FwdCtl *ctl, int D, int n_head, int T, float freq_base, cudaStream_t st) {
     if (T == 0) return EB_OK;
     if (D > 256 || D % 4) return eb_set_err(EB_ERR_ARG, "rope: D=%d", D);
     const int64_t plane = (int64_t)T * n_head * D;
     const int E = n_head * D;
     const int threads = 512, gy = (int)cdiv(E / 4, threads);
-    rope_kv_store_fused_kernel<<<dim3(T, gy), threads, 0, st>>>(Parts{qp, qks, plane}, Parts{kp, kks, plane}, Parts{vp, vks, plane}, q, pos,
+    rope_kv_store_fused_kernel<<<dim3(T, gy), threads, 0, st>>>(Parts{qp, qks, plane}, Parts{kp, kks, plane}, Parts{vp, vks, plane}, q, (__half *)q16, pos,
                                                                  (__half *)kc, (__half *)vc, ctl, D, n_head, powf(freq_base, -2.0f / D));
     EB_CHECK_LAUNCH();
     return EB_OK;
 }
 int eb_swiglu_quant(const float *gate, int gks, const float *up, int uks, int n, int T, const ActQ &aq, cudaStream_t st) {
     if (T == 0) return EB_OK;
-    if (n % 4) return eb_set_err(EB_ERR_ARG, "swiglu: n");
+    const int per = aq.kq ? 256 : 128;
+    if (n % per || aq.K != n) return eb_set_err(EB_ERR_ARG, "swiglu: n=%d", n);
     const int64_t plane = (int64_t)T * n;
-    swiglu_quant_kernel<<<T, 512, (size_t)n * 4, st>>>(Parts{gate, gks, plane}, Parts{up, uks, plane}, n, aq);
+    swiglu_quant_kernel<<<dim3((unsigned)cdiv(n / per, 8), T), 256, 0, st>>>(Parts{gate, gks, plane}, Parts{up, uks, plane}, n, aq);
     EB_CHECK_LAUNCH();
     return EB_OK;
 }
 int eb_fused_init() {
     EB_CUDA(cudaFuncSetAttribute(resid_norm_quant_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 65536));
-    EB_CUDA(cudaFuncSetAttribute(swiglu_quant_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 131072));
     return EB_OK;
 }

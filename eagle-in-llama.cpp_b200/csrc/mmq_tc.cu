@@ -383,6 +383,12 @@ int make_map_2d(CUtensorMap *m, CUtensorMapDataType dt, int esize, const void *b
 
 }  // namespace
 
+int eb_tc_map_2d_f16(CUtensorMap *m, const void *base, uint64_t d0, uint64_t d1, uint64_t stride1_bytes, uint32_t b0, uint32_t b1) {
+    if (!g_encode) return eb_set_err(EB_ERR_CUDA, "tensor maps unavailable");
+    return make_map_2d(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, base, d0, d1, stride1_bytes, b0, b1, CU_TENSOR_MAP_SWIZZLE_128B);
+}
+int eb_tc_ready() { return g_encode != nullptr; }
+
 int eb_mmq_tc_init() {
     if (!g_encode) {
         void *fn = nullptr; cudaDriverEntryPointQueryResult qres;

@@ -92,6 +92,44 @@ __device__ __forceinline__ void mma_f16_ts_x8(uint32_t d_tmem, uint32_t a_tmem, 
                  "tcgen05.mma.cta_group::1.kind::f16 [%0], [a7], b7, %4, q;\n\t}"
                  ::"r"(d_tmem), "r"(a_tmem), "l"(b_lo), "l"(b_hi), "r"(idesc), "r"(acc_first) : "memory");
 }
+// D[tmem] (+)= A[smem desc] * B[smem desc], eight K = 16 steps over two 64-element (128-byte) K-major boxes per operand:
+// step j uses a_lo/b_lo + 32j bytes (j < 4) and a_hi/b_hi + 32(j-4) bytes
+__device__ __forceinline__ void mma_f16_ss_x8(uint32_t d_tmem, uint64_t a_lo, uint64_t a_hi, uint64_t b_lo, uint64_t b_hi, uint32_t idesc, uint32_t acc_first) {
+    asm volatile("{\n\t.reg .pred p, q;\n\t.reg .b64 a1, a2, a3, a5, a6, a7, b1, b2, b3, b5, b6, b7;\n\t"
+                 "setp.ne.b32 p, %6, 0;\n\tsetp.eq.b32 q, 0, 0;\n\t"
+                 "add.u64 a1, %1, 2;\n\tadd.u64 a2, %1, 4;\n\tadd.u64 a3, %1, 6;\n\t"
+                 "add.u64 a5, %2, 2;\n\tadd.u64 a6, %2, 4;\n\tadd.u64 a7, %2, 6;\n\t"
+                 "add.u64 b1, %3, 2;\n\tadd.u64 b2, %3, 4;\n\tadd.u64 b3, %3, 6;\n\t"
+                 "add.u64 b5, %4, 2;\n\tadd.u64 b6, %4, 4;\n\tadd.u64 b7, %4, 6;\n\t"
+                 "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %3, %5, p;\n\t"
+                 "tcgen05.mma.cta_group::1.kind::f16 [%0], a1, b1, %5, q;\n\t"
+                 "tcgen05.mma.cta_group::1.kind::f16 [%0], a2, b2, %5, q;\n\t"
+                 "tcgen05.mma.cta_group::1.kind::f16 [%0], a3, b3, %5, q;\n\t"
+                 "tcgen05.mma.cta_group::1.kind::f16 [%0], %2, %4, %5, q;\n\t"
+                 "tcgen05.mma.cta_group::1.kind::f16 [%0], a5, b5, %5, q;\n\t"
+                 "tcgen05.mma.cta_group::1.kind::f16 [%0], a6, b6, %5, q;\n\t"
+                 "tcgen05.mma.cta_group::1.kind::f16 [%0], a7, b7, %5, q;\n\t}"
+                 ::"r"(d_tmem), "l"(a_lo), "l"(a_hi), "l"(b_lo), "l"(b_hi), "r"(idesc), "r"(acc_first) : "memory");
+}
+// D[tmem] (+)= A[tmem] * B[smem desc], eight K = 16 steps: A columns a_tmem + 8j, B descriptor b_desc + j * 128 (2048 bytes:
+// sixteen 128-byte rows of an MN-major operand)
+__device__ __forceinline__ void mma_f16_ts_x8_rows(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t idesc, uint32_t acc_first) {
+    asm volatile("{\n\t.reg .pred p, q;\n\t.reg .b32 a1, a2, a3, a4, a5, a6, a7;\n\t.reg .b64 b1, b2, b3, b4, b5, b6, b7;\n\t"
+                 "setp.ne.b32 p, %4, 0;\n\tsetp.eq.b32 q, 0, 0;\n\t"
+                 "add.u32 a1, %1, 8;\n\tadd.u32 a2, %1, 16;\n\tadd.u32 a3, %1, 24;\n\tadd.u32 a4, %1, 32;\n\t"
+                 "add.u32 a5, %1, 40;\n\tadd.u32 a6, %1, 48;\n\tadd.u32 a7, %1, 56;\n\t"
+                 "add.u64 b1, %2, 128;\n\tadd.u64 b2, %2, 256;\n\tadd.u64 b3, %2, 384;\n\tadd.u64 b4, %2, 512;\n\t"
+                 "add.u64 b5, %2, 640;\n\tadd.u64 b6, %2, 768;\n\tadd.u64 b7, %2, 896;\n\t"
+                 "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t"
+                 "tcgen05.mma.cta_group::1.kind::f16 [%0], [a1], b1, %3, q;\n\t"
+                 "tcgen05.mma.cta_group::1.kind::f16 [%0], [a2], b2, %3, q;\n\t"
+                 "tcgen05.mma.cta_group::1.kind::f16 [%0], [a3], b3, %3, q;\n\t"
+                 "tcgen05.mma.cta_group::1.kind::f16 [%0], [a4], b4, %3, q;\n\t"
+                 "tcgen05.mma.cta_group::1.kind::f16 [%0], [a5], b5, %3, q;\n\t"
+                 "tcgen05.mma.cta_group::1.kind::f16 [%0], [a6], b6, %3, q;\n\t"
+                 "tcgen05.mma.cta_group::1.kind::f16 [%0], [a7], b7, %3, q;\n\t}"
+                 ::"r"(d_tmem), "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(acc_first) : "memory");
+}
 template <int N> __device__ __forceinline__ void setmaxnreg_inc() { asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(N)); }
 template <int N> __device__ __forceinline__ void setmaxnreg_dec() { asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(N)); }
 __device__ __forceinline__ bool elect_one() {
@@ -114,6 +152,18 @@ __device__ __forceinline__ uint64_t smem_desc_sw128(uint32_t saddr) {
     d |= (uint64_t)2 << 61;                           // SWIZZLE_128B
     return d;
 }
+// MN-major, 128-byte swizzled smem operand: 64 MN elements contiguous per 128-byte row, 8 K rows per 1024-byte atom,
+// the next 64 MN elements lbo_bytes away (canonical layout ((8,n),(8,k)):((1,LBO),(8,SBO)) in 16-byte units)
+__device__ __forceinline__ uint64_t smem_desc_sw128_mn(uint32_t saddr, uint32_t lbo_bytes) {
+    uint64_t d = 0;
+    d |= (uint64_t)((saddr & 0x3FFFF) >> 4);
+    d |= (uint64_t)(lbo_bytes >> 4) << 16;
+    d |= (uint64_t)(1024 >> 4) << 32;
+    d |= (uint64_t)1 << 46;
+    d |= (uint64_t)2 << 61;
+    return d;
+}
+#define TC_IDESC_B_MN (1u << 16)     // instruction-descriptor bit: B operand is MN-major
 // instruction descriptor: f16 x f16 -> f32, both K-major, M = 128
 __host__ __device__ __forceinline__ uint32_t idesc_f16_m128(int n) {
     return (1u << 4) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
@@ -152,3 +202,8 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
 }
 
 }  // namespace tc
+
+// host: 2-D f16 tensor map (defined in mmq_tc.cu next to the driver entry point); swizzle = 128 B
+int eb_tc_map_2d_f16(CUtensorMap *m, const void *base, uint64_t d0, uint64_t d1, uint64_t stride1_bytes, uint32_t b0, uint32_t b1);
+int eb_tc_ready();
+

@@ -132,7 +132,9 @@ def test_flash_attn_golden_both_mask_forms(eb):
     mask = np.full((Tp, n_kv), -np.inf, np.float16); mask[:T][vis.astype(bool)] = 0
     got2 = eb.flash_attn_ext(OPS["fa_q"], OPS["fa_k"], OPS["fa_v"], 1 / np.sqrt(128), mask_f16=mask)
     assert nmse(got2, OPS["fa_out"]) < 5e-4
-    assert np.abs(got - got2).max() < 1e-6               # the two mask forms are the same computation
+    # compact form = tcgen05 kernel (P rounded to f16 once, like the reference's CUDA kernel); f16-mask form = mma.sync
+    # kernel (P carried as f16 hi + lo): same computation up to the f16 rounding of P
+    assert np.abs(got - got2).max() < 5e-4
 
 
 @pytest.mark.parametrize("T,n_past,H", [(1, 0, 2), (1, 513, 4), (8, 100, 4), (16, 1000, 3), (27, 512, 2), (65, 4031, 2), (128, 300, 1), (65, 61, 32)])
