@@ -39,12 +39,14 @@ extern "C" eb_model *eb_model_create(int E, int H, int F, int V, int L, float ep
     eb_model *m = new eb_model();
     m->E = E; m->H = H; m->F = F; m->V = V; m->L = L; m->eps = eps; m->freq_base = freq_base; m->is_eagle = is_eagle;
     m->layers.assign(L, std::vector<DTensor>(EB_L_COUNT));
+    m->fuse.assign(L, LayerFuse());
     return m;
 }
 extern "C" void eb_model_free(eb_model *m) {
     if (!m) return;
     for (auto &t : m->g) if (t.owned) cudaFree(t.data);
     for (auto &l : m->layers) for (auto &t : l) if (t.owned) cudaFree(t.data);
+    for (void *b : m->fused_bufs) cudaFree(b);
     delete m;
 }
 static int alloc_tensor(eb_model *m, int layer, int which, int type, DTensor **out) {
@@ -55,6 +57,7 @@ static int alloc_tensor(eb_model *m, int layer, int which, int type, DTensor **o
     const size_t bytes = eb_row_size(type, cols) * rows;
     if (bytes == 0) return eb_set_err(EB_ERR_UNSUPPORTED, "tensor type %d", type);
     if (t->owned) cudaFree(t->data);
+    if (layer >= 0) { m->fuse[layer] = LayerFuse(); m->finalized = false; }   // views of a fused buffer stay valid, the fusion does not
     *t = DTensor();
     EB_CUDA(cudaMalloc(&t->data, bytes + 256));
     t->type = type; t->rows = rows; t->cols = cols; t->bytes = bytes; t->owned = true;
@@ -114,6 +117,47 @@ extern "C" size_t eb_model_weight_bytes(const eb_model *m) {
     return b;
 }
 
+// Re-home wq|wk(|wv) and gate|up of every layer into one allocation each when they are all Q4_K (verbatim GGUF blocks,
+// row-major): the slots become views, get_tensor keeps working, the forward launches one GEMM per group.
+static int fuse_group(eb_model *m, std::vector<DTensor> &t, const int *which, int n) {
+    size_t total = 0;
+    for (int i = 0; i < n; i++) total += t[which[i]].bytes;
+    uint8_t *buf; EB_CUDA(cudaMalloc((void **)&buf, total + 256));
+    size_t off = 0;
+    for (int i = 0; i < n; i++) {
+        DTensor &x = t[which[i]];
+        EB_CUDA(cudaMemcpy(buf + off, x.data, x.bytes, cudaMemcpyDeviceToDevice));
+        if (x.owned) cudaFree(x.data);
+        x.data = buf + off; x.owned = false; off += x.bytes;
+    }
+    m->fused_bufs.push_back(buf);
+    return EB_OK;
+}
+static int model_finalize(eb_model *m) {
+    if (m->finalized) return EB_OK;
+    static const int no_fuse = getenv("EB_NO_FUSE") ? 1 : 0;
+    for (int l = 0; l < m->L && !no_fuse; l++) {
+        std::vector<DTensor> &t = m->layers[l];
+        LayerFuse &f = m->fuse[l];
+        auto q4k = [&](int w) { return t[w].data && t[w].type == EB_Q4_K; };
+        auto adjacent = [&](int a, int b) { return (uint8_t *)t[a].data + t[a].bytes == (uint8_t *)t[b].data; };
+        if (f.n_qkv == 1 && q4k(EB_L_WQ) && q4k(EB_L_WK)) {
+            const int grp[3] = {EB_L_WQ, EB_L_WK, EB_L_WV};
+            const int n = q4k(EB_L_WV) ? 3 : 2;
+            if (!(adjacent(EB_L_WQ, EB_L_WK) && (n == 2 || adjacent(EB_L_WK, EB_L_WV)))) { int rc = fuse_group(m, t, grp, n); if (rc) return rc; }
+            f.n_qkv = n;
+        }
+        if (!f.gate_up && q4k(EB_L_GATE) && q4k(EB_L_UP)) {
+            const int grp[2] = {EB_L_GATE, EB_L_UP};
+            if (!adjacent(EB_L_GATE, EB_L_UP)) { int rc = fuse_group(m, t, grp, 2); if (rc) return rc; }
+            f.gate_up = true;
+        }
+    }
+    EB_CUDA(cudaDeviceSynchronize());
+    m->finalized = true;
+    return EB_OK;
+}
+
 // ------------------------------------------------------------------ mul_mat dispatch
 // T <= 8: dequant-dot matvec (K1); T > 8: int8 tensor-core GEMM (K2) for K-quants, else K1 in
 // column chunks.  actq_ws holds the quantised activations.
@@ -145,14 +189,15 @@ static int ws_alloc(Workspace &w, const eb_model *m, int Tmax, int n_ctx) {
     EB_CUDA(fa(&w.x, T * E)); EB_CUDA(fa(&w.cur, T * E)); EB_CUDA(fa(&w.q, T * E)); EB_CUDA(fa(&w.k, T * E)); EB_CUDA(fa(&w.v, T * E));
     EB_CUDA(fa(&w.att, T * E)); EB_CUDA(fa(&w.gate, T * F)); EB_CUDA(fa(&w.up, T * F)); EB_CUDA(fa(&w.cat, T * 2 * E));
     EB_CUDA(fa(&w.hidden, T * E)); EB_CUDA(fa(&w.feat, T * E)); EB_CUDA(fa(&w.logits, T * V));
-    EB_CUDA(fa(&w.pq, 8 * T * E)); EB_CUDA(fa(&w.pk, 8 * T * E)); EB_CUDA(fa(&w.pv, 8 * T * E)); EB_CUDA(fa(&w.po, 8 * T * E));
-    EB_CUDA(fa(&w.pgate, 8 * T * F)); EB_CUDA(fa(&w.pup, 8 * T * F));
+    EB_CUDA(fa(&w.pq, 8 * T * std::max(3 * E, F))); EB_CUDA(fa(&w.pk, 8 * T * E)); EB_CUDA(fa(&w.pv, 8 * T * E)); EB_CUDA(fa(&w.po, 8 * T * E));
+    EB_CUDA(fa(&w.pgate, 8 * T * 2 * F)); EB_CUDA(fa(&w.pup, 8 * T * F));
     const size_t Kmax = std::max<size_t>(2 * E, F), Nmax = std::max<size_t>(std::max<size_t>(F, V), E);
     w.actq_bytes = 2 * eb_actq_bytes(1, Kmax, Tmax) + 1024;   // generous: either grid
     EB_CUDA(cudaMalloc(&w.actq, w.actq_bytes)); EB_CUDA(cudaMalloc(&w.actq2, w.actq_bytes));
     w.partial_bytes = (size_t)8 * T * Nmax * 4;
     EB_CUDA(cudaMalloc((void **)&w.partial, w.partial_bytes));
     w.fa_bytes = std::max(eb_flash_attn_ws_size_impl(Tmax, m->H, m->E / m->H, n_ctx), eb_fattn_tc_ws_size(Tmax, m->H, n_ctx));
+    EB_CUDA(fa(&w.rope_tab, T * 256));
     EB_CUDA(cudaMalloc((void **)&w.q16, T * E * 2)); EB_CUDA(cudaMemset(w.q16, 0, T * E * 2));
     EB_CUDA(cudaMalloc(&w.fa_ws, w.fa_bytes));
     EB_CUDA(cudaMalloc((void **)&w.tokens, T * 4)); EB_CUDA(cudaMalloc((void **)&w.pos, T * 4));
@@ -161,7 +206,7 @@ static int ws_alloc(Workspace &w, const eb_model *m, int Tmax, int n_ctx) {
 }
 static void ws_free(Workspace &w) {
     for (void *p : {(void *)w.x, (void *)w.cur, (void *)w.q, (void *)w.k, (void *)w.v, (void *)w.att, (void *)w.gate, (void *)w.up, (void *)w.cat,
-                    (void *)w.hidden, (void *)w.feat, (void *)w.logits, (void *)w.partial, w.actq, w.actq2, (void *)w.pq, (void *)w.pk, (void *)w.pv, (void *)w.po, (void *)w.pgate, (void *)w.pup, w.fa_ws, (void *)w.tokens, (void *)w.pos, (void *)w.bits, (void *)w.ctl, (void *)w.q16})
+                    (void *)w.hidden, (void *)w.feat, (void *)w.logits, (void *)w.partial, w.actq, w.actq2, (void *)w.pq, (void *)w.pk, (void *)w.pv, (void *)w.po, (void *)w.pgate, (void *)w.pup, w.fa_ws, (void *)w.tokens, (void *)w.pos, (void *)w.bits, (void *)w.ctl, (void *)w.q16, (void *)w.rope_tab})
         cudaFree(p);
 }
 static int kv_alloc(KVCache &kv, const eb_model *m, int n_ctx) {
@@ -239,6 +284,7 @@ static int forward_dev(const eb_model *m, KVCache &kv, Workspace &w, const int32
         RC(eb_mul_mat_impl(fc.type, fc.data, E, 2 * E, w.cat, T, w.cur, w.actq, w.partial, st));
         RC(eb_bias_relu_impl(w.cur, (const float *)m->g[EB_T_FC_BIAS].data, w.x, TE, E, st));
     }
+    RC(eb_rope_table(pos, D, T, m->freq_base, w.rope_tab, st));
     const float *pend = nullptr; int pend_ks = 0;          // down-projection planes not yet added to x
     for (int l = 0; l < m->L; l++) {
         const std::vector<DTensor> &t = m->layers[l];
@@ -246,19 +292,25 @@ static int forward_dev(const eb_model *m, KVCache &kv, Workspace &w, const int32
         const int gq = grid_of(t[EB_L_WQ]);
         ActQ a = eb_actq_carve(w.actq, gq, E, T);
         RC(eb_resid_norm_quant(w.x, pend, pend_ks, (const float *)t[EB_L_ATTN_NORM].data, m->eps, E, T, a, nullptr, st));
-        int kq_, kk_, kv_;
-        RC(mm_parts(t[EB_L_WQ], a, w.pq, &kq_, st));
-        ActQ ak = a, av = a;
         if (grid_of(t[EB_L_WK]) != gq || grid_of(t[EB_L_WV]) != gq) return eb_set_err(EB_ERR_UNSUPPORTED, "layer %d: wq/wk/wv mix K-quant and 32-block formats", l);
-        RC(mm_parts(t[EB_L_WK], ak, w.pk, &kk_, st));
-        RC(mm_parts(t[EB_L_WV], av, w.pv, &kv_, st));
+        const LayerFuse &fu = m->fuse[l];
+        PlaneRef rq, rk, rv;
+        {
+            DTensor wqkv = t[EB_L_WQ]; wqkv.rows = (int64_t)fu.n_qkv * E;          // fused view: n_qkv matrices of E rows back to back
+            int ks_;
+            RC(mm_parts(wqkv, a, w.pq, &ks_, st));
+            rq = PlaneRef{w.pq, ks_, wqkv.rows};
+            if (fu.n_qkv >= 2) rk = PlaneRef{w.pq + E, ks_, wqkv.rows}; else { RC(mm_parts(t[EB_L_WK], a, w.pk, &ks_, st)); rk = PlaneRef{w.pk, ks_, E}; }
+            if (fu.n_qkv >= 3) rv = PlaneRef{w.pq + 2 * E, ks_, wqkv.rows}; else { RC(mm_parts(t[EB_L_WV], a, w.pv, &ks_, st)); rv = PlaneRef{w.pv, ks_, E}; }
+        }
         __half *kc = kv.k + (int64_t)l * kv.layer_stride, *vc = kv.v + (int64_t)l * kv.layer_stride;
         const bool fa_tc = eb_fattn_tc_supported(T, D);
-        RC(eb_rope_kv_store_fused(w.pq, kq_, w.pk, kk_, w.pv, kv_, w.q, fa_tc ? w.q16 : nullptr, pos, kc, vc, ctl, D, H, T, m->freq_base, st));
-        if (fa_tc) RC(eb_fattn_tc(w.q16, kc, vc, E, kv.n_ctx, bits, ctl, 0, 0, T, H, 1.0f / sqrtf((float)D), w.att, w.fa_ws, st));
-        else RC(eb_flash_attn_ctl(w.q, kc, vc, E, bits, ctl, T, H, D, kv.n_ctx, 1.0f / sqrtf((float)D), w.att, w.fa_ws, st));
+        RC(eb_rope_kv_store_fused(rq, rk, rv, w.q, fa_tc ? w.q16 : nullptr, w.rope_tab, kc, vc, ctl, D, H, T, st));
         ActQ ao = eb_actq_carve(w.actq, grid_of(t[EB_L_WO]), E, T);
-        RC(eb_quantize_act(w.att, ao, st));
+        int att_quantized = 0;
+        if (fa_tc) RC(eb_fattn_tc(w.q16, kc, vc, E, kv.n_ctx, bits, ctl, 0, 0, T, H, 1.0f / sqrtf((float)D), w.att, w.fa_ws, st, &ao, &att_quantized));
+        else RC(eb_flash_attn_ctl(w.q, kc, vc, E, bits, ctl, T, H, D, kv.n_ctx, 1.0f / sqrtf((float)D), w.att, w.fa_ws, st));
+        if (!att_quantized) RC(eb_quantize_act(w.att, ao, st));
         int ko_;
         RC(mm_parts(t[EB_L_WO], ao, w.po, &ko_, st));
         // ffn_inp = wo.att + x ; cur = rms_norm(ffn_inp) * ffn_norm -> grid of up/gate
@@ -266,11 +318,20 @@ static int forward_dev(const eb_model *m, KVCache &kv, Workspace &w, const int32
         if (grid_of(t[EB_L_GATE]) != gu) return eb_set_err(EB_ERR_UNSUPPORTED, "layer %d: ffn_up/ffn_gate mix formats", l);
         ActQ af = eb_actq_carve(w.actq, gu, E, T);
         RC(eb_resid_norm_quant(w.x, w.po, ko_, (const float *)t[EB_L_FFN_NORM].data, m->eps, E, T, af, nullptr, st));
-        int ku_, kg_;
-        RC(mm_parts(t[EB_L_UP], af, w.pup, &ku_, st));
-        RC(mm_parts(t[EB_L_GATE], af, w.pgate, &kg_, st));
+        PlaneRef rg, ru;
+        {
+            int ks_;
+            if (fu.gate_up) {
+                DTensor wgu = t[EB_L_GATE]; wgu.rows = 2 * (int64_t)F;
+                RC(mm_parts(wgu, af, w.pgate, &ks_, st));
+                rg = PlaneRef{w.pgate, ks_, 2 * (int64_t)F}; ru = PlaneRef{w.pgate + F, ks_, 2 * (int64_t)F};
+            } else {
+                RC(mm_parts(t[EB_L_UP], af, w.pup, &ks_, st)); ru = PlaneRef{w.pup, ks_, F};
+                RC(mm_parts(t[EB_L_GATE], af, w.pgate, &ks_, st)); rg = PlaneRef{w.pgate, ks_, F};
+            }
+        }
         ActQ ad = eb_actq_carve(w.actq2, grid_of(t[EB_L_DOWN]), F, T);
-        RC(eb_swiglu_quant(w.pgate, kg_, w.pup, ku_, F, T, ad, st));
+        RC(eb_swiglu_quant(rg, ru, F, T, ad, st));
         RC(mm_parts(t[EB_L_DOWN], ad, w.pq, &pend_ks, st));       // pq is free again: holds the down planes
         pend = w.pq;
     }
@@ -290,7 +351,7 @@ static int forward_dev(const eb_model *m, KVCache &kv, Workspace &w, const int32
     return EB_OK;
 }
 
-static int check_model(const eb_model *m) {
+static int check_model(eb_model *m) {
     for (int i = 0; i < EB_T_GLOBAL_COUNT; i++) {
         const bool need = (i == EB_T_TOK_EMBD || i == EB_T_OUTPUT) || (m->is_eagle && i == EB_T_FC) || (!m->is_eagle && i == EB_T_OUTPUT_NORM);
         if (need && !m->g[i].data) return eb_set_err(EB_ERR_ARG, "model: global tensor %d missing", i);
@@ -299,7 +360,7 @@ static int check_model(const eb_model *m) {
         const bool need = !(i == EB_L_ATTN_NORM && m->is_eagle);
         if (need && !m->layers[l][i].data) return eb_set_err(EB_ERR_ARG, "model: layer %d tensor %d missing", l, i);
     }
-    return EB_OK;
+    return model_finalize(m);
 }
 
 extern "C" int eb_session_n_past(const eb_session *s, int model) {

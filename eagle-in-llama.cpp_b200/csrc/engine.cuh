@@ -5,11 +5,15 @@
 #include "spec.cuh"
 
 struct DTensor { int type = -1; void *data = nullptr; int64_t rows = 0, cols = 0; size_t bytes = 0; bool owned = false; };
+// rows of wq|wk(|wv) and gate|up stored back to back (Q4_K keeps the GGUF row-major block layout, so a row-wise
+// concatenation is one bigger matrix): one GEMM launch instead of three / two
+struct LayerFuse { int n_qkv = 1; bool gate_up = false; };
 
 struct eb_model {
     int E, H, F, V, L, is_eagle; float eps, freq_base;
     DTensor g[EB_T_GLOBAL_COUNT];
     std::vector<std::vector<DTensor>> layers;
+    std::vector<LayerFuse> fuse; std::vector<void *> fused_bufs; bool finalized = false;
 };
 
 struct KVCache { __half *k = nullptr, *v = nullptr; int64_t layer_stride = 0; int L = 0, E = 0, n_ctx = 0; };
@@ -22,6 +26,7 @@ struct Workspace {
     void *actq2;                                  // second activation-grid buffer
     void *actq; size_t actq_bytes; void *fa_ws; size_t fa_bytes; size_t partial_bytes;
     int32_t *tokens, *pos; uint32_t *bits; FwdCtl *ctl;
+    float *rope_tab;                              // [T][D/2] (cos, sin)
     __half *q16;                                  // f16 copy of the rotated queries (TMA source of the tcgen05 attention)
 };
 
@@ -58,13 +63,15 @@ int eb_rope_kv_store_ctl(float *q, const float *k, const float *v, const int32_t
 int eb_flash_attn_ctl(const float *q, const void *k, const void *v, int64_t kv_stride, const uint32_t *tree_bits, const FwdCtl *ctl,
                       int T, int H, int D, int n_ctx, float scale, float *out, void *ws, cudaStream_t st);
 int eb_resid_norm_quant(float *x, const float *part, int ks, const float *w, float eps, int n, int T, const ActQ &aq, float *feat, cudaStream_t st);
-int eb_rope_kv_store_fused(const float *qp, int qks, const float *kp, int kks, const float *vp, int vks, float *q, void *q16, const int32_t *pos, void *kc, void *vc,
-                           const FwdCtl *ctl, int D, int n_head, int T, float freq_base, cudaStream_t st);
+struct PlaneRef { const float *p; int ks; int64_t ld; };   // split-K planes [ks][T][ld] of a (possibly fused) GEMM, first column of interest at p
+int eb_rope_table(const int32_t *pos, int D, int T, float freq_base, float *tab, cudaStream_t st);
+int eb_rope_kv_store_fused(PlaneRef qp, PlaneRef kp, PlaneRef vp, float *q, void *q16, const float *tab, void *kc, void *vc,
+                           const FwdCtl *ctl, int D, int n_head, int T, cudaStream_t st);
 // fattn_tc.cu: tcgen05 tree attention
 int eb_fattn_tc_init(); int eb_fattn_tc_supported(int T, int D); size_t eb_fattn_tc_ws_size(int T, int H, int n_kv);
 int eb_fattn_tc(const __half *q16, const void *k, const void *v, int64_t kv_stride, int64_t n_cells, const uint32_t *tree_bits, const FwdCtl *ctl,
-                int n_prefix, int n_kv, int T, int H, float scale, float *out, void *ws, cudaStream_t st);
+                int n_prefix, int n_kv, int T, int H, float scale, float *out, void *ws, cudaStream_t st, const ActQ *aq, int *quantized);
 int eb_fattn_tc_f32q(const float *q, const void *k, const void *v, int64_t kv_stride, const uint32_t *tree_bits, int n_prefix, int n_kv,
                      int T, int H, float scale, float *out, void *ws, cudaStream_t st);
-int eb_swiglu_quant(const float *gate, int gks, const float *up, int uks, int n, int T, const ActQ &aq, cudaStream_t st);
+int eb_swiglu_quant(PlaneRef gate, PlaneRef up, int n, int T, const ActQ &aq, cudaStream_t st);
 int eb_mul_mat_impl(int type, const void *W, int64_t N, int64_t K, const float *x, int T, float *y, void *actq_ws, float *partial, cudaStream_t st);

@@ -11,6 +11,7 @@
 // compact form (committed prefix + 128-bit ancestor set per row) kept in registers.
 #include "common.cuh"
 #include "spec.cuh"
+#include "quant_dev.cuh"
 
 #define FA_D 128
 #define FA_TILE 64
@@ -226,6 +227,35 @@ __global__ void fattn_combine_kernel(const float *__restrict__ part_o, const flo
     *(float4 *)(out + ((int64_t)r * H + h) * FA_D + lane * 4) = make_float4(acc.x * inv, acc.y * inv, acc.z * inv, acc.w * inv);
 }
 
+// merge the KV splits and quantise the result for the wo GEMM (Q8_K grid): one warp per (row, 256-value block = 2 heads),
+// lane = (head-in-pair, 8 dims); the f32 attention output never goes to memory
+__global__ void fattn_combine_quant_kernel(const float *__restrict__ part_o, const float *__restrict__ part_ml, int T, int H, int nsplit, ActQ a) {
+    const int w = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31, nb = H / 2;
+    if (w >= T * nb) return;
+    const int r = w / nb, b = w % nb, h = 2 * b + (lane >> 4), d0 = (lane & 15) * 8;
+    float M = -INFINITY;
+    for (int s = 0; s < nsplit; s++) M = fmaxf(M, part_ml[(((int64_t)h * nsplit + s) * T + r) * 2]);
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f}; float L = 0.f;
+    for (int s = 0; s < nsplit; s++) {
+        const int64_t pb = ((int64_t)h * nsplit + s) * T + r;
+        const float m = part_ml[pb * 2], l = part_ml[pb * 2 + 1];
+        if (l <= 0.f) continue;
+        const float wgt = l * exp2f(m - M);
+        const float4 x = *(const float4 *)(part_o + pb * FA_D + d0), y = *(const float4 *)(part_o + pb * FA_D + d0 + 4);
+        acc[0] += wgt * x.x; acc[1] += wgt * x.y; acc[2] += wgt * x.z; acc[3] += wgt * x.w;
+        acc[4] += wgt * y.x; acc[5] += wgt * y.y; acc[6] += wgt * y.z; acc[7] += wgt * y.w; L += wgt;
+    }
+    const float inv = L > 0.f ? 1.f / L : 0.f;
+    float v[8];
+#pragma unroll
+    for (int j = 0; j < 8; j++) v[j] = acc[j] * inv;
+    const int64_t K = (int64_t)H * FA_D;
+    quant_regs_q8K(v, a.qs + (int64_t)r * K + b * 256, a.d + (int64_t)r * nb + b, a.bsum + ((int64_t)r * nb + b) * 16, lane,
+                   a.h16 ? a.h16 + (int64_t)r * K + b * 256 : nullptr, (a.dT && r < EB_DT_PITCH) ? a.dT + (int64_t)b * EB_DT_PITCH + r : nullptr);
+}
+void eb_fattn_combine_quant(const float *part_o, const float *part_ml, int T, int H, int nsplit, const ActQ &a, cudaStream_t st) {
+    fattn_combine_quant_kernel<<<(unsigned)cdiv((int64_t)T * (H / 2), 8), 256, 0, st>>>(part_o, part_ml, T, H, nsplit, a);
+}
 void eb_fattn_combine(const float *part_o, const float *part_ml, float *out, int T, int H, int nsplit, cudaStream_t st) {
     fattn_combine_kernel<<<(unsigned)cdiv((int64_t)T * H, 8), 256, 0, st>>>(part_o, part_ml, out, T, H, nsplit);
 }

@@ -262,12 +262,14 @@ size_t eb_fattn_tc_ws_size(int T, int H, int n_kv) {
     return (size_t)H * ns * T * (128 + 2) * 4 + (size_t)T * H * 128 * 2 + 512;
 }
 void eb_fattn_combine(const float *part_o, const float *part_ml, float *out, int T, int H, int nsplit, cudaStream_t st);
+void eb_fattn_combine_quant(const float *part_o, const float *part_ml, int T, int H, int nsplit, const ActQ &a, cudaStream_t st);
 
 // q16: f16 copy of the (rotated) queries [T][H*128]; k, v: f16 cells with kv_stride elements between cells.
 // ctl != null: lengths are read on the device (engine); otherwise n_prefix / n_kv are used.
 int eb_fattn_tc(const __half *q16, const void *k, const void *v, int64_t kv_stride, int64_t n_cells, const uint32_t *tree_bits, const FwdCtl *ctl,
-                int n_prefix, int n_kv, int T, int H, float scale, float *out, void *ws, cudaStream_t st) {
+                int n_prefix, int n_kv, int T, int H, float scale, float *out, void *ws, cudaStream_t st, const ActQ *aq, int *quantized) {
     FtArgs p;
+    if (quantized) *quantized = 0;
     p.tree_bits = tree_bits; p.ctl = ctl; p.n_prefix = n_prefix; p.n_kv = n_kv; p.n_ctx = (int)n_cells;
     p.T = T; p.H = H; p.scale_log2 = scale * 1.44269504f;
     const int n_tiles_max = (int)cdiv(n_cells, FT_TILE);     // the split count depends on the buffer size only (workspace bound)
@@ -281,7 +283,11 @@ int eb_fattn_tc(const __half *q16, const void *k, const void *v, int64_t kv_stri
     if ((rc = eb_tc_map_2d_f16(&tmV, v, (uint64_t)H * 128, (uint64_t)n_cells, (uint64_t)kv_stride * 2, 64, 128))) return rc;
     fattn_tc_kernel<<<dim3(H, p.nsplit), 256, FT_SMEM, st>>>(tmQ, tmK, tmV, p);
     EB_CHECK_LAUNCH();
-    if (p.nsplit > 1) eb_fattn_combine(p.part_o, p.part_ml, out, T, H, p.nsplit, st);
+    if (p.nsplit > 1) {
+        // the caller's wo GEMM wants the Q8_K grid: merge the splits and quantise in one pass, skipping the f32 output
+        if (aq && aq->kq && aq->qs && H % 2 == 0 && aq->K == (int64_t)H * 128) { eb_fattn_combine_quant(p.part_o, p.part_ml, T, H, p.nsplit, *aq, st); if (quantized) *quantized = 1; }
+        else eb_fattn_combine(p.part_o, p.part_ml, out, T, H, p.nsplit, st);
+    }
     EB_CHECK_LAUNCH();
     return EB_OK;
 }
@@ -294,7 +300,7 @@ int eb_fattn_tc_f32q(const float *q, const void *k, const void *v, int64_t kv_st
     const int64_t nq = (int64_t)T * H * 128;
     q_to_f16_kernel<<<(unsigned)cdiv(nq / 4, 256), 256, 0, st>>>(q, q16, nq);
     EB_CHECK_LAUNCH();
-    return eb_fattn_tc(q16, k, v, kv_stride, n_kv, tree_bits, nullptr, n_prefix, std::min(n_kv, n_prefix + T), T, H, scale, out, ws, st);
+    return eb_fattn_tc(q16, k, v, kv_stride, n_kv, tree_bits, nullptr, n_prefix, std::min(n_kv, n_prefix + T), T, H, scale, out, ws, st, nullptr, nullptr);
 }
 int eb_fattn_tc_init() {
     EB_CUDA(cudaFuncSetAttribute(fattn_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FT_SMEM));

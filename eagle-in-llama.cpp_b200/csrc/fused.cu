@@ -9,8 +9,10 @@
 #include "common.cuh"
 #include "quant_dev.cuh"
 #include "spec.cuh"
+#include "engine.cuh"
 
-struct Parts { const float *p; int ks; int64_t plane; };   // plane = T*N elements between split planes
+struct Parts { const float *p; int ks; int64_t plane; int64_t ld; };   // plane = T*ld elements between split planes, ld = row pitch (a fused GEMM's N)
+static Parts parts_of(const PlaneRef &r, int T) { return Parts{r.p, r.ks, (int64_t)T * r.ld, r.ld}; }
 
 __device__ __forceinline__ float4 sum_parts(const Parts &s, int64_t off) {
     float4 a = *(const float4 *)(s.p + off);
@@ -97,27 +99,30 @@ __global__ void __launch_bounds__(1024) resid_norm_quant_regs_kernel(float *__re
     }
 }
 
-// grid (T, heads/8): thread = (head-in-group, pair).  cos/sin are computed once per (token, pair)
-// by the first 64 threads with the reference's sequential theta recurrence and shared via smem.
+// cos/sin of every (token, rotation pair), once per forward instead of once per layer: the reference's sequential theta
+// recurrence (theta *= theta_scale, R/ggml/src/ggml-cpu/ggml-cpu.c rope_yarn / ggml_rope_cache_init)
+__global__ void rope_table_kernel(const int32_t *__restrict__ pos, float theta_scale, int half, float2 *__restrict__ tab) {
+    const int t = blockIdx.x, i = threadIdx.x;
+    if (i >= half) return;
+    float theta = (float)pos[t];
+    for (int j = 0; j < i; j++) theta = __fmul_rn(theta, theta_scale);
+    tab[t * half + i] = make_float2(cosf(theta), sinf(theta));
+}
+// grid (T, E/2048): q, k, v = sums of the split-K planes of the (possibly fused) QKV GEMM; RoPE on q and k; K/V rows go
+// straight to their cache cells; q additionally as f16 for the tcgen05 attention
 __global__ void __launch_bounds__(512) rope_kv_store_fused_kernel(Parts qp, Parts kp, Parts vp, float *__restrict__ q, __half *__restrict__ q16,
-                                                                 const int32_t *__restrict__ pos, __half *__restrict__ kc, __half *__restrict__ vc,
-                                                                 const FwdCtl *__restrict__ ctl, int D, int n_head, float theta_scale) {
-    __shared__ float cs[128], sn[128];
+                                                                 const float2 *__restrict__ tab, __half *__restrict__ kc, __half *__restrict__ vc,
+                                                                 const FwdCtl *__restrict__ ctl, int D, int n_head) {
     const int t = blockIdx.x, tid = threadIdx.x, half = D / 2;
-    if (tid < half) {
-        float theta = (float)pos[t];
-        for (int j = 0; j < tid; j++) theta = __fmul_rn(theta, theta_scale);
-        cs[tid] = cosf(theta); sn[tid] = sinf(theta);
-    }
-    __syncthreads();
     const int64_t cell0 = ctl ? (int64_t)(ctl->n_prefix + ctl->node_base) * n_head * D : 0;
     const int E = n_head * D;
     // float4 = two rotation pairs
     for (int e = (blockIdx.y * blockDim.x + tid) * 4; e < E; e += gridDim.y * blockDim.x * 4) {
         const int i = (e % D) / 2;
-        const float c0 = cs[i], s0 = sn[i], c1 = cs[i + 1], s1 = sn[i + 1];
+        const float4 cs = *(const float4 *)(tab + t * half + i);     // (cos0, sin0, cos1, sin1)
+        const float c0 = cs.x, s0 = cs.y, c1 = cs.z, s1 = cs.w;
         const int64_t o = (int64_t)t * E + e;
-        const float4 a = sum_parts(qp, o), b = sum_parts(kp, o), v = sum_parts(vp, o);
+        const float4 a = sum_parts(qp, t * qp.ld + e), b = sum_parts(kp, t * kp.ld + e), v = sum_parts(vp, t * vp.ld + e);
         const float4 qr = make_float4(__fsub_rn(__fmul_rn(a.x, c0), __fmul_rn(a.y, s0)), __fadd_rn(__fmul_rn(a.x, s0), __fmul_rn(a.y, c0)),
                                       __fsub_rn(__fmul_rn(a.z, c1), __fmul_rn(a.w, s1)), __fadd_rn(__fmul_rn(a.z, s1), __fmul_rn(a.w, c1)));
         *(float4 *)(q + o) = qr;
@@ -136,8 +141,8 @@ __global__ void __launch_bounds__(512) rope_kv_store_fused_kernel(Parts qp, Part
 __device__ __forceinline__ float silu_ref(float x) { return x / (1.0f + expf(-x)); }   // ggml_silu_f32
 // one warp per quantisation block (256 values on the Q8_K grid, 4 x 32 on the Q8_0 grid): the blocks of a row are
 // independent, so the grid is (blocks, T) instead of one CTA per row — 65 x 43 warps for the 7B ffn instead of 65 CTAs
-__device__ __forceinline__ float4 swiglu4(const Parts &gate, const Parts &up, int64_t off) {
-    const float4 g = sum_parts(gate, off), u = sum_parts(up, off);
+__device__ __forceinline__ float4 swiglu4(const Parts &gate, const Parts &up, int r, int i) {
+    const float4 g = sum_parts(gate, r * gate.ld + i), u = sum_parts(up, r * up.ld + i);
     return make_float4(__fmul_rn(silu_ref(g.x), u.x), __fmul_rn(silu_ref(g.y), u.y), __fmul_rn(silu_ref(g.z), u.z), __fmul_rn(silu_ref(g.w), u.w));
 }
 __global__ void __launch_bounds__(256) swiglu_quant_kernel(Parts gate, Parts up, int n, ActQ a) {
@@ -146,14 +151,14 @@ __global__ void __launch_bounds__(256) swiglu_quant_kernel(Parts gate, Parts up,
     if (a.kq) {
         const int nb = n / 256;
         if (b >= nb) return;
-        const float4 x = swiglu4(gate, up, row0 + b * 256 + lane * 8), y = swiglu4(gate, up, row0 + b * 256 + lane * 8 + 4);
+        const float4 x = swiglu4(gate, up, r, b * 256 + lane * 8), y = swiglu4(gate, up, r, b * 256 + lane * 8 + 4);
         const float v[8] = {x.x, x.y, x.z, x.w, y.x, y.y, y.z, y.w};
         quant_regs_q8K(v, a.qs + row0 + b * 256, a.d + (int64_t)r * nb + b, a.bsum + ((int64_t)r * nb + b) * 16, lane,
                        a.h16 ? a.h16 + row0 + b * 256 : nullptr, (a.dT && r < EB_DT_PITCH) ? a.dT + (int64_t)b * EB_DT_PITCH + r : nullptr);
     } else {
         const int ng = n / 128;
         if (b >= ng) return;
-        quant_regs_q8_0x4(swiglu4(gate, up, row0 + b * 128 + lane * 4), a.qs + row0 + b * 128, a.d + (int64_t)r * (n / 32) + b * 4, lane);
+        quant_regs_q8_0x4(swiglu4(gate, up, r, b * 128 + lane * 4), a.qs + row0 + b * 128, a.d + (int64_t)r * (n / 32) + b * 4, lane);
     }
 }
 
@@ -161,7 +166,7 @@ __global__ void __launch_bounds__(256) swiglu_quant_kernel(Parts gate, Parts up,
 int eb_resid_norm_quant(float *x, const float *part, int ks, const float *w, float eps, int n, int T, const ActQ &aq, float *feat, cudaStream_t st) {
     if (n % 4 || n > 16384) return eb_set_err(EB_ERR_ARG, "resid_norm_quant: n=%d", n);
     if (T == 0) return EB_OK;
-    Parts p{part, ks, (int64_t)T * n};
+    Parts p{part, ks, (int64_t)T * n, n};
     if (n % 256 == 0 && n <= 8192 && (!aq.qs || (aq.kq && aq.K == n)))
         resid_norm_quant_regs_kernel<<<T, n / 8, 0, st>>>(x, p, w, eps, n, aq, feat);
     else
@@ -169,24 +174,29 @@ int eb_resid_norm_quant(float *x, const float *part, int ks, const float *w, flo
     EB_CHECK_LAUNCH();
     return EB_OK;
 }
-int eb_rope_kv_store_fused(const float *qp, int qks, const float *kp, int kks, const float *vp, int vks, float *q, void *q16, const int32_t *pos, void *kc, void *vc,
-                           const FwdCtl *ctl, int D, int n_head, int T, float freq_base, cudaStream_t st) {
+int eb_rope_table(const int32_t *pos, int D, int T, float freq_base, float *tab, cudaStream_t st) {
     if (T == 0) return EB_OK;
     if (D > 256 || D % 4) return eb_set_err(EB_ERR_ARG, "rope: D=%d", D);
-    const int64_t plane = (int64_t)T * n_head * D;
-    const int E = n_head * D;
-    const int threads = 512, gy = (int)cdiv(E / 4, threads);
-    rope_kv_store_fused_kernel<<<dim3(T, gy), threads, 0, st>>>(Parts{qp, qks, plane}, Parts{kp, kks, plane}, Parts{vp, vks, plane}, q, (__half *)q16, pos,
-                                                                 (__half *)kc, (__half *)vc, ctl, D, n_head, powf(freq_base, -2.0f / D));
+    rope_table_kernel<<<T, 128, 0, st>>>(pos, powf(freq_base, -2.0f / D), D / 2, (float2 *)tab);
     EB_CHECK_LAUNCH();
     return EB_OK;
 }
-int eb_swiglu_quant(const float *gate, int gks, const float *up, int uks, int n, int T, const ActQ &aq, cudaStream_t st) {
+int eb_rope_kv_store_fused(PlaneRef qp, PlaneRef kp, PlaneRef vp, float *q, void *q16, const float *tab, void *kc, void *vc,
+                           const FwdCtl *ctl, int D, int n_head, int T, cudaStream_t st) {
+    if (T == 0) return EB_OK;
+    if (D > 256 || D % 4) return eb_set_err(EB_ERR_ARG, "rope: D=%d", D);
+    const int E = n_head * D;
+    const int threads = 512, gy = (int)cdiv(E / 4, threads);
+    rope_kv_store_fused_kernel<<<dim3(T, gy), threads, 0, st>>>(parts_of(qp, T), parts_of(kp, T), parts_of(vp, T), q, (__half *)q16, (const float2 *)tab,
+                                                                 (__half *)kc, (__half *)vc, ctl, D, n_head);
+    EB_CHECK_LAUNCH();
+    return EB_OK;
+}
+int eb_swiglu_quant(PlaneRef gate, PlaneRef up, int n, int T, const ActQ &aq, cudaStream_t st) {
     if (T == 0) return EB_OK;
     const int per = aq.kq ? 256 : 128;
     if (n % per || aq.K != n) return eb_set_err(EB_ERR_ARG, "swiglu: n=%d", n);
-    const int64_t plane = (int64_t)T * n;
-    swiglu_quant_kernel<<<dim3((unsigned)cdiv(n / per, 8), T), 256, 0, st>>>(Parts{gate, gks, plane}, Parts{up, uks, plane}, n, aq);
+    swiglu_quant_kernel<<<dim3((unsigned)cdiv(n / per, 8), T), 256, 0, st>>>(parts_of(gate, T), parts_of(up, T), n, aq);
     EB_CHECK_LAUNCH();
     return EB_OK;
 }
