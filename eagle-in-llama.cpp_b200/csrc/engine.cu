@@ -342,7 +342,10 @@ static int forward_dev(const eb_model *m, KVCache &kv, Workspace &w, const int32
     RC(eb_resid_norm_quant(w.x, pend, pend_ks, (const float *)m->g[EB_T_OUTPUT_NORM].data, m->eps, E, T, al, w.feat, st));
     if (want_logits) {
         int kl_;
-        if (eb_mmq_supported(o.type, o.rows, o.cols, T) && eb_mmq_pick_ksplit(o.type, o.rows, o.cols, T) > 1)
+        if (eb_mmq_tc_supported(o.type, o.rows, o.cols, T)) {
+            RC(eb_mmq_tc_parts(o.type, o.data, o.rows, o.cols, al, w.partial, &kl_, st));
+            RC(eb_splitk_reduce(w.partial, w.logits, (int64_t)T * o.rows, kl_, st));
+        } else if (eb_mmq_supported(o.type, o.rows, o.cols, T) && eb_mmq_pick_ksplit(o.type, o.rows, o.cols, T) > 1)
             RC(eb_mmq(o.type, o.data, o.rows, o.cols, al, w.logits, w.partial, eb_mmq_pick_ksplit(o.type, o.rows, o.cols, T), st));
         else
             RC(mm_parts(o, al, w.logits, &kl_, st));

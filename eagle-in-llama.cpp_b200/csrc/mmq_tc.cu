@@ -47,9 +47,18 @@ constexpr int D_STRIDE = 160, D_MIN = 80, A_OFF = 320, AM_OFF = 448;
 enum { W_FULL = 0, W_EMPTY = 6, B_FULL = 12, B_EMPTY = 14, BS_FULL = 16, BS_EMPTY = 18, A_FULL = 20, A_EMPTY = 22,
        D_FULL = 24, D_EMPTY = 26, HDR_FULL = 28, N_BARS = 32 };
 
+// Q6_K variant (FMT = 1): stage = ql tile (128 rows x 128 B, 128B-swizzled) | qh tile (128 x 64 B, 64B-swizzled) | scales (128 x 16 B);
+// one accumulator of 80 columns per stage (no mins term); A operand = two exact f16 addends per half-super-block
+constexpr int S_W6 = 4;
+constexpr int W6_QH = 128 * 128, W6_SC = W6_QH + 128 * 64, W6_STAGE = W6_SC + 128 * 16;    // 16384, 24576, 26624
+static_assert(S_W6 * W6_STAGE <= S_W * W_STAGE, "Q6_K weight ring must fit the Q4_K one");
+constexpr int D6_STRIDE = 80, A6_OFF = 192, A6_HALF = 128, A6_SECOND = 64;
+
 struct TcArgs {
     const float *dT; float *out; int64_t N; int nbr, T, npad, n_rb, n_items, spp; long long *prof;
     uint32_t k_lo, k_hi, k_magic;    // 0x000f000f, 0x00f000f0, 0x64006400 passed as data: kept in registers so that (x & m) | c is ONE LOP3
+    uint32_t k_q2;                   // 0x03000300
+    const __half *w_d;               // Q6_K: per-block d plane [N][nbr]
 };
 
 // optional in-kernel profile (EB_TC_PROF=1): cycles each role of CTA 0 spends waiting on its barriers
@@ -153,8 +162,109 @@ __device__ __forceinline__ void dequant_q4_K(const TcArgs &p, uint8_t *smem, uin
     }
 }
 
+// signed byte b of word w as half2 (v, v), v in [-128,127] exact
+__device__ __forceinline__ __half2 sbyte_to_h2(uint32_t w, int b) {
+    const uint32_t v = ((w >> (8 * b)) & 0xffu) ^ 0x80u;
+    return __hsub2(u2h(v | (v << 16) | 0x64006400u), u2h(0x64806480u));     // (1024 + v + 128) - 1152
+}
+// Q6_K: weight = d * sc * (q - 32), q = ql | qh << 4, |sc * (q - 32)| <= 4096 does not fit f16 exactly, so the A operand is
+// the sum of two exact f16 integers fed to two MMAs on the same accumulator:
+//     A1 = sc * ql             (0 .. 15 * 128)          = (1024 + 16 ql) * (sc / 16) - 64 sc      nibble at mantissa bits 4-7
+//     A2 = 16 sc * (qh - 2)    (multiples of 16 <= 4096) = (1024 + 256 qh) * (sc / 16) - 96 sc     2-bit field at mantissa bits 8-9
+// (the bias product stays <= 96 * 128, inside the f16 range; a bias in the low mantissa bits would need 1024 * sc).
+// One 32-element group G of a 128-element half (dequantize_row_q6_K, R/ggml/src/ggml-quants.c:1709): ql bytes 32 (G & 1) + l,
+// nibble G >> 1; qh byte l, bits 2G..2G+1; K-steps 2G (l < 16) and 2G + 1.
+template <int G>
+__device__ __forceinline__ void dequant_group_q6(uint32_t (&r1)[16], uint32_t (&r2)[16], const uint4 &x0, const uint4 &x1, const uint4 &y0, const uint4 &y1,
+                                                 __half2 sa, __half2 sb, uint32_t k_hi, uint32_t k_q2, uint32_t k_magic) {
+    const uint32_t xs[8] = {x0.x, x0.y, x0.z, x0.w, x1.x, x1.y, x1.z, x1.w}, ys[8] = {y0.x, y0.y, y0.z, y0.w, y1.x, y1.y, y1.z, y1.w};
+    const __half2 k16 = __float2half2_rn(0.0625f), k64 = __float2half2_rn(-64.f), k96 = __float2half2_rn(-96.f);
+#pragma unroll
+    for (int w = 0; w < 8; w++) {
+        const __half2 sc = w < 4 ? sa : sb;
+        const __half2 m = __hmul2(sc, k16), c1 = __hmul2(sc, k64), c2 = __hmul2(sc, k96);
+        const uint32_t x = xs[w], y = ys[w];
+        const uint32_t a = G < 2 ? x << 4 : x, b = G < 2 ? x >> 4 : x >> 8;            // elements (4w, 4w+2) and (4w+1, 4w+3)
+        const uint32_t a2 = y << (8 - 2 * G), b2 = y >> (2 * G);
+        r1[2 * w]     = h2u(__hfma2(u2h(and_or(a, k_hi, k_magic)), m, c1));
+        r1[2 * w + 1] = h2u(__hfma2(u2h(and_or(b, k_hi, k_magic)), m, c1));
+        r2[2 * w]     = h2u(__hfma2(u2h(and_or(a2, k_q2, k_magic)), m, c2));
+        r2[2 * w + 1] = h2u(__hfma2(u2h(and_or(b2, k_q2, k_magic)), m, c2));
+    }
+}
+__device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t (&r)[16]) {
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16};"
+                 ::"r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]),
+                   "r"(r[8]), "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]) : "memory");
+}
+// dequant role for Q6_K: MEMBER m handles groups m and m + 2 of each half (same 32 ql bytes: low / high nibbles)
+template <int MEMBER, bool PROF>
+__device__ __forceinline__ void dequant_q6_K(const TcArgs &p, uint8_t *smem, uint32_t bar0, uint32_t tmem, int q, int lane) {
+    auto bar = [&](int i) { return bar0 + 8u * i; };
+    const int row = 32 * q + lane;
+    const uint32_t lane_base = tmem + ((uint32_t)(32 * q) << 16);
+    float2 *hdr_sm = (float2 *)(smem + OFF_HDR);
+    const uint32_t k_hi = p.k_hi, k_magic = p.k_magic, k_q2 = p.k_q2;
+    const int sw_ql = row & 7, sw_qh = (row >> 1) & 3;                  // TMA swizzle phases of this row
+    uint32_t i = 0;
+    long long pw[4] = {0, 0, 0, 0}; const long long pt0 = PROF ? clock64() : 0;
+    for (int item = blockIdx.x; item < p.n_items; item += gridDim.x) {
+        const int ks = item / p.n_rb, rb = item % p.n_rb;
+        const int sb0 = ks * p.spp, sb1 = min(p.nbr, sb0 + p.spp);
+        const int64_t grow = (int64_t)rb * 128 + row;
+        const __half *dp = p.w_d + grow * p.nbr;
+        float dcur = (MEMBER == 0 && grow < p.N) ? __half2float(__ldg(dp + sb0)) : 0.f;
+        for (int sb = sb0; sb < sb1; sb++, i++) {
+            const uint32_t s = i % S_W6;
+            TCP_WAIT(0, bar(W_FULL + s), (i / S_W6) & 1);
+            const uint8_t *st = smem + OFF_W + s * W6_STAGE;
+            const uint8_t *qlp = st + row * 128, *qhp = st + W6_QH + row * 64;
+            uint4 xl[2][2], yh[2][2];
+#pragma unroll
+            for (int h = 0; h < 2; h++) {
+#pragma unroll
+                for (int c = 0; c < 2; c++) {
+                    xl[h][c] = *(const uint4 *)(qlp + (((4 * h + 2 * MEMBER + c) ^ sw_ql) << 4));
+                    yh[h][c] = *(const uint4 *)(qhp + (((2 * h + c) ^ sw_qh) << 4));
+                }
+            }
+            const uint4 sc = *(const uint4 *)(st + W6_SC + row * 16);
+            __syncwarp();
+            if (lane == 0) tc::mbar_arrive(bar(W_EMPTY + s));
+            const float dnow = dcur;
+            if (MEMBER == 0 && sb + 1 < sb1 && grow < p.N) dcur = __half2float(__ldg(dp + sb + 1));
+            const uint32_t scw[4] = {sc.x, sc.y, sc.z, sc.w};
+#pragma unroll
+            for (int h = 0; h < 2; h++) {
+                uint32_t r1a[16], r2a[16], r1b[16], r2b[16];
+                dequant_group_q6<MEMBER>(r1a, r2a, xl[h][0], xl[h][1], yh[h][0], yh[h][1], sbyte_to_h2(scw[2 * h], 2 * MEMBER), sbyte_to_h2(scw[2 * h], 2 * MEMBER + 1),
+                                         k_hi, k_q2, k_magic);
+                dequant_group_q6<MEMBER + 2>(r1b, r2b, xl[h][0], xl[h][1], yh[h][0], yh[h][1], sbyte_to_h2(scw[2 * h + 1], 2 * MEMBER), sbyte_to_h2(scw[2 * h + 1], 2 * MEMBER + 1),
+                                             k_hi, k_q2, k_magic);
+                TCP_WAIT(1 + h, bar(A_EMPTY + h), (i & 1) ^ 1);
+                tc::fence_after();
+                if (MEMBER == 0 && h == 0) hdr_sm[(i & 3) * 128 + row] = make_float2(dnow, 0.f);
+                const uint32_t a = lane_base + A6_OFF + A6_HALF * h;
+                tmem_st16(a + 16 * MEMBER, r1a); tmem_st16(a + 16 * (MEMBER + 2), r1b);
+                tmem_st16(a + A6_SECOND + 16 * MEMBER, r2a); tmem_st16(a + A6_SECOND + 16 * (MEMBER + 2), r2b);
+                tc::wait_st();
+                tc::fence_before();
+                __syncwarp();
+                if (lane == 0) {
+                    tc::mbar_arrive(bar(A_FULL + h));
+                    if (MEMBER == 0 && h == 0) tc::mbar_arrive(bar(HDR_FULL + (i & 3)));
+                }
+            }
+        }
+    }
+    if (PROF && blockIdx.x == 0 && q == 0 && lane == 0) {
+        long long *o = p.prof + 16 + 8 * MEMBER;
+        o[0] = clock64() - pt0; o[1] = pw[0]; o[2] = pw[1]; o[3] = pw[2]; o[4] = pw[3]; o[5] = i;
+    }
+}
+
 // epilogue role: 8 warps; warp (q, hf) owns TMEM lanes 32q..32q+31 (weight rows) and columns [40hf, 40hf+40)
-template <bool PROF>
+template <int FMT, bool PROF>
 __device__ __forceinline__ void epilogue_role(const TcArgs &p, uint8_t *smem, uint32_t bar0, uint32_t tmem, int warp, int lane) {
     auto bar = [&](int i) { return bar0 + 8u * i; };
     const int q = warp & 3, hf = (warp - 12) >> 2, row = 32 * q + lane, c_base = 40 * hf;
@@ -191,7 +301,7 @@ __device__ __forceinline__ void epilogue_role(const TcArgs &p, uint8_t *smem, ui
             tc::fence_after();
             const long long te_ = PROF ? clock64() : 0;
             __syncwarp();
-            const uint32_t t_main = lane_base + s * D_STRIDE + c_base, t_min = t_main + D_MIN;
+            const uint32_t t_main = lane_base + s * (FMT == 0 ? D_STRIDE : D6_STRIDE) + c_base, t_min = t_main + D_MIN;
             // two passes keep the live registers under the 120 granted by setmaxnreg: columns [0,16) then [16,40)
             auto fold4 = [&](const uint32_t *vm, const uint32_t *vn, int col0, int n4) {
 #pragma unroll
@@ -200,22 +310,26 @@ __device__ __forceinline__ void epilogue_role(const TcArgs &p, uint8_t *smem, ui
                     const int k = 4 * e4, a = (col0 >> 1) + 2 * e4;
                     unsigned long long t0 = mul2(hd2, pk2(__uint_as_float(vm[k]), __uint_as_float(vm[k + 1])));
                     unsigned long long t1 = mul2(hd2, pk2(__uint_as_float(vm[k + 2]), __uint_as_float(vm[k + 3])));
-                    t0 = fma2(hm2, pk2(__uint_as_float(vn[k]), __uint_as_float(vn[k + 1])), t0);
-                    t1 = fma2(hm2, pk2(__uint_as_float(vn[k + 2]), __uint_as_float(vn[k + 3])), t1);
+                    if (FMT == 0) {
+                        t0 = fma2(hm2, pk2(__uint_as_float(vn[k]), __uint_as_float(vn[k + 1])), t0);
+                        t1 = fma2(hm2, pk2(__uint_as_float(vn[k + 2]), __uint_as_float(vn[k + 3])), t1);
+                    }
                     acc2[a] = fma2(dx.x, t0, acc2[a]);
                     acc2[a + 1] = fma2(dx.y, t1, acc2[a + 1]);
                 }
             };
             {
                 uint32_t vm[16], vn[16];
-                tc::tmem_ld16(t_main, vm); tc::tmem_ld16(t_min, vn);
+                tc::tmem_ld16(t_main, vm);
+                if (FMT == 0) tc::tmem_ld16(t_min, vn);
                 tc::wait_ld();
                 fold4(vm, vn, 0, 4);
             }
             {
                 uint32_t vm[16], vn[16], wm[8], wn[8];
-                tc::tmem_ld16(t_main + 16, vm); tc::tmem_ld16(t_min + 16, vn);
-                if (tail) { tc::tmem_ld8(t_main + 32, wm); tc::tmem_ld8(t_min + 32, wn); }
+                tc::tmem_ld16(t_main + 16, vm);
+                if (FMT == 0) tc::tmem_ld16(t_min + 16, vn);
+                if (tail) { tc::tmem_ld8(t_main + 32, wm); if (FMT == 0) tc::tmem_ld8(t_min + 32, wn); }
                 tc::wait_ld();
                 tc::fence_before();
                 __syncwarp();
@@ -238,9 +352,12 @@ __device__ __forceinline__ void epilogue_role(const TcArgs &p, uint8_t *smem, ui
     if (PROF && blockIdx.x == 0 && warp == 12 && lane == 0) { long long *o = p.prof + 32; o[0] = clock64() - pt0; o[1] = pw[0]; o[2] = pw[1]; o[3] = pw[2]; }
 }
 
-template <bool PROF>
+// FMT 0 = Q4_K (tmW = the 144-byte blocks, tmBS = 16-element activation sums); FMT 1 = Q6_K (tmW = ql plane, tmQH / tmSC = qh / scales planes)
+template <int FMT, bool PROF>
 __global__ void __launch_bounds__(TC_THREADS, 1)
-mmq_tc_q4_K(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmB, const __grid_constant__ CUtensorMap tmBS, TcArgs p) {
+mmq_tc_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmB, const __grid_constant__ CUtensorMap tmBS,
+              const __grid_constant__ CUtensorMap tmQH, const __grid_constant__ CUtensorMap tmSC, TcArgs p) {
+    constexpr int NSW = FMT == 0 ? S_W : S_W6;
     extern __shared__ uint8_t smem_raw[];
     uint8_t *smem = (uint8_t *)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     const uint32_t sbase = tc::smem_u32(smem);
@@ -250,7 +367,7 @@ mmq_tc_q4_K(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUt
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
     if (threadIdx.x == 0) {
-        for (int i = 0; i < S_W; i++) { tc::mbar_init(bar(W_FULL + i), 1); tc::mbar_init(bar(W_EMPTY + i), 8); }
+        for (int i = 0; i < NSW; i++) { tc::mbar_init(bar(W_FULL + i), 1); tc::mbar_init(bar(W_EMPTY + i), 8); }
         for (int i = 0; i < 2; i++) {
             tc::mbar_init(bar(B_FULL + i), 1); tc::mbar_init(bar(B_EMPTY + i), 1);
             tc::mbar_init(bar(BS_FULL + i), 1); tc::mbar_init(bar(BS_EMPTY + i), 1);
@@ -259,7 +376,8 @@ mmq_tc_q4_K(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUt
         }
         for (int i = 0; i < 4; i++) tc::mbar_init(bar(HDR_FULL + i), 4);
         tc::fence_barrier_init();
-        tc::tma_prefetch_desc(&tmW); tc::tma_prefetch_desc(&tmB); tc::tma_prefetch_desc(&tmBS);
+        tc::tma_prefetch_desc(&tmW); tc::tma_prefetch_desc(&tmB);
+        if (FMT == 0) tc::tma_prefetch_desc(&tmBS); else { tc::tma_prefetch_desc(&tmQH); tc::tma_prefetch_desc(&tmSC); }
     }
     if (warp == 3) tc::tmem_alloc(tc::smem_u32((const void *)tmem_slot), 512);
     tc::fence_before();
@@ -278,10 +396,18 @@ mmq_tc_q4_K(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUt
                     const int ks = item / p.n_rb, rb = item % p.n_rb;
                     const int sb0 = ks * p.spp, sb1 = min(p.nbr, sb0 + p.spp);
                     for (int sb = sb0; sb < sb1; sb++, i++) {
-                        const uint32_t s = i % S_W, ph = (i / S_W) & 1;
+                        const uint32_t s = i % NSW, ph = (i / NSW) & 1;
                         TCP_WAIT(0, bar(W_EMPTY + s), ph ^ 1);
-                        tc::mbar_expect_tx(bar(W_FULL + s), W_STAGE);
-                        tc::tma_load_2d(sbase + OFF_W + s * W_STAGE, &tmW, sb * 144, rb * 128, bar(W_FULL + s));
+                        if (FMT == 0) {
+                            tc::mbar_expect_tx(bar(W_FULL + s), W_STAGE);
+                            tc::tma_load_2d(sbase + OFF_W + s * W_STAGE, &tmW, sb * 144, rb * 128, bar(W_FULL + s));
+                        } else {
+                            const uint32_t dst = sbase + OFF_W + s * W6_STAGE;
+                            tc::mbar_expect_tx(bar(W_FULL + s), W6_STAGE);
+                            tc::tma_load_2d(dst, &tmW, sb * 128, rb * 128, bar(W_FULL + s));
+                            tc::tma_load_2d(dst + W6_QH, &tmQH, sb * 64, rb * 128, bar(W_FULL + s));
+                            tc::tma_load_2d(dst + W6_SC, &tmSC, sb * 16, rb * 128, bar(W_FULL + s));
+                        }
                     }
                 }
                 if (PROF && blockIdx.x == 0) { p.prof[0] = clock64() - pt0; p.prof[1] = pw[0]; }
@@ -295,7 +421,7 @@ mmq_tc_q4_K(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUt
                     const int ks = item / p.n_rb;
                     const int sb0 = ks * p.spp, sb1 = min(p.nbr, sb0 + p.spp);
                     for (int sb = sb0; sb < sb1; sb++, i++) {
-                        if (sb == sb0 || (sb & 3) == 0) {
+                        if (FMT == 0 && (sb == sb0 || (sb & 3) == 0)) {
                             const uint32_t s2 = nbx & 1, ph2 = (nbx >> 1) & 1;
                             tc::mbar_wait(bar(BS_EMPTY + s2), ph2 ^ 1);
                             tc::mbar_expect_tx(bar(BS_FULL + s2), box_bytes);
@@ -322,7 +448,7 @@ mmq_tc_q4_K(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUt
                 const int ks = item / p.n_rb;
                 const int sb0 = ks * p.spp, sb1 = min(p.nbr, sb0 + p.spp);
                 for (int sb = sb0; sb < sb1; sb++, i++) {
-                    if (sb == sb0 || (sb & 3) == 0) {
+                    if (FMT == 0 && (sb == sb0 || (sb & 3) == 0)) {
                         if (cur_bs >= 0 && leader) tc::mma_commit(bar(BS_EMPTY + (cur_bs & 1)));
                         cur_bs = (int)nbx;
                         TCP_WAIT(0, bar(BS_FULL + (nbx & 1)), (nbx >> 1) & 1);
@@ -331,7 +457,7 @@ mmq_tc_q4_K(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUt
                     const uint32_t s = i & 1, ph = (i >> 1) & 1;
                     TCP_WAIT(1, bar(B_FULL + s), ph);
                     TCP_WAIT(2, bar(D_EMPTY + s), ph ^ 1);
-                    const uint32_t d_main = tmem + s * D_STRIDE, d_min = d_main + D_MIN;
+                    const uint32_t d_main = tmem + s * (FMT == 0 ? D_STRIDE : D6_STRIDE), d_min = d_main + D_MIN;
                     const uint64_t bdesc = tc::smem_desc_sw128(sbase + OFF_B + s * B_STAGE);
                     const uint64_t mdesc = tc::smem_desc_sw128(sbase + OFF_BS + (cur_bs & 1) * B_BOX + 32 * (sb & 3));
 #pragma unroll
@@ -339,9 +465,14 @@ mmq_tc_q4_K(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUt
                         TCP_WAIT(3, bar(A_FULL + h), i & 1);
                         tc::fence_after();
                         if (leader) {
-                            tc::mma_f16_ts_x8(d_main, tmem + A_OFF + 64 * h, bdesc + (uint64_t)((2 * h) * (B_BOX >> 4)),
-                                              bdesc + (uint64_t)((2 * h + 1) * (B_BOX >> 4)), idesc, h != 0);
-                            if (h == 0) tc::mma_f16_ts(d_min, tmem + AM_OFF + 8 * (i & 1), mdesc, idesc, 0);
+                            const uint64_t b_lo = bdesc + (uint64_t)((2 * h) * (B_BOX >> 4)), b_hi = bdesc + (uint64_t)((2 * h + 1) * (B_BOX >> 4));
+                            if (FMT == 0) {
+                                tc::mma_f16_ts_x8(d_main, tmem + A_OFF + 64 * h, b_lo, b_hi, idesc, h != 0);
+                                if (h == 0) tc::mma_f16_ts(d_min, tmem + AM_OFF + 8 * (i & 1), mdesc, idesc, 0);
+                            } else {                                    // two exact addends of the weight, same activations, same accumulator
+                                tc::mma_f16_ts_x8(d_main, tmem + A6_OFF + A6_HALF * h, b_lo, b_hi, idesc, h != 0);
+                                tc::mma_f16_ts_x8(d_main, tmem + A6_OFF + A6_HALF * h + A6_SECOND, b_lo, b_hi, idesc, 1);
+                            }
                             tc::mma_commit(bar(A_EMPTY + h));
                             if (h == 1) { tc::mma_commit(bar(B_EMPTY + s)); tc::mma_commit(bar(D_FULL + s)); }
                         }
@@ -353,11 +484,16 @@ mmq_tc_q4_K(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUt
         }
         __syncwarp();
     } else if (warp < 12) {
-        if (warp < 8) dequant_q4_K<0, PROF>(p, smem, bar0, tmem, warp & 3, lane);
-        else dequant_q4_K<1, PROF>(p, smem, bar0, tmem, warp & 3, lane);
+        if (FMT == 0) {
+            if (warp < 8) dequant_q4_K<0, PROF>(p, smem, bar0, tmem, warp & 3, lane);
+            else dequant_q4_K<1, PROF>(p, smem, bar0, tmem, warp & 3, lane);
+        } else {
+            if (warp < 8) dequant_q6_K<0, PROF>(p, smem, bar0, tmem, warp & 3, lane);
+            else dequant_q6_K<1, PROF>(p, smem, bar0, tmem, warp & 3, lane);
+        }
     } else {
         tc::setmaxnreg_inc<120>();   // CTA pool: 128*40 + 256*96 + 256*120 = 60416 <= 640*96
-        epilogue_role<PROF>(p, smem, bar0, tmem, warp, lane);
+        epilogue_role<FMT, PROF>(p, smem, bar0, tmem, warp, lane);
     }
     tc::fence_before();
     __syncthreads();
@@ -398,15 +534,18 @@ int eb_mmq_tc_init() {
         }
         g_encode = (EncodeTiledFn)fn;
     }
-    EB_CUDA(cudaFuncSetAttribute(mmq_tc_q4_K<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
-    EB_CUDA(cudaFuncSetAttribute(mmq_tc_q4_K<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+    EB_CUDA(cudaFuncSetAttribute(mmq_tc_kernel<0, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+    EB_CUDA(cudaFuncSetAttribute(mmq_tc_kernel<0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+    EB_CUDA(cudaFuncSetAttribute(mmq_tc_kernel<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+    EB_CUDA(cudaFuncSetAttribute(mmq_tc_kernel<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
     return EB_OK;
 }
 
 int eb_mmq_tc_supported(int type, int64_t N, int64_t K, int T) {
     static const int off = getenv("EB_NO_TC") ? 1 : 0;
     if (off || !g_encode) return 0;
-    return type == EB_Q4_K && K % 256 == 0 && N >= 128 && T > 8 && T <= 80;
+    static const int off6 = getenv("EB_NO_TC_Q6") ? 1 : 0;
+    return (type == EB_Q4_K || (type == EB_Q6_K && !off6)) && K % 256 == 0 && N >= 128 && T > 8 && T <= 80;
 }
 
 // split-K factor: planes <= 8, minimise rounds x (super-blocks per item + pipeline fill)
@@ -431,19 +570,33 @@ int eb_mmq_tc_parts(int type, const void *W, int64_t N, int64_t K, const ActQ &a
     const int ks = tc_pick_ksplit(N, nbr);
     TcArgs p;
     p.dT = a.dT; p.out = planes; p.N = N; p.nbr = nbr; p.T = a.T; p.npad = (a.T + 15) / 16 * 16;
-    p.k_lo = 0x000f000fu; p.k_hi = 0x00f000f0u; p.k_magic = 0x64006400u;
+    p.k_lo = 0x000f000fu; p.k_hi = 0x00f000f0u; p.k_magic = 0x64006400u; p.k_q2 = 0x03000300u; p.w_d = nullptr;
     p.n_rb = (int)cdiv(N, 128); p.spp = (int)cdiv(nbr, ks); p.n_items = p.n_rb * ks;
-    CUtensorMap tmW, tmB, tmBS;
+    CUtensorMap tmW, tmB, tmBS, tmQH, tmSC;
     int rc;
-    if ((rc = make_map_2d(&tmW, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, W, (uint64_t)nbr * 144, (uint64_t)N, (uint64_t)nbr * 144, 144, 128, CU_TENSOR_MAP_SWIZZLE_NONE))) return rc;
+    if (type == EB_Q4_K) {
+        if ((rc = make_map_2d(&tmW, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, W, (uint64_t)nbr * 144, (uint64_t)N, (uint64_t)nbr * 144, 144, 128, CU_TENSOR_MAP_SWIZZLE_NONE))) return rc;
+        tmQH = tmW; tmSC = tmW;
+    } else {                                             // Q6_K planes (common.cuh WPlanes): ql | qh | scales | d
+        const uint8_t *base = (const uint8_t *)W; const uint64_t nb = (uint64_t)N * nbr;
+        if ((rc = make_map_2d(&tmW, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, base, (uint64_t)nbr * 128, (uint64_t)N, (uint64_t)nbr * 128, 128, 128, CU_TENSOR_MAP_SWIZZLE_128B))) return rc;
+        if ((rc = make_map_2d(&tmQH, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, base + nb * 128, (uint64_t)nbr * 64, (uint64_t)N, (uint64_t)nbr * 64, 64, 128, CU_TENSOR_MAP_SWIZZLE_64B))) return rc;
+        if ((rc = make_map_2d(&tmSC, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, base + nb * 192, (uint64_t)nbr * 16, (uint64_t)N, (uint64_t)nbr * 16, 16, 128, CU_TENSOR_MAP_SWIZZLE_NONE))) return rc;
+        p.w_d = (const __half *)(base + nb * 208);
+    }
     if ((rc = make_map_2d(&tmB, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, a.h16, (uint64_t)K, (uint64_t)a.T, (uint64_t)K * 2, 64, (uint32_t)p.npad, CU_TENSOR_MAP_SWIZZLE_128B))) return rc;
     if ((rc = make_map_2d(&tmBS, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, a.bsum, (uint64_t)K / 16, (uint64_t)a.T, (uint64_t)K / 16 * 2, 64, (uint32_t)p.npad, CU_TENSOR_MAP_SWIZZLE_128B))) return rc;
     static long long *prof_buf = nullptr; static const int want_prof = getenv("EB_TC_PROF") ? 1 : 0;
     if (want_prof && !prof_buf) { cudaMalloc((void **)&prof_buf, 512 * 8); cudaMemset(prof_buf, 0, 512 * 8); }
     p.prof = want_prof ? prof_buf : nullptr;
     const int grid = std::min(p.n_items, eb_sm_count());
-    if (want_prof) mmq_tc_q4_K<true><<<grid, TC_THREADS, SMEM_BYTES, st>>>(tmW, tmB, tmBS, p);
-    else mmq_tc_q4_K<false><<<grid, TC_THREADS, SMEM_BYTES, st>>>(tmW, tmB, tmBS, p);
+    if (type == EB_Q4_K) {
+        if (want_prof) mmq_tc_kernel<0, true><<<grid, TC_THREADS, SMEM_BYTES, st>>>(tmW, tmB, tmBS, tmQH, tmSC, p);
+        else mmq_tc_kernel<0, false><<<grid, TC_THREADS, SMEM_BYTES, st>>>(tmW, tmB, tmBS, tmQH, tmSC, p);
+    } else {
+        if (want_prof) mmq_tc_kernel<1, true><<<grid, TC_THREADS, SMEM_BYTES, st>>>(tmW, tmB, tmBS, tmQH, tmSC, p);
+        else mmq_tc_kernel<1, false><<<grid, TC_THREADS, SMEM_BYTES, st>>>(tmW, tmB, tmBS, tmQH, tmSC, p);
+    }
     EB_CHECK_LAUNCH();
     *ks_out = ks;
     if (want_prof) {
