@@ -20,6 +20,8 @@ long eb_launches_now() { return g_launches.load(); }
 void eb_launches_add(long n) { g_launches.fetch_add(n); }
 int eb_sm_count() { return g_sm_count > 0 ? g_sm_count : 148; }
 
+int eb_pdl_enabled() { static const int on = getenv("EB_NO_PDL") ? 0 : 1; return on; }
+
 extern "C" {
 
 const char *eb_last_error(void) { return g_eb_err.c_str(); }

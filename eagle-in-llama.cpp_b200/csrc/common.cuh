@@ -65,6 +65,24 @@ int eb_mmq_init(); int eb_fattn_init(); int eb_spec_init();
 
 static inline int64_t cdiv(int64_t a, int64_t b) { return (a + b - 1) / b; }
 
+// ---- programmatic dependent launch (PDL): a kernel launched through eb_launch_pdl may start while its predecessor in the
+// stream is still running; it must execute pdl_wait() before it touches ANY global data written by earlier kernels (or
+// writes data they read).  Everything before pdl_wait() — barrier init, TMEM allocation, tensor-map prefetch, the TMA
+// stream of the (constant) weights — overlaps the predecessor's tail.  pdl_trigger() lets the successor start early.
+// In a kernel launched the ordinary way both are no-ops.  EB_NO_PDL=1 turns the launch attribute off.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+int eb_pdl_enabled();
+template <typename... KArgs, typename... Args>
+static inline cudaError_t eb_launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization; at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = eb_pdl_enabled() ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);
+}
+
 // ---- device helpers
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll

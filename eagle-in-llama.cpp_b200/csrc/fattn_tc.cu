@@ -59,10 +59,6 @@ fattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     const uint32_t bars = sbase + FT_OFF_BAR, slot = bars + FB_COUNT * 8;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int h = blockIdx.x, split = blockIdx.y;
-    int n_prefix = p.n_prefix, n_kv = p.n_kv;
-    if (p.ctl) { n_prefix = p.ctl->n_prefix; n_kv = min(p.n_ctx, n_prefix + p.ctl->n_tree); }
-    const int n_tiles = (n_kv + FT_TILE - 1) / FT_TILE, tps = (n_tiles + p.nsplit - 1) / p.nsplit;
-    const int t0 = split * tps, n = max(0, min(n_tiles, t0 + tps) - t0);
     const int nsw = (p.T + 31) >> 5;                                         // softmax warps with at least one live row
 
     if (threadIdx.x == 0) {
@@ -82,6 +78,13 @@ fattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     fence_after();
     uint32_t tmem;
     asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem) : "r"(slot));
+    // everything above overlapped the predecessor's tail (PDL); lengths, Q, K/V and the tree bits are earlier kernels' outputs
+    pdl_trigger();
+    pdl_wait();
+    int n_prefix = p.n_prefix, n_kv = p.n_kv;
+    if (p.ctl) { n_prefix = p.ctl->n_prefix; n_kv = min(p.n_ctx, n_prefix + p.ctl->n_tree); }
+    const int n_tiles = (n_kv + FT_TILE - 1) / FT_TILE, tps = (n_tiles + p.nsplit - 1) / p.nsplit;
+    const int t0 = split * tps, n = max(0, min(n_tiles, t0 + tps) - t0);
 
     if (warp == 0) {
         // ------------------------------------------------------------------ TMA producer
@@ -281,7 +284,7 @@ int eb_fattn_tc(const __half *q16, const void *k, const void *v, int64_t kv_stri
     if ((rc = eb_tc_map_2d_f16(&tmQ, q16, (uint64_t)H * 128, (uint64_t)T, (uint64_t)H * 128 * 2, 64, 128))) return rc;
     if ((rc = eb_tc_map_2d_f16(&tmK, k, (uint64_t)H * 128, (uint64_t)n_cells, (uint64_t)kv_stride * 2, 64, 128))) return rc;
     if ((rc = eb_tc_map_2d_f16(&tmV, v, (uint64_t)H * 128, (uint64_t)n_cells, (uint64_t)kv_stride * 2, 64, 128))) return rc;
-    fattn_tc_kernel<<<dim3(H, p.nsplit), 256, FT_SMEM, st>>>(tmQ, tmK, tmV, p);
+    eb_launch_pdl(fattn_tc_kernel, dim3(H, p.nsplit), dim3(256), FT_SMEM, st, tmQ, tmK, tmV, p);
     EB_CHECK_LAUNCH();
     if (p.nsplit > 1) {
         // the caller's wo GEMM wants the Q8_K grid: merge the splits and quantise in one pass, skipping the f32 output

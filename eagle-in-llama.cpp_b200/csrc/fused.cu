@@ -65,6 +65,7 @@ __global__ void __launch_bounds__(256) resid_norm_quant_kernel(float *__restrict
 __global__ void __launch_bounds__(1024) resid_norm_quant_regs_kernel(float *__restrict__ x, Parts add, const float *__restrict__ w, float eps,
                                                                     int n, ActQ a, float *__restrict__ feat) {
     __shared__ double red[32];
+    pdl_trigger(); pdl_wait();
     const int r = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nw = blockDim.x >> 5;
     const int64_t off = (int64_t)r * n + tid * 8;
     float4 v0 = *(const float4 *)(x + off), v1 = *(const float4 *)(x + off + 4);
@@ -113,6 +114,7 @@ __global__ void rope_table_kernel(const int32_t *__restrict__ pos, float theta_s
 __global__ void __launch_bounds__(512) rope_kv_store_fused_kernel(Parts qp, Parts kp, Parts vp, float *__restrict__ q, __half *__restrict__ q16,
                                                                  const float2 *__restrict__ tab, __half *__restrict__ kc, __half *__restrict__ vc,
                                                                  const FwdCtl *__restrict__ ctl, int D, int n_head) {
+    pdl_trigger(); pdl_wait();
     const int t = blockIdx.x, tid = threadIdx.x, half = D / 2;
     const int64_t cell0 = ctl ? (int64_t)(ctl->n_prefix + ctl->node_base) * n_head * D : 0;
     const int E = n_head * D;
@@ -146,6 +148,7 @@ __device__ __forceinline__ float4 swiglu4(const Parts &gate, const Parts &up, in
     return make_float4(__fmul_rn(silu_ref(g.x), u.x), __fmul_rn(silu_ref(g.y), u.y), __fmul_rn(silu_ref(g.z), u.z), __fmul_rn(silu_ref(g.w), u.w));
 }
 __global__ void __launch_bounds__(256) swiglu_quant_kernel(Parts gate, Parts up, int n, ActQ a) {
+    pdl_trigger(); pdl_wait();
     const int r = blockIdx.y, lane = threadIdx.x & 31, b = blockIdx.x * 8 + (threadIdx.x >> 5);
     const int64_t row0 = (int64_t)r * n;
     if (a.kq) {
@@ -168,7 +171,7 @@ int eb_resid_norm_quant(float *x, const float *part, int ks, const float *w, flo
     if (T == 0) return EB_OK;
     Parts p{part, ks, (int64_t)T * n, n};
     if (n % 256 == 0 && n <= 8192 && (!aq.qs || (aq.kq && aq.K == n)))
-        resid_norm_quant_regs_kernel<<<T, n / 8, 0, st>>>(x, p, w, eps, n, aq, feat);
+        eb_launch_pdl(resid_norm_quant_regs_kernel, dim3(T), dim3(n / 8), 0, st, x, p, w, eps, n, aq, feat);
     else
         resid_norm_quant_kernel<<<T, 256, (size_t)n * 4, st>>>(x, p, w, eps, n, aq, feat);
     EB_CHECK_LAUNCH();
@@ -187,8 +190,8 @@ int eb_rope_kv_store_fused(PlaneRef qp, PlaneRef kp, PlaneRef vp, float *q, void
     if (D > 256 || D % 4) return eb_set_err(EB_ERR_ARG, "rope: D=%d", D);
     const int E = n_head * D;
     const int threads = 512, gy = (int)cdiv(E / 4, threads);
-    rope_kv_store_fused_kernel<<<dim3(T, gy), threads, 0, st>>>(parts_of(qp, T), parts_of(kp, T), parts_of(vp, T), q, (__half *)q16, (const float2 *)tab,
-                                                                 (__half *)kc, (__half *)vc, ctl, D, n_head);
+    eb_launch_pdl(rope_kv_store_fused_kernel, dim3(T, gy), dim3(threads), 0, st, parts_of(qp, T), parts_of(kp, T), parts_of(vp, T), q, (__half *)q16, (const float2 *)tab,
+                  (__half *)kc, (__half *)vc, ctl, D, n_head);
     EB_CHECK_LAUNCH();
     return EB_OK;
 }
@@ -196,7 +199,7 @@ int eb_swiglu_quant(PlaneRef gate, PlaneRef up, int n, int T, const ActQ &aq, cu
     if (T == 0) return EB_OK;
     const int per = aq.kq ? 256 : 128;
     if (n % per || aq.K != n) return eb_set_err(EB_ERR_ARG, "swiglu: n=%d", n);
-    swiglu_quant_kernel<<<dim3((unsigned)cdiv(n / per, 8), T), 256, 0, st>>>(parts_of(gate, T), parts_of(up, T), n, aq);
+    eb_launch_pdl(swiglu_quant_kernel, dim3((unsigned)cdiv(n / per, 8), T), dim3(256), 0, st, parts_of(gate, T), parts_of(up, T), n, aq);
     EB_CHECK_LAUNCH();
     return EB_OK;
 }

@@ -272,6 +272,7 @@ __device__ __forceinline__ void epilogue_role(const TcArgs &p, uint8_t *smem, ui
     const float2 *hdr_sm = (const float2 *)(smem + OFF_HDR);
     float *dx_sm = (float *)(smem + OFF_DX) + (warp - 12) * 80;
     const bool tail = c_base + 32 < p.T;                                // columns [32,40) of this warp hold tokens
+    pdl_wait();                                                         // dT is read and the output planes are written below
     uint32_t i = 0;
     long long pw[3] = {0, 0, 0}; const long long pt0 = PROF ? clock64() : 0;
     for (int item = blockIdx.x; item < p.n_items; item += gridDim.x) {
@@ -384,6 +385,7 @@ mmq_tc_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ C
     __syncthreads();
     tc::fence_after();
     const uint32_t tmem = *tmem_slot;
+    pdl_trigger();                                  // the next kernel may start its own prologue on SMs this grid has left
 
     if (warp < 4) {
         tc::setmaxnreg_dec<40>();                   // hand registers to the epilogue warps
@@ -415,6 +417,7 @@ mmq_tc_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ C
         } else if (warp == 2) {
             // ------------------------------------------------------------ activation producer
             if (lane == 0) {
+                pdl_wait();                         // activations are the predecessor's output (the weight producer does not wait)
                 uint32_t i = 0, nbx = 0;
                 const uint32_t box_bytes = (uint32_t)p.npad * 128u;
                 for (int item = blockIdx.x; item < p.n_items; item += gridDim.x) {
@@ -592,10 +595,10 @@ int eb_mmq_tc_parts(int type, const void *W, int64_t N, int64_t K, const ActQ &a
     const int grid = std::min(p.n_items, eb_sm_count());
     if (type == EB_Q4_K) {
         if (want_prof) mmq_tc_kernel<0, true><<<grid, TC_THREADS, SMEM_BYTES, st>>>(tmW, tmB, tmBS, tmQH, tmSC, p);
-        else mmq_tc_kernel<0, false><<<grid, TC_THREADS, SMEM_BYTES, st>>>(tmW, tmB, tmBS, tmQH, tmSC, p);
+        else eb_launch_pdl(mmq_tc_kernel<0, false>, dim3(grid), dim3(TC_THREADS), SMEM_BYTES, st, tmW, tmB, tmBS, tmQH, tmSC, p);
     } else {
         if (want_prof) mmq_tc_kernel<1, true><<<grid, TC_THREADS, SMEM_BYTES, st>>>(tmW, tmB, tmBS, tmQH, tmSC, p);
-        else mmq_tc_kernel<1, false><<<grid, TC_THREADS, SMEM_BYTES, st>>>(tmW, tmB, tmBS, tmQH, tmSC, p);
+        else eb_launch_pdl(mmq_tc_kernel<1, false>, dim3(grid), dim3(TC_THREADS), SMEM_BYTES, st, tmW, tmB, tmBS, tmQH, tmSC, p);
     }
     EB_CHECK_LAUNCH();
     *ks_out = ks;
