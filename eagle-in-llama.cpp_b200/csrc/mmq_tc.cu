@@ -99,6 +99,9 @@ __device__ __forceinline__ void dequant_group(uint32_t (&r)[32], const uint4 &q0
 
 // dequant role: raw Q4_K rows in smem -> TMEM A operand (lane = weight row).  MEMBER 0 handles groups 0 and 2
 // (+ the header and the mins operand), MEMBER 1 groups 1 and 3; half-super-block h = groups 2h, 2h+1.
+// Software-pipelined over the CTA's super-blocks (the role never needs to know which row block / K range a stage
+// belongs to): every tcgen05.st is followed by the arithmetic of the NEXT group before its wait::st, so the TMEM
+// store latency is never exposed — the second half's store overlaps loading + dequantising the next super-block.
 template <int MEMBER, bool PROF>
 __device__ __forceinline__ void dequant_q4_K(const TcArgs &p, uint8_t *smem, uint32_t bar0, uint32_t tmem, int q, int lane) {
     auto bar = [&](int i) { return bar0 + 8u * i; };
@@ -106,59 +109,76 @@ __device__ __forceinline__ void dequant_q4_K(const TcArgs &p, uint8_t *smem, uin
     const uint32_t lane_base = tmem + ((uint32_t)(32 * q) << 16);
     float2 *hdr_sm = (float2 *)(smem + OFF_HDR);
     const uint32_t k_lo = p.k_lo, k_hi = p.k_hi, k_magic = p.k_magic;
-    uint32_t i = 0;
-    long long pw[4] = {0, 0, 0, 0}; const long long pt0 = PROF ? clock64() : 0;
+    uint32_t n_total = 0;
     for (int item = blockIdx.x; item < p.n_items; item += gridDim.x) {
-        const int ks = item / p.n_rb;
-        const int sb0 = ks * p.spp, sb1 = min(p.nbr, sb0 + p.spp);
-        for (int sb = sb0; sb < sb1; sb++, i++) {
-            const uint32_t s = i % S_W;
-            TCP_WAIT(0, bar(W_FULL + s), (i / S_W) & 1);
-            const uint8_t *rp = smem + OFF_W + s * W_STAGE + row * 144;
-            const uint4 hd = *(const uint4 *)rp;
-            const uint4 qa0 = *(const uint4 *)(rp + 16 + 32 * MEMBER), qa1 = *(const uint4 *)(rp + 32 + 32 * MEMBER);
-            const uint4 qb0 = *(const uint4 *)(rp + 16 + 32 * (MEMBER + 2)), qb1 = *(const uint4 *)(rp + 32 + 32 * (MEMBER + 2));
-            __syncwarp();
-            if (lane == 0) tc::mbar_arrive(bar(W_EMPTY + s));
-            // 6-bit scales / mins (get_scale_min_k4, R/ggml/src/ggml-quants.c:631) as bytes of u0..u1 / u2..u3
-            const uint32_t u0 = hd.y & 0x3f3f3f3fu, u1 = (hd.w & 0x0f0f0f0fu) | (((hd.y >> 6) & 0x03030303u) << 4);
-            uint32_t r[32];
-            // ---- first half-super-block (group MEMBER)
-            dequant_group(r, qa0, qa1, byte_to_h2(u0, 2 * MEMBER), byte_to_h2(u0, 2 * MEMBER + 1), k_lo, k_hi, k_magic);
-            TCP_WAIT(1, bar(A_EMPTY + 0), (i & 1) ^ 1);
-            tc::fence_after();
-            if (MEMBER == 0) {                                          // header + mins operand, once per super-block
-                const uint32_t u2 = hd.z & 0x3f3f3f3fu, u3 = ((hd.w >> 4) & 0x0f0f0f0fu) | (((hd.z >> 6) & 0x03030303u) << 4);
-                const __half2 dm = u2h(hd.x);
-                hdr_sm[(i & 3) * 128 + row] = make_float2(__low2float(dm), __high2float(dm));
-                uint32_t mr[8];
+        const int sb0 = (item / p.n_rb) * p.spp;
+        n_total += min(p.nbr, sb0 + p.spp) - sb0;
+    }
+    long long pw[4] = {0, 0, 0, 0}; const long long pt0 = PROF ? clock64() : 0;
+    uint4 hd, qb0, qb1; uint32_t u1 = 0;
+    uint32_t ra[32];
+    // stage i: read this thread's row (header, its group of each half), release the stage, dequantise the first-half group
+    auto fetch = [&](uint32_t i) {
+        const uint32_t s = i % S_W;
+        const uint8_t *rp = smem + OFF_W + s * W_STAGE + row * 144;
+        hd = *(const uint4 *)rp;
+        const uint4 qa0 = *(const uint4 *)(rp + 16 + 32 * MEMBER), qa1 = *(const uint4 *)(rp + 32 + 32 * MEMBER);
+        qb0 = *(const uint4 *)(rp + 16 + 32 * (MEMBER + 2)); qb1 = *(const uint4 *)(rp + 32 + 32 * (MEMBER + 2));
+        __syncwarp();
+        if (lane == 0) tc::mbar_arrive(bar(W_EMPTY + s));
+        // 6-bit scales / mins (get_scale_min_k4, R/ggml/src/ggml-quants.c:631) as bytes of u0..u1 / u2..u3
+        const uint32_t u0 = hd.y & 0x3f3f3f3fu;
+        u1 = (hd.w & 0x0f0f0f0fu) | (((hd.y >> 6) & 0x03030303u) << 4);
+        dequant_group(ra, qa0, qa1, byte_to_h2(u0, 2 * MEMBER), byte_to_h2(u0, 2 * MEMBER + 1), k_lo, k_hi, k_magic);
+    };
+    if (n_total > 0) {
+        TCP_WAIT(0, bar(W_FULL + 0), 0);
+        if (PROF && blockIdx.x == 0 && MEMBER == 0 && q == 0 && lane == 0) p.prof[64 + 3] = clock64();
+        fetch(0);
+    }
+    for (uint32_t i = 0; i < n_total; i++) {
+        // ---- first half-super-block (group MEMBER)
+        TCP_WAIT(1, bar(A_EMPTY + 0), (i & 1) ^ 1);
+        tc::fence_after();
+        if (MEMBER == 0) {                                          // header for the epilogue, once per super-block
+            const __half2 dm = u2h(hd.x);
+            hdr_sm[(i & 3) * 128 + row] = make_float2(__low2float(dm), __high2float(dm));
+        } else {                                                    // mins operand (the other member of the row pair: evens out the two)
+            const uint32_t u2 = hd.z & 0x3f3f3f3fu, u3 = ((hd.w >> 4) & 0x0f0f0f0fu) | (((hd.z >> 6) & 0x03030303u) << 4);
+            uint32_t mr[8];
 #pragma unroll
-                for (int j = 0; j < 8; j++) mr[j] = h2u(byte_to_h2(j < 4 ? u2 : u3, j & 3));
-                tc::tmem_st8(lane_base + AM_OFF + 8 * (i & 1), mr);
-            }
-            tc::tmem_st32(lane_base + A_OFF + 32 * MEMBER, r);
-            // ---- second half (group MEMBER + 2): its arithmetic overlaps the TMEM store above
-            uint32_t r2[32];
-            dequant_group(r2, qb0, qb1, byte_to_h2(u1, 2 * MEMBER), byte_to_h2(u1, 2 * MEMBER + 1), k_lo, k_hi, k_magic);
-            tc::wait_st();
-            tc::fence_before();
-            __syncwarp();
-            if (lane == 0) {
-                tc::mbar_arrive(bar(A_FULL + 0));
-                if (MEMBER == 0) tc::mbar_arrive(bar(HDR_FULL + (i & 3)));
-            }
-            TCP_WAIT(2, bar(A_EMPTY + 1), (i & 1) ^ 1);
-            tc::fence_after();
-            tc::tmem_st32(lane_base + A_OFF + 64 + 32 * MEMBER, r2);
-            tc::wait_st();
-            tc::fence_before();
-            __syncwarp();
-            if (lane == 0) tc::mbar_arrive(bar(A_FULL + 1));
+            for (int j = 0; j < 8; j++) mr[j] = h2u(byte_to_h2(j < 4 ? u2 : u3, j & 3));
+            tc::tmem_st8(lane_base + AM_OFF + 8 * (i & 1), mr);
         }
+        tc::tmem_st32(lane_base + A_OFF + 32 * MEMBER, ra);
+        // ---- second half (group MEMBER + 2): its arithmetic overlaps the TMEM store above
+        uint32_t rb[32];
+        dequant_group(rb, qb0, qb1, byte_to_h2(u1, 2 * MEMBER), byte_to_h2(u1, 2 * MEMBER + 1), k_lo, k_hi, k_magic);
+        tc::wait_st();
+        tc::fence_before();
+        __syncwarp();
+        if (lane == 0) {
+            tc::mbar_arrive(bar(A_FULL + 0));
+            if (MEMBER == 0) tc::mbar_arrive(bar(HDR_FULL + (i & 3)));
+        }
+        TCP_WAIT(2, bar(A_EMPTY + 1), (i & 1) ^ 1);
+        tc::fence_after();
+        tc::tmem_st32(lane_base + A_OFF + 64 + 32 * MEMBER, rb);
+        // ---- next super-block's load + first group while that store is in flight (only if its weights have landed:
+        // the hand-off of this half must not wait for HBM)
+        const uint32_t nx = i + 1;
+        const bool more = nx < n_total;
+        const bool early = more && __all_sync(0xffffffffu, tc::mbar_test_wait(bar(W_FULL + nx % S_W), (nx / S_W) & 1));
+        if (early) fetch(nx);
+        tc::wait_st();
+        tc::fence_before();
+        __syncwarp();
+        if (lane == 0) tc::mbar_arrive(bar(A_FULL + 1));
+        if (more && !early) { TCP_WAIT(0, bar(W_FULL + nx % S_W), (nx / S_W) & 1); fetch(nx); }
     }
     if (PROF && blockIdx.x == 0 && q == 0 && lane == 0) {
         long long *o = p.prof + 16 + 8 * MEMBER;
-        o[0] = clock64() - pt0; o[1] = pw[0]; o[2] = pw[1]; o[3] = pw[2]; o[4] = pw[3]; o[5] = i;
+        o[0] = clock64() - pt0; o[1] = pw[0]; o[2] = pw[1]; o[3] = pw[2]; o[4] = pw[3]; o[5] = n_total;
     }
 }
 
@@ -275,6 +295,8 @@ __device__ __forceinline__ void epilogue_role(const TcArgs &p, uint8_t *smem, ui
     pdl_wait();                                                         // dT is read and the output planes are written below
     uint32_t i = 0;
     long long pw[3] = {0, 0, 0}; const long long pt0 = PROF ? clock64() : 0;
+    long long sec[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0}; long long ck = 0;
+#define EPI_CK(k) do { if (PROF) { const long long n_ = clock64(); sec[k] += n_ - ck; ck = n_; } } while (0)
     for (int item = blockIdx.x; item < p.n_items; item += gridDim.x) {
         const int ks = item / p.n_rb, rb = item % p.n_rb;
         const int sb0 = ks * p.spp, sb1 = min(p.nbr, sb0 + p.spp);
@@ -287,6 +309,7 @@ __device__ __forceinline__ void epilogue_role(const TcArgs &p, uint8_t *smem, ui
         float dxa = va ? __ldg(p.dT + (int64_t)sb0 * EB_DT_PITCH + c_base + lane) : 0.f;
         float dxb = vb ? __ldg(p.dT + (int64_t)sb0 * EB_DT_PITCH + c_base + 32 + lane) : 0.f;
         for (int sb = sb0; sb < sb1; sb++, i++) {
+            if (PROF) ck = clock64();
             float *dxs = dx_sm + (i & 1) * 40;
             dxs[lane] = dxa;
             if (lane < 8) dxs[32 + lane] = dxb;
@@ -294,12 +317,17 @@ __device__ __forceinline__ void epilogue_role(const TcArgs &p, uint8_t *smem, ui
                 if (va) dxa = __ldg(p.dT + (int64_t)(sb + 1) * EB_DT_PITCH + c_base + lane);
                 if (vb) dxb = __ldg(p.dT + (int64_t)(sb + 1) * EB_DT_PITCH + c_base + 32 + lane);
             }
+            EPI_CK(0);
             TCP_WAIT(0, bar(HDR_FULL + (i & 3)), (i >> 2) & 1);
+            EPI_CK(1);
             const float2 h = hdr_sm[(i & 3) * 128 + row];
             const unsigned long long hd2 = pk2(h.x, h.x), hm2 = pk2(-h.y, -h.y);
             const uint32_t s = i & 1;
             TCP_WAIT(1, bar(D_FULL + s), (i >> 1) & 1);
+            EPI_CK(2);
+            if (PROF && i == 0 && blockIdx.x == 0 && warp == 12 && lane == 0) p.prof[64 + 6] = clock64();
             tc::fence_after();
+            EPI_CK(3);
             const long long te_ = PROF ? clock64() : 0;
             __syncwarp();
             const uint32_t t_main = lane_base + s * (FMT == 0 ? D_STRIDE : D6_STRIDE) + c_base, t_min = t_main + D_MIN;
@@ -324,7 +352,9 @@ __device__ __forceinline__ void epilogue_role(const TcArgs &p, uint8_t *smem, ui
                 tc::tmem_ld16(t_main, vm);
                 if (FMT == 0) tc::tmem_ld16(t_min, vn);
                 tc::wait_ld();
+                EPI_CK(4);
                 fold4(vm, vn, 0, 4);
+                EPI_CK(5);
             }
             {
                 uint32_t vm[16], vn[16], wm[8], wn[8];
@@ -332,25 +362,42 @@ __device__ __forceinline__ void epilogue_role(const TcArgs &p, uint8_t *smem, ui
                 if (FMT == 0) tc::tmem_ld16(t_min + 16, vn);
                 if (tail) { tc::tmem_ld8(t_main + 32, wm); if (FMT == 0) tc::tmem_ld8(t_min + 32, wn); }
                 tc::wait_ld();
+                EPI_CK(6);
                 tc::fence_before();
                 __syncwarp();
                 if (lane == 0) tc::mbar_arrive(bar(D_EMPTY + s));       // accumulators are in registers: hand the stage back
+                EPI_CK(7);
                 fold4(vm, vn, 16, 4);
                 if (tail) fold4(wm, wn, 32, 2);
+                EPI_CK(8);
             }
             if (PROF) pw[2] += clock64() - te_;
         }
+        const long long tst_ = PROF ? clock64() : 0;
+        // plane store: lanes = consecutive weight rows -> every warp store is one full 128-byte line; one running pointer,
+        // warp-uniform column count (40 stores with per-store address arithmetic and branches cost ~3000 clk per item)
         const int64_t grow = (int64_t)rb * 128 + row;
         if (grow < p.N) {
-            float *o = p.out + (int64_t)ks * p.T * p.N + grow;
+            float *o = p.out + ((int64_t)ks * p.T + c_base) * p.N + grow;
+            const int64_t ld = p.N;
+            const int nc = min(40, p.T - c_base);
+            if (nc == 40) {
 #pragma unroll
-            for (int c = 0; c < 40; c++) {
-                const uint32_t bits = (c & 1) ? (uint32_t)(acc2[c >> 1] >> 32) : (uint32_t)acc2[c >> 1];
-                if (c_base + c < p.T) o[(int64_t)(c_base + c) * p.N] = __uint_as_float(bits);
+                for (int c = 0; c < 20; c++) { o[0] = __uint_as_float((uint32_t)acc2[c]); o[ld] = __uint_as_float((uint32_t)(acc2[c] >> 32)); o += 2 * ld; }
+            } else {
+#pragma unroll
+                for (int c = 0; c < 20; c++) {
+                    if (2 * c < nc) o[0] = __uint_as_float((uint32_t)acc2[c]);
+                    if (2 * c + 1 < nc) o[ld] = __uint_as_float((uint32_t)(acc2[c] >> 32));
+                    o += 2 * ld;
+                }
             }
         }
+        if (PROF && blockIdx.x == 0 && warp == 12 && lane == 0) p.prof[89] += clock64() - tst_;
     }
-    if (PROF && blockIdx.x == 0 && warp == 12 && lane == 0) { long long *o = p.prof + 32; o[0] = clock64() - pt0; o[1] = pw[0]; o[2] = pw[1]; o[3] = pw[2]; }
+    if (PROF && blockIdx.x == 0 && warp == 12 && lane == 0) p.prof[64 + 7] = clock64();
+    if (PROF && blockIdx.x == 0 && warp == 12 && lane == 0) { long long *o = p.prof + 32; o[0] = clock64() - pt0; o[1] = pw[0]; o[2] = pw[1]; o[3] = pw[2]; for (int k = 0; k < 9; k++) p.prof[80 + k] = sec[k]; }
+#undef EPI_CK
 }
 
 // FMT 0 = Q4_K (tmW = the 144-byte blocks, tmBS = 16-element activation sums); FMT 1 = Q6_K (tmW = ql plane, tmQH / tmSC = qh / scales planes)
@@ -366,6 +413,8 @@ mmq_tc_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ C
     auto bar = [&](int i) { return bar0 + 8u * i; };
     volatile uint32_t *tmem_slot = (volatile uint32_t *)(smem + OFF_BAR + 8 * N_BARS);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+#define TCP_STAMP(k) do { if (PROF && blockIdx.x == 0) p.prof[64 + (k)] = clock64(); } while (0)
+    if (threadIdx.x == 0) TCP_STAMP(0);
 
     if (threadIdx.x == 0) {
         for (int i = 0; i < NSW; i++) { tc::mbar_init(bar(W_FULL + i), 1); tc::mbar_init(bar(W_EMPTY + i), 8); }
@@ -385,12 +434,31 @@ mmq_tc_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ C
     __syncthreads();
     tc::fence_after();
     const uint32_t tmem = *tmem_slot;
+    if (threadIdx.x == 0) TCP_STAMP(1);
     pdl_trigger();                                  // the next kernel may start its own prologue on SMs this grid has left
 
     if (warp < 4) {
+        // ------------------------------------------------------------ weight producer (warp 0): the first tile goes out
+        // before anything else (the register hand-over below costs several hundred cycles)
+        auto issue_w = [&](uint32_t s, int sb, int rb) {
+            if (FMT == 0) {
+                tc::mbar_expect_tx(bar(W_FULL + s), W_STAGE);
+                tc::tma_load_2d(sbase + OFF_W + s * W_STAGE, &tmW, sb * 144, rb * 128, bar(W_FULL + s));
+            } else {
+                const uint32_t dst = sbase + OFF_W + s * W6_STAGE;
+                tc::mbar_expect_tx(bar(W_FULL + s), W6_STAGE);
+                tc::tma_load_2d(dst, &tmW, sb * 128, rb * 128, bar(W_FULL + s));
+                tc::tma_load_2d(dst + W6_QH, &tmQH, sb * 64, rb * 128, bar(W_FULL + s));
+                tc::tma_load_2d(dst + W6_SC, &tmSC, sb * 16, rb * 128, bar(W_FULL + s));
+            }
+        };
+        if (warp == 0 && lane == 0 && (int)blockIdx.x < p.n_items) {
+            TCP_STAMP(2);
+            issue_w(0, ((int)blockIdx.x / p.n_rb) * p.spp, (int)blockIdx.x % p.n_rb);
+        }
+        __syncwarp();
         tc::setmaxnreg_dec<40>();                   // hand registers to the epilogue warps
         if (warp == 0) {
-            // ------------------------------------------------------------ weight producer
             if (lane == 0) {
                 uint32_t i = 0;
                 long long pw[1] = {0}; const long long pt0 = PROF ? clock64() : 0;
@@ -398,18 +466,10 @@ mmq_tc_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ C
                     const int ks = item / p.n_rb, rb = item % p.n_rb;
                     const int sb0 = ks * p.spp, sb1 = min(p.nbr, sb0 + p.spp);
                     for (int sb = sb0; sb < sb1; sb++, i++) {
+                        if (i == 0) continue;           // already in flight
                         const uint32_t s = i % NSW, ph = (i / NSW) & 1;
                         TCP_WAIT(0, bar(W_EMPTY + s), ph ^ 1);
-                        if (FMT == 0) {
-                            tc::mbar_expect_tx(bar(W_FULL + s), W_STAGE);
-                            tc::tma_load_2d(sbase + OFF_W + s * W_STAGE, &tmW, sb * 144, rb * 128, bar(W_FULL + s));
-                        } else {
-                            const uint32_t dst = sbase + OFF_W + s * W6_STAGE;
-                            tc::mbar_expect_tx(bar(W_FULL + s), W6_STAGE);
-                            tc::tma_load_2d(dst, &tmW, sb * 128, rb * 128, bar(W_FULL + s));
-                            tc::tma_load_2d(dst + W6_QH, &tmQH, sb * 64, rb * 128, bar(W_FULL + s));
-                            tc::tma_load_2d(dst + W6_SC, &tmSC, sb * 16, rb * 128, bar(W_FULL + s));
-                        }
+                        issue_w(s, sb, rb);
                     }
                 }
                 if (PROF && blockIdx.x == 0) { p.prof[0] = clock64() - pt0; p.prof[1] = pw[0]; }
@@ -466,6 +526,7 @@ mmq_tc_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ C
 #pragma unroll
                     for (int h = 0; h < 2; h++) {
                         TCP_WAIT(3, bar(A_FULL + h), i & 1);
+                        if (i == 0 && h == 0 && lane == 0) TCP_STAMP(4);
                         tc::fence_after();
                         if (leader) {
                             const uint64_t b_lo = bdesc + (uint64_t)((2 * h) * (B_BOX >> 4)), b_hi = bdesc + (uint64_t)((2 * h + 1) * (B_BOX >> 4));
@@ -477,7 +538,7 @@ mmq_tc_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ C
                                 tc::mma_f16_ts_x8(d_main, tmem + A6_OFF + A6_HALF * h + A6_SECOND, b_lo, b_hi, idesc, 1);
                             }
                             tc::mma_commit(bar(A_EMPTY + h));
-                            if (h == 1) { tc::mma_commit(bar(B_EMPTY + s)); tc::mma_commit(bar(D_FULL + s)); }
+                            if (h == 1) { tc::mma_commit(bar(B_EMPTY + s)); tc::mma_commit(bar(D_FULL + s)); if (i == 0) TCP_STAMP(5); }
                         }
                         __syncwarp();
                     }
@@ -501,6 +562,8 @@ mmq_tc_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ C
     tc::fence_before();
     __syncthreads();
     if (warp == 3) tc::tmem_dealloc(tmem, 512);
+    if (threadIdx.x == 96 + 0) TCP_STAMP(8);
+#undef TCP_STAMP
 }
 // ------------------------------------------------------------------ host side
 typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
@@ -608,6 +671,11 @@ int eb_mmq_tc_parts(int type, const void *W, int64_t N, int64_t K, const ActQ &a
                 "DQ0 total %lld w_full %lld a_empty0 %lld a_empty1 %lld - %lld n=%lld | DQ1 total %lld w_full %lld a_e0 %lld a_e1 %lld - %lld | EPI total %lld hdr %lld d_full %lld work %lld\n",
                 (long long)N, (long long)K, a.T, ks, p.n_items, grid, h[0], h[1], h[8], h[9], h[10], h[11], h[12], h[16], h[17], h[18], h[19], h[20], h[21],
                 h[24], h[25], h[26], h[27], h[28], h[32], h[33], h[34], h[35]);
+        fprintf(stderr, "[tc epi sections] top %lld | hdr wait %lld | d_full wait %lld | fence_after %lld | ld1 %lld | fold1 %lld | ld2 %lld | arrive %lld | fold2 %lld | final stores %lld\n",
+                h[80], h[81], h[82], h[83], h[84], h[85], h[86], h[87], h[88], h[89]);
+        cudaMemsetAsync(prof_buf + 89, 0, 8, st);
+        fprintf(stderr, "[tc timeline clk since entry] setup %lld | first TMA issue %lld | DQ sees W %lld | MMA sees A %lld | first D commit %lld | EPI sees D %lld | EPI done %lld | exit %lld\n",
+                h[65] - h[64], h[66] - h[64], h[67] - h[64], h[68] - h[64], h[69] - h[64], h[70] - h[64], h[71] - h[64], h[72] - h[64]);
     }
     return EB_OK;
 }
