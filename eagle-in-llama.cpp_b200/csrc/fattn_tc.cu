@@ -36,6 +36,7 @@ struct FtArgs {
     int T, H, nsplit;
     float scale_log2;
     float *out, *part_o, *part_ml;
+    long long *prof;        // EB_FA_PROF=1: per-section cycle totals of CTA (0,0)
 };
 
 __device__ __forceinline__ float ex2(float x) { float y; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
@@ -60,6 +61,7 @@ fattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int h = blockIdx.x, split = blockIdx.y;
     const int nsw = (p.T + 31) >> 5;                                         // softmax warps with at least one live row
+    if (p.prof && blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 128) p.prof[10] = clock64();
 
     if (threadIdx.x == 0) {
         mbar_init(bars + FB_Q * 8, 1);
@@ -81,6 +83,7 @@ fattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     // everything above overlapped the predecessor's tail (PDL); lengths, Q, K/V and the tree bits are earlier kernels' outputs
     pdl_trigger();
     pdl_wait();
+    if (p.prof && blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 128) p.prof[11] = clock64();
     int n_prefix = p.n_prefix, n_kv = p.n_kv;
     if (p.ctl) { n_prefix = p.ctl->n_prefix; n_kv = min(p.n_ctx, n_prefix + p.ctl->n_tree); }
     const int n_tiles = (n_kv + FT_TILE - 1) / FT_TILE, tps = (n_tiles + p.nsplit - 1) / p.nsplit;
@@ -151,14 +154,19 @@ fattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         if (live) { const uint4 w = *(const uint4 *)(p.tree_bits + row * 4); tb[0] = w.x; tb[1] = w.y; tb[2] = w.z; tb[3] = w.w; }
         const float c = p.scale_log2;
         float m = -INFINITY, l = 0.f;                                       // m in raw score units (before the scale)
+        const bool prof = p.prof && blockIdx.x == 0 && blockIdx.y == 0 && warp == 4 && lane == 0;
+        long long sec[6] = {0, 0, 0, 0, 0, 0}, ck = prof ? clock64() : 0; const long long t_start = ck;
+#define FA_CK(k) do { if (prof) { const long long n_ = clock64(); sec[k] += n_ - ck; ck = n_; } } while (0)
         for (int i = 0; i < n; i++) {
             const int b = i & 1;
             mbar_wait(bars + (FB_S_FULL + b) * 8, (i >> 1) & 1);
+            FA_CK(0);
             fence_after();
             const uint32_t ts = lane_base + b * 128;
             uint32_t sr[4][32];
             tmem_ld32(ts, sr[0]); tmem_ld32(ts + 32, sr[1]); tmem_ld32(ts + 64, sr[2]); tmem_ld32(ts + 96, sr[3]);
             wait_ld();
+            FA_CK(1);
             const int cb0 = (t0 + i) * FT_TILE;
             if (cb0 + FT_TILE > n_prefix) {                                  // tile touches the tree cells (or the cache tail)
 #pragma unroll
@@ -168,11 +176,16 @@ fattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
                     for (int k = 0; k < 32; k++) if (!((vw >> k) & 1u)) sr[ch][k] = 0xff800000u;   // -inf
                 }
             }
-            float tm = -INFINITY;
+            // 8 independent max chains (one dependent chain of 128 FMNMX costs ~600 clk on a single warp per scheduler)
+            float tmx[8];
+#pragma unroll
+            for (int a = 0; a < 8; a++) tmx[a] = -INFINITY;
 #pragma unroll
             for (int ch = 0; ch < 4; ch++)
 #pragma unroll
-                for (int k = 0; k < 32; k++) tm = fmaxf(tm, __uint_as_float(sr[ch][k]));
+                for (int k = 0; k < 32; k++) tmx[k & 7] = fmaxf(tmx[k & 7], __uint_as_float(sr[ch][k]));
+            const float tm = fmaxf(fmaxf(fmaxf(tmx[0], tmx[1]), fmaxf(tmx[2], tmx[3])), fmaxf(fmaxf(tmx[4], tmx[5]), fmaxf(tmx[6], tmx[7])));
+            FA_CK(2);
             // running max: O is rescaled only when the max moves by more than 2^8 (P stays within f16 range, the row sum is f32)
             const bool grow = m != -INFINITY && (tm - m) * c > 8.f;
             if (i > 0 && __any_sync(0xffffffffu, grow)) {
@@ -193,24 +206,28 @@ fattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
             } else if (m == -INFINITY) {
                 m = tm;
             }
+            FA_CK(3);
             const float base = m == -INFINITY ? 0.f : m * c;
-            float rs = 0.f;
+            float rs[4] = {0.f, 0.f, 0.f, 0.f};                                // independent partial row sums (ILP)
             uint32_t pk[2][32];
 #pragma unroll
             for (int ch = 0; ch < 4; ch++)
 #pragma unroll
                 for (int k = 0; k < 32; k += 2) {
                     const float p0 = ex2(fmaf(__uint_as_float(sr[ch][k]), c, -base)), p1 = ex2(fmaf(__uint_as_float(sr[ch][k + 1]), c, -base));
-                    rs += p0 + p1;
+                    rs[(k >> 1) & 3] += p0 + p1;
                     pk[ch >> 1][(ch & 1) * 16 + (k >> 1)] = pack_h2(p0, p1);
                 }
-            l += rs;
+            l += (rs[0] + rs[1]) + (rs[2] + rs[3]);
+            FA_CK(4);
             tmem_st32(ts, pk[0]); tmem_st32(ts + 32, pk[1]);
             wait_st();
             fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(bars + (FB_P_READY + b) * 8);
+            FA_CK(5);
         }
+        if (prof) { for (int k = 0; k < 6; k++) p.prof[k] = sec[k]; p.prof[6] = n; p.prof[7] = clock64() - t_start; }
         // epilogue: O / l -> output (or the split's partial + (max, sum) in the log2 domain)
         float *dst = nullptr;
         if (live) {
@@ -222,6 +239,7 @@ fattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
             }
         }
         if (n > 0) { mbar_wait(bars + FB_O_DONE * 8, (n - 1) & 1); fence_after(); }
+        if (prof) p.prof[8] = clock64() - t_start;
         const float inv = l > 0.f ? 1.f / l : 0.f;
 #pragma unroll
         for (int ch = 0; ch < 4; ch++) {
@@ -235,6 +253,8 @@ fattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
             }
         }
     }
+    if (p.prof && blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 128) p.prof[9] = clock64();
+#undef FA_CK
     fence_before();
     __syncthreads();
     if (warp == 2) tmem_dealloc(tmem, 512);
@@ -279,6 +299,9 @@ int eb_fattn_tc(const __half *q16, const void *k, const void *v, int64_t kv_stri
     p.nsplit = eb_fattn_tc_nsplit(H, n_tiles_max);
     p.out = out; p.part_o = (float *)ws; p.part_ml = p.part_o + (size_t)H * p.nsplit * T * 128;
     if (p.nsplit > 1 && !ws) return eb_set_err(EB_ERR_ARG, "flash_attn: workspace required");
+    static long long *prof_buf = nullptr; static const int want_prof = getenv("EB_FA_PROF") ? 1 : 0;
+    if (want_prof && !prof_buf) { cudaMalloc((void **)&prof_buf, 64 * 8); cudaMemset(prof_buf, 0, 64 * 8); }
+    p.prof = want_prof ? prof_buf : nullptr;
     CUtensorMap tmQ, tmK, tmV;
     int rc;
     if ((rc = eb_tc_map_2d_f16(&tmQ, q16, (uint64_t)H * 128, (uint64_t)T, (uint64_t)H * 128 * 2, 64, 128))) return rc;
@@ -286,6 +309,11 @@ int eb_fattn_tc(const __half *q16, const void *k, const void *v, int64_t kv_stri
     if ((rc = eb_tc_map_2d_f16(&tmV, v, (uint64_t)H * 128, (uint64_t)n_cells, (uint64_t)kv_stride * 2, 64, 128))) return rc;
     eb_launch_pdl(fattn_tc_kernel, dim3(H, p.nsplit), dim3(256), FT_SMEM, st, tmQ, tmK, tmV, p);
     EB_CHECK_LAUNCH();
+    if (want_prof) {
+        long long h[16]; cudaStreamSynchronize(st); cudaMemcpy(h, prof_buf, sizeof(h), cudaMemcpyDeviceToHost);
+        fprintf(stderr, "[fa prof] T=%d H=%d nsplit=%d tiles=%lld | softmax warp: s_full wait %lld | ld %lld | mask+max %lld | rescale %lld | exp+pack %lld | st+arrive %lld | loop %lld | +o_done %lld | setup %lld | exit-entry %lld\n",
+                T, H, p.nsplit, h[6], h[0], h[1], h[2], h[3], h[4], h[5], h[7], h[8], h[11] - h[10], h[9] - h[10]);
+    }
     if (p.nsplit > 1) {
         // the caller's wo GEMM wants the Q8_K grid: merge the splits and quantise in one pass, skipping the f32 output
         if (aq && aq->kq && aq->qs && H % 2 == 0 && aq->K == (int64_t)H * 128) { eb_fattn_combine_quant(p.part_o, p.part_ml, T, H, p.nsplit, *aq, st); if (quantized) *quantized = 1; }
