@@ -292,6 +292,7 @@ __device__ __forceinline__ void epilogue_role(const TcArgs &p, uint8_t *smem, ui
     const float2 *hdr_sm = (const float2 *)(smem + OFF_HDR);
     float *dx_sm = (float *)(smem + OFF_DX) + (warp - 12) * 80;
     const bool tail = c_base + 32 < p.T;                                // columns [32,40) of this warp hold tokens
+    const bool small = p.npad <= 16;
     pdl_wait();                                                         // dT is read and the output planes are written below
     uint32_t i = 0;
     long long pw[3] = {0, 0, 0}; const long long pt0 = PROF ? clock64() : 0;
@@ -347,6 +348,19 @@ __device__ __forceinline__ void epilogue_role(const TcArgs &p, uint8_t *smem, ui
                     acc2[a + 1] = fma2(dx.y, t1, acc2[a + 1]);
                 }
             };
+            if (small) {                                                // T <= 16: 16 accumulator columns, owned by the hf = 0 warps
+                uint32_t vm[16], vn[16];
+                if (hf == 0) {
+                    tc::tmem_ld16(t_main, vm);
+                    if (FMT == 0) tc::tmem_ld16(t_min, vn);
+                    tc::wait_ld();
+                }
+                tc::fence_before();
+                __syncwarp();
+                if (lane == 0) tc::mbar_arrive(bar(D_EMPTY + s));
+                if (hf == 0) fold4(vm, vn, 0, 4);
+                continue;
+            }
             {
                 uint32_t vm[16], vn[16];
                 tc::tmem_ld16(t_main, vm);
@@ -611,7 +625,10 @@ int eb_mmq_tc_supported(int type, int64_t N, int64_t K, int T) {
     static const int off = getenv("EB_NO_TC") ? 1 : 0;
     if (off || !g_encode) return 0;
     static const int off6 = getenv("EB_NO_TC_Q6") ? 1 : 0;
-    return (type == EB_Q4_K || (type == EB_Q6_K && !off6)) && K % 256 == 0 && N >= 128 && T > 8 && T <= 80;
+    // T <= 8 (draft head) stays on the dp4a / mma.sync kernels: measured 17.9 us vs 26.0 us for 22016 x 4096 at T = 8 — this
+    // kernel is bound by its dequant role, not by N.  EB_TC_TMIN=1 routes small batches here (N = 16 MMAs) for experiments.
+    static const int tmin = getenv("EB_TC_TMIN") ? atoi(getenv("EB_TC_TMIN")) : 9;
+    return (type == EB_Q4_K || (type == EB_Q6_K && !off6)) && K % 256 == 0 && N >= 128 && T >= tmin && T <= 80;
 }
 
 // split-K factor: planes <= 8, minimise rounds x (super-blocks per item + pipeline fill)

@@ -208,3 +208,46 @@ def test_fixed_accept_round_properties(eb):
             seq.append((list(res.tokens[:n]), res.bonus))
         runs.append(seq); s.free()
     assert runs[0] == runs[1]
+
+
+def test_forward_7b_width_one_layer(eb):
+    """One target layer at the BASELINE width (E 4096, 32 heads, F 11008; Q4_K_M mix incl. the Q6_K attn_v / ffn_down / output)
+    on a 65-row tree after a short prefix: exercises the launch shapes of the headline step — fused wq|wk and gate|up
+    tcgen05 GEMMs, the Q6_K tcgen05 GEMM, the register-resident norm+quant (512 threads per row), 32-head tcgen05
+    attention with its KV splits and the fused split-merge + quantisation — against the oracle."""
+    hp = dict(E=4096, H=32, F=11008, V=1024, L=1)
+    rng = np.random.default_rng(77)
+
+    def mat(rows, cols, t):
+        return (t, fx.random_blocks(t, rows * cols, rng))
+
+    def vec(n):
+        return (po.F32, (1 + rng.normal(0, 0.02, n)).astype(np.float32).view(np.uint8).reshape(-1).copy())
+
+    E, F, V = hp["E"], hp["F"], hp["V"]
+    layer = {po.L_ATTN_NORM: vec(E), po.L_WQ: mat(E, E, po.Q4_K), po.L_WK: mat(E, E, po.Q4_K), po.L_WV: mat(E, E, po.Q6_K),
+             po.L_WO: mat(E, E, po.Q4_K), po.L_FFN_NORM: vec(E), po.L_GATE: mat(F, E, po.Q4_K), po.L_UP: mat(F, E, po.Q4_K),
+             po.L_DOWN: mat(E, F, po.Q6_K)}
+    tgt = {"hparams": dict(**hp, eps=1e-5, freq_base=10000.0, is_eagle=False),
+           "globals": {po.T_TOK_EMBD: mat(V, E, po.Q4_K), po.T_OUTPUT_NORM: vec(E), po.T_OUTPUT: mat(V, E, po.Q6_K)}, "layers": [layer]}
+    o = po.oracle(); n_ctx = 512
+    mo = fx.to_cpu_model(o, tgt); kv = o._g("kv_new")(1, E, n_ctx)
+    mg = fx.to_gpu_model(eb, tgt)
+    s = eb.Session(mg, None, n_ctx=n_ctx, max_nodes=65, use_graph=False)
+    P, T = 300, 65
+    prompt = rng.integers(3, V, P).astype(np.int32)
+    po.set_fattn_acc_f32(1)
+    # prefix through both paths in chunks of 100 rows (the oracle forward is O(T) GEMV work per row)
+    for c0 in range(0, P, 100):
+        ids = prompt[c0:c0 + 100]; n = len(ids)
+        vis = np.zeros((n, n_ctx), np.uint8); vis[:, :c0] = 1; vis[:, c0:c0 + n] = np.tril(np.ones((n, n), np.uint8))
+        o.forward(mo, kv, ids, np.arange(c0, c0 + n), None, c0, n_ctx, vis, E, V)
+        s.forward(0, ids, np.arange(c0, c0 + n)); s.commit(0, n)
+    par = fx.tree_parents(T, rng, 6)
+    toks = rng.integers(3, V, T).astype(np.int32); pos = (P + fx.tree_depths(par)).astype(np.int32)
+    lo, fo = o.forward(mo, kv, toks, pos, None, P, n_ctx, fx.vis_matrix(par, P, n_ctx), E, V)
+    po.set_fattn_acc_f32(0)
+    lg, fg = s.forward(0, toks, pos, parent=par)
+    assert rel_max(lg, lo) < MODEL_REL and nmse(lg, lo) < MODEL_NMSE and nmse(fg, fo) < MODEL_NMSE
+    assert greedy_agree(lg, lo, REF_TIE)[0] == 0
+    s.free()

@@ -164,3 +164,26 @@ def test_top_k_argmax(eb):
     assert np.array_equal(eb.argmax(x), np.array([np.flatnonzero(r == r.max())[0] for r in x], np.int32))
     ids1, _, p1 = eb.top_k(np.log(np.array([[0.1, 0.2, 0.3, 0.4]], np.float32)), 1)   # R/tests/test-sampling.cpp:317
     assert ids1[0, 0] == 3 and abs(p1[0, 0] - 1) < 1e-6
+
+
+def test_mul_mat_q6_K_extreme_blocks(eb):
+    """Q6_K at the corners of its range: scales -128 / 127, quants 0 / 63 (|sc * (q - 32)| up to 4096) against activations that
+    quantise to +-127 everywhere.  The tcgen05 path feeds the weight as two exact f16 addends (sc*ql and 16*sc*(qh-2)); the
+    per-super-block integer sum reaches 1.3e8 > 2^24 here, where the f32 accumulation of exact products may round (<= 1 ulp
+    per add) — the result must still match the CPU's int32 sum to f32 accuracy."""
+    rng = np.random.default_rng(5)
+    N, K, T = 256, 2048, 33
+    nb = N * K // 256
+    raw = np.zeros((nb, 210), np.uint8)
+    pick = rng.integers(0, 4, nb)
+    raw[:, 0:128] = np.where(pick[:, None] & 1, 0xFF, 0x00)                       # ql nibbles all 15 or all 0
+    raw[:, 128:192] = np.where(pick[:, None] & 1, 0xFF, 0x00)                     # qh all 3 or all 0 -> q = 63 or 0
+    raw[:, 192:208] = np.where(pick[:, None] & 2, 0x80, 0x7F)                     # scales -128 or 127
+    raw[:, 208:210] = np.frombuffer(np.float16(2.0 ** -12).tobytes(), np.uint8)           # d = 2^-12
+    X = np.where(rng.random((T, K)) < 0.5, -1.0, 1.0).astype(np.float32)
+    X[1] = 1.0; X[2] = -1.0                                                        # every product with the same sign
+    w = eb.Weights(po.Q6_K, raw.reshape(-1), N, K)
+    got = eb.mul_mat(w, X)
+    want = po.oracle().mul_mat(po.Q6_K, raw.reshape(-1), N, K, X)
+    assert np.abs(want).max() > 1e3                                                # rows 1, 2: |isum| = 1.3e8 per super-block
+    assert rel_max(got, want) < 2e-6
