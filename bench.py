@@ -30,7 +30,7 @@ N_PAST0 = 4096 - 65                                       # KV cells committed b
 TREE = dict(max_nodes=65, n_branch=8, n_draft=64, max_depth=10, top_k=10, p_split=0.1)
 FIXED_ACCEPT = 3
 Q4_K_BPW, Q6_K_BPW = 144 / 256, 210 / 256
-ROOFLINE_TRAFFIC_BYTES = None   # filled from profiles/r1c_summary.md (ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum per launch)
+ROOFLINE_TRAFFIC_BYTES = 51.65e6   # profiles/r1c_summary.md: ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum per launch, N=22016 K=4096 T=65
 
 
 def q4_k_m_more_bits(l, n):                               # R/src/llama-quant.cpp:129-131
