@@ -292,7 +292,6 @@ __device__ __forceinline__ void epilogue_role(const TcArgs &p, uint8_t *smem, ui
     const float2 *hdr_sm = (const float2 *)(smem + OFF_HDR);
     float *dx_sm = (float *)(smem + OFF_DX) + (warp - 12) * 80;
     const bool tail = c_base + 32 < p.T;                                // columns [32,40) of this warp hold tokens
-    const bool small = p.npad <= 16;
     pdl_wait();                                                         // dT is read and the output planes are written below
     uint32_t i = 0;
     long long pw[3] = {0, 0, 0}; const long long pt0 = PROF ? clock64() : 0;
@@ -348,19 +347,6 @@ __device__ __forceinline__ void epilogue_role(const TcArgs &p, uint8_t *smem, ui
                     acc2[a + 1] = fma2(dx.y, t1, acc2[a + 1]);
                 }
             };
-            if (small) {                                                // T <= 16: 16 accumulator columns, owned by the hf = 0 warps
-                uint32_t vm[16], vn[16];
-                if (hf == 0) {
-                    tc::tmem_ld16(t_main, vm);
-                    if (FMT == 0) tc::tmem_ld16(t_min, vn);
-                    tc::wait_ld();
-                }
-                tc::fence_before();
-                __syncwarp();
-                if (lane == 0) tc::mbar_arrive(bar(D_EMPTY + s));
-                if (hf == 0) fold4(vm, vn, 0, 4);
-                continue;
-            }
             {
                 uint32_t vm[16], vn[16];
                 tc::tmem_ld16(t_main, vm);
