@@ -9,6 +9,7 @@
 // Per super-block (K = 256):   Q4_K: 8 x mma.m16n8k32.u8.s8 per 8-column tile + 1 f16 MMA for the
 // min term (m_j x bsum_j, exact in f16/f32);   Q6_K: 16 x mma.m16n8k16.s8.s8 per tile.
 #include "common.cuh"
+#include <cstdlib>
 
 __device__ __forceinline__ void cp_async16(void *smem, const void *gmem) {
     const uint32_t s = (uint32_t)__cvta_generic_to_shared(smem);
@@ -268,10 +269,14 @@ int eb_mmq_supported(int type, int64_t N, int64_t K, int T) {
 }
 
 int eb_mmq_pick_ksplit(int type, int64_t N, int64_t K, int T) {
-    (void)type; (void)T;
+    (void)type;
     const int nbr = (int)(K / 256);
     const int64_t row_blocks = cdiv(N, 64);
-    const int target = eb_sm_count() * 3;
+    // CTAs per SM that stream concurrently: 3 fit when the activation tile is 9 x 8 columns; with one 8-column tile (T <= 8,
+    // draft head) 16 fit, and the kernel needs them all in flight to cover the HBM latency (each CTA walks its
+    // super-blocks serially)
+    static const int small_mult = getenv("EB_MMQ_SMALL_MULT") ? atoi(getenv("EB_MMQ_SMALL_MULT")) : 8;
+    const int target = eb_sm_count() * (T <= 8 ? small_mult : 3);
     int ks = (int)cdiv(target, row_blocks);
     if (ks > nbr / 2) ks = nbr / 2;          // at least 2 super-blocks per CTA
     if (ks > 8) ks = 8;
