@@ -407,7 +407,8 @@ mmq_tc_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ C
               const __grid_constant__ CUtensorMap tmQH, const __grid_constant__ CUtensorMap tmSC, TcArgs p) {
     constexpr int NSW = FMT == 0 ? S_W : S_W6;
     extern __shared__ uint8_t smem_raw[];
-    uint8_t *smem = (uint8_t *)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    // pointer arithmetic on the __shared__ array (not an integer round-trip) keeps the address space: LDS/STS instead of generic LD/ST
+    uint8_t *smem = smem_raw + ((1024u - (tc::smem_u32(smem_raw) & 1023u)) & 1023u);
     const uint32_t sbase = tc::smem_u32(smem);
     const uint32_t bar0 = sbase + OFF_BAR;
     auto bar = [&](int i) { return bar0 + 8u * i; };
