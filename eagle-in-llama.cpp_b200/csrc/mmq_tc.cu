@@ -239,34 +239,36 @@ __device__ __forceinline__ void dequant_q6_K(const TcArgs &p, uint8_t *smem, uin
             TCP_WAIT(0, bar(W_FULL + s), (i / S_W6) & 1);
             const uint8_t *st = smem + OFF_W + s * W6_STAGE;
             const uint8_t *qlp = st + row * 128, *qhp = st + W6_QH + row * 64;
-            uint4 xl[2][2], yh[2][2];
-#pragma unroll
-            for (int h = 0; h < 2; h++) {
-#pragma unroll
-                for (int c = 0; c < 2; c++) {
-                    xl[h][c] = *(const uint4 *)(qlp + (((4 * h + 2 * MEMBER + c) ^ sw_ql) << 4));
-                    yh[h][c] = *(const uint4 *)(qhp + (((2 * h + c) ^ sw_qh) << 4));
-                }
-            }
             const uint4 sc = *(const uint4 *)(st + W6_SC + row * 16);
-            __syncwarp();
-            if (lane == 0) tc::mbar_arrive(bar(W_EMPTY + s));
             const float dnow = dcur;
             if (MEMBER == 0 && sb + 1 < sb1 && grow < p.N) dcur = __half2float(__ldg(dp + sb + 1));
             const uint32_t scw[4] = {sc.x, sc.y, sc.z, sc.w};
 #pragma unroll
             for (int h = 0; h < 2; h++) {
-                uint32_t r1a[16], r2a[16], r1b[16], r2b[16];
-                dequant_group_q6<MEMBER>(r1a, r2a, xl[h][0], xl[h][1], yh[h][0], yh[h][1], sbyte_to_h2(scw[2 * h], 2 * MEMBER), sbyte_to_h2(scw[2 * h], 2 * MEMBER + 1),
+                // this half's 32 ql bytes + 32 qh bytes (loaded per half: keeps the role inside its 96 registers)
+                uint4 xl[2], yh[2];
+#pragma unroll
+                for (int c = 0; c < 2; c++) {
+                    xl[c] = *(const uint4 *)(qlp + (((4 * h + 2 * MEMBER + c) ^ sw_ql) << 4));
+                    yh[c] = *(const uint4 *)(qhp + (((2 * h + c) ^ sw_qh) << 4));
+                }
+                if (h == 1) {                                       // last read of the stage
+                    __syncwarp();
+                    if (lane == 0) tc::mbar_arrive(bar(W_EMPTY + s));
+                }
+                // group MEMBER: dequantise, store; group MEMBER + 2 is dequantised while those stores are in flight
+                uint32_t r1a[16], r2a[16];
+                dequant_group_q6<MEMBER>(r1a, r2a, xl[0], xl[1], yh[0], yh[1], sbyte_to_h2(scw[2 * h], 2 * MEMBER), sbyte_to_h2(scw[2 * h], 2 * MEMBER + 1),
                                          k_hi, k_q2, k_magic);
-                dequant_group_q6<MEMBER + 2>(r1b, r2b, xl[h][0], xl[h][1], yh[h][0], yh[h][1], sbyte_to_h2(scw[2 * h + 1], 2 * MEMBER), sbyte_to_h2(scw[2 * h + 1], 2 * MEMBER + 1),
-                                             k_hi, k_q2, k_magic);
                 TCP_WAIT(1 + h, bar(A_EMPTY + h), (i & 1) ^ 1);
                 tc::fence_after();
                 if (MEMBER == 0 && h == 0) hdr_sm[(i & 3) * 128 + row] = make_float2(dnow, 0.f);
                 const uint32_t a = lane_base + A6_OFF + A6_HALF * h;
-                tmem_st16(a + 16 * MEMBER, r1a); tmem_st16(a + 16 * (MEMBER + 2), r1b);
-                tmem_st16(a + A6_SECOND + 16 * MEMBER, r2a); tmem_st16(a + A6_SECOND + 16 * (MEMBER + 2), r2b);
+                tmem_st16(a + 16 * MEMBER, r1a); tmem_st16(a + A6_SECOND + 16 * MEMBER, r2a);
+                uint32_t r1b[16], r2b[16];
+                dequant_group_q6<MEMBER + 2>(r1b, r2b, xl[0], xl[1], yh[0], yh[1], sbyte_to_h2(scw[2 * h + 1], 2 * MEMBER), sbyte_to_h2(scw[2 * h + 1], 2 * MEMBER + 1),
+                                             k_hi, k_q2, k_magic);
+                tmem_st16(a + 16 * (MEMBER + 2), r1b); tmem_st16(a + A6_SECOND + 16 * (MEMBER + 2), r2b);
                 tc::wait_st();
                 tc::fence_before();
                 __syncwarp();
