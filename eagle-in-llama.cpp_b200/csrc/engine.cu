@@ -174,12 +174,6 @@ int eb_mul_mat_impl(int type, const void *W, int64_t N, int64_t K, const float *
     if (eb_mmq_supported(type, N, K, T)) return eb_mmq(type, W, N, K, a, y, partial, eb_mmq_pick_ksplit(type, N, K, T), st);
     return eb_mmvq(type, W, N, K, a, y, st);
 }
-// same activations for several weight matrices (wq/wk/wv, gate/up): quantise once
-static int mul_mat_preq(const DTensor &w, const ActQ &a, float *y, float *partial, cudaStream_t st) {
-    if (eb_mmq_supported(w.type, w.rows, w.cols, a.T)) return eb_mmq(w.type, w.data, w.rows, w.cols, a, y, partial, eb_mmq_pick_ksplit(w.type, w.rows, w.cols, a.T), st);
-    return eb_mmvq(w.type, w.data, w.rows, w.cols, a, y, st);
-}
-static int kq_of(const DTensor &w) { return w.type == EB_Q4_K || w.type == EB_Q6_K; }
 
 // ------------------------------------------------------------------ session
 static int ws_alloc(Workspace &w, const eb_model *m, int Tmax, int n_ctx) {
@@ -271,27 +265,31 @@ static int mm_parts(const DTensor &w, const ActQ &a, float *planes, int *ks, cud
 static int grid_of(const DTensor &w) { return w.type == EB_Q4_K || w.type == EB_Q6_K; }
 
 static int forward_dev(const eb_model *m, KVCache &kv, Workspace &w, const int32_t *tokens, const int32_t *pos, const uint32_t *bits,
-                       const float *hidden, const FwdCtl *ctl, int T, bool want_logits, cudaStream_t st) {
+                       const float *hidden, const FwdCtl *ctl, int T, bool want_logits, cudaStream_t st, int *logit_ks = nullptr) {
     const int E = m->E, H = m->H, F = m->F, D = E / H;
-    const int64_t TE = (int64_t)T * E;
     int rc;
 #define RC(x) do { rc = (x); if (rc) return rc; } while (0)
     const DTensor &emb = m->g[EB_T_TOK_EMBD];
     RC(eb_get_rows_dev(emb.type, emb.data, emb.rows, E, tokens, T, w.x, st));
+    const float *pend = nullptr; int pend_ks = 0;          // GEMM planes not yet folded into x (down projection; fc for the head)
+    const float *pend_bias = nullptr;
     if (m->is_eagle) {
-        RC(eb_concat2_impl(w.x, hidden, w.cat, E, T, st));
+        // cur = relu(fc([embd | hidden]) + bias): the concatenation is quantised straight into fc's activation grid, the
+        // bias + ReLU is applied by the first layer's norm kernel while it sums the fc planes
         const DTensor &fc = m->g[EB_T_FC];
-        RC(eb_mul_mat_impl(fc.type, fc.data, E, 2 * E, w.cat, T, w.cur, w.actq, w.partial, st));
-        RC(eb_bias_relu_impl(w.cur, (const float *)m->g[EB_T_FC_BIAS].data, w.x, TE, E, st));
+        ActQ ac = eb_actq_carve(w.actq2, grid_of(fc), 2 * E, T);
+        RC(eb_concat_quant(w.x, hidden, E, ac, st));
+        RC(mm_parts(fc, ac, w.pup, &pend_ks, st));
+        pend = w.pup; pend_bias = (const float *)m->g[EB_T_FC_BIAS].data;
     }
     RC(eb_rope_table(pos, D, T, m->freq_base, w.rope_tab, st));
-    const float *pend = nullptr; int pend_ks = 0;          // down-projection planes not yet added to x
     for (int l = 0; l < m->L; l++) {
         const std::vector<DTensor> &t = m->layers[l];
         // x += pending; cur = rms_norm(x) * attn_norm -> activation grid of wq
         const int gq = grid_of(t[EB_L_WQ]);
         ActQ a = eb_actq_carve(w.actq, gq, E, T);
-        RC(eb_resid_norm_quant(w.x, pend, pend_ks, (const float *)t[EB_L_ATTN_NORM].data, m->eps, E, T, a, nullptr, st));
+        RC(eb_resid_norm_quant(w.x, pend, pend_ks, (const float *)t[EB_L_ATTN_NORM].data, m->eps, E, T, a, nullptr, st, pend_bias));
+        pend_bias = nullptr;
         if (grid_of(t[EB_L_WK]) != gq || grid_of(t[EB_L_WV]) != gq) return eb_set_err(EB_ERR_UNSUPPORTED, "layer %d: wq/wk/wv mix K-quant and 32-block formats", l);
         const LayerFuse &fu = m->fuse[l];
         PlaneRef rq, rk, rv;
@@ -340,7 +338,10 @@ static int forward_dev(const eb_model *m, KVCache &kv, Workspace &w, const int32
     ActQ al = eb_actq_carve(w.actq, grid_of(o), E, T);
     if (!want_logits) al.qs = nullptr;
     RC(eb_resid_norm_quant(w.x, pend, pend_ks, (const float *)m->g[EB_T_OUTPUT_NORM].data, m->eps, E, T, al, w.feat, st));
-    if (want_logits) {
+    if (want_logits && logit_ks) {
+        // the caller's top-k / argmax sums the lm_head's split-K planes [ks][T][V] (w.partial) itself
+        RC(mm_parts(o, al, w.partial, logit_ks, st));
+    } else if (want_logits) {
         int kl_;
         if (eb_mmq_tc_supported(o.type, o.rows, o.cols, T)) {
             RC(eb_mmq_tc_parts(o.type, o.data, o.rows, o.cols, al, w.partial, &kl_, st));
@@ -442,7 +443,11 @@ extern "C" int eb_session_synth_kv(eb_session *s, int n_past, uint64_t seed) {
 // ------------------------------------------------------------------ the round
 static int verify_dev(eb_session *s, int T, cudaStream_t st) {
     SpecState *d = s->state;
-    return forward_dev(s->tgt, s->kv_t, s->ws_t, d->tokens, d->pos, d->tree_bits, nullptr, &d->ctl_tgt, T, true, st);
+    // tree-verify forward + per-node greedy token; the argmax sums the lm_head's split-K planes, so it belongs to the step
+    int ks = 1;
+    int rc = forward_dev(s->tgt, s->kv_t, s->ws_t, d->tokens, d->pos, d->tree_bits, nullptr, &d->ctl_tgt, T, true, st, &ks);
+    if (rc) return rc;
+    return eb_argmax_impl(s->ws_t.partial, T, s->tgt->V, s->best, st, ks, (int64_t)T * s->tgt->V);
 }
 static int round_dev(eb_session *s, cudaStream_t st) {
     SpecState *d = s->state; const SpecCfg &c = s->cfg; const int E = s->tgt->E, V = s->tgt->V;
@@ -453,14 +458,14 @@ static int round_dev(eb_session *s, cudaStream_t st) {
         // head forward over the nodes created at this depth (depth 0: the root)
         RC(eb_spec_gather_hidden(d, s->root_feat, s->node_feat, s->ws_h.hidden, E, c.n_branch, st));
         const bool last = depth == c.max_depth;
-        RC(forward_dev(s->head, s->kv_h, s->ws_h, d->dft_tokens, d->dft_pos, d->dft_bits, s->ws_h.hidden, &d->ctl_head, c.n_branch, !last, st));
+        int ks_h = 1;
+        RC(forward_dev(s->head, s->kv_h, s->ws_h, d->dft_tokens, d->dft_pos, d->dft_bits, s->ws_h.hidden, &d->ctl_head, c.n_branch, !last, st, &ks_h));
         RC(eb_spec_scatter_feat(d, s->ws_h.feat, s->node_feat, E, c.n_branch, st));
         if (last) break;
-        RC(eb_top_k_impl(s->ws_h.logits, c.n_branch, V, c.top_k, s->cand_ids, s->cand_vals, s->cand_p, st));
+        RC(eb_top_k_impl(s->ws_h.partial, c.n_branch, V, c.top_k, s->cand_ids, s->cand_vals, s->cand_p, st, ks_h, (int64_t)c.n_branch * V));
         RC(eb_spec_expand(d, c, s->cand_ids, s->cand_p, st));
     }
     RC(verify_dev(s, c.max_nodes, st));
-    RC(eb_argmax_impl(s->ws_t.logits, c.max_nodes, V, s->best, st));
     RC(eb_spec_accept(d, c, s->best, st));
     RC(eb_spec_compact(d, s->kv_t.k, s->kv_t.v, s->stage, s->kv_t.layer_stride, E, s->tgt->L, s->max_acc, st));
     RC(eb_spec_compact(d, s->kv_h.k, s->kv_h.v, s->stage, s->kv_h.layer_stride, E, s->head->L, s->max_acc, st));

@@ -21,8 +21,9 @@ __device__ __forceinline__ float4 sum_parts(const Parts &s, int64_t off) {
 }
 
 // one CTA (256 threads) per token row
+// bias != null: x = relu(sum_s part[s] + bias) instead of x += sum_s part[s]  (the EAGLE head's fc + bias + ReLU, R/src/llama.cpp:1886-1890)
 __global__ void __launch_bounds__(256) resid_norm_quant_kernel(float *__restrict__ x, Parts add, const float *__restrict__ w, float eps,
-                                                              int n, ActQ aq, float *__restrict__ feat) {
+                                                              int n, ActQ aq, float *__restrict__ feat, const float *__restrict__ bias) {
     extern __shared__ float row[];
     __shared__ double red[8];
     __shared__ float s_scale;
@@ -30,10 +31,15 @@ __global__ void __launch_bounds__(256) resid_norm_quant_kernel(float *__restrict
     float *xr = x + (int64_t)r * n;
     double acc = 0.0;
     for (int i = tid * 4; i < n; i += 1024) {
-        float4 v = *(const float4 *)(xr + i);
+        float4 v = bias ? make_float4(0.f, 0.f, 0.f, 0.f) : *(const float4 *)(xr + i);
         if (add.p) {                                       // ffn_inp = cur + inpSA (ggml_add(cur, inpSA))
             const float4 c = sum_parts(add, (int64_t)r * n + i);
-            v.x = __fadd_rn(c.x, v.x); v.y = __fadd_rn(c.y, v.y); v.z = __fadd_rn(c.z, v.z); v.w = __fadd_rn(c.w, v.w);
+            if (bias) {
+                const float4 b = *(const float4 *)(bias + i);
+                v = make_float4(fmaxf(__fadd_rn(c.x, b.x), 0.f), fmaxf(__fadd_rn(c.y, b.y), 0.f), fmaxf(__fadd_rn(c.z, b.z), 0.f), fmaxf(__fadd_rn(c.w, b.w), 0.f));
+            } else {
+                v.x = __fadd_rn(c.x, v.x); v.y = __fadd_rn(c.y, v.y); v.z = __fadd_rn(c.z, v.z); v.w = __fadd_rn(c.w, v.w);
+            }
             *(float4 *)(xr + i) = v;
         }
         *(float4 *)(row + i) = v;
@@ -63,16 +69,23 @@ __global__ void __launch_bounds__(256) resid_norm_quant_kernel(float *__restrict
 // Q8_K-grid rows of n = 8 * blockDim.x <= 8192 values: thread t owns elements 8t..8t+7 in registers for the whole kernel
 // (warp w = quantisation block w), one __syncthreads for the row sum, no shared-memory staging of the row
 __global__ void __launch_bounds__(1024) resid_norm_quant_regs_kernel(float *__restrict__ x, Parts add, const float *__restrict__ w, float eps,
-                                                                    int n, ActQ a, float *__restrict__ feat) {
+                                                                    int n, ActQ a, float *__restrict__ feat, const float *__restrict__ bias) {
     __shared__ double red[32];
     pdl_trigger(); pdl_wait();
     const int r = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nw = blockDim.x >> 5;
     const int64_t off = (int64_t)r * n + tid * 8;
-    float4 v0 = *(const float4 *)(x + off), v1 = *(const float4 *)(x + off + 4);
+    float4 v0 = make_float4(0.f, 0.f, 0.f, 0.f), v1 = v0;
+    if (!bias) { v0 = *(const float4 *)(x + off); v1 = *(const float4 *)(x + off + 4); }
     if (add.p) {
         const float4 c0 = sum_parts(add, off), c1 = sum_parts(add, off + 4);
-        v0.x = __fadd_rn(c0.x, v0.x); v0.y = __fadd_rn(c0.y, v0.y); v0.z = __fadd_rn(c0.z, v0.z); v0.w = __fadd_rn(c0.w, v0.w);
-        v1.x = __fadd_rn(c1.x, v1.x); v1.y = __fadd_rn(c1.y, v1.y); v1.z = __fadd_rn(c1.z, v1.z); v1.w = __fadd_rn(c1.w, v1.w);
+        if (bias) {
+            const float4 b0 = *(const float4 *)(bias + tid * 8), b1 = *(const float4 *)(bias + tid * 8 + 4);
+            v0 = make_float4(fmaxf(__fadd_rn(c0.x, b0.x), 0.f), fmaxf(__fadd_rn(c0.y, b0.y), 0.f), fmaxf(__fadd_rn(c0.z, b0.z), 0.f), fmaxf(__fadd_rn(c0.w, b0.w), 0.f));
+            v1 = make_float4(fmaxf(__fadd_rn(c1.x, b1.x), 0.f), fmaxf(__fadd_rn(c1.y, b1.y), 0.f), fmaxf(__fadd_rn(c1.z, b1.z), 0.f), fmaxf(__fadd_rn(c1.w, b1.w), 0.f));
+        } else {
+            v0.x = __fadd_rn(c0.x, v0.x); v0.y = __fadd_rn(c0.y, v0.y); v0.z = __fadd_rn(c0.z, v0.z); v0.w = __fadd_rn(c0.w, v0.w);
+            v1.x = __fadd_rn(c1.x, v1.x); v1.y = __fadd_rn(c1.y, v1.y); v1.z = __fadd_rn(c1.z, v1.z); v1.w = __fadd_rn(c1.w, v1.w);
+        }
         *(float4 *)(x + off) = v0; *(float4 *)(x + off + 4) = v1;
     }
     float4 g0 = make_float4(1.f, 1.f, 1.f, 1.f), g1 = g0;
@@ -166,14 +179,15 @@ __global__ void __launch_bounds__(256) swiglu_quant_kernel(Parts gate, Parts up,
 }
 
 // plain row quantisation of an f32 [T][K] tensor that is already final (attention output)
-int eb_resid_norm_quant(float *x, const float *part, int ks, const float *w, float eps, int n, int T, const ActQ &aq, float *feat, cudaStream_t st) {
+int eb_resid_norm_quant(float *x, const float *part, int ks, const float *w, float eps, int n, int T, const ActQ &aq, float *feat, cudaStream_t st, const float *bias) {
+    if (bias && !part) return eb_set_err(EB_ERR_ARG, "resid_norm_quant: bias without planes");
     if (n % 4 || n > 16384) return eb_set_err(EB_ERR_ARG, "resid_norm_quant: n=%d", n);
     if (T == 0) return EB_OK;
     Parts p{part, ks, (int64_t)T * n, n};
     if (n % 256 == 0 && n <= 8192 && (!aq.qs || (aq.kq && aq.K == n)))
-        eb_launch_pdl(resid_norm_quant_regs_kernel, dim3(T), dim3(n / 8), 0, st, x, p, w, eps, n, aq, feat);
+        eb_launch_pdl(resid_norm_quant_regs_kernel, dim3(T), dim3(n / 8), 0, st, x, p, w, eps, n, aq, feat, bias);
     else
-        resid_norm_quant_kernel<<<T, 256, (size_t)n * 4, st>>>(x, p, w, eps, n, aq, feat);
+        resid_norm_quant_kernel<<<T, 256, (size_t)n * 4, st>>>(x, p, w, eps, n, aq, feat, bias);
     EB_CHECK_LAUNCH();
     return EB_OK;
 }

@@ -617,7 +617,8 @@ int eb_mmq_tc_supported(int type, int64_t N, int64_t K, int T) {
     // T <= 8 (draft head) stays on the dp4a / mma.sync kernels: measured 17.9 us vs 26.0 us for 22016 x 4096 at T = 8 — this
     // kernel is bound by its dequant role, not by N.  EB_TC_TMIN=1 routes small batches here (N = 16 MMAs) for experiments.
     static const int tmin = getenv("EB_TC_TMIN") ? atoi(getenv("EB_TC_TMIN")) : 9;
-    return (type == EB_Q4_K || (type == EB_Q6_K && !off6)) && K % 256 == 0 && N >= 128 && T >= tmin && T <= 80;
+    static const int tmin6 = getenv("EB_TC_TMIN6") ? atoi(getenv("EB_TC_TMIN6")) : 9;
+    return ((type == EB_Q4_K && T >= tmin) || (type == EB_Q6_K && !off6 && T >= tmin6)) && K % 256 == 0 && N >= 128 && T <= 80;
 }
 
 // split-K factor: planes <= 8, minimise rounds x (super-blocks per item + pipeline fill)

@@ -117,6 +117,32 @@ __global__ void quant_act_kernel(const float *__restrict__ x, ActQ a) {
     }
 }
 
+// EAGLE head input: row t = [token embedding (E) | parent feature (E)] (ggml_concat, R/src/llama.cpp:1880) quantised for the fc
+// GEMM without materialising the concatenation: quantisation block b comes from `x` (b < E / block) or from `hid`
+__global__ void concat_quant_kernel(const float *__restrict__ x, const float *__restrict__ hid, int E, ActQ a) {
+    pdl_trigger(); pdl_wait();
+    const int lane = threadIdx.x & 31;
+    const int64_t warp = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const int per = a.kq ? 256 : 128;
+    const int64_t nb = a.K / per;
+    if (warp >= nb * a.T) return;
+    const int64_t t = warp / nb, b = warp % nb;
+    const int64_t col = b * per;
+    const float *src = col < E ? x + t * E + col : hid + t * E + (col - E);
+    if (a.kq) quant_block_q8K(src, a.qs + warp * 256, a.d + warp, a.bsum + warp * 16, lane,
+                              a.h16 ? a.h16 + warp * 256 : nullptr, (a.dT && t < EB_DT_PITCH) ? a.dT + b * EB_DT_PITCH + t : nullptr);
+    else quant_block_q8_0x4(src, a.qs + warp * 128, a.d + warp * 4, lane);
+}
+int eb_concat_quant(const float *x, const float *hid, int E, const ActQ &a, cudaStream_t st) {
+    const int per = a.kq ? 256 : 128;
+    if (a.K != 2 * (int64_t)E || E % per) return eb_set_err(EB_ERR_ARG, "concat_quant: E=%d K=%lld", E, (long long)a.K);
+    const int64_t warps = a.K / per * a.T;
+    if (warps == 0) return EB_OK;
+    eb_launch_pdl(concat_quant_kernel, dim3((unsigned)cdiv(warps, 8)), dim3(256), 0, st, x, hid, E, a);
+    EB_CHECK_LAUNCH();
+    return EB_OK;
+}
+
 size_t eb_actq_bytes(int kq, int64_t K, int T) {
     size_t qs = (size_t)T * K, d = (size_t)T * (K / (kq ? 256 : 32)) * 4, bs = kq ? (size_t)T * (K / 16) * 2 : 0;
     size_t h16 = kq ? (size_t)T * K * 2 : 0, dT = kq ? (size_t)(K / 256) * EB_DT_PITCH * 4 : 0;

@@ -18,7 +18,8 @@ __device__ __forceinline__ void warp_argmax(float &bv, int &bi) {
         if (ov > bv || (ov == bv && oi < bi)) { bv = ov; bi = oi; }
     }
 }
-__global__ void __launch_bounds__(1024) top_k_kernel(const float *__restrict__ logits, int V, int k,
+// logits may be split-K planes [ks][rows][V] of the lm_head GEMM: they are summed (plane order, like splitk_reduce) while staging the row
+__global__ void __launch_bounds__(1024) top_k_kernel(const float *__restrict__ logits, int ks, int64_t plane, int V, int k,
                                                      int32_t *__restrict__ ids, float *__restrict__ vals, float *__restrict__ probs) {
     extern __shared__ float row[];
     __shared__ float cv[32 * 16]; __shared__ int ci[32 * 16];
@@ -34,11 +35,19 @@ __global__ void __launch_bounds__(1024) top_k_kernel(const float *__restrict__ l
             float4 t[8];
 #pragma unroll
             for (int u = 0; u < 8; u++) { const int i = i0 + u * 1024 + tid; if (i < n4) t[u] = x4[i]; }
+            for (int s = 1; s < ks; s++) {
+                const float4 *p4 = (const float4 *)(x + s * plane);
+#pragma unroll
+                for (int u = 0; u < 8; u++) {
+                    const int i = i0 + u * 1024 + tid;
+                    if (i < n4) { const float4 p = p4[i]; t[u].x += p.x; t[u].y += p.y; t[u].z += p.z; t[u].w += p.w; }
+                }
+            }
 #pragma unroll
             for (int u = 0; u < 8; u++) { const int i = i0 + u * 1024 + tid; if (i < n4) r4[i] = t[u]; }
         }
     } else {
-        for (int i = tid; i < V; i += 1024) row[i] = x[i];
+        for (int i = tid; i < V; i += 1024) { float v = x[i]; for (int s = 1; s < ks; s++) v += x[s * plane + i]; row[i] = v; }
     }
     __syncthreads();
     const int chunk = ((V + 31) / 32 + 31) & ~31, lo = warp * chunk, hi = min(V, lo + chunk);
@@ -76,15 +85,16 @@ __global__ void __launch_bounds__(1024) top_k_kernel(const float *__restrict__ l
         }
     }
 }
-int eb_top_k_impl(const float *logits, int rows, int V, int k, int32_t *ids, float *vals, float *probs, cudaStream_t st) {
+int eb_top_k_impl(const float *logits, int rows, int V, int k, int32_t *ids, float *vals, float *probs, cudaStream_t st, int ks, int64_t plane) {
     if (k < 1 || k > 16 || V > 56000) return eb_set_err(EB_ERR_ARG, "top_k: k=%d V=%d", k, V);
     if (rows == 0) return EB_OK;
-    eb_launch_pdl(top_k_kernel, dim3(rows), dim3(1024), (size_t)V * 4, st, logits, V, k, ids, vals, probs);
+    if (ks > 1 && (plane & 3)) return eb_set_err(EB_ERR_ARG, "top_k: plane stride %lld", (long long)plane);
+    eb_launch_pdl(top_k_kernel, dim3(rows), dim3(1024), (size_t)V * 4, st, logits, ks, plane, V, k, ids, vals, probs);
     EB_CHECK_LAUNCH();
     return EB_OK;
 }
 
-__global__ void __launch_bounds__(1024) argmax_kernel(const float *__restrict__ logits, int V, int32_t *__restrict__ ids) {
+__global__ void __launch_bounds__(1024) argmax_kernel(const float *__restrict__ logits, int ks, int64_t plane, int V, int32_t *__restrict__ ids) {
     __shared__ float wv[32]; __shared__ int wi[32];
     const int r = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const float *x = logits + (int64_t)r * V;
@@ -93,6 +103,10 @@ __global__ void __launch_bounds__(1024) argmax_kernel(const float *__restrict__ 
         float t[8];
 #pragma unroll
         for (int u = 0; u < 8; u++) { const int i = i0 + u * 1024; t[u] = i < V ? x[i] : -INFINITY; }
+        for (int s = 1; s < ks; s++) {                  // split-K planes of the lm_head, summed in plane order
+#pragma unroll
+            for (int u = 0; u < 8; u++) { const int i = i0 + u * 1024; if (i < V) t[u] += x[s * plane + i]; }
+        }
 #pragma unroll
         for (int u = 0; u < 8; u++) if (t[u] > bv) { bv = t[u]; bi = i0 + u * 1024; }
     }
@@ -113,9 +127,9 @@ __global__ void __launch_bounds__(1024) argmax_kernel(const float *__restrict__ 
         if (lane == 0) ids[r] = bi == 0x7fffffff ? 0 : bi;
     }
 }
-int eb_argmax_impl(const float *logits, int rows, int V, int32_t *ids, cudaStream_t st) {
+int eb_argmax_impl(const float *logits, int rows, int V, int32_t *ids, cudaStream_t st, int ks, int64_t plane) {
     if (rows == 0) return EB_OK;
-    argmax_kernel<<<rows, 1024, 0, st>>>(logits, V, ids);
+    argmax_kernel<<<rows, 1024, 0, st>>>(logits, ks, plane, V, ids);
     EB_CHECK_LAUNCH();
     return EB_OK;
 }
