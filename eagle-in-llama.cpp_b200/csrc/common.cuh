@@ -122,4 +122,7 @@ int eb_mmq_tc_supported(int type, int64_t N, int64_t K, int T);
 int eb_mmq_tc_parts(int type, const void *W, int64_t N, int64_t K, const ActQ &a, float *planes, int *ks_out, cudaStream_t st);
 int eb_splitk_reduce(const float *partial, float *y, int64_t n, int ksplit, cudaStream_t st);
 int eb_mmq_supported(int type, int64_t N, int64_t K, int T);
+// mmq_small.cu: T <= 8 (draft head)
+int eb_mmq_small_init(); int eb_mmq_small_supported(int type, int64_t N, int64_t K, int T);
+int eb_mmq_small_parts(int type, const void *W, int64_t N, int64_t K, const ActQ &a, float *planes, int *ks_out, cudaStream_t st);
 int eb_mmq_pick_ksplit(int type, int64_t N, int64_t K, int T);

@@ -171,6 +171,11 @@ int eb_mul_mat_impl(int type, const void *W, int64_t N, int64_t K, const float *
         rc = eb_mmq_tc_parts(type, W, N, K, a, partial, &ks, st); if (rc) return rc;
         return eb_splitk_reduce(partial, y, (int64_t)T * N, ks, st);
     }
+    if (T > 1 && eb_mmq_small_supported(type, N, K, T)) {
+        int ks = 1;
+        rc = eb_mmq_small_parts(type, W, N, K, a, partial, &ks, st); if (rc) return rc;
+        return eb_splitk_reduce(partial, y, (int64_t)T * N, ks, st);
+    }
     if (eb_mmq_supported(type, N, K, T)) return eb_mmq(type, W, N, K, a, y, partial, eb_mmq_pick_ksplit(type, N, K, T), st);
     return eb_mmvq(type, W, N, K, a, y, st);
 }
@@ -256,11 +261,19 @@ extern "C" void eb_session_free(eb_session *s) {
 // All inputs are device-resident: tokens/pos/bits [T], hidden [T][E] (head), ctl (n_prefix,
 // node_base, n_tree).  K/V rows go to cells n_prefix + node_base + t.
 // GEMM into split-K planes (T > 8, K-quants) or a single plane (matvec path)
+static bool skip_class(const char *name);
 static int mm_parts(const DTensor &w, const ActQ &a, float *planes, int *ks, cudaStream_t st) {
+    if (skip_class("gemm")) { *ks = 1; return EB_OK; }
     if (eb_mmq_tc_supported(w.type, w.rows, w.cols, a.T)) return eb_mmq_tc_parts(w.type, w.data, w.rows, w.cols, a, planes, ks, st);
+    if (eb_mmq_small_supported(w.type, w.rows, w.cols, a.T)) return eb_mmq_small_parts(w.type, w.data, w.rows, w.cols, a, planes, ks, st);
     if (eb_mmq_supported(w.type, w.rows, w.cols, a.T)) return eb_mmq_parts(w.type, w.data, w.rows, w.cols, a, planes, ks, st);
     *ks = 1;
     return eb_mmvq(w.type, w.data, w.rows, w.cols, a, planes, st);
+}
+// EB_SKIP=resid,rope,attn,swiglu,gemm: timing experiments only (results are garbage): the marginal in-graph cost of a kernel class
+static bool skip_class(const char *name) {
+    static const char *e = getenv("EB_SKIP");
+    return e && strstr(e, name);
 }
 static int grid_of(const DTensor &w) { return w.type == EB_Q4_K || w.type == EB_Q6_K; }
 
@@ -288,7 +301,7 @@ static int forward_dev(const eb_model *m, KVCache &kv, Workspace &w, const int32
         // x += pending; cur = rms_norm(x) * attn_norm -> activation grid of wq
         const int gq = grid_of(t[EB_L_WQ]);
         ActQ a = eb_actq_carve(w.actq, gq, E, T);
-        RC(eb_resid_norm_quant(w.x, pend, pend_ks, (const float *)t[EB_L_ATTN_NORM].data, m->eps, E, T, a, nullptr, st, pend_bias));
+        if (!skip_class("resid")) RC(eb_resid_norm_quant(w.x, pend, pend_ks, (const float *)t[EB_L_ATTN_NORM].data, m->eps, E, T, a, nullptr, st, pend_bias));
         pend_bias = nullptr;
         if (grid_of(t[EB_L_WK]) != gq || grid_of(t[EB_L_WV]) != gq) return eb_set_err(EB_ERR_UNSUPPORTED, "layer %d: wq/wk/wv mix K-quant and 32-block formats", l);
         const LayerFuse &fu = m->fuse[l];
@@ -303,10 +316,11 @@ static int forward_dev(const eb_model *m, KVCache &kv, Workspace &w, const int32
         }
         __half *kc = kv.k + (int64_t)l * kv.layer_stride, *vc = kv.v + (int64_t)l * kv.layer_stride;
         const bool fa_tc = eb_fattn_tc_supported(T, D);
-        RC(eb_rope_kv_store_fused(rq, rk, rv, w.q, fa_tc ? w.q16 : nullptr, w.rope_tab, kc, vc, ctl, D, H, T, st));
+        if (!skip_class("rope")) RC(eb_rope_kv_store_fused(rq, rk, rv, w.q, fa_tc ? w.q16 : nullptr, w.rope_tab, kc, vc, ctl, D, H, T, st));
         ActQ ao = eb_actq_carve(w.actq, grid_of(t[EB_L_WO]), E, T);
         int att_quantized = 0;
-        if (fa_tc) RC(eb_fattn_tc(w.q16, kc, vc, E, kv.n_ctx, bits, ctl, 0, 0, T, H, 1.0f / sqrtf((float)D), w.att, w.fa_ws, st, &ao, &att_quantized));
+        if (skip_class("attn")) att_quantized = 1;
+        else if (fa_tc) RC(eb_fattn_tc(w.q16, kc, vc, E, kv.n_ctx, bits, ctl, 0, 0, T, H, 1.0f / sqrtf((float)D), w.att, w.fa_ws, st, &ao, &att_quantized));
         else RC(eb_flash_attn_ctl(w.q, kc, vc, E, bits, ctl, T, H, D, kv.n_ctx, 1.0f / sqrtf((float)D), w.att, w.fa_ws, st));
         if (!att_quantized) RC(eb_quantize_act(w.att, ao, st));
         int ko_;
@@ -315,7 +329,7 @@ static int forward_dev(const eb_model *m, KVCache &kv, Workspace &w, const int32
         const int gu = grid_of(t[EB_L_UP]);
         if (grid_of(t[EB_L_GATE]) != gu) return eb_set_err(EB_ERR_UNSUPPORTED, "layer %d: ffn_up/ffn_gate mix formats", l);
         ActQ af = eb_actq_carve(w.actq, gu, E, T);
-        RC(eb_resid_norm_quant(w.x, w.po, ko_, (const float *)t[EB_L_FFN_NORM].data, m->eps, E, T, af, nullptr, st));
+        if (!skip_class("resid")) RC(eb_resid_norm_quant(w.x, w.po, ko_, (const float *)t[EB_L_FFN_NORM].data, m->eps, E, T, af, nullptr, st));
         PlaneRef rg, ru;
         {
             int ks_;
@@ -329,7 +343,7 @@ static int forward_dev(const eb_model *m, KVCache &kv, Workspace &w, const int32
             }
         }
         ActQ ad = eb_actq_carve(w.actq2, grid_of(t[EB_L_DOWN]), F, T);
-        RC(eb_swiglu_quant(rg, ru, F, T, ad, st));
+        if (!skip_class("swiglu")) RC(eb_swiglu_quant(rg, ru, F, T, ad, st));
         RC(mm_parts(t[EB_L_DOWN], ad, w.pq, &pend_ks, st));       // pq is free again: holds the down planes
         pend = w.pq;
     }

@@ -234,17 +234,42 @@ __global__ void fattn_combine_quant_kernel(const float *__restrict__ part_o, con
     const int w = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31, nb = H / 2;
     if (w >= T * nb) return;
     const int r = w / nb, b = w % nb, h = 2 * b + (lane >> 4), d0 = (lane & 15) * 8;
-    float M = -INFINITY;
-    for (int s = 0; s < nsplit; s++) M = fmaxf(M, part_ml[(((int64_t)h * nsplit + s) * T + r) * 2]);
     float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f}; float L = 0.f;
-    for (int s = 0; s < nsplit; s++) {
-        const int64_t pb = ((int64_t)h * nsplit + s) * T + r;
-        const float m = part_ml[pb * 2], l = part_ml[pb * 2 + 1];
-        if (l <= 0.f) continue;
-        const float wgt = l * exp2f(m - M);
-        const float4 x = *(const float4 *)(part_o + pb * FA_D + d0), y = *(const float4 *)(part_o + pb * FA_D + d0 + 4);
-        acc[0] += wgt * x.x; acc[1] += wgt * x.y; acc[2] += wgt * x.z; acc[3] += wgt * x.w;
-        acc[4] += wgt * y.x; acc[5] += wgt * y.y; acc[6] += wgt * y.z; acc[7] += wgt * y.w; L += wgt;
+    if (nsplit <= 4) {
+        // every load of the (up to four) splits in flight at once: the rolled loops below cost two L2 round trips per split
+        float2 ml[4]; float4 x[4], y[4];
+#pragma unroll
+        for (int s = 0; s < 4; s++) {
+            ml[s] = make_float2(-INFINITY, 0.f);
+            if (s < nsplit) {
+                const int64_t pb = ((int64_t)h * nsplit + s) * T + r;
+                ml[s] = *(const float2 *)(part_ml + pb * 2);
+                x[s] = *(const float4 *)(part_o + pb * FA_D + d0); y[s] = *(const float4 *)(part_o + pb * FA_D + d0 + 4);
+            }
+        }
+        float M = -INFINITY;
+#pragma unroll
+        for (int s = 0; s < 4; s++) if (s < nsplit) M = fmaxf(M, ml[s].x);
+#pragma unroll
+        for (int s = 0; s < 4; s++) {
+            if (s < nsplit && ml[s].y > 0.f) {
+                const float wgt = ml[s].y * exp2f(ml[s].x - M);
+                acc[0] += wgt * x[s].x; acc[1] += wgt * x[s].y; acc[2] += wgt * x[s].z; acc[3] += wgt * x[s].w;
+                acc[4] += wgt * y[s].x; acc[5] += wgt * y[s].y; acc[6] += wgt * y[s].z; acc[7] += wgt * y[s].w; L += wgt;
+            }
+        }
+    } else {
+        float M = -INFINITY;
+        for (int s = 0; s < nsplit; s++) M = fmaxf(M, part_ml[(((int64_t)h * nsplit + s) * T + r) * 2]);
+        for (int s = 0; s < nsplit; s++) {
+            const int64_t pb = ((int64_t)h * nsplit + s) * T + r;
+            const float m = part_ml[pb * 2], l = part_ml[pb * 2 + 1];
+            if (l <= 0.f) continue;
+            const float wgt = l * exp2f(m - M);
+            const float4 x = *(const float4 *)(part_o + pb * FA_D + d0), y = *(const float4 *)(part_o + pb * FA_D + d0 + 4);
+            acc[0] += wgt * x.x; acc[1] += wgt * x.y; acc[2] += wgt * x.z; acc[3] += wgt * x.w;
+            acc[4] += wgt * y.x; acc[5] += wgt * y.y; acc[6] += wgt * y.z; acc[7] += wgt * y.w; L += wgt;
+        }
     }
     const float inv = L > 0.f ? 1.f / L : 0.f;
     float v[8];

@@ -14,9 +14,22 @@
 struct Parts { const float *p; int ks; int64_t plane; int64_t ld; };   // plane = T*ld elements between split planes, ld = row pitch (a fused GEMM's N)
 static Parts parts_of(const PlaneRef &r, int T) { return Parts{r.p, r.ks, (int64_t)T * r.ld, r.ld}; }
 
+// sum of the split-K planes in plane order.  The loads of four planes are issued together: a rolled loop pays one L2 round
+// trip per plane (5 planes = 3 us in a kernel whose whole job is 65 rows)
 __device__ __forceinline__ float4 sum_parts(const Parts &s, int64_t off) {
-    float4 a = *(const float4 *)(s.p + off);
-    for (int k = 1; k < s.ks; k++) { const float4 b = *(const float4 *)(s.p + (int64_t)k * s.plane + off); a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w; }
+    const float *p = s.p + off;
+    float4 b[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) if (k == 0 || k < s.ks) b[k] = *(const float4 *)(p + k * s.plane);
+    float4 a = b[0];
+#pragma unroll
+    for (int k = 1; k < 4; k++) if (k < s.ks) { a.x += b[k].x; a.y += b[k].y; a.z += b[k].z; a.w += b[k].w; }
+    if (s.ks > 4) {
+#pragma unroll
+        for (int k = 0; k < 4; k++) if (k + 4 < s.ks) b[k] = *(const float4 *)(p + (k + 4) * s.plane);
+#pragma unroll
+        for (int k = 0; k < 4; k++) if (k + 4 < s.ks) { a.x += b[k].x; a.y += b[k].y; a.z += b[k].z; a.w += b[k].w; }
+    }
     return a;
 }
 
@@ -68,7 +81,8 @@ __global__ void __launch_bounds__(256) resid_norm_quant_kernel(float *__restrict
 
 // Q8_K-grid rows of n = 8 * blockDim.x <= 8192 values: thread t owns elements 8t..8t+7 in registers for the whole kernel
 // (warp w = quantisation block w), one __syncthreads for the row sum, no shared-memory staging of the row
-__global__ void __launch_bounds__(1024) resid_norm_quant_regs_kernel(float *__restrict__ x, Parts add, const float *__restrict__ w, float eps,
+template <int MAXT>
+__global__ void __launch_bounds__(MAXT) resid_norm_quant_regs_kernel(float *__restrict__ x, Parts add, const float *__restrict__ w, float eps,
                                                                     int n, ActQ a, float *__restrict__ feat, const float *__restrict__ bias) {
     __shared__ double red[32];
     pdl_trigger(); pdl_wait();
@@ -185,7 +199,8 @@ int eb_resid_norm_quant(float *x, const float *part, int ks, const float *w, flo
     if (T == 0) return EB_OK;
     Parts p{part, ks, (int64_t)T * n, n};
     if (n % 256 == 0 && n <= 8192 && (!aq.qs || (aq.kq && aq.K == n)))
-        eb_launch_pdl(resid_norm_quant_regs_kernel, dim3(T), dim3(n / 8), 0, st, x, p, w, eps, n, aq, feat, bias);
+        if (n <= 4096) eb_launch_pdl(resid_norm_quant_regs_kernel<512>, dim3(T), dim3(n / 8), 0, st, x, p, w, eps, n, aq, feat, bias);
+        else eb_launch_pdl(resid_norm_quant_regs_kernel<1024>, dim3(T), dim3(n / 8), 0, st, x, p, w, eps, n, aq, feat, bias);
     else
         resid_norm_quant_kernel<<<T, 256, (size_t)n * 4, st>>>(x, p, w, eps, n, aq, feat, bias);
     EB_CHECK_LAUNCH();
