@@ -107,7 +107,8 @@ __device__ __forceinline__ void q4k_scale_min(int j, const uint8_t *q, int &sc, 
 
 // ---- internal kernels' host launchers (defined across the .cu files)
 int eb_quantize_act(const float *d_x, const ActQ &a, cudaStream_t st);                 // quant.cu
-int eb_concat_quant(const float *x, const float *hid, int E, const ActQ &a, cudaStream_t st);
+struct SpecState;
+int eb_concat_quant(const float *x, const float *hid, int E, const ActQ &a, cudaStream_t st, const SpecState *spec = nullptr, const float *root_feat = nullptr, const float *node_feat = nullptr);
 size_t eb_actq_bytes(int kq, int64_t K, int T);
 ActQ   eb_actq_carve(void *ws, int kq, int64_t K, int T);
 int eb_dequantize_impl(int type, const void *src, int64_t nb_total, int64_t blk0, float *dst, int64_t n, cudaStream_t st);

@@ -278,7 +278,10 @@ static bool skip_class(const char *name) {
 static int grid_of(const DTensor &w) { return w.type == EB_Q4_K || w.type == EB_Q6_K; }
 
 static int forward_dev(const eb_model *m, KVCache &kv, Workspace &w, const int32_t *tokens, const int32_t *pos, const uint32_t *bits,
-                       const float *hidden, const FwdCtl *ctl, int T, bool want_logits, cudaStream_t st, int *logit_ks = nullptr) {
+                       const float *hidden, const FwdCtl *ctl, int T, bool want_logits, cudaStream_t st, int *logit_ks = nullptr,
+                       const SpecState *spec = nullptr, const float *root_feat = nullptr, float *node_feat = nullptr) {
+    // spec != null (draft level): hidden rows are gathered from root_feat / node_feat by the state's dft_src, and the result
+    // features are scattered to node_feat, inside the kernels that read / produce them
     const int E = m->E, H = m->H, F = m->F, D = E / H;
     int rc;
 #define RC(x) do { rc = (x); if (rc) return rc; } while (0)
@@ -291,11 +294,12 @@ static int forward_dev(const eb_model *m, KVCache &kv, Workspace &w, const int32
         // bias + ReLU is applied by the first layer's norm kernel while it sums the fc planes
         const DTensor &fc = m->g[EB_T_FC];
         ActQ ac = eb_actq_carve(w.actq2, grid_of(fc), 2 * E, T);
-        RC(eb_concat_quant(w.x, hidden, E, ac, st));
+        RC(eb_concat_quant(w.x, hidden, E, ac, st, spec, root_feat, node_feat));
         RC(mm_parts(fc, ac, w.pup, &pend_ks, st));
         pend = w.pup; pend_bias = (const float *)m->g[EB_T_FC_BIAS].data;
     }
-    RC(eb_rope_table(pos, D, T, m->freq_base, w.rope_tab, st));
+    const bool use_tab = m->L > 1;                          // one layer: the rotation angles are computed where they are used
+    if (use_tab) RC(eb_rope_table(pos, D, T, m->freq_base, w.rope_tab, st));
     for (int l = 0; l < m->L; l++) {
         const std::vector<DTensor> &t = m->layers[l];
         // x += pending; cur = rms_norm(x) * attn_norm -> activation grid of wq
@@ -316,7 +320,7 @@ static int forward_dev(const eb_model *m, KVCache &kv, Workspace &w, const int32
         }
         __half *kc = kv.k + (int64_t)l * kv.layer_stride, *vc = kv.v + (int64_t)l * kv.layer_stride;
         const bool fa_tc = eb_fattn_tc_supported(T, D);
-        if (!skip_class("rope")) RC(eb_rope_kv_store_fused(rq, rk, rv, w.q, fa_tc ? w.q16 : nullptr, w.rope_tab, kc, vc, ctl, D, H, T, st));
+        if (!skip_class("rope")) RC(eb_rope_kv_store_fused(rq, rk, rv, w.q, fa_tc ? w.q16 : nullptr, use_tab ? w.rope_tab : nullptr, kc, vc, ctl, D, H, T, st, pos, m->freq_base));
         ActQ ao = eb_actq_carve(w.actq, grid_of(t[EB_L_WO]), E, T);
         int att_quantized = 0;
         if (skip_class("attn")) att_quantized = 1;
@@ -351,7 +355,7 @@ static int forward_dev(const eb_model *m, KVCache &kv, Workspace &w, const int32
     const DTensor &o = m->g[EB_T_OUTPUT];
     ActQ al = eb_actq_carve(w.actq, grid_of(o), E, T);
     if (!want_logits) al.qs = nullptr;
-    RC(eb_resid_norm_quant(w.x, pend, pend_ks, (const float *)m->g[EB_T_OUTPUT_NORM].data, m->eps, E, T, al, w.feat, st));
+    RC(eb_resid_norm_quant(w.x, pend, pend_ks, (const float *)m->g[EB_T_OUTPUT_NORM].data, m->eps, E, T, al, w.feat, st, nullptr, spec, node_feat));
     if (want_logits && logit_ks) {
         // the caller's top-k / argmax sums the lm_head's split-K planes [ks][T][V] (w.partial) itself
         RC(mm_parts(o, al, w.partial, logit_ks, st));
@@ -470,11 +474,13 @@ static int round_dev(eb_session *s, cudaStream_t st) {
     RC(eb_spec_round_begin(d, c, st));
     for (int depth = 0; depth <= c.max_depth; depth++) {
         // head forward over the nodes created at this depth (depth 0: the root)
-        RC(eb_spec_gather_hidden(d, s->root_feat, s->node_feat, s->ws_h.hidden, E, c.n_branch, st));
         const bool last = depth == c.max_depth;
         int ks_h = 1;
-        RC(forward_dev(s->head, s->kv_h, s->ws_h, d->dft_tokens, d->dft_pos, d->dft_bits, s->ws_h.hidden, &d->ctl_head, c.n_branch, !last, st, &ks_h));
-        RC(eb_spec_scatter_feat(d, s->ws_h.feat, s->node_feat, E, c.n_branch, st));
+        const bool fused_io = s->head->E % 256 == 0 && s->head->E <= 8192 && (s->head->g[EB_T_OUTPUT].type == EB_Q4_K || s->head->g[EB_T_OUTPUT].type == EB_Q6_K);
+        if (!fused_io) RC(eb_spec_gather_hidden(d, s->root_feat, s->node_feat, s->ws_h.hidden, E, c.n_branch, st));
+        RC(forward_dev(s->head, s->kv_h, s->ws_h, d->dft_tokens, d->dft_pos, d->dft_bits, s->ws_h.hidden, &d->ctl_head, c.n_branch, !last, st, &ks_h,
+                       fused_io ? d : nullptr, s->root_feat, s->node_feat));
+        if (!fused_io) RC(eb_spec_scatter_feat(d, s->ws_h.feat, s->node_feat, E, c.n_branch, st));
         if (last) break;
         RC(eb_top_k_impl(s->ws_h.partial, c.n_branch, V, c.top_k, s->cand_ids, s->cand_vals, s->cand_p, st, ks_h, (int64_t)c.n_branch * V));
         RC(eb_spec_expand(d, c, s->cand_ids, s->cand_p, st));

@@ -62,11 +62,12 @@ int eb_rope_kv_store_ctl(float *q, const float *k, const float *v, const int32_t
                          int D, int n_head, int T, float freq_base, cudaStream_t st);
 int eb_flash_attn_ctl(const float *q, const void *k, const void *v, int64_t kv_stride, const uint32_t *tree_bits, const FwdCtl *ctl,
                       int T, int H, int D, int n_ctx, float scale, float *out, void *ws, cudaStream_t st);
-int eb_resid_norm_quant(float *x, const float *part, int ks, const float *w, float eps, int n, int T, const ActQ &aq, float *feat, cudaStream_t st, const float *bias = nullptr);
+int eb_resid_norm_quant(float *x, const float *part, int ks, const float *w, float eps, int n, int T, const ActQ &aq, float *feat, cudaStream_t st, const float *bias = nullptr,
+                        const SpecState *spec = nullptr, float *node_feat = nullptr);
 struct PlaneRef { const float *p; int ks; int64_t ld; };   // split-K planes [ks][T][ld] of a (possibly fused) GEMM, first column of interest at p
 int eb_rope_table(const int32_t *pos, int D, int T, float freq_base, float *tab, cudaStream_t st);
 int eb_rope_kv_store_fused(PlaneRef qp, PlaneRef kp, PlaneRef vp, float *q, void *q16, const float *tab, void *kc, void *vc,
-                           const FwdCtl *ctl, int D, int n_head, int T, cudaStream_t st);
+                           const FwdCtl *ctl, int D, int n_head, int T, cudaStream_t st, const int32_t *pos = nullptr, float freq_base = 10000.f);
 // fattn_tc.cu: tcgen05 tree attention
 int eb_fattn_tc_init(); int eb_fattn_tc_supported(int T, int D); size_t eb_fattn_tc_ws_size(int T, int H, int n_kv);
 int eb_fattn_tc(const __half *q16, const void *k, const void *v, int64_t kv_stride, int64_t n_cells, const uint32_t *tree_bits, const FwdCtl *ctl,

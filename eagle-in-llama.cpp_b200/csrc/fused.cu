@@ -83,7 +83,8 @@ __global__ void __launch_bounds__(256) resid_norm_quant_kernel(float *__restrict
 // (warp w = quantisation block w), one __syncthreads for the row sum, no shared-memory staging of the row
 template <int MAXT>
 __global__ void __launch_bounds__(MAXT) resid_norm_quant_regs_kernel(float *__restrict__ x, Parts add, const float *__restrict__ w, float eps,
-                                                                    int n, ActQ a, float *__restrict__ feat, const float *__restrict__ bias) {
+                                                                    int n, ActQ a, float *__restrict__ feat, const float *__restrict__ bias,
+                                                                    const SpecState *__restrict__ spec, float *__restrict__ node_feat) {
     __shared__ double red[32];
     pdl_trigger(); pdl_wait();
     const int r = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nw = blockDim.x >> 5;
@@ -120,6 +121,10 @@ __global__ void __launch_bounds__(MAXT) resid_norm_quant_regs_kernel(float *__re
         v[4] = __fmul_rn(v[4], g1.x); v[5] = __fmul_rn(v[5], g1.y); v[6] = __fmul_rn(v[6], g1.z); v[7] = __fmul_rn(v[7], g1.w);
     }
     if (feat) { *(float4 *)(feat + off) = make_float4(v[0], v[1], v[2], v[3]); *(float4 *)(feat + off + 4) = make_float4(v[4], v[5], v[6], v[7]); }
+    if (spec && r < spec->dft_n) {                          // draft level: the row is also the node's feature (input of its children)
+        float *nf = node_feat + (int64_t)(spec->dft_node_base + r) * n + tid * 8;
+        *(float4 *)nf = make_float4(v[0], v[1], v[2], v[3]); *(float4 *)(nf + 4) = make_float4(v[4], v[5], v[6], v[7]);
+    }
     if (a.qs) {
         const int nb = n / 256;
         quant_regs_q8K(v, a.qs + (int64_t)r * n + warp * 256, a.d + (int64_t)r * nb + warp, a.bsum + ((int64_t)r * nb + warp) * 16, lane,
@@ -140,7 +145,8 @@ __global__ void rope_table_kernel(const int32_t *__restrict__ pos, float theta_s
 // straight to their cache cells; q additionally as f16 for the tcgen05 attention
 __global__ void __launch_bounds__(512) rope_kv_store_fused_kernel(Parts qp, Parts kp, Parts vp, float *__restrict__ q, __half *__restrict__ q16,
                                                                  const float2 *__restrict__ tab, __half *__restrict__ kc, __half *__restrict__ vc,
-                                                                 const FwdCtl *__restrict__ ctl, int D, int n_head) {
+                                                                 const FwdCtl *__restrict__ ctl, int D, int n_head,
+                                                                 const int32_t *__restrict__ pos, float theta_scale) {
     pdl_trigger(); pdl_wait();
     const int t = blockIdx.x, tid = threadIdx.x, half = D / 2;
     const int64_t cell0 = ctl ? (int64_t)(ctl->n_prefix + ctl->node_base) * n_head * D : 0;
@@ -148,7 +154,14 @@ __global__ void __launch_bounds__(512) rope_kv_store_fused_kernel(Parts qp, Part
     // float4 = two rotation pairs
     for (int e = (blockIdx.y * blockDim.x + tid) * 4; e < E; e += gridDim.y * blockDim.x * 4) {
         const int i = (e % D) / 2;
-        const float4 cs = *(const float4 *)(tab + t * half + i);     // (cos0, sin0, cos1, sin1)
+        float4 cs;                                                   // (cos0, sin0, cos1, sin1)
+        if (tab) cs = *(const float4 *)(tab + t * half + i);
+        else {                                                       // single-layer model (the EAGLE head): no table pass, same recurrence
+            float theta = (float)pos[t];
+            for (int j = 0; j < i; j++) theta = __fmul_rn(theta, theta_scale);
+            const float th1 = __fmul_rn(theta, theta_scale);
+            cs = make_float4(cosf(theta), sinf(theta), cosf(th1), sinf(th1));
+        }
         const float c0 = cs.x, s0 = cs.y, c1 = cs.z, s1 = cs.w;
         const int64_t o = (int64_t)t * E + e;
         const float4 a = sum_parts(qp, t * qp.ld + e), b = sum_parts(kp, t * kp.ld + e), v = sum_parts(vp, t * vp.ld + e);
@@ -193,16 +206,19 @@ __global__ void __launch_bounds__(256) swiglu_quant_kernel(Parts gate, Parts up,
 }
 
 // plain row quantisation of an f32 [T][K] tensor that is already final (attention output)
-int eb_resid_norm_quant(float *x, const float *part, int ks, const float *w, float eps, int n, int T, const ActQ &aq, float *feat, cudaStream_t st, const float *bias) {
+int eb_resid_norm_quant(float *x, const float *part, int ks, const float *w, float eps, int n, int T, const ActQ &aq, float *feat, cudaStream_t st, const float *bias,
+                        const SpecState *spec, float *node_feat) {
     if (bias && !part) return eb_set_err(EB_ERR_ARG, "resid_norm_quant: bias without planes");
     if (n % 4 || n > 16384) return eb_set_err(EB_ERR_ARG, "resid_norm_quant: n=%d", n);
     if (T == 0) return EB_OK;
     Parts p{part, ks, (int64_t)T * n, n};
     if (n % 256 == 0 && n <= 8192 && (!aq.qs || (aq.kq && aq.K == n)))
-        if (n <= 4096) eb_launch_pdl(resid_norm_quant_regs_kernel<512>, dim3(T), dim3(n / 8), 0, st, x, p, w, eps, n, aq, feat, bias);
-        else eb_launch_pdl(resid_norm_quant_regs_kernel<1024>, dim3(T), dim3(n / 8), 0, st, x, p, w, eps, n, aq, feat, bias);
-    else
+        if (n <= 4096) eb_launch_pdl(resid_norm_quant_regs_kernel<512>, dim3(T), dim3(n / 8), 0, st, x, p, w, eps, n, aq, feat, bias, spec, node_feat);
+        else eb_launch_pdl(resid_norm_quant_regs_kernel<1024>, dim3(T), dim3(n / 8), 0, st, x, p, w, eps, n, aq, feat, bias, spec, node_feat);
+    else {
+        if (spec) return eb_set_err(EB_ERR_UNSUPPORTED, "resid_norm_quant: node-feature scatter needs the register kernel (n %% 256 == 0, n <= 8192, K-quant grid)");
         resid_norm_quant_kernel<<<T, 256, (size_t)n * 4, st>>>(x, p, w, eps, n, aq, feat, bias);
+    }
     EB_CHECK_LAUNCH();
     return EB_OK;
 }
@@ -214,13 +230,14 @@ int eb_rope_table(const int32_t *pos, int D, int T, float freq_base, float *tab,
     return EB_OK;
 }
 int eb_rope_kv_store_fused(PlaneRef qp, PlaneRef kp, PlaneRef vp, float *q, void *q16, const float *tab, void *kc, void *vc,
-                           const FwdCtl *ctl, int D, int n_head, int T, cudaStream_t st) {
+                           const FwdCtl *ctl, int D, int n_head, int T, cudaStream_t st, const int32_t *pos, float freq_base) {
+    if (!tab && !pos) return eb_set_err(EB_ERR_ARG, "rope: neither table nor positions");
     if (T == 0) return EB_OK;
     if (D > 256 || D % 4) return eb_set_err(EB_ERR_ARG, "rope: D=%d", D);
     const int E = n_head * D;
     const int threads = 512, gy = (int)cdiv(E / 4, threads);
     eb_launch_pdl(rope_kv_store_fused_kernel, dim3(T, gy), dim3(threads), 0, st, parts_of(qp, T), parts_of(kp, T), parts_of(vp, T), q, (__half *)q16, (const float2 *)tab,
-                  (__half *)kc, (__half *)vc, ctl, D, n_head);
+                  (__half *)kc, (__half *)vc, ctl, D, n_head, pos, powf(freq_base, -2.0f / D));
     EB_CHECK_LAUNCH();
     return EB_OK;
 }

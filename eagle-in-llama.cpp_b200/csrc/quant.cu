@@ -1,6 +1,7 @@
 // quant.cu — dequantisation (bit-exact to the reference), activation quantisers on the CPU
 // backend's grids, and synthetic-tensor generators for bench fixtures.
 #include "common.cuh"
+#include "spec.cuh"
 #include "quant_dev.cuh"
 
 // ------------------------------------------------------------------ dequantize (K13)
@@ -119,7 +120,8 @@ __global__ void quant_act_kernel(const float *__restrict__ x, ActQ a) {
 
 // EAGLE head input: row t = [token embedding (E) | parent feature (E)] (ggml_concat, R/src/llama.cpp:1880) quantised for the fc
 // GEMM without materialising the concatenation: quantisation block b comes from `x` (b < E / block) or from `hid`
-__global__ void concat_quant_kernel(const float *__restrict__ x, const float *__restrict__ hid, int E, ActQ a) {
+__global__ void concat_quant_kernel(const float *__restrict__ x, const float *__restrict__ hid, int E, ActQ a,
+                                    const SpecState *__restrict__ spec, const float *__restrict__ root_feat, const float *__restrict__ node_feat) {
     pdl_trigger(); pdl_wait();
     const int lane = threadIdx.x & 31;
     const int64_t warp = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
@@ -128,17 +130,22 @@ __global__ void concat_quant_kernel(const float *__restrict__ x, const float *__
     if (warp >= nb * a.T) return;
     const int64_t t = warp / nb, b = warp % nb;
     const int64_t col = b * per;
-    const float *src = col < E ? x + t * E + col : hid + t * E + (col - E);
+    const float *src;
+    if (col < E) src = x + t * E + col;
+    else if (spec) {                                        // hidden row of draft row t: root <- target feature, others <- the head's own
+        const int par = spec->dft_src[t];                   // result_norm of the parent node (R/src/llama.cpp:10170, R/src/llama-context.cpp:83-88)
+        src = (par < 0 ? root_feat : node_feat + (int64_t)par * E) + (col - E);
+    } else src = hid + t * E + (col - E);
     if (a.kq) quant_block_q8K(src, a.qs + warp * 256, a.d + warp, a.bsum + warp * 16, lane,
                               a.h16 ? a.h16 + warp * 256 : nullptr, (a.dT && t < EB_DT_PITCH) ? a.dT + b * EB_DT_PITCH + t : nullptr);
     else quant_block_q8_0x4(src, a.qs + warp * 128, a.d + warp * 4, lane);
 }
-int eb_concat_quant(const float *x, const float *hid, int E, const ActQ &a, cudaStream_t st) {
+int eb_concat_quant(const float *x, const float *hid, int E, const ActQ &a, cudaStream_t st, const SpecState *spec, const float *root_feat, const float *node_feat) {
     const int per = a.kq ? 256 : 128;
     if (a.K != 2 * (int64_t)E || E % per) return eb_set_err(EB_ERR_ARG, "concat_quant: E=%d K=%lld", E, (long long)a.K);
     const int64_t warps = a.K / per * a.T;
     if (warps == 0) return EB_OK;
-    eb_launch_pdl(concat_quant_kernel, dim3((unsigned)cdiv(warps, 8)), dim3(256), 0, st, x, hid, E, a);
+    eb_launch_pdl(concat_quant_kernel, dim3((unsigned)cdiv(warps, 8)), dim3(256), 0, st, x, hid, E, a, spec, root_feat, node_feat);
     EB_CHECK_LAUNCH();
     return EB_OK;
 }

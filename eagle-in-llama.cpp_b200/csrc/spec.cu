@@ -182,8 +182,23 @@ __global__ void scatter_feat_kernel(const SpecState *s, const float *feat, float
 
 // One depth level of the reference's tree expansion (speculative-eagle.cpp:527-642), on device.
 // cand_ids/cand_p: [n_branch][top_k] sorted candidates of the rows of the last draft batch.
-__global__ void tree_expand_kernel(SpecState *s, SpecCfg c, const int32_t *cand_ids, const float *cand_p) {
-    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+// The walk is serial (one thread), but every access to the state would be a dependent global round trip: the CTA copies
+// the state and the candidate lists into shared memory, thread 0 works there, the CTA copies the state back.
+__device__ void tree_expand_serial(SpecState *s, const SpecCfg &c, const int32_t *cand_ids, const float *cand_p);
+__global__ void __launch_bounds__(256) tree_expand_kernel(SpecState *gs, SpecCfg c, const int32_t *g_ids, const float *g_p) {
+    __shared__ __align__(16) uint32_t sm_state[(sizeof(SpecState) + 3) / 4];
+    __shared__ int32_t sm_ids[256]; __shared__ float sm_p[256];
+    pdl_trigger(); pdl_wait();
+    constexpr int NW = (int)(sizeof(SpecState) / 4);
+    static_assert(sizeof(SpecState) % 4 == 0, "SpecState is copied word-wise");
+    for (int i = threadIdx.x; i < NW; i += blockDim.x) sm_state[i] = ((const uint32_t *)gs)[i];
+    for (int i = threadIdx.x; i < c.n_branch * c.top_k; i += blockDim.x) { sm_ids[i] = g_ids[i]; sm_p[i] = g_p[i]; }
+    __syncthreads();
+    if (threadIdx.x == 0) tree_expand_serial((SpecState *)sm_state, c, sm_ids, sm_p);
+    __syncthreads();
+    for (int i = threadIdx.x; i < NW; i += blockDim.x) ((uint32_t *)gs)[i] = sm_state[i];
+}
+__device__ void tree_expand_serial(SpecState *s, const SpecCfg &c, const int32_t *cand_ids, const float *cand_p) {
     if (s->done) {                                     // nothing left to draft: park the dummy rows behind the real nodes
         const int base = s->n_nodes;
         s->dft_n = 0; s->dft_node_base = base;
@@ -308,7 +323,8 @@ int eb_spec_scatter_feat(const SpecState *s, const float *feat, float *node_feat
     scatter_feat_kernel<<<dim3((unsigned)cdiv(E / 4, 256), n_branch), 256, 0, st>>>(s, feat, node_feat, E, n_branch); EB_CHECK_LAUNCH(); return EB_OK;
 }
 int eb_spec_expand(SpecState *s, const SpecCfg &c, const int32_t *cand_ids, const float *cand_p, cudaStream_t st) {
-    tree_expand_kernel<<<1, 32, 0, st>>>(s, c, cand_ids, cand_p); EB_CHECK_LAUNCH(); return EB_OK;
+    if (c.n_branch * c.top_k > 256) return eb_set_err(EB_ERR_ARG, "expand: n_branch * top_k > 256");
+    eb_launch_pdl(tree_expand_kernel, dim3(1), dim3(256), 0, st, s, c, cand_ids, cand_p); EB_CHECK_LAUNCH(); return EB_OK;
 }
 int eb_spec_accept(SpecState *s, const SpecCfg &c, const int32_t *best, cudaStream_t st) { accept_kernel<<<1, 32, 0, st>>>(s, c, best); EB_CHECK_LAUNCH(); return EB_OK; }
 int eb_spec_compact(SpecState *s, void *kc, void *vc, void *stage, int64_t layer_stride, int E, int L, int max_acc, cudaStream_t st) {

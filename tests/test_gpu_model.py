@@ -133,13 +133,14 @@ def test_forward_vs_oracle(eb, ftype, T):
     s.free()
 
 
+@pytest.mark.parametrize("head_ftype", [po.Q4_0, "q4_k_m"])
 @pytest.mark.parametrize("use_graph", [False, True])
-def test_spec_rounds_vs_oracle(eb, use_graph):
+def test_spec_rounds_vs_oracle(eb, use_graph, head_ftype):
     """multi-round greedy decoding: draft-tree token ids, accepted paths and bonus tokens must be
     identical to the oracle composition round after round (KV compaction feeds the next round)."""
     hp = dict(E=256, H=2, F=512, V=1024, L=2)
     tgt = fx.make_model(**hp, ftype="q4_k_m", seed=31)
-    head = fx.make_model(**{**hp, "L": 1}, ftype=po.Q4_0, seed=32, is_eagle=True)
+    head = fx.make_model(**{**hp, "L": 1}, ftype=head_ftype, seed=32, is_eagle=True)
     cfg = dict(n_branch=4, n_draft=12, max_depth=5, top_k=10, p_split=0.1, max_nodes=16)
     n_ctx = 128
     cpu = CpuStream(po.oracle(), tgt, head, n_ctx)
