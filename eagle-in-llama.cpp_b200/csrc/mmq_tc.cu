@@ -24,6 +24,7 @@
 // super-block of A, a whole super-block of D) and the TMEM stores overlap the next group's arithmetic.
 #include "common.cuh"
 #include "tc.cuh"
+#include <algorithm>
 #include <cstdlib>
 #include <cuda.h>
 
@@ -624,6 +625,8 @@ int eb_mmq_tc_supported(int type, int64_t N, int64_t K, int T) {
 // split-K factor: planes <= 8, minimise rounds x (super-blocks per item + pipeline fill)
 static int tc_pick_ksplit(int64_t N, int nbr) {
     const int n_rb = (int)cdiv(N, 128), G = eb_sm_count();
+    static const int force = getenv("EB_TC_KS") ? atoi(getenv("EB_TC_KS")) : 0;     // tuning experiments
+    if (force > 0) { const int ks = std::min(force, nbr), spp = (int)cdiv(nbr, ks); return (int)cdiv(nbr, spp); }
     int best = 1; double best_cost = 1e30;
     for (int ks = 1; ks <= 8 && ks <= nbr; ks++) {
         const int spp = (int)cdiv(nbr, ks), eff_ks = (int)cdiv(nbr, spp);
