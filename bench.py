@@ -296,16 +296,21 @@ class CpuSlice:
         return verify + (TREE["max_depth"] + 1) * t_head, verify
 
 
-def cpu_baseline(budget_s=25.0):
+def cpu_baseline(budget_s=12.0):
+    """reference CPU path on the host cores: a bounded sample (about budget_s seconds of CPU work) of the same workload"""
     c = CpuSlice()
-    t_over = c.forward_s(0, False, 65)                       # embeddings + final norm + lm_head
-    t_l1 = c.forward_s(1, False, 65)                         # + one decoder layer at n_kv = 4096
-    t_head = c.forward_s(1, True, 8)                         # one draft level: head forward over 8 branches
+    c.forward_s(1, False, 65)                                # warm the thread pool and the page cache
+    t_first = c.forward_s(1, False, 65)
+    reps = int(min(64, max(3, budget_s * 0.8 / max(t_first, 1e-3))))
+    t_l1 = float(np.median([c.forward_s(1, False, 65) for _ in range(reps)]))      # one decoder layer at n_kv = 4096 (+ lm_head slice)
+    t_over = float(np.median([c.forward_s(0, False, 65) for _ in range(5)]))       # embeddings + final norm + lm_head
+    t_head = float(np.median([c.forward_s(1, True, 8) for _ in range(5)]))         # one draft level: head forward over 8 branches
     rnd, ver = c.round_seconds(t_l1, t_over, t_head)
     return {"value": (FIXED_ACCEPT + 1) / rnd, "unit": "tok/s", "cores": c.cores, "kind": c.kind,
             "verify_step_us": ver * 1e6,
-            "sample": f"1 of 32 target layers (T=65, n_kv=4096) + lm_head slice + one 8-row draft-head level, timed once each "
-                      f"({t_l1:.2f}s, {t_over:.2f}s, {t_head:.2f}s) and scaled to 32 layers + {TREE['max_depth'] + 1} draft levels"}
+            "sample": f"1 of 32 target layers (T=65, n_kv=4096) timed {reps}x + lm_head slice 5x + one 8-row draft-head level 5x "
+                      f"(medians {t_l1:.2f}s, {t_over:.2f}s, {t_head:.2f}s; {reps * t_l1 + 5 * (t_over + t_head):.0f}s of CPU work), "
+                      f"scaled to 32 layers + {TREE['max_depth'] + 1} draft levels"}
 
 
 def run_reference(args, rank, world):
