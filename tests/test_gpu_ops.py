@@ -88,6 +88,22 @@ def test_mul_mat_model_shapes(eb, t, N, K, T):
     assert rel_max(got, want) < 2e-5
 
 
+@pytest.mark.parametrize("t,N,K", [(po.Q4_K, 12288, 4096), (po.Q6_K, 4816, 11008), (po.Q4_K, 4096, 8192)])
+@pytest.mark.parametrize("T", [4, 8])
+def test_mul_mat_draft_shapes(eb, t, N, K, T):
+    """T <= 8 (one draft level) on the persistent small-batch kernel: several (32-row block, K split) items per CTA with
+    the weight prefetch running across item boundaries, a row count that is not a multiple of 32, K = 11008 (43 super-blocks
+    over 8 K groups: uneven), random blocks (every scale / min bit pattern)."""
+    rng = np.random.default_rng(N + K + T)
+    raw = fx.random_blocks(t, N * K, rng)
+    X = rng.normal(0, 1, (T, K)).astype(np.float32)
+    X[1, 256:512] = 0
+    got = eb.mul_mat(eb.Weights(t, raw, N, K), X)
+    want = po.oracle().mul_mat(t, raw, N, K, X)
+    assert got.shape == want.shape
+    assert rel_max(got, want) < 2e-5
+
+
 def test_mul_mat_linearity_full_size(eb):
     """size-independent property at the BASELINE shape (lm_head 32000 x 4096, Q6_K, T = 65):
     a column that is an exact copy of another must give identical outputs, zero columns zero."""
