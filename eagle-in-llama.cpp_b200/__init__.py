@@ -53,7 +53,8 @@ def lib():
     vp, i32, i64, f32, sz = C.c_void_p, C.c_int, C.c_int64, C.c_float, C.c_size_t
     sig = {
         "eb_last_error": ([], C.c_char_p), "eb_version": ([], i32), "eb_device_init": ([i32], i32),
-        "eb_device_sm_count": ([], i32), "eb_row_size": ([i32, i64], sz),
+        "eb_device_sm_count": ([], i32), "eb_device_memory": ([C.POINTER(sz), C.POINTER(sz)], i32),
+        "eb_copy": ([vp, vp, sz, vp], i32), "eb_concat2": ([vp, vp, vp, i32, i32, vp], i32), "eb_row_size": ([i32, i64], sz),
         "eb_malloc": ([C.POINTER(vp), sz], i32), "eb_free": ([vp], i32), "eb_memset": ([vp, i32, sz, vp], i32),
         "eb_upload": ([vp, vp, sz, vp], i32), "eb_download": ([vp, vp, sz, vp], i32), "eb_synchronize": ([vp], i32),
         "eb_repack": ([i32, vp, vp, i64, vp], i32), "eb_unpack": ([i32, vp, vp, i64, vp], i32),

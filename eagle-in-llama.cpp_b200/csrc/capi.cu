@@ -42,6 +42,12 @@ int eb_device_init(int device) {
     return EB_OK;
 }
 int eb_device_sm_count(void) { return g_sm_count; }
+int eb_device_memory(size_t *free_bytes, size_t *total_bytes) {
+    if (g_device < 0) { int rc = eb_device_init(0); if (rc) return rc; }
+    size_t f = 0, t = 0; EB_CUDA(cudaMemGetInfo(&f, &t));
+    if (free_bytes) *free_bytes = f; if (total_bytes) *total_bytes = t;
+    return EB_OK;
+}
 
 size_t eb_row_size(int type, int64_t k) {
     switch (type) {
@@ -63,6 +69,7 @@ int eb_free(void *p) { EB_CUDA(cudaFree(p)); return EB_OK; }
 int eb_memset(void *p, int v, size_t bytes, void *st) { EB_CUDA(cudaMemsetAsync(p, v, bytes, S(st))); return EB_OK; }
 int eb_upload(void *d, const void *h, size_t bytes, void *st) { NEED_DEV(); EB_CUDA(cudaMemcpyAsync(d, h, bytes, cudaMemcpyHostToDevice, S(st))); EB_CUDA(cudaStreamSynchronize(S(st))); return EB_OK; }
 int eb_download(void *h, const void *d, size_t bytes, void *st) { EB_CUDA(cudaMemcpyAsync(h, d, bytes, cudaMemcpyDeviceToHost, S(st))); EB_CUDA(cudaStreamSynchronize(S(st))); return EB_OK; }
+int eb_copy(void *d, const void *s, size_t bytes, void *st) { if (bytes && d != s) EB_CUDA(cudaMemcpyAsync(d, s, bytes, cudaMemcpyDeviceToDevice, S(st))); return EB_OK; }
 int eb_synchronize(void *st) { EB_CUDA(cudaStreamSynchronize(S(st))); return EB_OK; }
 
 // GGUF block layout <-> device layout (aligned planes), see common.cuh WPlanes
@@ -116,6 +123,7 @@ int eb_add(const float *a, const float *b, float *y, int64_t n, int64_t nb, void
 int eb_mul(const float *a, const float *b, float *y, int64_t n, int64_t nb, void *st) { NEED_DEV(); return eb_mul_impl(a, b, y, n, nb, S(st)); }
 int eb_silu(const float *x, float *y, int64_t n, void *st) { NEED_DEV(); return eb_silu_impl(x, y, n, S(st)); }
 int eb_relu(const float *x, float *y, int64_t n, void *st) { NEED_DEV(); return eb_relu_impl(x, y, n, S(st)); }
+int eb_concat2(const float *a, const float *b, float *y, int E, int T, void *st) { NEED_DEV(); return eb_concat2_impl(a, b, y, E, T, S(st)); }
 int eb_cpy_f32_f16(const float *x, void *y, int64_t n, void *st) { NEED_DEV(); return eb_cpy_f32_f16_impl(x, y, n, S(st)); }
 
 size_t eb_flash_attn_ws_size(int T, int H, int D, int n_kv) { return std::max(eb_flash_attn_ws_size_impl(T, H, D, n_kv), eb_fattn_tc_ws_size(T, H, n_kv)); }

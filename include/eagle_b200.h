@@ -36,6 +36,8 @@ EB_API const char *eb_last_error(void);
 EB_API int  eb_version(void);
 EB_API int  eb_device_init(int device);                 /* selects the device, checks sm_100 */
 EB_API int  eb_device_sm_count(void);
+/* ggml_backend_device_i::get_memory, R/ggml/src/ggml-backend-impl.h:143 (CUDA: ggml-cuda.cu:2944) */
+EB_API int  eb_device_memory(size_t *free_bytes, size_t *total_bytes);
 EB_API size_t eb_row_size(int type, int64_t k);         /* ggml_row_size, R/ggml/src/ggml.c:1183 */
 
 /* ---- device memory (ggml_backend_buffer_i alloc/set/get, R/ggml/src/ggml-backend-impl.h:41-72) */
@@ -45,6 +47,9 @@ EB_API int eb_memset(void *d_ptr, int value, size_t bytes, void *stream);
 EB_API int eb_upload(void *d_dst, const void *h_src, size_t bytes, void *stream);    /* set_tensor */
 EB_API int eb_download(void *h_dst, const void *d_src, size_t bytes, void *stream);  /* get_tensor */
 EB_API int eb_synchronize(void *stream);
+/* device-to-device copy: GGML_OP_CPY / CONT / DUP of a contiguous same-type tensor and buffer_i::cpy_tensor
+ * (R/ggml/src/ggml-cuda/cpy.cu:526, ggml-cuda.cu:603) */
+EB_API int eb_copy(void *d_dst, const void *d_src, size_t bytes, void *stream);
 
 /* ---- operator layer ------------------------------------------------------------------ */
 /* Device layout of quantised weights.  Q4_K blocks (16-byte aligned) stay in GGUF order; the
@@ -87,6 +92,9 @@ EB_API int eb_add(const float *d_a, const float *d_b, float *d_y, int64_t n, int
 EB_API int eb_mul(const float *d_a, const float *d_b, float *d_y, int64_t n, int64_t nb, void *stream);
 EB_API int eb_silu(const float *d_x, float *d_y, int64_t n, void *stream);
 EB_API int eb_relu(const float *d_x, float *d_y, int64_t n, void *stream);
+/* GGML_OP_CONCAT along dim 0 of two f32 [E][T] tensors -> [2E][T] (build_eagle's [embd | hidden],
+ * R/src/llama.cpp:1893; R/ggml/src/ggml-cuda/concat.cu:4) */
+EB_API int eb_concat2(const float *d_a, const float *d_b, float *d_y, int E, int T, void *stream);
 /* GGML_OP_CPY f32 -> f16 (KV store), R/ggml/src/ggml-cuda/cpy.cu:35 */
 EB_API int eb_cpy_f32_f16(const float *d_x, void *d_y_f16, int64_t n, void *stream);
 

@@ -1,0 +1,214 @@
+"""The drop-in boundary proper: libggml-b200.so is loaded by the REFERENCE's own plugin loader
+(ggml_backend_load, R/ggml/src/ggml-backend-reg.cpp:220) and handed the same ggml graphs libllama
+builds (build_llama / build_eagle, R/src/llama.cpp:1647-2019), with backend-allocated buffers.
+
+CPU (-m "not gpu"): the plugin exports the loader's entry points, scores 0 without a GPU (the
+loader skips it: no CPU fallback), and the graph harness itself is pinned — its ggml-cpu leg must
+reproduce oracle/_ref's ref_forward bit for bit.
+GPU (-m gpu): the same graph on the plugin vs on the reference's ggml-cpu backend — what
+R/tests/test-backend-ops.cpp does per op — plus set_tensor/get_tensor round trips of the
+repacked weight formats.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+import fixtures as fx
+import pyoracle as po
+from conftest import ROOT
+
+PLUGIN = os.path.join(ROOT, "eagle-in-llama.cpp_b200", "ggml_backend", "libggml-b200.so")
+HARNESS = os.path.join(ROOT, "oracle", "_ref", "libggml_graph_harness.so")
+
+needs_build = pytest.mark.skipif(not (os.path.exists(PLUGIN) and os.path.exists(HARNESS) and po.have_ref()),
+                                 reason="libggml-b200.so / graph harness need the reference headers at build time (__graft_entry__.build())")
+
+_h = None
+
+
+def harness():
+    global _h
+    if _h is None:
+        C.CDLL(os.path.join(ROOT, "oracle", "_ref", "libggml-ref.so"), mode=C.RTLD_GLOBAL)     # the host's ggml-base: resolves the plugin's ggml_* symbols
+        h = C.CDLL(HARNESS)
+        vp, i32, f32 = C.c_void_p, C.c_int, C.c_float
+        h.gh_last_error.restype = C.c_char_p
+        h.gh_plugin_name.restype = C.c_char_p
+        h.gh_load_plugin.argtypes = [C.c_char_p]
+        h.gh_model_new.argtypes = [i32, i32, i32, i32, i32, f32, f32, i32]; h.gh_model_new.restype = vp
+        h.gh_model_free.argtypes = [vp]
+        h.gh_model_set_global.argtypes = [vp, i32, i32, vp]
+        h.gh_model_set_layer.argtypes = [vp, i32, i32, i32, vp]
+        h.gh_roundtrip.argtypes = [i32, i32, C.c_int64, C.c_int64, vp, vp]
+        h.gh_forward.argtypes = [i32, vp, vp, vp, i32, vp, vp, vp, i32, i32, i32, vp, vp, vp, C.POINTER(i32)]
+        _h = h
+    return _h
+
+
+def gh_model(h, f):
+    hp = f["hparams"]
+    m = h.gh_model_new(hp["E"], hp["H"], hp["F"], hp["V"], hp["L"], hp["eps"], hp["freq_base"], int(hp["is_eagle"]))
+    for which, (t, raw) in f["globals"].items():
+        h.gh_model_set_global(m, which, t, po._ptr(raw))
+    for l, d in enumerate(f["layers"]):
+        for which, (t, raw) in d.items():
+            h.gh_model_set_layer(m, l, which, t, po._ptr(raw))
+    return m
+
+
+def gh_forward(h, which, m, f, kv_k, kv_v, tokens, pos, hidden, kv_head, n_kv, vis, want_logits=True):
+    hp = f["hparams"]
+    T = len(tokens)
+    logits = np.empty((T, hp["V"]), np.float32) if want_logits else None
+    feat = np.empty((T, hp["E"]), np.float32)
+    n_nodes = C.c_int(0)
+    hid = None if hidden is None else np.ascontiguousarray(hidden, np.float32)
+    rc = h.gh_forward(which, m, po._ptr(kv_k), po._ptr(kv_v), kv_k.shape[1], po._ptr(np.ascontiguousarray(tokens, np.int32)),
+                      po._ptr(np.ascontiguousarray(pos, np.int32)), po._ptr(hid), T, kv_head, n_kv, po._ptr(np.ascontiguousarray(vis, np.uint8)),
+                      po._ptr(logits), po._ptr(feat), C.byref(n_nodes))
+    assert rc == 0, h.gh_last_error().decode()
+    return logits, feat, n_nodes.value
+
+
+def case(ftype, is_eagle, seed, E=256, H=2, F=512, V=1024, L=2, T=27, n_past=40, n_ctx=128):
+    rng = np.random.default_rng(seed)
+    f = fx.make_model(E, H, F, V, 1 if is_eagle else L, ftype, seed, is_eagle=is_eagle)
+    if is_eagle:                                                   # the head shares the target's lm_head (R/src/llama.cpp:1867-1869)
+        out_t = po.Q6_K if ftype in ("q4_k_m", po.Q4_0) else ftype
+        f["globals"][po.T_OUTPUT] = (out_t, fx.quantize(out_t, rng.normal(0, 0.02, (V, E)).astype(np.float32), rng))
+    Lm = f["hparams"]["L"]
+    par = fx.tree_parents(T, rng)
+    n_kv = n_ctx
+    vis = fx.vis_matrix(par, n_past, n_kv)
+    tokens = rng.integers(3, V, T).astype(np.int32)
+    pos = (n_past + fx.tree_depths(par)).astype(np.int32)
+    hidden = rng.normal(0, 1, (T, E)).astype(np.float32) if is_eagle else None
+    kv = rng.normal(0, 1, (2, Lm, n_ctx, E)).astype(np.float16)
+    kv[:, :, n_past:] = 0
+    return f, tokens, pos, hidden, vis, kv, n_past, n_kv
+
+
+@needs_build
+def test_plugin_exports_the_loader_entry_points():
+    out = subprocess.check_output(["nm", "-D", "--defined-only", PLUGIN], text=True)
+    for sym in ("ggml_backend_init", "ggml_backend_score", "ggml_backend_b200_reg"):
+        assert f" T {sym}" in out, sym
+    und = subprocess.check_output(["nm", "-D", "--undefined-only", PLUGIN], text=True)
+    assert "ggml_backend_buffer_init" in und and "eb_mul_mat" in und           # ggml-base from the host, kernels from libeagle_b200
+    assert "ref_" not in und and "eo_" not in und                                # never the oracle
+
+
+@needs_build
+def test_plugin_is_skipped_without_a_gpu():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    h = harness()
+    assert h.gh_load_plugin(PLUGIN.encode()) != 0                                # ggml_backend_score() == 0: "not supported on this system"
+    f, tokens, pos, hidden, vis, kv, n_past, n_kv = case(po.Q4_0, False, 3, L=1, T=4)
+    m = gh_model(h, f)
+    n = C.c_int(0)
+    rc = h.gh_forward(1, m, po._ptr(kv[0].copy()), po._ptr(kv[1].copy()), kv.shape[2], po._ptr(tokens), po._ptr(pos), None, 4, n_past, n_kv,
+                      po._ptr(vis), None, po._ptr(np.empty((4, 256), np.float32)), C.byref(n))
+    assert rc != 0                                                               # no backend, and nothing falls back to the CPU
+    h.gh_model_free(m)
+
+
+@needs_build
+@pytest.mark.parametrize("ftype,is_eagle", [("q4_k_m", False), (po.Q4_0, True)])
+def test_graph_harness_cpu_leg_equals_ref_forward(ftype, is_eagle):
+    """pins the harness: same graph, same ggml-cpu code, backend-allocated buffers instead of aliased host memory"""
+    h = harness()
+    f, tokens, pos, hidden, vis, kv, n_past, n_kv = case(ftype, is_eagle, 11)
+    hp = f["hparams"]
+    m = gh_model(h, f)
+    kk, vv = kv[0].copy().view(np.uint16), kv[1].copy().view(np.uint16)
+    lg, ft, n_nodes = gh_forward(h, 0, m, f, kk, vv, tokens, pos, hidden, n_past, n_kv, vis)
+    r = po.ref()
+    rm = fx.to_cpu_model(r, f)
+    rkv = r._g("kv_new")(hp["L"], hp["E"], kv.shape[2])
+    ks, vs = r.kv_arrays(rkv, hp["L"], hp["E"], kv.shape[2])
+    for l in range(hp["L"]):
+        ks[l][:] = kv[0, l].view(np.uint16); vs[l][:] = kv[1, l].view(np.uint16)
+    lg_r, ft_r = r.forward(rm, rkv, tokens, pos, hidden, n_past, n_kv, vis, hp["E"], hp["V"])
+    assert n_nodes > 20 * hp["L"]
+    np.testing.assert_array_equal(ft, ft_r)
+    np.testing.assert_array_equal(lg, lg_r)
+    for l in range(hp["L"]):
+        np.testing.assert_array_equal(kk[l], ks[l]); np.testing.assert_array_equal(vv[l], vs[l])
+    h.gh_model_free(m)
+
+
+# --------------------------------------------------------------------------------------- GPU
+@pytest.fixture(scope="module")
+def plugin():
+    if not (os.path.exists(PLUGIN) and os.path.exists(HARNESS)):
+        pytest.fail("libggml-b200.so / libggml_graph_harness.so missing on the GPU box: they are built by __graft_entry__.build() and travel with the snapshot")
+    h = harness()
+    assert h.gh_load_plugin(PLUGIN.encode()) == 0, h.gh_last_error().decode()
+    assert h.gh_plugin_name() == b"B200"
+    return h
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("t", [po.Q4_K, po.Q6_K, po.Q4_0, po.Q8_0, po.F16, po.F32])
+def test_set_get_tensor_roundtrip(plugin, t):
+    """buffer_i::set_tensor (whole + partial) -> get_tensor returns the GGUF bytes (repacked formats included)"""
+    rng = np.random.default_rng(5)
+    K, N = 512, 24
+    raw = fx.random_blocks(t, K * N, rng) if t in fx.QTYPES else rng.integers(0, 255, K * N * (2 if t == po.F16 else 4), dtype=np.uint8)
+    out = np.zeros_like(raw)
+    assert plugin.gh_roundtrip(1, t, K, N, po._ptr(raw), po._ptr(out)) == 0, plugin.gh_last_error().decode()
+    np.testing.assert_array_equal(out, raw)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("ftype,is_eagle,T", [("q4_k_m", False, 27), ("q4_k_m", False, 65), (po.Q4_0, False, 16), (po.Q8_0, False, 5),
+                                              ("q4_k_m", True, 8), (po.Q4_0, True, 27)])
+def test_plugin_graph_matches_reference_cpu_backend(plugin, ftype, is_eagle, T):
+    """the verify graph (build_llama) and the draft-head graph (build_eagle) through ggml_backend_graph_compute on the
+    plugin vs on the reference's ggml-cpu backend: logits within the north star's 1e-2 (relative to the row maximum),
+    stored K/V cells within f16 rounding, greedy tokens equal wherever the CPU's own top-2 are not near-tied"""
+    h = plugin
+    f, tokens, pos, hidden, vis, kv, n_past, n_kv = case(ftype, is_eagle, 100 + T, T=T, n_ctx=192)
+    hp = f["hparams"]
+    m = gh_model(h, f)
+    outs = []
+    for which in (0, 1):
+        kk, vv = kv[0].copy().view(np.uint16), kv[1].copy().view(np.uint16)
+        lg, ft, n_nodes = gh_forward(h, which, m, f, kk, vv, tokens, pos, hidden, n_past, n_kv, vis)
+        outs.append((lg, ft, kk.view(np.float16).astype(np.float32), vv.view(np.float16).astype(np.float32)))
+    (lg_c, ft_c, k_c, v_c), (lg_g, ft_g, k_g, v_g) = outs
+    assert np.isfinite(lg_g).all()
+    tol = 1e-2 * 3                                                     # rounding flips of the Q8 grid, as in test_gpu_model.py
+    assert np.abs(lg_g - lg_c).max() <= tol * np.abs(lg_c).max()
+    assert np.abs(ft_g - ft_c).max() <= tol * np.abs(ft_c).max()
+    np.testing.assert_array_equal(k_g[:, :n_past], k_c[:, :n_past])    # the committed prefix is untouched
+    assert np.abs(k_g - k_c).max() <= tol * np.abs(k_c).max() and np.abs(v_g - v_c).max() <= tol * np.abs(v_c).max()
+    assert np.abs(k_g[:, n_past:n_past + T]).max() > 0                 # the T new cells were stored
+    top2 = np.sort(lg_c, axis=1)[:, -2:]
+    decided = (top2[:, 1] - top2[:, 0]) > 2 * tol * np.abs(lg_c).max()
+    assert (lg_g.argmax(1) == lg_c.argmax(1))[decided].all()
+    h.gh_model_free(m)
+
+
+@pytest.mark.gpu
+def test_plugin_graph_7b_width_layer(plugin):
+    """one Vicuna-7B-width layer (E 4096, 32 heads, F 11008, Q4_K_M mix) at the 65-row verify batch: the plugin's
+    MUL_MAT lands on the tcgen05 GEMM, FLASH_ATTN_EXT on the f16-mask kernel; compared with the reference's ggml-cpu"""
+    h = plugin
+    f, tokens, pos, hidden, vis, kv, n_past, n_kv = case("q4_k_m", False, 77, E=4096, H=32, F=11008, V=512, L=1, T=65, n_past=300, n_ctx=512)
+    m = gh_model(h, f)
+    outs = []
+    for which in (0, 1):
+        kk, vv = kv[0].copy().view(np.uint16), kv[1].copy().view(np.uint16)
+        lg, ft, _ = gh_forward(h, which, m, f, kk, vv, tokens, pos, hidden, n_past, n_kv, vis)
+        outs.append((lg, ft))
+    (lg_c, ft_c), (lg_g, ft_g) = outs
+    err = np.abs(lg_g - lg_c).max(1) / np.abs(lg_c).max()
+    assert err.max() <= 3e-2, err.max()
+    assert np.median(err) <= 1e-3, np.median(err)                      # rows without a Q8-grid rounding flip agree far tighter
+    h.gh_model_free(m)
