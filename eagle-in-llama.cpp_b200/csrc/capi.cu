@@ -20,6 +20,10 @@ long eb_launches_now() { return g_launches.load(); }
 void eb_launches_add(long n) { g_launches.fetch_add(n); }
 int eb_sm_count() { return g_sm_count > 0 ? g_sm_count : 148; }
 
+static thread_local const int *g_gate = nullptr;
+const int *eb_gate() { return g_gate; }
+void eb_gate_set(const int *g) { g_gate = g; }
+
 int eb_pdl_enabled() { static const int on = getenv("EB_NO_PDL") ? 0 : 1; return on; }
 
 extern "C" {

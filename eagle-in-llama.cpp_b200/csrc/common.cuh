@@ -83,6 +83,13 @@ static inline cudaError_t eb_launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 
     return cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);
 }
 
+// ---- launch gate: the draft levels of a round are captured in a CUDA graph with fixed geometry, but the reference's draft
+// loop stops as soon as no branch is drafting (R/examples/speculative/speculative-eagle.cpp:627-641).  A kernel launched
+// while a gate is set (host side, eb_gate_set) receives a device pointer and returns right after pdl_wait() when the word
+// it points to is 0 (the wait is kept so that the successor's wait still covers every earlier kernel).
+const int *eb_gate(); void eb_gate_set(const int *g);
+__device__ __forceinline__ bool gate_closed(const int *g) { return g != nullptr && *(const volatile int *)g == 0; }
+
 // ---- device helpers
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll

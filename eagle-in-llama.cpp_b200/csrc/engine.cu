@@ -279,7 +279,11 @@ static int grid_of(const DTensor &w) { return w.type == EB_Q4_K || w.type == EB_
 
 static int forward_dev(const eb_model *m, KVCache &kv, Workspace &w, const int32_t *tokens, const int32_t *pos, const uint32_t *bits,
                        const float *hidden, const FwdCtl *ctl, int T, bool want_logits, cudaStream_t st, int *logit_ks = nullptr,
-                       const SpecState *spec = nullptr, const float *root_feat = nullptr, float *node_feat = nullptr) {
+                       const SpecState *spec = nullptr, const float *root_feat = nullptr, float *node_feat = nullptr,
+                       const int *gate_fwd = nullptr, const int *gate_lm = nullptr) {
+    // gate_fwd / gate_lm (draft levels of a captured round): device words that switch the whole forward / its lm_head off
+    // when the tree stopped growing (common.cuh "launch gate"); the caller clears the gate after the call
+    eb_gate_set(gate_fwd);
     // spec != null (draft level): hidden rows are gathered from root_feat / node_feat by the state's dft_src, and the result
     // features are scattered to node_feat, inside the kernels that read / produce them
     const int E = m->E, H = m->H, F = m->F, D = E / H;
@@ -356,6 +360,7 @@ static int forward_dev(const eb_model *m, KVCache &kv, Workspace &w, const int32
     ActQ al = eb_actq_carve(w.actq, grid_of(o), E, T);
     if (!want_logits) al.qs = nullptr;
     RC(eb_resid_norm_quant(w.x, pend, pend_ks, (const float *)m->g[EB_T_OUTPUT_NORM].data, m->eps, E, T, al, w.feat, st, nullptr, spec, node_feat));
+    if (gate_lm) eb_gate_set(gate_lm);
     if (want_logits && logit_ks) {
         // the caller's top-k / argmax sums the lm_head's split-K planes [ks][T][V] (w.partial) itself
         RC(mm_parts(o, al, w.partial, logit_ks, st));
@@ -478,11 +483,17 @@ static int round_dev(eb_session *s, cudaStream_t st) {
         int ks_h = 1;
         const bool fused_io = s->head->E % 256 == 0 && s->head->E <= 8192 && (s->head->g[EB_T_OUTPUT].type == EB_Q4_K || s->head->g[EB_T_OUTPUT].type == EB_Q6_K);
         if (!fused_io) RC(eb_spec_gather_hidden(d, s->root_feat, s->node_feat, s->ws_h.hidden, E, c.n_branch, st));
-        RC(forward_dev(s->head, s->kv_h, s->ws_h, d->dft_tokens, d->dft_pos, d->dft_bits, s->ws_h.hidden, &d->ctl_head, c.n_branch, !last, st, &ks_h,
-                       fused_io ? d : nullptr, s->root_feat, s->node_feat));
+        // idle levels (tree full / no branch drafting: the reference leaves its draft loop, speculative-eagle.cpp:627-641) switch themselves off
+        static const bool no_gate = getenv("EB_NO_GATE") != nullptr;
+        const bool gated = fused_io && !no_gate;
+        rc = forward_dev(s->head, s->kv_h, s->ws_h, d->dft_tokens, d->dft_pos, d->dft_bits, s->ws_h.hidden, &d->ctl_head, c.n_branch, !last, st, &ks_h,
+                       fused_io ? d : nullptr, s->root_feat, s->node_feat, gated ? &d->gate_fwd : nullptr, gated ? &d->gate_lm : nullptr);
+        if (rc) { eb_gate_set(nullptr); return rc; }
         if (!fused_io) RC(eb_spec_scatter_feat(d, s->ws_h.feat, s->node_feat, E, c.n_branch, st));
-        if (last) break;
-        RC(eb_top_k_impl(s->ws_h.partial, c.n_branch, V, c.top_k, s->cand_ids, s->cand_vals, s->cand_p, st, ks_h, (int64_t)c.n_branch * V));
+        if (last) { eb_gate_set(nullptr); break; }
+        rc = eb_top_k_impl(s->ws_h.partial, c.n_branch, V, c.top_k, s->cand_ids, s->cand_vals, s->cand_p, st, ks_h, (int64_t)c.n_branch * V);
+        eb_gate_set(nullptr);
+        if (rc) return rc;
         RC(eb_spec_expand(d, c, s->cand_ids, s->cand_p, st));
     }
     RC(verify_dev(s, c.max_nodes, st));

@@ -229,8 +229,9 @@ __global__ void fattn_combine_kernel(const float *__restrict__ part_o, const flo
 
 // merge the KV splits and quantise the result for the wo GEMM (Q8_K grid): one warp per (row, 256-value block = 2 heads),
 // lane = (head-in-pair, 8 dims); the f32 attention output never goes to memory
-__global__ void fattn_combine_quant_kernel(const float *__restrict__ part_o, const float *__restrict__ part_ml, int T, int H, int nsplit, ActQ a) {
+__global__ void fattn_combine_quant_kernel(const float *__restrict__ part_o, const float *__restrict__ part_ml, int T, int H, int nsplit, ActQ a, const int *__restrict__ gate) {
     pdl_trigger(); pdl_wait();
+    if (gate_closed(gate)) return;
     const int w = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31, nb = H / 2;
     if (w >= T * nb) return;
     const int r = w / nb, b = w % nb, h = 2 * b + (lane >> 4), d0 = (lane & 15) * 8;
@@ -280,7 +281,7 @@ __global__ void fattn_combine_quant_kernel(const float *__restrict__ part_o, con
                    a.h16 ? a.h16 + (int64_t)r * K + b * 256 : nullptr, (a.dT && r < EB_DT_PITCH) ? a.dT + (int64_t)b * EB_DT_PITCH + r : nullptr);
 }
 void eb_fattn_combine_quant(const float *part_o, const float *part_ml, int T, int H, int nsplit, const ActQ &a, cudaStream_t st) {
-    eb_launch_pdl(fattn_combine_quant_kernel, dim3((unsigned)cdiv((int64_t)T * (H / 2), 8)), dim3(256), 0, st, part_o, part_ml, T, H, nsplit, a);
+    eb_launch_pdl(fattn_combine_quant_kernel, dim3((unsigned)cdiv((int64_t)T * (H / 2), 8)), dim3(256), 0, st, part_o, part_ml, T, H, nsplit, a, eb_gate());
 }
 void eb_fattn_combine(const float *part_o, const float *part_ml, float *out, int T, int H, int nsplit, cudaStream_t st) {
     fattn_combine_kernel<<<(unsigned)cdiv((int64_t)T * H, 8), 256, 0, st>>>(part_o, part_ml, out, T, H, nsplit);

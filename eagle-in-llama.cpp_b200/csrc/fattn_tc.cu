@@ -38,6 +38,7 @@ struct FtArgs {
     int T, H, nsplit;
     float scale_log2;
     float *out, *part_o, *part_ml;
+    const int *gate;        // launch gate (common.cuh): closed -> the CTA runs the zero-tile path
     long long *prof;        // EB_FA_PROF=1: per-section cycle totals of CTA (0,0)
 };
 
@@ -88,6 +89,7 @@ fattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     if (p.prof && blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 128) p.prof[11] = clock64();
     int n_prefix = p.n_prefix, n_kv = p.n_kv;
     if (p.ctl) { n_prefix = p.ctl->n_prefix; n_kv = min(p.n_ctx, n_prefix + p.ctl->n_tree); }
+    if (gate_closed(p.gate)) n_kv = 0;
     const int n_tiles = (n_kv + FT_TILE - 1) / FT_TILE, tps = (n_tiles + p.nsplit - 1) / p.nsplit;
     const int t0 = split * tps, n = max(0, min(n_tiles, t0 + tps) - t0);
 
@@ -303,7 +305,7 @@ int eb_fattn_tc(const __half *q16, const void *k, const void *v, int64_t kv_stri
     if (p.nsplit > 1 && !ws) return eb_set_err(EB_ERR_ARG, "flash_attn: workspace required");
     static long long *prof_buf = nullptr; static const int want_prof = getenv("EB_FA_PROF") ? 1 : 0;
     if (want_prof && !prof_buf) { cudaMalloc((void **)&prof_buf, 64 * 8); cudaMemset(prof_buf, 0, 64 * 8); }
-    p.prof = want_prof ? prof_buf : nullptr;
+    p.prof = want_prof ? prof_buf : nullptr; p.gate = eb_gate();
     CUtensorMap tmQ, tmK, tmV;
     int rc;
     if ((rc = eb_tc_map_2d_f16(&tmQ, q16, (uint64_t)H * 128, (uint64_t)T, (uint64_t)H * 128 * 2, 64, 128))) return rc;

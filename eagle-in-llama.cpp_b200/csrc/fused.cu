@@ -84,9 +84,10 @@ __global__ void __launch_bounds__(256) resid_norm_quant_kernel(float *__restrict
 template <int MAXT>
 __global__ void __launch_bounds__(MAXT) resid_norm_quant_regs_kernel(float *__restrict__ x, Parts add, const float *__restrict__ w, float eps,
                                                                     int n, ActQ a, float *__restrict__ feat, const float *__restrict__ bias,
-                                                                    const SpecState *__restrict__ spec, float *__restrict__ node_feat) {
+                                                                    const SpecState *__restrict__ spec, float *__restrict__ node_feat, const int *__restrict__ gate) {
     __shared__ double red[32];
     pdl_trigger(); pdl_wait();
+    if (gate_closed(gate)) return;
     const int r = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nw = blockDim.x >> 5;
     const int64_t off = (int64_t)r * n + tid * 8;
     float4 v0 = make_float4(0.f, 0.f, 0.f, 0.f), v1 = v0;
@@ -146,8 +147,9 @@ __global__ void rope_table_kernel(const int32_t *__restrict__ pos, float theta_s
 __global__ void __launch_bounds__(512) rope_kv_store_fused_kernel(Parts qp, Parts kp, Parts vp, float *__restrict__ q, __half *__restrict__ q16,
                                                                  const float2 *__restrict__ tab, __half *__restrict__ kc, __half *__restrict__ vc,
                                                                  const FwdCtl *__restrict__ ctl, int D, int n_head,
-                                                                 const int32_t *__restrict__ pos, float theta_scale) {
+                                                                 const int32_t *__restrict__ pos, float theta_scale, const int *__restrict__ gate) {
     pdl_trigger(); pdl_wait();
+    if (gate_closed(gate)) return;
     const int t = blockIdx.x, tid = threadIdx.x, half = D / 2;
     const int64_t cell0 = ctl ? (int64_t)(ctl->n_prefix + ctl->node_base) * n_head * D : 0;
     const int E = n_head * D;
@@ -187,8 +189,9 @@ __device__ __forceinline__ float4 swiglu4(const Parts &gate, const Parts &up, in
     const float4 g = sum_parts(gate, r * gate.ld + i), u = sum_parts(up, r * up.ld + i);
     return make_float4(__fmul_rn(silu_ref(g.x), u.x), __fmul_rn(silu_ref(g.y), u.y), __fmul_rn(silu_ref(g.z), u.z), __fmul_rn(silu_ref(g.w), u.w));
 }
-__global__ void __launch_bounds__(256) swiglu_quant_kernel(Parts gate, Parts up, int n, ActQ a) {
+__global__ void __launch_bounds__(256) swiglu_quant_kernel(Parts gate, Parts up, int n, ActQ a, const int *__restrict__ lgate) {
     pdl_trigger(); pdl_wait();
+    if (gate_closed(lgate)) return;
     const int r = blockIdx.y, lane = threadIdx.x & 31, b = blockIdx.x * 8 + (threadIdx.x >> 5);
     const int64_t row0 = (int64_t)r * n;
     if (a.kq) {
@@ -213,8 +216,8 @@ int eb_resid_norm_quant(float *x, const float *part, int ks, const float *w, flo
     if (T == 0) return EB_OK;
     Parts p{part, ks, (int64_t)T * n, n};
     if (n % 256 == 0 && n <= 8192 && (!aq.qs || (aq.kq && aq.K == n)))
-        if (n <= 4096) eb_launch_pdl(resid_norm_quant_regs_kernel<512>, dim3(T), dim3(n / 8), 0, st, x, p, w, eps, n, aq, feat, bias, spec, node_feat);
-        else eb_launch_pdl(resid_norm_quant_regs_kernel<1024>, dim3(T), dim3(n / 8), 0, st, x, p, w, eps, n, aq, feat, bias, spec, node_feat);
+        if (n <= 4096) eb_launch_pdl(resid_norm_quant_regs_kernel<512>, dim3(T), dim3(n / 8), 0, st, x, p, w, eps, n, aq, feat, bias, spec, node_feat, eb_gate());
+        else eb_launch_pdl(resid_norm_quant_regs_kernel<1024>, dim3(T), dim3(n / 8), 0, st, x, p, w, eps, n, aq, feat, bias, spec, node_feat, eb_gate());
     else {
         if (spec) return eb_set_err(EB_ERR_UNSUPPORTED, "resid_norm_quant: node-feature scatter needs the register kernel (n %% 256 == 0, n <= 8192, K-quant grid)");
         resid_norm_quant_kernel<<<T, 256, (size_t)n * 4, st>>>(x, p, w, eps, n, aq, feat, bias);
@@ -237,7 +240,7 @@ int eb_rope_kv_store_fused(PlaneRef qp, PlaneRef kp, PlaneRef vp, float *q, void
     const int E = n_head * D;
     const int threads = 512, gy = (int)cdiv(E / 4, threads);
     eb_launch_pdl(rope_kv_store_fused_kernel, dim3(T, gy), dim3(threads), 0, st, parts_of(qp, T), parts_of(kp, T), parts_of(vp, T), q, (__half *)q16, (const float2 *)tab,
-                  (__half *)kc, (__half *)vc, ctl, D, n_head, pos, powf(freq_base, -2.0f / D));
+                  (__half *)kc, (__half *)vc, ctl, D, n_head, pos, powf(freq_base, -2.0f / D), eb_gate());
     EB_CHECK_LAUNCH();
     return EB_OK;
 }
@@ -245,7 +248,7 @@ int eb_swiglu_quant(PlaneRef gate, PlaneRef up, int n, int T, const ActQ &aq, cu
     if (T == 0) return EB_OK;
     const int per = aq.kq ? 256 : 128;
     if (n % per || aq.K != n) return eb_set_err(EB_ERR_ARG, "swiglu: n=%d", n);
-    eb_launch_pdl(swiglu_quant_kernel, dim3((unsigned)cdiv(n / per, 8), T), dim3(256), 0, st, parts_of(gate, T), parts_of(up, T), n, aq);
+    eb_launch_pdl(swiglu_quant_kernel, dim3((unsigned)cdiv(n / per, 8), T), dim3(256), 0, st, parts_of(gate, T), parts_of(up, T), n, aq, eb_gate());
     EB_CHECK_LAUNCH();
     return EB_OK;
 }

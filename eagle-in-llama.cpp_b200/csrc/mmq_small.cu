@@ -150,7 +150,7 @@ __device__ __forceinline__ void compute_sb(float (&facc)[4], const W6 &w, const 
 }
 
 struct SmallArgs {
-    const void *W; int64_t N, nb_total; int nbr, n_rb, n_items, spp; ActQ a; float *out;
+    const void *W; int64_t N, nb_total; int nbr, n_rb, n_items, spp; ActQ a; float *out; const int *gate;
 };
 
 template <int FMT>
@@ -185,6 +185,7 @@ __global__ void __launch_bounds__(SM_THREADS, 1) mmq_small_kernel(SmallArgs p) {
     if (have) load_w(nxt, p.W, p_r0 + g, p_r0 + g + 8, p.nbr, p.nb_total, p_sb, t);
 
     pdl_wait();                                             // activations are the predecessor's output; weights are constants
+    if (gate_closed(p.gate)) return;                        // idle draft level: the (unconsumed) first weight loads are all that was issued
     {
         const ActQ &a = p.a;
         const int n_qs = p.nbr * 8 * 16;                    // 16-byte chunks of quants: [sb][col][16]
@@ -269,7 +270,7 @@ int eb_mmq_small_parts(int type, const void *W, int64_t N, int64_t K, const ActQ
         if (cost < best_cost) { best_cost = cost; best = ks; }
     }
     SmallArgs p;
-    p.W = W; p.N = N; p.nb_total = N * nbr; p.nbr = nbr; p.n_rb = n_rb; p.spp = (int)cdiv(nbr, best); p.n_items = n_rb * best; p.a = a; p.out = planes;
+    p.W = W; p.N = N; p.nb_total = N * nbr; p.nbr = nbr; p.n_rb = n_rb; p.spp = (int)cdiv(nbr, best); p.n_items = n_rb * best; p.a = a; p.out = planes; p.gate = eb_gate();
     *ks_out = best;
     const int grid = std::min(p.n_items, G);
     if (type == EB_Q4_K) eb_launch_pdl(mmq_small_kernel<0>, dim3(grid), dim3(SM_THREADS), small_smem<0>(nbr), st, p);

@@ -192,7 +192,9 @@ __global__ void get_rows_f16_kernel(const __half *__restrict__ W, int64_t K, con
     if (i < K) out[(int64_t)r * K + i] = __half2float(W[(int64_t)ids[r] * K + i]);
 }
 // quantised: one CTA of 64 threads per (block, row); same arithmetic as the dequant kernels
-__global__ void get_rows_q_kernel(int type, const uint8_t *__restrict__ W, int64_t nb_total, int nbr, const int32_t *__restrict__ ids, float *__restrict__ out) {
+__global__ void get_rows_q_kernel(int type, const uint8_t *__restrict__ W, int64_t nb_total, int nbr, const int32_t *__restrict__ ids, float *__restrict__ out,
+                                  const int *__restrict__ gate) {
+    if (gate_closed(gate)) return;
     const int r = blockIdx.y, b = blockIdx.x, tid = threadIdx.x;
     const int64_t blk = (int64_t)ids[r] * nbr + b;
     WPlanes w{W, nb_total};
@@ -237,7 +239,7 @@ int eb_get_rows_dev(int type, const void *W, int64_t n_rows, int64_t K, const in
         const int be = (type == EB_Q4_K || type == EB_Q6_K) ? 256 : 32;
         if (K % be) return eb_set_err(EB_ERR_ARG, "get_rows: K");
         const int nbr = (int)(K / be);
-        get_rows_q_kernel<<<dim3(nbr, n), 64, 0, st>>>(type, (const uint8_t *)W, n_rows * nbr, nbr, d_ids, out);
+        get_rows_q_kernel<<<dim3(nbr, n), 64, 0, st>>>(type, (const uint8_t *)W, n_rows * nbr, nbr, d_ids, out, eb_gate());
     }
     EB_CHECK_LAUNCH();
     return EB_OK;

@@ -121,8 +121,10 @@ __global__ void quant_act_kernel(const float *__restrict__ x, ActQ a) {
 // EAGLE head input: row t = [token embedding (E) | parent feature (E)] (ggml_concat, R/src/llama.cpp:1880) quantised for the fc
 // GEMM without materialising the concatenation: quantisation block b comes from `x` (b < E / block) or from `hid`
 __global__ void concat_quant_kernel(const float *__restrict__ x, const float *__restrict__ hid, int E, ActQ a,
-                                    const SpecState *__restrict__ spec, const float *__restrict__ root_feat, const float *__restrict__ node_feat) {
+                                    const SpecState *__restrict__ spec, const float *__restrict__ root_feat, const float *__restrict__ node_feat,
+                                    const int *__restrict__ gate) {
     pdl_trigger(); pdl_wait();
+    if (gate_closed(gate)) return;
     const int lane = threadIdx.x & 31;
     const int64_t warp = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     const int per = a.kq ? 256 : 128;
@@ -145,7 +147,7 @@ int eb_concat_quant(const float *x, const float *hid, int E, const ActQ &a, cuda
     if (a.K != 2 * (int64_t)E || E % per) return eb_set_err(EB_ERR_ARG, "concat_quant: E=%d K=%lld", E, (long long)a.K);
     const int64_t warps = a.K / per * a.T;
     if (warps == 0) return EB_OK;
-    eb_launch_pdl(concat_quant_kernel, dim3((unsigned)cdiv(warps, 8)), dim3(256), 0, st, x, hid, E, a, spec, root_feat, node_feat);
+    eb_launch_pdl(concat_quant_kernel, dim3((unsigned)cdiv(warps, 8)), dim3(256), 0, st, x, hid, E, a, spec, root_feat, node_feat, eb_gate());
     EB_CHECK_LAUNCH();
     return EB_OK;
 }

@@ -20,11 +20,12 @@ __device__ __forceinline__ void warp_argmax(float &bv, int &bi) {
 }
 // logits may be split-K planes [ks][rows][V] of the lm_head GEMM: they are summed (plane order, like splitk_reduce) while staging the row
 __global__ void __launch_bounds__(1024) top_k_kernel(const float *__restrict__ logits, int ks, int64_t plane, int V, int k,
-                                                     int32_t *__restrict__ ids, float *__restrict__ vals, float *__restrict__ probs) {
+                                                     int32_t *__restrict__ ids, float *__restrict__ vals, float *__restrict__ probs, const int *__restrict__ gate) {
     extern __shared__ float row[];
     __shared__ float cv[32 * 16]; __shared__ int ci[32 * 16];
     __shared__ float kv[16]; __shared__ int ki[16];
     pdl_trigger(); pdl_wait();
+    if (gate_closed(gate)) return;
     const int r = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const float *x = logits + (int64_t)r * V;
     // stage the row: all loads of a thread in flight at once (a rolled scalar loop pays the L2 latency 31 times: 11 us)
@@ -89,7 +90,7 @@ int eb_top_k_impl(const float *logits, int rows, int V, int k, int32_t *ids, flo
     if (k < 1 || k > 16 || V > 56000) return eb_set_err(EB_ERR_ARG, "top_k: k=%d V=%d", k, V);
     if (rows == 0) return EB_OK;
     if (ks > 1 && (plane & 3)) return eb_set_err(EB_ERR_ARG, "top_k: plane stride %lld", (long long)plane);
-    eb_launch_pdl(top_k_kernel, dim3(rows), dim3(1024), (size_t)V * 4, st, logits, ks, plane, V, k, ids, vals, probs);
+    eb_launch_pdl(top_k_kernel, dim3(rows), dim3(1024), (size_t)V * 4, st, logits, ks, plane, V, k, ids, vals, probs, eb_gate());
     EB_CHECK_LAUNCH();
     return EB_OK;
 }
@@ -154,7 +155,7 @@ __global__ void round_begin_kernel(SpecState *s, SpecCfg c) {
     s->tokens[0] = s->root_token; s->n_nodes = 1; s->n_seq_cur = 1; s->cur_depth = 0; s->done = 0;
     for (int b = 0; b < 16; b++) { s->br_drafting[b] = 0; s->br_last_node[b] = 0; s->br_row[b] = 0; }
     s->br_drafting[0] = 1;
-    s->dft_n = 1; s->dft_node_base = 0;
+    s->dft_n = 1; s->dft_node_base = 0; s->gate_fwd = 1; s->gate_lm = 1;
     for (int r = 0; r < c.n_branch; r++) {
         s->dft_tokens[r] = r == 0 ? s->root_token : 0; s->dft_pos[r] = s->n_past; s->dft_src[r] = -1;
         uint32_t *b = s->dft_bits + r * 4; b[0] = b[1] = b[2] = b[3] = 0; b[r >> 5] = 1u << (r & 31);   // bit of cell node_base + r
@@ -201,7 +202,7 @@ __global__ void __launch_bounds__(256) tree_expand_kernel(SpecState *gs, SpecCfg
 __device__ void tree_expand_serial(SpecState *s, const SpecCfg &c, const int32_t *cand_ids, const float *cand_p) {
     if (s->done) {                                     // nothing left to draft: park the dummy rows behind the real nodes
         const int base = s->n_nodes;
-        s->dft_n = 0; s->dft_node_base = base;
+        s->dft_n = 0; s->dft_node_base = base; s->gate_fwd = 0; s->gate_lm = 0;
         for (int r = 0; r < c.n_branch; r++) {
             s->dft_tokens[r] = 0; s->dft_pos[r] = s->n_past; s->dft_src[r] = -1;
             uint32_t *b = s->dft_bits + r * 4; b[0] = b[1] = b[2] = b[3] = 0;
@@ -257,6 +258,7 @@ __device__ void tree_expand_serial(SpecState *s, const SpecCfg &c, const int32_t
     int any = 0;
     for (int b = 0; b < n_seq_dft; b++) any |= s->br_drafting[b];
     if (n_new == 0 || !any || s->n_nodes > c.n_draft) s->done = 1;                    // :627-641
+    s->gate_fwd = n_new > 0; s->gate_lm = !s->done;      // the new nodes still need their draft-KV cells; their logits only if drafting goes on
 }
 
 // Greedy accept walk (speculative-eagle.cpp:395-449) + state update.  best[t] = target argmax at

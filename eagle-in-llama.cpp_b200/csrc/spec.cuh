@@ -17,6 +17,7 @@ struct SpecState {
     int n_seq_cur; int br_drafting[16]; int br_last_node[16]; int br_row[16];
     int cur_depth; int done;
     // draft batch for the next head forward
+    int gate_fwd, gate_lm;      // launch gates of the next head forward / of its lm_head + top-k (common.cuh)
     int dft_n; int dft_node_base; int dft_tokens[16]; int dft_pos[16]; int dft_src[16];
     alignas(16) uint32_t dft_bits[16 * 4];
     // accept
