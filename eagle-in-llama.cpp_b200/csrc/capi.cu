@@ -138,7 +138,7 @@ int eb_flash_attn(const float *q, const void *k, const void *v, int64_t kv_strid
         return eb_fattn_tc_f32q(q, k, v, kv_stride, tree_bits, n_prefix, n_kv, T, H, scale, out, ws, S(st));
     return eb_flash_attn_impl(q, k, v, kv_stride, mask, mask_stride, tree_bits, n_prefix, T, H, D, n_kv, scale, out, ws, S(st));
 }
-int eb_top_k(const float *logits, int rows, int V, int k, int32_t *ids, float *vals, float *probs, void *st) { NEED_DEV(); return eb_top_k_impl(logits, rows, V, k, ids, vals, probs, S(st)); }
+int eb_top_k(const float *logits, int rows, int V, int k, int32_t *ids, float *vals, float *probs, void *st) { NEED_DEV(); return eb_top_k_impl(logits, rows, V, k, ids, vals, probs, S(st), 1, 0, rows <= 128 ? eb_top_k_default_scratch() : nullptr); }
 int eb_argmax(const float *logits, int rows, int V, int32_t *ids, void *st) { NEED_DEV(); return eb_argmax_impl(logits, rows, V, ids, S(st)); }
 
 

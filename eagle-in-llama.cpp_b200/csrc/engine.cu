@@ -237,6 +237,7 @@ extern "C" eb_session *eb_session_create(eb_model *target, eb_model *head, const
         cudaMalloc((void **)&s->node_feat, (size_t)128 * E * 4) ||
         cudaMalloc((void **)&s->cand_ids, 16 * 16 * 4) || cudaMalloc((void **)&s->cand_vals, 16 * 16 * 4) || cudaMalloc((void **)&s->cand_p, 16 * 16 * 4) ||
         cudaMalloc((void **)&s->best, 128 * 4) ||
+        cudaMalloc(&s->topk_scr, eb_top_k_scratch_bytes(16)) || cudaMemset(s->topk_scr, 0, eb_top_k_scratch_bytes(16)) ||
         cudaMalloc((void **)&s->stage, Lmax * s->max_acc * 2 * (size_t)E * 2) ||
         cudaMalloc((void **)&s->d_res, sizeof(eb_round_result)) || cudaMallocHost((void **)&s->h_res, sizeof(eb_round_result))) {
         eb_set_err(EB_ERR_OOM, "session_create: %s", cudaGetErrorString(cudaGetLastError())); return fail();
@@ -250,7 +251,7 @@ extern "C" void eb_session_free(eb_session *s) {
     if (s->graph_verify) cudaGraphExecDestroy(s->graph_verify);
     ws_free(s->ws_t); cudaFree(s->kv_t.k); cudaFree(s->kv_t.v);
     if (s->head) { ws_free(s->ws_h); cudaFree(s->kv_h.k); cudaFree(s->kv_h.v); }
-    for (void *p : {(void *)s->state, (void *)s->root_feat, (void *)s->node_feat, (void *)s->cand_ids, (void *)s->cand_vals, (void *)s->cand_p, (void *)s->best, (void *)s->stage, (void *)s->d_res})
+    for (void *p : {(void *)s->state, (void *)s->root_feat, (void *)s->node_feat, (void *)s->cand_ids, (void *)s->cand_vals, (void *)s->cand_p, s->topk_scr, (void *)s->best, (void *)s->stage, (void *)s->d_res})
         cudaFree(p);
     if (s->h_res) cudaFreeHost(s->h_res);
     cudaEventDestroy(s->ev0); cudaEventDestroy(s->ev1); cudaStreamDestroy(s->st);
@@ -491,7 +492,7 @@ static int round_dev(eb_session *s, cudaStream_t st) {
         if (rc) { eb_gate_set(nullptr); return rc; }
         if (!fused_io) RC(eb_spec_scatter_feat(d, s->ws_h.feat, s->node_feat, E, c.n_branch, st));
         if (last) { eb_gate_set(nullptr); break; }
-        rc = eb_top_k_impl(s->ws_h.partial, c.n_branch, V, c.top_k, s->cand_ids, s->cand_vals, s->cand_p, st, ks_h, (int64_t)c.n_branch * V);
+        rc = eb_top_k_impl(s->ws_h.partial, c.n_branch, V, c.top_k, s->cand_ids, s->cand_vals, s->cand_p, st, ks_h, (int64_t)c.n_branch * V, s->topk_scr);
         eb_gate_set(nullptr);
         if (rc) return rc;
         RC(eb_spec_expand(d, c, s->cand_ids, s->cand_p, st));

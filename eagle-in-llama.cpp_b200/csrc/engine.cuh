@@ -33,7 +33,7 @@ struct Workspace {
 struct eb_session {
     eb_model *tgt, *head; eb_session_params p; SpecCfg cfg;
     KVCache kv_t, kv_h; Workspace ws_t, ws_h;
-    SpecState *state; float *root_feat, *node_feat; int32_t *cand_ids; float *cand_vals, *cand_p; int32_t *best;
+    SpecState *state; float *root_feat, *node_feat; int32_t *cand_ids; float *cand_vals, *cand_p; void *topk_scr; int32_t *best;
     __half *stage; int max_acc;
     eb_round_result *d_res, *h_res;
     cudaStream_t st; cudaEvent_t ev0, ev1;

@@ -86,10 +86,124 @@ __global__ void __launch_bounds__(1024) top_k_kernel(const float *__restrict__ l
         }
     }
 }
-int eb_top_k_impl(const float *logits, int rows, int V, int k, int32_t *ids, float *vals, float *probs, cudaStream_t st, int ks, int64_t plane) {
+
+// Draft-level form: grid (rows, TK_S).  A single CTA per row (above) reads its 128 KB x ks of planes at one SM's L2 bandwidth and
+// leaves 140 SMs idle; here each CTA takes 1/TK_S of a row, writes its k sorted candidates to a scratch list, and the CTA that
+// arrives last for a row (device counter) merges the TK_S lists.  Same comparator at every level (value, then lower id), so the
+// result is identical to the single-CTA kernel and to the oracle.  scr: unsigned cnt[128] (zero before the first launch; every
+// launch leaves it zero again; at a fixed place whatever `rows` is), then float v[rows][TK_S][16], int i[rows][TK_S][16].
+constexpr int TK_S = 16, TK_THREADS = 256, TK_W = TK_THREADS / 32, TK_PER = 8;
+size_t eb_top_k_scratch_bytes(int rows) { return 512 + (size_t)rows * TK_S * 16 * 8; }
+// order-preserving float -> u32 key; 0 = "no candidate" (-inf is never picked, as in the single-CTA kernel)
+__device__ __forceinline__ uint32_t tk_key(float v) {
+    uint32_t u = __float_as_uint(v);
+    if (u == 0x80000000u) u = 0u;                                   // -0 == +0: the tie goes to the lower id
+    return v == -INFINITY ? 0u : (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+__device__ __forceinline__ float tk_val(uint32_t key) { return key == 0u ? -INFINITY : __uint_as_float((key & 0x80000000u) ? key ^ 0x80000000u : ~key); }
+// Top k of the <= 32 x TK_PER candidates a warp holds in registers, by (value desc, id asc).  A candidate is one u64:
+// (key << 32) | ~id, so "greater" is exactly the required order; 0 = none.  Each lane first sorts its own 8 (19 compare-exchanges,
+// branch-free), then a round is two hardware warp reductions (redux.sync max of the head keys, then of ~id among the lanes
+// that hold it) and a register shift in the winning lane — no shuffle trees, no rescans (those cost ~300 clk per round, three
+// phases deep).  Lane j < k returns the j-th pick in (ov, oi).
+__device__ __forceinline__ void tk_cex(uint64_t &a, uint64_t &b) { const uint64_t hi = a > b ? a : b, lo = a > b ? b : a; a = hi; b = lo; }
+__device__ __forceinline__ void warp_topk_regs(uint64_t (&c)[TK_PER], int k, float &ov, int &oi) {
+    static_assert(TK_PER == 8, "sorting network below is for 8 inputs");
+    tk_cex(c[0], c[1]); tk_cex(c[2], c[3]); tk_cex(c[4], c[5]); tk_cex(c[6], c[7]);
+    tk_cex(c[0], c[2]); tk_cex(c[1], c[3]); tk_cex(c[4], c[6]); tk_cex(c[5], c[7]);
+    tk_cex(c[1], c[2]); tk_cex(c[5], c[6]); tk_cex(c[0], c[4]); tk_cex(c[3], c[7]);
+    tk_cex(c[1], c[5]); tk_cex(c[2], c[6]);
+    tk_cex(c[1], c[4]); tk_cex(c[3], c[6]);
+    tk_cex(c[2], c[4]); tk_cex(c[3], c[5]);
+    tk_cex(c[3], c[4]);
+    ov = -INFINITY; oi = 0x7fffffff;
+    const int lane = threadIdx.x & 31;
+    for (int r = 0; r < k; r++) {
+        const uint32_t hk = (uint32_t)(c[0] >> 32), hl = (uint32_t)c[0];
+        const uint32_t mk = __reduce_max_sync(0xffffffffu, hk);
+        if (mk == 0u) break;                                        // fewer candidates than k: the rest stay (-inf, 0x7fffffff)
+        const uint32_t ml = __reduce_max_sync(0xffffffffu, hk == mk ? hl : 0u);
+        if (lane == r) { ov = tk_val(mk); oi = (int)~ml; }
+        if (hk == mk && hl == ml) {
+#pragma unroll
+            for (int j = 0; j + 1 < TK_PER; j++) c[j] = c[j + 1];
+            c[TK_PER - 1] = 0ull;
+        }
+    }
+}
+__device__ __forceinline__ uint64_t tk_pack(float v, int id) { const uint32_t key = tk_key(v); return key == 0u ? 0ull : ((uint64_t)key << 32) | (uint32_t)~id; }
+__global__ void __launch_bounds__(TK_THREADS) top_k_split_kernel(const float *__restrict__ logits, int ks, int64_t plane, int V, int k,
+                                                                 int32_t *__restrict__ ids, float *__restrict__ vals, float *__restrict__ probs,
+                                                                 const int *__restrict__ gate, float *scr_v, int *scr_i, unsigned *cnt) {
+    __shared__ float cv[TK_S * 16]; __shared__ int ci[TK_S * 16];
+    pdl_trigger(); pdl_wait();
+    if (gate_closed(gate)) return;
+    const int r = blockIdx.x, sl = blockIdx.y, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int per = (V + TK_S - 1) / TK_S;                          // slice length (<= TK_THREADS * TK_PER, checked by the launcher)
+    const int base = sl * per, n = max(0, min(V, base + per) - base);
+    const float *x = logits + (int64_t)r * V + base;
+    // phase 1: every warp takes 1/8 of the slice, 8 values per lane straight from the planes (coalesced, all loads in flight)
+    float val[TK_PER]; uint64_t c[TK_PER];
+    const int wchunk = (n + TK_W - 1) / TK_W, lo = warp * wchunk, hi = min(n, lo + wchunk);
+#pragma unroll
+    for (int j = 0; j < TK_PER; j++) { const int i = lo + lane + 32 * j; val[j] = i < hi ? x[i] : -INFINITY; }
+    for (int s = 1; s < ks; s++) {
+#pragma unroll
+        for (int j = 0; j < TK_PER; j++) { const int i = lo + lane + 32 * j; if (i < hi) val[j] += x[s * plane + i]; }
+    }
+#pragma unroll
+    for (int j = 0; j < TK_PER; j++) c[j] = tk_pack(val[j], base + lo + lane + 32 * j);      // -inf (also every i >= hi) packs to "none"
+    float ov; int oi;
+    warp_topk_regs(c, k, ov, oi);
+    if (lane < 16) { cv[warp * 16 + lane] = ov; ci[warp * 16 + lane] = oi; }
+    __syncthreads();
+    if (warp != 0) return;
+    // phase 2: warp 0 merges the 8 warp lists (128 slots, 4 per lane)
+    auto take = [&](const float *lv, const int *li, int slots) {
+#pragma unroll
+        for (int j = 0; j < TK_PER; j++) {
+            const int q = lane + 32 * j; const bool ok = q < slots && (q & 15) < k && li[q] != 0x7fffffff;
+            c[j] = ok ? tk_pack(lv[q], li[q]) : 0ull;
+        }
+    };
+    take(cv, ci, TK_W * 16);
+    warp_topk_regs(c, k, ov, oi);
+    float *gv = scr_v + ((int64_t)r * TK_S + sl) * 16; int *gi = scr_i + ((int64_t)r * TK_S + sl) * 16;
+    if (lane < 16) { __stcg(gv + lane, ov); __stcg(gi + lane, oi); }
+    __threadfence();
+    __syncwarp();
+    int last = 0;
+    if (lane == 0) last = atomicAdd(cnt + r, 1u) == TK_S - 1;
+    last = __shfl_sync(0xffffffffu, last, 0);
+    if (!last) return;
+    // phase 3: the slice that arrives last merges the TK_S slice lists of the row (256 slots, 8 per lane)
+    __threadfence();
+    for (int i = lane; i < TK_S * 16; i += 32) { cv[i] = __ldcg(scr_v + (int64_t)r * TK_S * 16 + i); ci[i] = __ldcg(scr_i + (int64_t)r * TK_S * 16 + i); }
+    __syncwarp();
+    take(cv, ci, TK_S * 16);
+    warp_topk_regs(c, k, ov, oi);
+    if (lane == 0) cnt[r] = 0;
+    // probs = softmax over the k kept logits, summed in list order like the single-CTA kernel (llama_sampler_softmax_impl)
+    const float mx = __shfl_sync(0xffffffffu, ov, 0);
+    const float pe = lane < k ? expf(ov - mx) : 0.f;
+    float sum = 0.f;
+    for (int j = 0; j < k; j++) sum += __shfl_sync(0xffffffffu, pe, j);
+    if (lane < k) {
+        ids[r * k + lane] = oi; vals[r * k + lane] = ov;
+        if (probs) probs[r * k + lane] = pe / sum;
+    }
+}
+int eb_top_k_impl(const float *logits, int rows, int V, int k, int32_t *ids, float *vals, float *probs, cudaStream_t st, int ks, int64_t plane, void *scratch) {
     if (k < 1 || k > 16 || V > 56000) return eb_set_err(EB_ERR_ARG, "top_k: k=%d V=%d", k, V);
     if (rows == 0) return EB_OK;
     if (ks > 1 && (plane & 3)) return eb_set_err(EB_ERR_ARG, "top_k: plane stride %lld", (long long)plane);
+    static const bool no_split = getenv("EB_NO_TOPK_SPLIT") != nullptr;
+    if (scratch && !no_split && V >= TK_S * 64 && V <= TK_S * TK_THREADS * TK_PER && rows <= 128) {
+        unsigned *cnt = (unsigned *)scratch; float *sv = (float *)((char *)scratch + 512); int *si = (int *)(sv + (size_t)rows * TK_S * 16);
+        eb_launch_pdl(top_k_split_kernel, dim3(rows, TK_S), dim3(TK_THREADS), 0, st, logits, ks, plane, V, k, ids, vals, probs, eb_gate(), sv, si, cnt);
+        EB_CHECK_LAUNCH();
+        return EB_OK;
+    }
     eb_launch_pdl(top_k_kernel, dim3(rows), dim3(1024), (size_t)V * 4, st, logits, ks, plane, V, k, ids, vals, probs, eb_gate());
     EB_CHECK_LAUNCH();
     return EB_OK;
@@ -341,4 +455,10 @@ int eb_spec_round_end(SpecState *s, const float *tgt_feat, float *root_feat, int
     return EB_OK;
 }
 
-int eb_spec_init() { EB_CUDA(cudaFuncSetAttribute(top_k_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 56000 * 4)); return EB_OK; }
+static void *g_topk_scr = nullptr;      // scratch of the operator-layer eb_top_k (sessions own theirs)
+void *eb_top_k_default_scratch() { return g_topk_scr; }
+int eb_spec_init() {
+    EB_CUDA(cudaFuncSetAttribute(top_k_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 56000 * 4));
+    if (!g_topk_scr) { EB_CUDA(cudaMalloc(&g_topk_scr, eb_top_k_scratch_bytes(128))); EB_CUDA(cudaMemset(g_topk_scr, 0, eb_top_k_scratch_bytes(128))); }
+    return EB_OK;
+}

@@ -32,5 +32,7 @@ int eb_spec_expand(SpecState *s, const SpecCfg &c, const int32_t *cand_ids, cons
 int eb_spec_accept(SpecState *s, const SpecCfg &c, const int32_t *best, cudaStream_t st);
 int eb_spec_compact(SpecState *s, void *kc, void *vc, void *stage, int64_t layer_stride, int E, int L, int max_acc, cudaStream_t st);
 int eb_spec_round_end(SpecState *s, const float *tgt_feat, float *root_feat, int E, eb_round_result *res, cudaStream_t st);
-int eb_top_k_impl(const float *logits, int rows, int V, int k, int32_t *ids, float *vals, float *probs, cudaStream_t st, int ks = 1, int64_t plane = 0);
+int eb_top_k_impl(const float *logits, int rows, int V, int k, int32_t *ids, float *vals, float *probs, cudaStream_t st, int ks = 1, int64_t plane = 0, void *scratch = nullptr);
+size_t eb_top_k_scratch_bytes(int rows);
+void *eb_top_k_default_scratch();
 int eb_argmax_impl(const float *logits, int rows, int V, int32_t *ids, cudaStream_t st, int ks = 1, int64_t plane = 0);

@@ -182,6 +182,24 @@ def test_top_k_argmax(eb):
     assert ids1[0, 0] == 3 and abs(p1[0, 0] - 1) < 1e-6
 
 
+@pytest.mark.parametrize("V,k", [(32003, 16), (1030, 7), (4096, 10)])
+def test_top_k_split_slices(eb, V, k):
+    """the 16-slice form (one CTA per 1/16 row, last arriver merges): ragged last slice, V % 4 != 0, heavy ties that straddle
+    slice and warp boundaries, fewer finite values than k, repeated launches (the arrival counters must come back to zero)"""
+    rng = np.random.default_rng(V)
+    x = rng.integers(-3, 4, (8, V)).astype(np.float32)            # 7 distinct values: every pick is a tie broken by id
+    x[1] = rng.normal(0, 1, V)
+    x[2] = -np.inf; x[2, [V - 1, 7, V // 2]] = [1.0, 1.0, 2.0]
+    x[3, :] = 5.0
+    for _ in range(3):
+        ids, vals, probs = eb.top_k(x, k)
+        for r in range(x.shape[0]):
+            oi, ov, op = po.top_k(x[r], k)
+            if r != 2:
+                assert np.array_equal(ids[r], oi) and np.array_equal(vals[r], ov) and np.abs(probs[r] - op).max() < 1e-6, r
+        assert ids[2, :3].tolist() == [V // 2, 7, V - 1] and ids[3].tolist() == list(range(k))
+
+
 def test_mul_mat_q6_K_extreme_blocks(eb):
     """Q6_K at the corners of its range: scales -128 / 127, quants 0 / 63 (|sc * (q - 32)| up to 4096) against activations that
     quantise to +-127 everywhere.  The tcgen05 path feeds the weight as two exact f16 addends (sc*ql and 16*sc*(qh-2)); the
