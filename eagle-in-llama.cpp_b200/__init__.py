@@ -83,6 +83,7 @@ def lib():
         "eb_session_round": ([vp, C.POINTER(RoundResult)], i32),
         "eb_session_verify_only": ([vp, i32, C.POINTER(f32)], i32),
         "eb_bench_mul_mat_kernel": ([i32, i64, i64, i32, i32, i32, C.POINTER(f32)], i32),
+        "eb_bench_flash_attn": ([i32, i32, i32, i32, i32, i32, C.POINTER(f32)], i32),
         "eb_launch_count": ([i32], C.c_long),
     }
     for name, (args, res) in sig.items():
@@ -407,6 +408,12 @@ class Session:
 def bench_mul_mat_kernel(t, N, K, T, n_bufs=8, iters=50):
     ms = C.c_float()
     _ck(lib().eb_bench_mul_mat_kernel(t, N, K, T, n_bufs, iters, C.byref(ms)))
+    return ms.value
+
+
+def bench_flash_attn(T, H, D, n_kv, n_bufs=4, iters=50):
+    ms = C.c_float()
+    _ck(lib().eb_bench_flash_attn(T, H, D, n_kv, n_bufs, iters, C.byref(ms)))
     return ms.value
 
 

@@ -208,4 +208,58 @@ int eb_bench_mul_mat_kernel(int type, int64_t N, int64_t K, int T, int n_bufs, i
     return rc;
 }
 
+// Micro-bench of the FLASH_ATTN_EXT operator with the compact tree mask (BASELINE config 5): `iters` calls replayed from a CUDA
+// graph, cycling through n_bufs distinct K/V caches (so K/V come from HBM), CUDA events on the launching stream.  The tree is a
+// chain over the last T cells; the first n_kv - T cells are the committed prefix.
+int eb_bench_flash_attn(int T, int H, int D, int n_kv, int n_bufs, int iters, float *ms_per_call) {
+    NEED_DEV();
+    if (T < 1 || T > 128 || n_kv <= T || n_bufs < 1 || iters < 1 || D != 128) return eb_set_err(EB_ERR_ARG, "bench_flash_attn: bad arguments");
+    const int64_t E = (int64_t)H * D;
+    std::vector<void *> kc(n_bufs, nullptr), vc(n_bufs, nullptr);
+    float *q = nullptr, *out = nullptr; void *ws = nullptr; uint32_t *bits = nullptr;
+    cudaStream_t st; cudaEvent_t e0, e1;
+    EB_CUDA(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking)); EB_CUDA(cudaEventCreate(&e0)); EB_CUDA(cudaEventCreate(&e1));
+    int rc = EB_OK;
+    for (int i = 0; i < n_bufs && !rc; i++) {
+        if (cudaMalloc(&kc[i], (size_t)n_kv * E * 2) != cudaSuccess || cudaMalloc(&vc[i], (size_t)n_kv * E * 2) != cudaSuccess) { rc = eb_set_err(EB_ERR_OOM, "bench_flash_attn: KV"); break; }
+        rc = eb_synth_impl(EB_F16, kc[i], (int64_t)n_kv * E, 500 + 2 * i, 1.0f, 0, st);
+        if (!rc) rc = eb_synth_impl(EB_F16, vc[i], (int64_t)n_kv * E, 501 + 2 * i, 1.0f, 0, st);
+    }
+    if (!rc && (cudaMalloc((void **)&q, (size_t)T * E * 4) || cudaMalloc((void **)&out, (size_t)T * E * 4) || cudaMalloc(&ws, eb_flash_attn_ws_size(T, H, D, n_kv)) ||
+                cudaMalloc((void **)&bits, (size_t)T * 16)))
+        rc = eb_set_err(EB_ERR_OOM, "bench_flash_attn: activations");
+    if (!rc) rc = eb_synth_impl(EB_F32, q, (int64_t)T * E, 7, 1.0f, 0, st);
+    if (!rc) {
+        std::vector<uint32_t> hb((size_t)T * 4, 0u);
+        for (int t = 0; t < T; t++) for (int j = 0; j <= t; j++) hb[t * 4 + (j >> 5)] |= 1u << (j & 31);
+        if (cudaMemcpyAsync(bits, hb.data(), hb.size() * 4, cudaMemcpyHostToDevice, st) != cudaSuccess || cudaStreamSynchronize(st) != cudaSuccess) rc = eb_set_err(EB_ERR_CUDA, "bench_flash_attn: bits");
+    }
+    auto one = [&](int i) { return eb_flash_attn(q, kc[i % n_bufs], vc[i % n_bufs], E, nullptr, 0, bits, n_kv - T, T, H, D, n_kv, 1.0f / sqrtf((float)D), out, ws, st); };
+    for (int i = 0; i < 3 && !rc; i++) rc = one(i);
+    if (!rc) {
+        cudaStreamSynchronize(st);
+        cudaGraph_t g = nullptr; cudaGraphExec_t ge = nullptr;
+        const long before = eb_launches_now();
+        if (cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal) != cudaSuccess) rc = eb_set_err(EB_ERR_CUDA, "bench_flash_attn: capture");
+        for (int i = 0; i < iters && !rc; i++) rc = one(i);
+        if (cudaStreamEndCapture(st, &g) != cudaSuccess && !rc) rc = eb_set_err(EB_ERR_CUDA, "bench_flash_attn: end capture");
+        eb_launches_add(before - eb_launches_now());
+        if (!rc && cudaGraphInstantiate(&ge, g, 0) != cudaSuccess) rc = eb_set_err(EB_ERR_CUDA, "bench_flash_attn: instantiate");
+        if (!rc) {
+            cudaGraphLaunch(ge, st); cudaStreamSynchronize(st);
+            cudaEventRecord(e0, st); cudaGraphLaunch(ge, st); cudaEventRecord(e1, st);
+            if (cudaStreamSynchronize(st) != cudaSuccess) rc = eb_set_err(EB_ERR_CUDA, "bench_flash_attn: %s", cudaGetErrorString(cudaGetLastError()));
+            float ms = 0; cudaEventElapsedTime(&ms, e0, e1);
+            if (ms_per_call) *ms_per_call = ms / iters;
+        }
+        if (ge) cudaGraphExecDestroy(ge);
+        if (g) cudaGraphDestroy(g);
+    }
+    for (void *p : kc) cudaFree(p);
+    for (void *p : vc) cudaFree(p);
+    cudaFree(q); cudaFree(out); cudaFree(ws); cudaFree(bits);
+    cudaEventDestroy(e0); cudaEventDestroy(e1); cudaStreamDestroy(st);
+    return rc;
+}
+
 }  // extern "C"

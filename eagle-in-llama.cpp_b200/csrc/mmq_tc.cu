@@ -632,7 +632,8 @@ static int tc_pick_ksplit(int64_t N, int nbr) {
         const int spp = (int)cdiv(nbr, ks), eff_ks = (int)cdiv(nbr, spp);
         if (eff_ks != ks) continue;
         const int rounds = (int)cdiv((int64_t)n_rb * ks, G);
-        const double cost = rounds * (spp + 2.0) + 0.25 * ks;
+        static const double c_item = getenv("EB_TC_CITEM") ? atof(getenv("EB_TC_CITEM")) : 2.0;   // per-item fill in super-block units
+        const double cost = rounds * (spp + c_item) + 0.25 * ks;
         if (cost < best_cost) { best_cost = cost; best = ks; }
     }
     return best;

@@ -189,6 +189,8 @@ EB_API int eb_session_verify_only(eb_session *s, int T, float *gpu_ms);
  * launch over `iters` launches cycling through n_bufs distinct weight buffers (HBM-resident,
  * larger than L2 in total), CUDA events on the launching stream */
 EB_API int eb_bench_mul_mat_kernel(int type, int64_t N, int64_t K, int T, int n_bufs, int iters, float *ms_per_launch);
+/* same for GGML_OP_FLASH_ATTN_EXT with the compact tree mask (chain tree over the last T cells; n_bufs distinct K/V caches) */
+EB_API int eb_bench_flash_attn(int T, int H, int D, int n_kv, int n_bufs, int iters, float *ms_per_call);
 /* launches of this library's kernels since the last call (bench "gpu_launches") */
 EB_API long eb_launch_count(int reset);
 

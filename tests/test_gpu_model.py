@@ -252,3 +252,41 @@ def test_forward_7b_width_one_layer(eb):
     assert rel_max(lg, lo) < MODEL_REL and nmse(lg, lo) < MODEL_NMSE and nmse(fg, fo) < MODEL_NMSE
     assert greedy_agree(lg, lo, REF_TIE)[0] == 0
     s.free()
+
+
+@pytest.mark.parametrize("ftype", [po.Q8_0, "q4_k_m"])
+def test_independent_streams_share_weights(eb, ftype):
+    """BASELINE config 3 (independent request streams replicated, no collective): several sessions over ONE resident copy of the
+    weights, each with its own KV caches, tree state and CUDA graph.  Rounds interleaved across the streams must give every stream
+    exactly what it gets when it runs alone (no shared scratch leaks between streams), and different prompts must diverge."""
+    hp = dict(E=256, H=2, F=512, V=1024, L=2)
+    tgt = fx.make_model(**hp, ftype=ftype, seed=41)
+    head = fx.make_model(**{**hp, "L": 1}, ftype=ftype, seed=42, is_eagle=True)
+    mt = fx.to_gpu_model(eb, tgt); mh = fx.to_gpu_model(eb, head, target=mt)
+    cfg = dict(n_branch=4, n_draft=12, max_depth=5, top_k=10, p_split=0.1, max_nodes=16)
+
+    def start(seed):
+        s = eb.Session(mt, mh, n_ctx=160, use_graph=True, **cfg)
+        prompt = np.random.default_rng(seed).integers(3, hp["V"], 10).astype(np.int32)
+        lg, ft = s.forward(0, prompt, np.arange(len(prompt)))
+        hid = np.zeros((len(prompt), hp["E"]), np.float32); hid[1:] = ft[:-1]
+        s.forward(1, prompt, np.arange(len(prompt)), hidden=hid)
+        s.commit(0, len(prompt)); s.set_root(int(lg[-1].argmax()), ft[-1])
+        return s
+
+    def record(r):
+        return (r.n_nodes, list(r.tokens[:r.n_nodes]), list(r.parent[:r.n_nodes]), list(r.path[:r.n_accept]), r.bonus)
+
+    seeds = (1, 2, 3, 4)
+    alone = []
+    for sd in seeds:
+        s = start(sd); alone.append([record(s.round()) for _ in range(4)]); s.free()
+    streams = [start(sd) for sd in seeds]
+    inter = [[] for _ in seeds]
+    for rnd in range(4):
+        for i in (2, 0, 3, 1):                                # interleaved, not in creation order
+            inter[i].append(record(streams[i].round()))
+    for s in streams:
+        s.free()
+    assert inter == alone
+    assert len({tuple(a[0][1]) for a in alone}) > 1
