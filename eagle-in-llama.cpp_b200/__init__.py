@@ -78,6 +78,8 @@ def lib():
         "eb_model_share_lm_head": ([vp, vp], i32), "eb_model_weight_bytes": ([vp], sz),
         "eb_session_create": ([vp, vp, C.POINTER(SessionParams)], vp), "eb_session_free": ([vp], None),
         "eb_session_forward": ([vp, i32, vp, vp, vp, vp, i32, vp, vp], i32),
+        "eb_tree_bits_from_batch": ([i32, vp, vp, vp, vp], i32),
+        "eb_session_forward_batch": ([vp, i32, vp, vp, vp, vp, vp, i32, vp, vp], i32),
         "eb_session_commit": ([vp, i32, i32], i32), "eb_session_n_past": ([vp, i32], i32),
         "eb_session_synth_kv": ([vp, i32, C.c_uint64], i32), "eb_session_set_root": ([vp, C.c_int32, vp], i32),
         "eb_session_round": ([vp, C.POINTER(RoundResult)], i32),
@@ -376,6 +378,18 @@ class Session:
         _ck(lib().eb_session_forward(self.h, model, _hp(tokens), _hp(pos), _hp(par), _hp(hid), T, _hp(logits), _hp(feat)))
         return logits, feat
 
+    def forward_batch(self, model, tokens, pos, seq_ids, hidden=None, want_logits=True):
+        """the same forward from a tree-shaped llama_batch: seq_ids[i] = the seq-id list of token i (llama_batch.seq_id)"""
+        tokens = np.ascontiguousarray(tokens, np.int32); pos = np.ascontiguousarray(pos, np.int32)
+        T = tokens.size
+        m = self.head if model else self.target
+        n_seq, ptrs, keep = _seq_id_arrays(seq_ids)
+        hid = None if hidden is None else np.ascontiguousarray(hidden, np.float32)
+        logits = np.empty((T, m.V), np.float32) if want_logits else None
+        feat = np.empty((T, m.E), np.float32)
+        _ck(lib().eb_session_forward_batch(self.h, model, _hp(tokens), _hp(pos), _hp(n_seq), C.cast(ptrs, C.c_void_p), _hp(hid), T, _hp(logits), _hp(feat)))
+        return logits, feat
+
     def commit(self, model, n):
         _ck(lib().eb_session_commit(self.h, model, n))
 
@@ -415,6 +429,23 @@ def bench_flash_attn(T, H, D, n_kv, n_bufs=4, iters=50):
     ms = C.c_float()
     _ck(lib().eb_bench_flash_attn(T, H, D, n_kv, n_bufs, iters, C.byref(ms)))
     return ms.value
+
+
+def _seq_id_arrays(seq_ids):
+    """llama_batch.n_seq_id / llama_batch.seq_id (int32 **) from a list of per-token seq-id lists"""
+    keep = [np.ascontiguousarray(x, np.int32) for x in seq_ids]
+    n_seq = np.array([len(x) for x in keep], np.int32)
+    ptrs = (C.c_void_p * len(keep))(*[x.ctypes.data for x in keep])
+    return n_seq, ptrs, keep
+
+
+def tree_bits_from_batch(pos, seq_ids):
+    """visibility sets [T][4] u32 of a tree-shaped llama_batch (eb_tree_bits_from_batch; host-only, needs no GPU)"""
+    pos = np.ascontiguousarray(pos, np.int32)
+    n_seq, ptrs, keep = _seq_id_arrays(seq_ids)
+    out = np.zeros((len(keep), 4), np.uint32)
+    _ck(lib().eb_tree_bits_from_batch(len(keep), _hp(pos), _hp(n_seq), C.cast(ptrs, C.c_void_p), _hp(out)))
+    return out
 
 
 def launch_count(reset=False):

@@ -397,22 +397,32 @@ extern "C" int eb_session_n_past(const eb_session *s, int model) {
     return n;
 }
 
-extern "C" int eb_session_forward(eb_session *s, int model, const int32_t *h_tokens, const int32_t *h_pos, const int32_t *h_parent,
-                                  const float *h_hidden, int T, float *h_logits, float *h_feat) {
+// Visibility among the tokens of a tree-shaped llama_batch (R/include/llama.h:247-257), by the rule of the reference's KQ-mask
+// builder (R/src/llama-context.cpp:163-172: cell i is visible to token j iff cell i carries token j's FIRST seq id and
+// pos_i <= pos_j), applied to the cells the batch itself is about to occupy (token i -> cell n_past + i, whose seq-id set is
+// token i's, R/src/llama-kv-cache.cpp find_slot).  A row always sees itself.  Pure host arithmetic.
+extern "C" int eb_tree_bits_from_batch(int n_tokens, const int32_t *pos, const int32_t *n_seq_id, const int32_t *const *seq_id, uint32_t *bits_out) {
+    if (n_tokens < 1 || n_tokens > 128 || !pos || !n_seq_id || !seq_id || !bits_out) return eb_set_err(EB_ERR_ARG, "tree_bits_from_batch: n_tokens=%d", n_tokens);
+    memset(bits_out, 0, (size_t)n_tokens * 16);
+    for (int j = 0; j < n_tokens; j++) {
+        if (n_seq_id[j] < 1) return eb_set_err(EB_ERR_ARG, "tree_bits_from_batch: token %d has no seq id", j);
+        const int32_t sj = seq_id[j][0];
+        for (int i = 0; i < n_tokens; i++) {
+            bool has = false;
+            for (int k = 0; k < n_seq_id[i] && !has; k++) has = seq_id[i][k] == sj;
+            if ((has && pos[i] <= pos[j]) || i == j) bits_out[j * 4 + (i >> 5)] |= 1u << (i & 31);
+        }
+    }
+    return EB_OK;
+}
+
+static int forward_bits(eb_session *s, int model, const int32_t *h_tokens, const int32_t *h_pos, const uint32_t *bits,
+                        const float *h_hidden, int T, float *h_logits, float *h_feat) {
     eb_model *m = model ? s->head : s->tgt;
-    if (!m) return eb_set_err(EB_ERR_ARG, "forward: no such model");
-    if (T < 1 || T > 128) return eb_set_err(EB_ERR_ARG, "forward: T=%d", T);
     int rc = check_model(m); if (rc) return rc;
     KVCache &kv = model ? s->kv_h : s->kv_t; Workspace &w = model ? s->ws_h : s->ws_t;
     const int n_past = eb_session_n_past(s, model);
     if (n_past + T > kv.n_ctx) return eb_set_err(EB_ERR_ARG, "forward: KV cache full (%d + %d > %d)", n_past, T, kv.n_ctx);
-    uint32_t bits[128 * 4]; memset(bits, 0, sizeof(bits));
-    for (int t = 0; t < T; t++) {
-        const int par = h_parent ? h_parent[t] : t - 1;
-        if (par >= t) return eb_set_err(EB_ERR_ARG, "forward: parent[%d]=%d", t, par);
-        if (par >= 0) memcpy(bits + t * 4, bits + par * 4, 16);
-        bits[t * 4 + (t >> 5)] |= 1u << (t & 31);
-    }
     FwdCtl ctl{n_past, 0, T};
     EB_CUDA(cudaMemcpyAsync(w.tokens, h_tokens, T * 4, cudaMemcpyHostToDevice, s->st));
     EB_CUDA(cudaMemcpyAsync(w.pos, h_pos, T * 4, cudaMemcpyHostToDevice, s->st));
@@ -428,6 +438,28 @@ extern "C" int eb_session_forward(eb_session *s, int model, const int32_t *h_tok
     EB_CUDA(cudaStreamSynchronize(s->st));
     s->last_T[model ? 1 : 0] = T;
     return EB_OK;
+}
+extern "C" int eb_session_forward(eb_session *s, int model, const int32_t *h_tokens, const int32_t *h_pos, const int32_t *h_parent,
+                                  const float *h_hidden, int T, float *h_logits, float *h_feat) {
+    if (!(model ? s->head : s->tgt)) return eb_set_err(EB_ERR_ARG, "forward: no such model");
+    if (T < 1 || T > 128) return eb_set_err(EB_ERR_ARG, "forward: T=%d", T);
+    uint32_t bits[128 * 4]; memset(bits, 0, sizeof(bits));
+    for (int t = 0; t < T; t++) {
+        const int par = h_parent ? h_parent[t] : t - 1;
+        if (par >= t) return eb_set_err(EB_ERR_ARG, "forward: parent[%d]=%d", t, par);
+        if (par >= 0) memcpy(bits + t * 4, bits + par * 4, 16);
+        bits[t * 4 + (t >> 5)] |= 1u << (t & 31);
+    }
+    return forward_bits(s, model, h_tokens, h_pos, bits, h_hidden, T, h_logits, h_feat);
+}
+// the same forward driven by a tree-shaped llama_batch (token, pos, seq-id sets), as llama_decode receives it
+extern "C" int eb_session_forward_batch(eb_session *s, int model, const int32_t *h_tokens, const int32_t *h_pos, const int32_t *n_seq_id,
+                                        const int32_t *const *seq_id, const float *h_hidden, int T, float *h_logits, float *h_feat) {
+    if (!(model ? s->head : s->tgt)) return eb_set_err(EB_ERR_ARG, "forward: no such model");
+    if (T < 1 || T > 128) return eb_set_err(EB_ERR_ARG, "forward: T=%d", T);
+    uint32_t bits[128 * 4];
+    const int rc = eb_tree_bits_from_batch(T, h_pos, n_seq_id, seq_id, bits); if (rc) return rc;
+    return forward_bits(s, model, h_tokens, h_pos, bits, h_hidden, T, h_logits, h_feat);
 }
 
 __global__ void set_n_past_kernel(SpecState *s, int n) { s->n_past = n; }

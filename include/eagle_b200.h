@@ -161,6 +161,14 @@ EB_API void        eb_session_free(eb_session *s);
 EB_API int eb_session_forward(eb_session *s, int model, const int32_t *h_tokens, const int32_t *h_pos,
                               const int32_t *h_parent, const float *h_hidden, int T,
                               float *h_logits, float *h_feat);
+/* The same forward driven by a tree-shaped llama_batch (R/include/llama.h:247-257; built by common_batch_add,
+ * R/common/common.cpp:1784, with the seq-id sets of R/examples/speculative/speculative-eagle.cpp:556-625): token i goes to cell
+ * n_past + i, and token j sees it iff token i's seq-id set contains token j's first seq id and pos[i] <= pos[j] — the rule of
+ * the reference's KQ-mask builder, R/src/llama-context.cpp:163-172.  eb_tree_bits_from_batch is that rule alone (pure host code:
+ * bits_out[j*4 ..] = 128-bit visibility set of row j, the compact mask form of eb_flash_attn). */
+EB_API int eb_tree_bits_from_batch(int n_tokens, const int32_t *h_pos, const int32_t *h_n_seq_id, const int32_t *const *h_seq_id, uint32_t *bits_out);
+EB_API int eb_session_forward_batch(eb_session *s, int model, const int32_t *h_tokens, const int32_t *h_pos, const int32_t *h_n_seq_id,
+                                    const int32_t *const *h_seq_id, const float *h_hidden, int T, float *h_logits, float *h_feat);
 /* commit the first n of the T tokens of the last forward of `model` (chain prefill) */
 EB_API int eb_session_commit(eb_session *s, int model, int n);
 EB_API int eb_session_n_past(const eb_session *s, int model);

@@ -290,3 +290,36 @@ def test_independent_streams_share_weights(eb, ftype):
         s.free()
     assert inter == alone
     assert len({tuple(a[0][1]) for a in alone}) > 1
+
+
+def test_forward_from_llama_batch_equals_parent_form(eb):
+    """llama_decode's input is a tree-shaped llama_batch (token, pos, seq-id sets); the engine's forward driven by it must equal
+    the forward driven by the parent array, bit for bit (same kernels, same mask)."""
+    hp = dict(E=256, H=2, F=512, V=1024, L=2)
+    tgt = fx.make_model(**hp, ftype="q4_k_m", seed=51)
+    mt = fx.to_gpu_model(eb, tgt)
+    rng = np.random.default_rng(9)
+    T = 23
+    par = fx.tree_parents(T, rng); depth = fx.tree_depths(par)
+    # seq ids as the tree driver assigns them: one branch per leaf-to-root path; a node's first id is the branch that created it
+    children = [[j for j in range(T) if par[j] == i] for i in range(T)]
+    seqs = [[] for _ in range(T)]; nxt = [1]
+
+    def walk(i, sid):
+        seqs[i].insert(0, sid) if not seqs[i] else None
+        for n, ch in enumerate(children[i]):
+            s = sid if n == 0 else nxt[0]
+            if n: nxt[0] += 1
+            walk(ch, s)
+            seqs[i].extend(x for x in seqs[ch] if x not in seqs[i])
+    walk(0, 0)
+    prompt = rng.integers(3, hp["V"], 9).astype(np.int32)
+    tokens = rng.integers(3, hp["V"], T).astype(np.int32)
+    outs = []
+    for mode in ("parent", "batch"):
+        s = eb.Session(mt, None, n_ctx=96, max_nodes=32)
+        s.forward(0, prompt, np.arange(len(prompt))); s.commit(0, len(prompt))
+        pos = len(prompt) + depth
+        outs.append(s.forward(0, tokens, pos, parent=par) if mode == "parent" else s.forward_batch(0, tokens, pos, seqs))
+        s.free()
+    assert np.array_equal(outs[0][0], outs[1][0]) and np.array_equal(outs[0][1], outs[1][1])

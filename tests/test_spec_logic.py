@@ -55,6 +55,15 @@ def test_tree_mask_equals_reference_seq_id_rule():
             cell_seq[n_past + i] = np.uint64(sum(1 << s for s in seqs[i]))
         vis_ref = po.build_kq_mask(cell_pos, cell_seq, n_past + depth, first_seq)
         assert np.array_equal(vis_ref, fx.vis_matrix(par, n_past, n_kv))
+        # the product's host-side entry for a tree-shaped llama_batch (token i carries [first_seq[i]] + the branches that
+        # split off below it) gives the same sets as the oracle's rule and as the parent form
+        from conftest import load_package
+        eb = load_package()
+        seq_ids = [[int(first_seq[i])] + sorted(x for x in seqs[i] if x != first_seq[i]) for i in range(T)]
+        bits = eb.tree_bits_from_batch(n_past + depth, seq_ids)
+        assert np.array_equal(bits, eb.tree_bits_from_parent(par))
+        got = np.array([[(bits[j, i >> 5] >> np.uint32(i & 31)) & 1 for i in range(T)] for j in range(T)], np.uint8)
+        assert np.array_equal(got, vis_ref[:, n_past:])
 
 
 def test_accept_walk():
