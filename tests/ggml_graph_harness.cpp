@@ -91,7 +91,8 @@ static ggml_tensor *norm(ggml_context *c, ggml_tensor *x, ggml_tensor *w, float 
 // One forward of the model over T tree tokens; K/V caches are host arrays [L][n_ctx][E] f16 that are
 // uploaded before and downloaded after (so the caller sees the stored cells).  vis [T][n_kv] 0/1.
 GH_API int gh_forward(int which, const GModel *m, uint16_t *kv_k, uint16_t *kv_v, int n_ctx, const int32_t *tokens, const int32_t *pos,
-                      const float *hidden_in, int T, int kv_head, int n_kv, const uint8_t *vis, float *logits, float *feat, int *n_nodes_out) {
+                      const float *hidden_in, int T, int kv_head, int n_kv, const uint8_t *vis, float *logits, float *feat, int *n_nodes_out,
+                      int use_sched, int *n_splits_out) {
     ggml_backend_t be = backend(which); if (!be) { snprintf(g_err, sizeof g_err, "no backend %d", which); return -1; }
     const int E = m->E, H = m->H, F = m->F, D = E / H, V = m->V, L = m->L;
     ggml_init_params pw = {ggml_tensor_overhead() * (size_t)(16 + 16 * L), nullptr, true};
@@ -161,28 +162,57 @@ GH_API int gh_forward(int which, const GModel *m, uint16_t *kv_k, uint16_t *kv_v
         cur = ggml_mul_mat(c, lw[l].down, ggml_mul(c, gt, up));
         inpL = ggml_add(c, cur, ffn_inp);
     }
-    b.res_norm = norm(c, inpL, out_norm, m->eps); ggml_set_output(b.res_norm);
+    b.res_norm = norm(c, inpL, out_norm, m->eps);
+    // use_sched: an op the plugin does not claim (SCALE) sits between the norm and the lm_head, so ggml_backend_sched has to cut the graph
+    // into plugin | CPU | plugin splits and move tensors across the backends in both directions
+    if (use_sched) b.res_norm = ggml_scale(c, b.res_norm, 1.0f);
+    ggml_set_output(b.res_norm);
     ggml_build_forward_expand(gf, b.res_norm);
     if (logits) { b.logits = ggml_mul_mat(c, output, b.res_norm); ggml_set_output(b.logits); ggml_build_forward_expand(gf, b.logits); }
 
-    // ---- every node must be claimed by the backend (this is what ggml_backend_sched asks before assigning a split)
     ggml_backend_dev_t dev = ggml_backend_get_device(be);
     int rc = 0;
-    for (int i = 0; i < ggml_graph_n_nodes(gf) && !rc; i++)
-        if (!ggml_backend_dev_supports_op(dev, ggml_graph_node(gf, i))) {
-            snprintf(g_err, sizeof g_err, "backend %s refuses node %d: %s", ggml_backend_name(be), i, ggml_op_name(ggml_graph_node(gf, i)->op)); rc = -3;
-        }
-    ggml_gallocr_t ga = ggml_gallocr_new(ggml_backend_get_default_buffer_type(be));
-    if (!rc && !ggml_gallocr_alloc_graph(ga, gf)) { snprintf(g_err, sizeof g_err, "graph allocation failed"); rc = -4; }
-    if (!rc) {
+    ggml_gallocr_t ga = nullptr; ggml_backend_sched_t sched = nullptr;
+    auto set_inputs = [&]() {
         std::vector<float> m32((size_t)n_kv * Tp);
         for (int j = 0; j < Tp; j++) for (int i = 0; i < n_kv; i++) m32[(size_t)j * n_kv + i] = (j < T && vis[(size_t)j * n_kv + i]) ? 0.0f : -INFINITY;
         ggml_backend_tensor_set(b.tok, tokens, 0, (size_t)T * 4);
         ggml_backend_tensor_set(b.pos, pos, 0, (size_t)T * 4);
         ggml_backend_tensor_set(b.mask32, m32.data(), 0, m32.size() * 4);
         if (b.hid) ggml_backend_tensor_set(b.hid, hidden_in, 0, (size_t)T * E * 4);
-        const ggml_status st = ggml_backend_graph_compute(be, gf);
-        if (st != GGML_STATUS_SUCCESS) { snprintf(g_err, sizeof g_err, "graph_compute -> %s", ggml_status_to_string(st)); rc = -5; }
+    };
+    if (!use_sched) {
+        // ---- every node must be claimed by the backend (this is what ggml_backend_sched asks before assigning a split)
+        for (int i = 0; i < ggml_graph_n_nodes(gf) && !rc; i++)
+            if (!ggml_backend_dev_supports_op(dev, ggml_graph_node(gf, i))) {
+                snprintf(g_err, sizeof g_err, "backend %s refuses node %d: %s", ggml_backend_name(be), i, ggml_op_name(ggml_graph_node(gf, i)->op)); rc = -3;
+            }
+        ga = ggml_gallocr_new(ggml_backend_get_default_buffer_type(be));
+        if (!rc && !ggml_gallocr_alloc_graph(ga, gf)) { snprintf(g_err, sizeof g_err, "graph allocation failed"); rc = -4; }
+        if (!rc) {
+            set_inputs();
+            const ggml_status st = ggml_backend_graph_compute(be, gf);
+            if (st != GGML_STATUS_SUCCESS) { snprintf(g_err, sizeof g_err, "graph_compute -> %s", ggml_status_to_string(st)); rc = -5; }
+        }
+    } else {
+        // ---- the way libllama runs it: ggml_backend_sched over {this backend, CPU} (R/src/llama.cpp:11700-11760, R/ggml/src/ggml-backend.cpp:1448)
+        ggml_backend_t bes[2] = {be, backend(0)};
+        const int nb = which == 0 ? 1 : 2;
+        sched = ggml_backend_sched_new(which == 0 ? bes + 1 : bes, nullptr, nb, 8192, false);
+        if (!sched || !ggml_backend_sched_alloc_graph(sched, gf)) { snprintf(g_err, sizeof g_err, "sched allocation failed"); rc = -4; }
+        if (!rc) {
+            set_inputs();
+            const ggml_status st = ggml_backend_sched_graph_compute(sched, gf);
+            if (st != GGML_STATUS_SUCCESS) { snprintf(g_err, sizeof g_err, "sched_graph_compute -> %s", ggml_status_to_string(st)); rc = -5; }
+            if (n_splits_out) *n_splits_out = ggml_backend_sched_get_n_splits(sched);
+            // every MUL_MAT and the attention must have been placed on the plugin, the SCALE on the CPU
+            for (int i = 0; i < ggml_graph_n_nodes(gf) && !rc && which == 1; i++) {
+                ggml_tensor *nd = ggml_graph_node(gf, i);
+                const bool on_plugin = ggml_backend_sched_get_tensor_backend(sched, nd) == be;
+                if ((nd->op == GGML_OP_MUL_MAT || nd->op == GGML_OP_FLASH_ATTN_EXT) && !on_plugin) { snprintf(g_err, sizeof g_err, "node %d (%s) was not given to the plugin", i, ggml_op_name(nd->op)); rc = -6; }
+                if (nd->op == GGML_OP_SCALE && on_plugin) { snprintf(g_err, sizeof g_err, "SCALE was given to the plugin"); rc = -6; }
+            }
+        }
     }
     if (!rc) {
         if (feat) ggml_backend_tensor_get(b.res_norm, feat, 0, (size_t)T * E * 4);
@@ -193,6 +223,8 @@ GH_API int gh_forward(int which, const GModel *m, uint16_t *kv_k, uint16_t *kv_v
         }
         if (n_nodes_out) *n_nodes_out = ggml_graph_n_nodes(gf);
     }
-    ggml_gallocr_free(ga); ggml_backend_buffer_free(wbuf); ggml_free(c); ggml_free(cw);
+    if (ga) ggml_gallocr_free(ga);
+    if (sched) ggml_backend_sched_free(sched);
+    ggml_backend_buffer_free(wbuf); ggml_free(c); ggml_free(cw);
     return rc;
 }

@@ -43,7 +43,7 @@ def harness():
         h.gh_model_set_global.argtypes = [vp, i32, i32, vp]
         h.gh_model_set_layer.argtypes = [vp, i32, i32, i32, vp]
         h.gh_roundtrip.argtypes = [i32, i32, C.c_int64, C.c_int64, vp, vp]
-        h.gh_forward.argtypes = [i32, vp, vp, vp, i32, vp, vp, vp, i32, i32, i32, vp, vp, vp, C.POINTER(i32)]
+        h.gh_forward.argtypes = [i32, vp, vp, vp, i32, vp, vp, vp, i32, i32, i32, vp, vp, vp, C.POINTER(i32), i32, C.POINTER(i32)]
         _h = h
     return _h
 
@@ -59,18 +59,18 @@ def gh_model(h, f):
     return m
 
 
-def gh_forward(h, which, m, f, kv_k, kv_v, tokens, pos, hidden, kv_head, n_kv, vis, want_logits=True):
+def gh_forward(h, which, m, f, kv_k, kv_v, tokens, pos, hidden, kv_head, n_kv, vis, want_logits=True, sched=False):
     hp = f["hparams"]
     T = len(tokens)
     logits = np.empty((T, hp["V"]), np.float32) if want_logits else None
     feat = np.empty((T, hp["E"]), np.float32)
-    n_nodes = C.c_int(0)
+    n_nodes, n_splits = C.c_int(0), C.c_int(0)
     hid = None if hidden is None else np.ascontiguousarray(hidden, np.float32)
     rc = h.gh_forward(which, m, po._ptr(kv_k), po._ptr(kv_v), kv_k.shape[1], po._ptr(np.ascontiguousarray(tokens, np.int32)),
                       po._ptr(np.ascontiguousarray(pos, np.int32)), po._ptr(hid), T, kv_head, n_kv, po._ptr(np.ascontiguousarray(vis, np.uint8)),
-                      po._ptr(logits), po._ptr(feat), C.byref(n_nodes))
+                      po._ptr(logits), po._ptr(feat), C.byref(n_nodes), int(sched), C.byref(n_splits))
     assert rc == 0, h.gh_last_error().decode()
-    return logits, feat, n_nodes.value
+    return logits, feat, (n_splits.value if sched else n_nodes.value)
 
 
 def case(ftype, is_eagle, seed, E=256, H=2, F=512, V=1024, L=2, T=27, n_past=40, n_ctx=128):
@@ -112,7 +112,7 @@ def test_plugin_is_skipped_without_a_gpu():
     m = gh_model(h, f)
     n = C.c_int(0)
     rc = h.gh_forward(1, m, po._ptr(kv[0].copy()), po._ptr(kv[1].copy()), kv.shape[2], po._ptr(tokens), po._ptr(pos), None, 4, n_past, n_kv,
-                      po._ptr(vis), None, po._ptr(np.empty((4, 256), np.float32)), C.byref(n))
+                      po._ptr(vis), None, po._ptr(np.empty((4, 256), np.float32)), C.byref(n), 0, C.byref(n))
     assert rc != 0                                                               # no backend, and nothing falls back to the CPU
     h.gh_model_free(m)
 
@@ -227,4 +227,29 @@ def test_plugin_graph_7b_width_layer(plugin):
     err_o = np.abs(lg_g - lg_o).max(1) / np.abs(lg_o).max()
     # rows whose activations hit no Q8-grid rounding flip agree to f32 summation order; a flipped row moves ~1e-2
     assert err_o.min() <= 1e-5 and err_o.max() <= 3e-2, (err_o.min(), err_o.max())
+    h.gh_model_free(m)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("ftype,is_eagle", [("q4_k_m", False), (po.Q4_0, True)])
+def test_plugin_under_ggml_backend_sched(plugin, ftype, is_eagle):
+    """the way libllama drives a backend: ggml_backend_sched over {plugin, CPU} (R/ggml/src/ggml-backend.cpp:1353,1448).  A SCALE node
+    the plugin does not claim forces plugin | CPU | plugin splits, so tensors cross the backends in both directions; every
+    MUL_MAT / FLASH_ATTN_EXT must have been assigned to the plugin (checked inside the harness)."""
+    h = plugin
+    f, tokens, pos, hidden, vis, kv, n_past, n_kv = case(ftype, is_eagle, 321, T=27, n_ctx=192)
+    m = gh_model(h, f)
+    outs = []
+    for which in (0, 1):
+        kk, vv = kv[0].copy().view(np.uint16), kv[1].copy().view(np.uint16)
+        lg, ft, n_splits = gh_forward(h, which, m, f, kk, vv, tokens, pos, hidden, n_past, n_kv, vis, sched=True)
+        outs.append((lg, ft, n_splits))
+    (lg_c, ft_c, sp_c), (lg_g, ft_g, sp_g) = outs
+    assert sp_c == 1 and sp_g >= 3, (sp_c, sp_g)
+    tol = 3e-2
+    assert np.abs(lg_g - lg_c).max() <= tol * np.abs(lg_c).max() and np.abs(ft_g - ft_c).max() <= tol * np.abs(ft_c).max()
+    # and the sched path gives exactly what the direct graph_compute path gives on the plugin
+    kk, vv = kv[0].copy().view(np.uint16), kv[1].copy().view(np.uint16)
+    lg_d, ft_d, _ = gh_forward(h, 1, m, f, kk, vv, tokens, pos, hidden, n_past, n_kv, vis)
+    np.testing.assert_array_equal(lg_d, lg_g); np.testing.assert_array_equal(ft_d, ft_g)
     h.gh_model_free(m)
