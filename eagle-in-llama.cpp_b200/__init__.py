@@ -54,7 +54,9 @@ def lib():
     sig = {
         "eb_last_error": ([], C.c_char_p), "eb_version": ([], i32), "eb_device_init": ([i32], i32),
         "eb_device_sm_count": ([], i32), "eb_device_memory": ([C.POINTER(sz), C.POINTER(sz)], i32),
-        "eb_copy": ([vp, vp, sz, vp], i32), "eb_concat2": ([vp, vp, vp, i32, i32, vp], i32), "eb_row_size": ([i32, i64], sz),
+        "eb_copy": ([vp, vp, sz, vp], i32), "eb_copy_strided": ([i32, i32, vp, vp, vp, vp, vp, vp, vp], i32),
+        "eb_mul_mat_dense": ([i32, vp, i64, i64, i64, vp, i64, i64, vp, i64, i64, i64, i64, vp], i32),
+        "eb_soft_max_ext": ([vp, vp, i32, i64, vp, i64, i64, i64, f32, vp], i32), "eb_concat2": ([vp, vp, vp, i32, i32, vp], i32), "eb_row_size": ([i32, i64], sz),
         "eb_malloc": ([C.POINTER(vp), sz], i32), "eb_free": ([vp], i32), "eb_memset": ([vp, i32, sz, vp], i32),
         "eb_upload": ([vp, vp, sz, vp], i32), "eb_download": ([vp, vp, sz, vp], i32), "eb_synchronize": ([vp], i32),
         "eb_repack": ([i32, vp, vp, i64, vp], i32), "eb_unpack": ([i32, vp, vp, i64, vp], i32),
@@ -268,6 +270,40 @@ def silu(x):
 
 def relu(x):
     return _unary(lib().eb_relu, x)
+
+
+def soft_max_ext(x, mask, scale):
+    """GGML_OP_SOFT_MAX: x f32 [B][T][n]; mask f16 / f32 [>= T][n] or None (shared by the B batches)"""
+    x = np.ascontiguousarray(x, np.float32)
+    B, T, n = x.shape
+    dx, dy = DeviceBuffer.from_host(x), DeviceBuffer(x.nbytes)
+    dm, mt = None, 0
+    if mask is not None:
+        mask = np.ascontiguousarray(mask); mt = F16 if mask.dtype == np.float16 else F32
+        dm = DeviceBuffer.from_host(mask)
+    _ck(lib().eb_soft_max_ext(dx.ptr, dm.ptr if dm else None, mt, n, dy.ptr, n, B * T, T, scale, None))
+    return dy.to_host(np.float32, x.shape)
+
+
+def mul_mat_dense(a, x):
+    """GGML_OP_MUL_MAT with f16 / f32 src0: a [Ba][N][K], x f32 [B][T][K] (B % Ba == 0) -> [B][T][N]"""
+    a = np.ascontiguousarray(a); x = np.ascontiguousarray(x, np.float32)
+    Ba, N, K = a.shape; B, T, _ = x.shape
+    da, dx, dy = DeviceBuffer.from_host(a), DeviceBuffer.from_host(x), DeviceBuffer(B * T * N * 4)
+    _ck(lib().eb_mul_mat_dense(F16 if a.dtype == np.float16 else F32, da.ptr, K * a.itemsize, N * K * a.itemsize, Ba, dx.ptr, K * 4, T * K * 4,
+                               dy.ptr, N, K, T, B, None))
+    return dy.to_host(np.float32, (B, T, N))
+
+
+def copy_strided(src, ne, nb_src, dst_dtype, dne, nb_dst, dst_bytes):
+    """GGML_OP_CPY over byte strides: src = flat numpy array (f32 / f16); returns the destination buffer as bytes"""
+    src = np.ascontiguousarray(src)
+    ds, dd = DeviceBuffer.from_host(src), DeviceBuffer(dst_bytes)
+    _ck(lib().eb_memset(dd.ptr, 0, dst_bytes, None))
+    arr = lambda v: np.ascontiguousarray(v, np.int64)
+    a1, a2, a3, a4 = arr(ne), arr(nb_src), arr(dne), arr(nb_dst)
+    _ck(lib().eb_copy_strided(F16 if src.dtype == np.float16 else F32, F16 if dst_dtype == np.float16 else F32, ds.ptr, dd.ptr, _hp(a1), _hp(a2), _hp(a3), _hp(a4), None))
+    return dd.to_host(np.uint8, dst_bytes)
 
 
 def tree_bits_from_parent(parent):

@@ -127,6 +127,16 @@ int eb_add(const float *a, const float *b, float *y, int64_t n, int64_t nb, void
 int eb_mul(const float *a, const float *b, float *y, int64_t n, int64_t nb, void *st) { NEED_DEV(); return eb_mul_impl(a, b, y, n, nb, S(st)); }
 int eb_silu(const float *x, float *y, int64_t n, void *st) { NEED_DEV(); return eb_silu_impl(x, y, n, S(st)); }
 int eb_relu(const float *x, float *y, int64_t n, void *st) { NEED_DEV(); return eb_relu_impl(x, y, n, S(st)); }
+int eb_copy_strided(int src_type, int dst_type, const void *src, void *dst, const int64_t *ne, const int64_t *nb_src, const int64_t *dne, const int64_t *nb_dst, void *st) {
+    NEED_DEV(); return eb_copy_strided_impl(src_type, dst_type, src, dst, ne, nb_src, dne, nb_dst, S(st));
+}
+int eb_mul_mat_dense(int a_type, const void *a, int64_t a_nb1, int64_t a_nb2, int64_t a_batches, const float *x, int64_t x_nb1, int64_t x_nb2,
+                     float *y, int64_t N, int64_t K, int64_t T, int64_t B, void *st) {
+    NEED_DEV(); return eb_mul_mat_dense_impl(a_type, a, a_nb1, a_nb2, a_batches, x, x_nb1, x_nb2, y, N, K, T, B, S(st));
+}
+int eb_soft_max_ext(const float *x, const void *mask, int mask_type, int64_t mask_stride, float *y, int64_t n, int64_t rows, int64_t rows_per_batch, float scale, void *st) {
+    NEED_DEV(); return eb_soft_max_ext_impl(x, mask, mask_type, mask_stride, y, n, rows, rows_per_batch, scale, S(st));
+}
 int eb_concat2(const float *a, const float *b, float *y, int E, int T, void *st) { NEED_DEV(); return eb_concat2_impl(a, b, y, E, T, S(st)); }
 int eb_cpy_f32_f16(const float *x, void *y, int64_t n, void *st) { NEED_DEV(); return eb_cpy_f32_f16_impl(x, y, n, S(st)); }
 

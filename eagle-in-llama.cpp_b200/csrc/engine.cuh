@@ -51,6 +51,10 @@ int eb_silu_impl(const float *x, float *y, int64_t n, cudaStream_t st);
 int eb_relu_impl(const float *x, float *y, int64_t n, cudaStream_t st);
 int eb_bias_relu_impl(const float *x, const float *b, float *y, int64_t n, int nb, cudaStream_t st);
 int eb_cpy_f32_f16_impl(const float *x, void *y, int64_t n, cudaStream_t st);
+int eb_copy_strided_impl(int src_type, int dst_type, const void *src, void *dst, const int64_t *ne, const int64_t *nb_src, const int64_t *dne, const int64_t *nb_dst, cudaStream_t st);
+int eb_mul_mat_dense_impl(int a_type, const void *a, int64_t a_nb1, int64_t a_nb2, int64_t a_batches, const float *x, int64_t x_nb1, int64_t x_nb2,
+                          float *y, int64_t N, int64_t K, int64_t T, int64_t B, cudaStream_t st);
+int eb_soft_max_ext_impl(const float *x, const void *mask, int mask_type, int64_t mask_stride, float *y, int64_t n, int64_t rows, int64_t rows_per_batch, float scale, cudaStream_t st);
 int eb_concat2_impl(const float *a, const float *b, float *y, int E, int T, cudaStream_t st);
 int eb_swiglu_impl(const float *gate, const float *up, float *y, int64_t n, cudaStream_t st);
 int eb_get_rows_dev(int type, const void *W, int64_t n_rows, int64_t K, const int32_t *d_ids, int n, float *out, cudaStream_t st);

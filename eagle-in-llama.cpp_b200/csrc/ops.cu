@@ -244,3 +244,111 @@ int eb_get_rows_dev(int type, const void *W, int64_t n_rows, int64_t K, const in
     EB_CHECK_LAUNCH();
     return EB_OK;
 }
+
+// ------------------------------------------------------------------ FA-off operator surface (llm_build_kqv without flash attention,
+// R/src/llama.cpp:762-812; the reference's default unless -fa is given).  Off the engine's hot path (the engine always runs the tree
+// flash-attention kernel); here so that the ggml plugin keeps the whole attention block on the device for FA-off graphs too.
+struct Strides4 { int64_t ne[4]; int64_t sa[4]; int64_t sd[4]; };     // element counts, source / destination strides in BYTES
+
+// GGML_OP_CPY / CONT / DUP over arbitrary 4-D strides (R/ggml/src/ggml-cuda/cpy.cu:526: ggml_cuda_cpy); f32 -> f32 | f16, f16 -> f16.
+// The element index runs over the SOURCE's logical order; ggml_cpy into a differently shaped destination of the same size walks the
+// destination in its own logical order (ggml_compute_forward_dup_f32), so the destination is addressed through its own ne/strides.
+template <typename TS, typename TD>
+__global__ void strided_copy_kernel(const uint8_t *__restrict__ src, uint8_t *__restrict__ dst, Strides4 s, int64_t dne0, int64_t dne1, int64_t dne2, int64_t n) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int64_t i0 = i % s.ne[0], i1 = (i / s.ne[0]) % s.ne[1], i2 = (i / (s.ne[0] * s.ne[1])) % s.ne[2], i3 = i / (s.ne[0] * s.ne[1] * s.ne[2]);
+    const int64_t d0 = i % dne0, d1 = (i / dne0) % dne1, d2 = (i / (dne0 * dne1)) % dne2, d3 = i / (dne0 * dne1 * dne2);
+    const TS v = *(const TS *)(src + i0 * s.sa[0] + i1 * s.sa[1] + i2 * s.sa[2] + i3 * s.sa[3]);
+    *(TD *)(dst + d0 * s.sd[0] + d1 * s.sd[1] + d2 * s.sd[2] + d3 * s.sd[3]) = (TD)v;
+}
+int eb_copy_strided_impl(int src_type, int dst_type, const void *src, void *dst, const int64_t *ne, const int64_t *nb_src, const int64_t *dne, const int64_t *nb_dst, cudaStream_t st) {
+    Strides4 s; int64_t n = 1, dn = 1;
+    for (int k = 0; k < 4; k++) { s.ne[k] = ne[k]; s.sa[k] = nb_src[k]; s.sd[k] = nb_dst[k]; n *= ne[k]; dn *= dne[k]; }
+    if (n != dn) return eb_set_err(EB_ERR_ARG, "copy_strided: %lld source elements, %lld destination elements", (long long)n, (long long)dn);
+    if (n == 0) return EB_OK;
+    const unsigned grid = (unsigned)cdiv(n, 256);
+    if (src_type == EB_F32 && dst_type == EB_F32) strided_copy_kernel<float, float><<<grid, 256, 0, st>>>((const uint8_t *)src, (uint8_t *)dst, s, dne[0], dne[1], dne[2], n);
+    else if (src_type == EB_F32 && dst_type == EB_F16) strided_copy_kernel<float, __half><<<grid, 256, 0, st>>>((const uint8_t *)src, (uint8_t *)dst, s, dne[0], dne[1], dne[2], n);
+    else if (src_type == EB_F16 && dst_type == EB_F16) strided_copy_kernel<__half, __half><<<grid, 256, 0, st>>>((const uint8_t *)src, (uint8_t *)dst, s, dne[0], dne[1], dne[2], n);
+    else return eb_set_err(EB_ERR_UNSUPPORTED, "copy_strided: types %d -> %d", src_type, dst_type);
+    EB_CHECK_LAUNCH();
+    return EB_OK;
+}
+
+// GGML_OP_MUL_MAT with an f16 (or f32) src0 and batch dimension: y[b][t][n] = sum_k a[b / r][n][k] * x[b][t][k] (KQ and KQV of the
+// FA-off attention).  The CPU converts x to f16 first when a is f16 (vec_dot_type, R/ggml/src/ggml-cpu/ggml-cpu.c:7588-7623) and
+// accumulates the f16 products in f32 (ggml_vec_dot_f16); restated here.  One warp per output element, lanes stride over k.
+template <typename TA>
+__global__ void __launch_bounds__(256) mul_mat_dense_kernel(const uint8_t *__restrict__ a, const uint8_t *__restrict__ x, float *__restrict__ y,
+                                                          int64_t N, int64_t K, int64_t T, int64_t B, int64_t bcast,
+                                                          int64_t a_nb1, int64_t a_nb2, int64_t x_nb1, int64_t x_nb2) {
+    const int64_t w = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5); const int lane = threadIdx.x & 31;
+    if (w >= N * T * B) return;
+    const int64_t n = w % N, t = (w / N) % T, b = w / (N * T);
+    const TA *ar = (const TA *)(a + n * a_nb1 + (b / bcast) * a_nb2);
+    const float *xr = (const float *)(x + t * x_nb1 + b * x_nb2);
+    float acc = 0.f;
+    for (int64_t k = lane; k < K; k += 32) {
+        if (sizeof(TA) == 2) acc += __half2float(((const __half *)ar)[k]) * __half2float(__float2half_rn(xr[k]));
+        else acc += ((const float *)ar)[k] * xr[k];
+    }
+    acc = warp_sum(acc);
+    if (lane == 0) y[w] = acc;
+}
+int eb_mul_mat_dense_impl(int a_type, const void *a, int64_t a_nb1, int64_t a_nb2, int64_t a_batches, const float *x, int64_t x_nb1, int64_t x_nb2,
+                          float *y, int64_t N, int64_t K, int64_t T, int64_t B, cudaStream_t st) {
+    if (a_batches < 1 || B % a_batches) return eb_set_err(EB_ERR_ARG, "mul_mat_dense: %lld batches of src0 for %lld of src1", (long long)a_batches, (long long)B);
+    const int64_t n = N * T * B;
+    if (n == 0) return EB_OK;
+    const unsigned grid = (unsigned)cdiv(n, 8);
+    if (a_type == EB_F16) mul_mat_dense_kernel<__half><<<grid, 256, 0, st>>>((const uint8_t *)a, (const uint8_t *)x, y, N, K, T, B, B / a_batches, a_nb1, a_nb2, x_nb1, x_nb2);
+    else if (a_type == EB_F32) mul_mat_dense_kernel<float><<<grid, 256, 0, st>>>((const uint8_t *)a, (const uint8_t *)x, y, N, K, T, B, B / a_batches, a_nb1, a_nb2, x_nb1, x_nb2);
+    else return eb_set_err(EB_ERR_UNSUPPORTED, "mul_mat_dense: src0 type %d", a_type);
+    EB_CHECK_LAUNCH();
+    return EB_OK;
+}
+
+// GGML_OP_SOFT_MAX with mask and scale (ggml_soft_max_ext, max_bias = 0): y = softmax(scale * x + mask) over rows of n values;
+// mask row = (row % rows_per_batch) of an f16 or f32 [n][>= rows_per_batch] tensor, shared by all heads
+// (ggml_compute_forward_soft_max_f32, R/ggml/src/ggml-cpu/ggml-cpu.c:9042: max, expf, sum in double, scale by 1/sum).
+__global__ void __launch_bounds__(256) soft_max_ext_kernel(const float *__restrict__ x, const void *__restrict__ mask, int mask_f16, int64_t mask_stride,
+                                                         float *__restrict__ y, int n, int64_t rows_per_batch, float scale) {
+    extern __shared__ float row[];
+    __shared__ float red_f[8]; __shared__ double red_d[8];
+    const int64_t r = blockIdx.x; const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const float *xr = x + r * n;
+    const int64_t mr = r % rows_per_batch;
+    float mx = -INFINITY;
+    for (int i = tid; i < n; i += 256) {
+        float v = xr[i] * scale;
+        if (mask) v += mask_f16 ? __half2float(((const __half *)mask)[mr * mask_stride + i]) : ((const float *)mask)[mr * mask_stride + i];
+        row[i] = v; mx = fmaxf(mx, v);
+    }
+    mx = warp_max(mx);
+    if (lane == 0) red_f[warp] = mx;
+    __syncthreads();
+    mx = red_f[0];
+    for (int i = 1; i < 8; i++) mx = fmaxf(mx, red_f[i]);
+    double sum = 0.0;
+    for (int i = tid; i < n; i += 256) { const float e = mx == -INFINITY ? 0.f : expf(row[i] - mx); row[i] = e; sum += (double)e; }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+    if (lane == 0) red_d[warp] = sum;
+    __syncthreads();
+    sum = 0.0;
+    for (int i = 0; i < 8; i++) sum += red_d[i];
+    const float inv = (float)(1.0 / sum);
+    float *yr = y + r * n;
+    for (int i = tid; i < n; i += 256) yr[i] = row[i] * inv;
+}
+int eb_soft_max_ext_impl(const float *x, const void *mask, int mask_type, int64_t mask_stride, float *y, int64_t n, int64_t rows, int64_t rows_per_batch, float scale, cudaStream_t st) {
+    if (n < 1 || n > 48000) return eb_set_err(EB_ERR_ARG, "soft_max: n=%lld", (long long)n);
+    if (mask && mask_type != EB_F16 && mask_type != EB_F32) return eb_set_err(EB_ERR_UNSUPPORTED, "soft_max: mask type %d", mask_type);
+    if (rows == 0) return EB_OK;
+    static bool attr_set = false;
+    if (!attr_set) { EB_CUDA(cudaFuncSetAttribute(soft_max_ext_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 48000 * 4)); attr_set = true; }
+    soft_max_ext_kernel<<<(unsigned)rows, 256, (size_t)n * 4, st>>>(x, mask, mask_type == EB_F16, mask_stride, y, (int)n, rows_per_batch > 0 ? rows_per_batch : rows, scale);
+    EB_CHECK_LAUNCH();
+    return EB_OK;
+}

@@ -129,6 +129,9 @@ static bool b200_dev_supports_op(ggml_backend_dev_t, const ggml_tensor *op) {
     switch (op->op) {
     case GGML_OP_NONE: case GGML_OP_RESHAPE: case GGML_OP_VIEW: case GGML_OP_PERMUTE: case GGML_OP_TRANSPOSE: return true;
     case GGML_OP_MUL_MAT:
+        if (a->type == GGML_TYPE_F16 || a->type == GGML_TYPE_F32)      // KQ / KQV of the FA-off attention: strided views, batched over heads
+            return b->type == GGML_TYPE_F32 && op->type == GGML_TYPE_F32 && a->nb[0] == ggml_type_size(a->type) && b->nb[0] == 4 && a->ne[3] == 1 && b->ne[3] == 1 &&
+                   a->ne[2] >= 1 && b->ne[2] % a->ne[2] == 0 && ggml_is_contiguous(op);
         return b200_weight_type(a->type) && ggml_is_contiguous(a) && a->ne[2] == 1 && a->ne[3] == 1 && b->type == GGML_TYPE_F32 && ggml_is_contiguous(b) &&
                b->ne[2] == 1 && b->ne[3] == 1 && a->ne[0] % (a->type == GGML_TYPE_Q4_K || a->type == GGML_TYPE_Q6_K ? 256 : 32) == 0 && op->type == GGML_TYPE_F32;
     case GGML_OP_FLASH_ATTN_EXT: {
@@ -151,10 +154,17 @@ static bool b200_dev_supports_op(ggml_backend_dev_t, const ggml_tensor *op) {
     case GGML_OP_UNARY: return (ggml_get_unary_op(op) == GGML_UNARY_OP_SILU || ggml_get_unary_op(op) == GGML_UNARY_OP_RELU) && a->type == GGML_TYPE_F32 && ggml_is_contiguous(a);
     case GGML_OP_CONCAT:    // [E, T] | [E, T] along dim 0 (build_eagle)
         return ((const int32_t *)op->op_params)[0] == 0 && a->type == GGML_TYPE_F32 && same_shape_contig(a, b) && a->ne[2] == 1 && a->ne[3] == 1;
-    case GGML_OP_CPY: case GGML_OP_DUP: case GGML_OP_CONT: {
+    case GGML_OP_CPY: case GGML_OP_DUP: case GGML_OP_CONT: {    // any strides (transposed V store, merge of the permuted KQV)
         const ggml_tensor *d = op->op == GGML_OP_CPY ? op->src[1] : op;
-        if (!ggml_is_contiguous(a) || !ggml_is_contiguous(d) || ggml_nelements(a) != ggml_nelements(d)) return false;
-        return (a->type == GGML_TYPE_F32 && d->type == GGML_TYPE_F16) || (a->type == d->type && !ggml_is_quantized(a->type));
+        if (ggml_nelements(a) != ggml_nelements(d)) return false;
+        if (ggml_is_contiguous(a) && ggml_is_contiguous(d) && a->type == d->type && !ggml_is_quantized(a->type)) return true;
+        return (a->type == GGML_TYPE_F32 && (d->type == GGML_TYPE_F16 || d->type == GGML_TYPE_F32)) || (a->type == GGML_TYPE_F16 && d->type == GGML_TYPE_F16);
+    }
+    case GGML_OP_SOFT_MAX: {    // ggml_soft_max_ext(kq, mask, scale, max_bias = 0)
+        const ggml_tensor *m = op->src[1];
+        return a->type == GGML_TYPE_F32 && ggml_is_contiguous(a) && a->ne[0] <= 48000 && op_f32(op, 1) == 0.0f &&
+               (!m || ((m->type == GGML_TYPE_F16 || m->type == GGML_TYPE_F32) && m->ne[0] == a->ne[0] && m->ne[1] >= a->ne[1] && m->ne[2] == 1 && m->ne[3] == 1 &&
+                       m->nb[0] == ggml_type_size(m->type)));
     }
     case GGML_OP_ARGMAX: return a->type == GGML_TYPE_F32 && ggml_is_contiguous(a);
     default: return false;
@@ -166,6 +176,9 @@ static int b200_compute_node(b200_backend_ctx *ctx, ggml_tensor *d) {
     switch (d->op) {
     case GGML_OP_NONE: case GGML_OP_RESHAPE: case GGML_OP_VIEW: case GGML_OP_PERMUTE: case GGML_OP_TRANSPOSE: return EB_OK;
     case GGML_OP_MUL_MAT: {     // a = weights [K, N], b = activations f32 [K, T] -> d f32 [N, T]
+        if (a->type == GGML_TYPE_F16 || a->type == GGML_TYPE_F32)
+            return eb_mul_mat_dense((int)a->type, a->data, (int64_t)a->nb[1], (int64_t)a->nb[2], a->ne[2], (const float *)b->data, (int64_t)b->nb[1], (int64_t)b->nb[2],
+                                    (float *)d->data, a->ne[1], a->ne[0], b->ne[1], b->ne[2], nullptr);
         void *ws = ctx->scratch(eb_mul_mat_ws_size((int)a->type, a->ne[1], a->ne[0], b->ne[1]));
         if (!ws) return EB_ERR_OOM;
         return eb_mul_mat((int)a->type, a->data, a->ne[1], a->ne[0], (const float *)b->data, b->ne[1], (float *)d->data, ws, nullptr);
@@ -192,8 +205,18 @@ static int b200_compute_node(b200_backend_ctx *ctx, ggml_tensor *d) {
     case GGML_OP_CONCAT: return eb_concat2((const float *)a->data, (const float *)b->data, (float *)d->data, (int)a->ne[0], (int)a->ne[1], nullptr);
     case GGML_OP_CPY: case GGML_OP_DUP: case GGML_OP_CONT: {
         const ggml_tensor *dst = d->op == GGML_OP_CPY ? d->src[1] : d;     // ggml_cpy: the node is a view of src[1]
-        if (a->type == GGML_TYPE_F32 && dst->type == GGML_TYPE_F16) return eb_cpy_f32_f16((const float *)a->data, dst->data, ggml_nelements(a), nullptr);   // KV store, mask cast
-        return eb_copy(dst->data, a->data, ggml_nbytes(a), nullptr);
+        if (ggml_is_contiguous(a) && ggml_is_contiguous(dst)) {
+            if (a->type == GGML_TYPE_F32 && dst->type == GGML_TYPE_F16) return eb_cpy_f32_f16((const float *)a->data, dst->data, ggml_nelements(a), nullptr);   // KV store, mask cast
+            if (a->type == dst->type) return eb_copy(dst->data, a->data, ggml_nbytes(a), nullptr);
+        }
+        const int64_t nbs[4] = {(int64_t)a->nb[0], (int64_t)a->nb[1], (int64_t)a->nb[2], (int64_t)a->nb[3]};
+        const int64_t nbd[4] = {(int64_t)dst->nb[0], (int64_t)dst->nb[1], (int64_t)dst->nb[2], (int64_t)dst->nb[3]};
+        return eb_copy_strided((int)a->type, (int)dst->type, a->data, dst->data, a->ne, nbs, dst->ne, nbd, nullptr);
+    }
+    case GGML_OP_SOFT_MAX: {
+        const ggml_tensor *m = d->src[1];
+        return eb_soft_max_ext((const float *)a->data, m ? m->data : nullptr, m ? (int)m->type : 0, m ? (int64_t)(m->nb[1] / ggml_type_size(m->type)) : 0,
+                               (float *)d->data, a->ne[0], ggml_nrows(a), a->ne[1], op_f32(d, 0), nullptr);
     }
     case GGML_OP_ARGMAX: return eb_argmax((const float *)a->data, (int)ggml_nrows(a), (int)a->ne[0], (int32_t *)d->data, nullptr);
     default: return EB_ERR_UNSUPPORTED;

@@ -98,6 +98,23 @@ EB_API int eb_concat2(const float *d_a, const float *d_b, float *d_y, int E, int
 /* GGML_OP_CPY f32 -> f16 (KV store), R/ggml/src/ggml-cuda/cpy.cu:35 */
 EB_API int eb_cpy_f32_f16(const float *d_x, void *d_y_f16, int64_t n, void *stream);
 
+/* ---- FA-off attention block (llm_build_kqv without flash attention, R/src/llama.cpp:762-812 — the reference's default unless -fa;
+ * off the engine's path, which always runs the tree flash-attention kernel).  Strides are in BYTES, as ggml's nb[]. */
+/* GGML_OP_CPY / CONT / DUP over arbitrary 4-D strides, f32 -> f32 | f16, f16 -> f16 (R/ggml/src/ggml-cuda/cpy.cu:526;
+ * CPU: ggml_compute_forward_dup, R/ggml/src/ggml-cpu/ggml-cpu.c:4113): element i of the source's logical order goes to
+ * element i of the destination's logical order (ne / dne may differ in shape, not in count). */
+EB_API int eb_copy_strided(int src_type, int dst_type, const void *d_src, void *d_dst, const int64_t ne[4], const int64_t nb_src[4],
+                           const int64_t dne[4], const int64_t nb_dst[4], void *stream);
+/* GGML_OP_MUL_MAT with an f16 / f32 src0 and a batch dimension (KQ = K x Q and KQV = V^T x softmax): y[b][t][n] = sum_k
+ * a[b / (B / a_batches)][n][k] * x[b][t][k]; x is rounded to f16 first when a is f16, products accumulate in f32, as the CPU's
+ * vec_dot_f16 path does (R/ggml/src/ggml-cpu/ggml-cpu.c:7588-7623).  a: rows nb1 apart, batches nb2 apart; y contiguous [B][T][N]. */
+EB_API int eb_mul_mat_dense(int a_type, const void *d_a, int64_t a_nb1, int64_t a_nb2, int64_t a_batches, const float *d_x, int64_t x_nb1,
+                            int64_t x_nb2, float *d_y, int64_t N, int64_t K, int64_t T, int64_t B, void *stream);
+/* GGML_OP_SOFT_MAX (ggml_soft_max_ext with max_bias = 0, R/ggml/src/ggml-cuda/softmax.cu:13; CPU R/ggml/src/ggml-cpu/ggml-cpu.c:9042):
+ * y = softmax(scale * x + mask) over rows of n; mask (f16 or f32, rows mask_stride elements apart, or NULL) row = row % rows_per_batch */
+EB_API int eb_soft_max_ext(const float *d_x, const void *d_mask, int mask_type, int64_t mask_stride, float *d_y, int64_t n, int64_t rows,
+                           int64_t rows_per_batch, float scale, void *stream);
+
 /* GGML_OP_FLASH_ATTN_EXT: replaces flash_attn_ext_f16 R/ggml/src/ggml-cuda/fattn-mma-f16.cuh:806
  * (CPU: R/ggml/src/ggml-cpu/ggml-cpu.c:10999).  q f32 [T][H][D]; k, v f16 cells, row stride
  * kv_stride elements between cells, head h at offset h*D; out f32 [T][H][D].  D must be 128.

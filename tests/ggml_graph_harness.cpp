@@ -94,6 +94,8 @@ GH_API int gh_forward(int which, const GModel *m, uint16_t *kv_k, uint16_t *kv_v
                       const float *hidden_in, int T, int kv_head, int n_kv, const uint8_t *vis, float *logits, float *feat, int *n_nodes_out,
                       int use_sched, int *n_splits_out) {
     ggml_backend_t be = backend(which); if (!be) { snprintf(g_err, sizeof g_err, "no backend %d", which); return -1; }
+    const bool fa_off = (use_sched & 2) != 0;      // bit 1: build the attention block without flash attention (V cache transposed)
+    use_sched &= 1;
     const int E = m->E, H = m->H, F = m->F, D = E / H, V = m->V, L = m->L;
     ggml_init_params pw = {ggml_tensor_overhead() * (size_t)(16 + 16 * L), nullptr, true};
     ggml_init_params pc = {ggml_tensor_overhead() * (size_t)(256 + 64 * L) + ggml_graph_overhead_custom(8192, false), nullptr, true};
@@ -149,13 +151,24 @@ GH_API int gh_forward(int which, const GModel *m, uint16_t *kv_k, uint16_t *kv_v
         Q = ggml_rope_ext(c, ggml_reshape_3d(c, Q, D, H, T), b.pos, nullptr, D, 0, 0, m->freq_base, 1.0f, 0.0f, 1.0f, 32.0f, 1.0f);
         K = ggml_rope_ext(c, ggml_reshape_3d(c, K, D, H, T), b.pos, nullptr, D, 0, 0, m->freq_base, 1.0f, 0.0f, 1.0f, 32.0f, 1.0f);
         ggml_build_forward_expand(gf, ggml_cpy(c, ggml_reshape_1d(c, K, (int64_t)T * E), ggml_view_1d(c, b.kc[l], (int64_t)T * E, row * kv_head)));    // llm_build_kv_store :228-270
-        ggml_build_forward_expand(gf, ggml_cpy(c, ggml_reshape_1d(c, Vc, (int64_t)T * E), ggml_view_1d(c, b.vc[l], (int64_t)T * E, row * kv_head)));
-        ggml_tensor *q = ggml_permute(c, Q, 0, 2, 1, 3);                                  // llm_build_kqv :706-828, flash-attn branch
+        ggml_tensor *q = ggml_permute(c, Q, 0, 2, 1, 3);
         ggml_tensor *k3 = ggml_view_3d(c, b.kc[l], D, n_kv, H, row, (size_t)D * 2, 0);
-        ggml_tensor *v3 = ggml_view_3d(c, b.vc[l], D, n_kv, H, row, (size_t)D * 2, 0);
-        cur = ggml_flash_attn_ext(c, q, k3, v3, mask, kq_scale, 0.0f, 0.0f);
-        ggml_flash_attn_ext_set_prec(cur, GGML_PREC_F32);
-        cur = ggml_mul_mat(c, lw[l].wo, ggml_reshape_2d(c, cur, E, T));
+        if (!fa_off) {                                                                    // llm_build_kqv :706-761, flash-attn branch
+            ggml_build_forward_expand(gf, ggml_cpy(c, ggml_reshape_1d(c, Vc, (int64_t)T * E), ggml_view_1d(c, b.vc[l], (int64_t)T * E, row * kv_head)));
+            ggml_tensor *v3 = ggml_view_3d(c, b.vc[l], D, n_kv, H, row, (size_t)D * 2, 0);
+            cur = ggml_flash_attn_ext(c, q, k3, v3, mask, kq_scale, 0.0f, 0.0f);
+            ggml_flash_attn_ext_set_prec(cur, GGML_PREC_F32);
+            cur = ggml_reshape_2d(c, cur, E, T);
+        } else {                                                                          // :762-812 and the transposed V store :258-264
+            ggml_build_forward_expand(gf, ggml_cpy(c, ggml_transpose(c, Vc), ggml_view_2d(c, b.vc[l], T, E, (size_t)n_ctx * 2, (size_t)kv_head * 2)));
+            ggml_tensor *kq = ggml_mul_mat(c, k3, q);
+            ggml_mul_mat_set_prec(kq, GGML_PREC_F32);
+            kq = ggml_soft_max_ext(c, kq, mask, kq_scale, 0.0f);
+            ggml_tensor *v3 = ggml_view_3d(c, b.vc[l], n_kv, D, H, (size_t)n_ctx * 2, (size_t)n_ctx * D * 2, 0);
+            ggml_tensor *kqv = ggml_mul_mat(c, v3, kq);
+            cur = ggml_cont_2d(c, ggml_permute(c, kqv, 0, 2, 1, 3), E, T);
+        }
+        cur = ggml_mul_mat(c, lw[l].wo, cur);
         ggml_tensor *ffn_inp = ggml_add(c, cur, inpSA);
         cur = norm(c, ffn_inp, lw[l].fn, m->eps);
         ggml_tensor *up = ggml_mul_mat(c, lw[l].up, cur), *gt = ggml_silu(c, ggml_mul_mat(c, lw[l].gate, cur));   // llm_build_ffn :456-581

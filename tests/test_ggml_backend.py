@@ -59,7 +59,7 @@ def gh_model(h, f):
     return m
 
 
-def gh_forward(h, which, m, f, kv_k, kv_v, tokens, pos, hidden, kv_head, n_kv, vis, want_logits=True, sched=False):
+def gh_forward(h, which, m, f, kv_k, kv_v, tokens, pos, hidden, kv_head, n_kv, vis, want_logits=True, sched=False, fa_off=False):
     hp = f["hparams"]
     T = len(tokens)
     logits = np.empty((T, hp["V"]), np.float32) if want_logits else None
@@ -68,7 +68,7 @@ def gh_forward(h, which, m, f, kv_k, kv_v, tokens, pos, hidden, kv_head, n_kv, v
     hid = None if hidden is None else np.ascontiguousarray(hidden, np.float32)
     rc = h.gh_forward(which, m, po._ptr(kv_k), po._ptr(kv_v), kv_k.shape[1], po._ptr(np.ascontiguousarray(tokens, np.int32)),
                       po._ptr(np.ascontiguousarray(pos, np.int32)), po._ptr(hid), T, kv_head, n_kv, po._ptr(np.ascontiguousarray(vis, np.uint8)),
-                      po._ptr(logits), po._ptr(feat), C.byref(n_nodes), int(sched), C.byref(n_splits))
+                      po._ptr(logits), po._ptr(feat), C.byref(n_nodes), int(sched) | (2 if fa_off else 0), C.byref(n_splits))
     assert rc == 0, h.gh_last_error().decode()
     return logits, feat, (n_splits.value if sched else n_nodes.value)
 
@@ -252,4 +252,31 @@ def test_plugin_under_ggml_backend_sched(plugin, ftype, is_eagle):
     kk, vv = kv[0].copy().view(np.uint16), kv[1].copy().view(np.uint16)
     lg_d, ft_d, _ = gh_forward(h, 1, m, f, kk, vv, tokens, pos, hidden, n_past, n_kv, vis)
     np.testing.assert_array_equal(lg_d, lg_g); np.testing.assert_array_equal(ft_d, ft_g)
+    h.gh_model_free(m)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("ftype,is_eagle,T", [("q4_k_m", False, 27), (po.Q4_0, True, 8), (po.Q8_0, False, 65)])
+def test_plugin_graph_without_flash_attention(plugin, ftype, is_eagle, T):
+    """the reference's default attention block (no -fa: KQ mul_mat over the f16 cache, soft_max_ext with the tree mask, transposed V
+    cache, KQV mul_mat, permute + cont; R/src/llama.cpp:258-264,762-812): every node is claimed by the plugin and the result agrees
+    with the same graph on ggml-cpu.  The V cache is compared in its transposed layout."""
+    h = plugin
+    f, tokens, pos, hidden, vis, kv, n_past, n_kv = case(ftype, is_eagle, 500 + T, T=T, n_ctx=192)
+    Lm, n_ctx, E = kv.shape[1], kv.shape[2], kv.shape[3]
+    kv_t = kv.copy()
+    kv_t[1] = kv[1].transpose(0, 2, 1).reshape(Lm, n_ctx, E)              # V^T: [E][n_ctx] per layer, stored in the same bytes
+    m = gh_model(h, f)
+    outs = []
+    for which in (0, 1):
+        kk, vv = kv_t[0].copy().view(np.uint16), kv_t[1].copy().view(np.uint16)
+        lg, ft, _ = gh_forward(h, which, m, f, kk, vv, tokens, pos, hidden, n_past, n_kv, vis, fa_off=True)
+        outs.append((lg, ft, kk.view(np.float16).astype(np.float32), vv.view(np.float16).astype(np.float32)))
+    (lg_c, ft_c, k_c, v_c), (lg_g, ft_g, k_g, v_g) = outs
+    tol = 3e-2
+    assert np.isfinite(lg_g).all()
+    assert np.abs(lg_g - lg_c).max() <= tol * np.abs(lg_c).max() and np.abs(ft_g - ft_c).max() <= tol * np.abs(ft_c).max()
+    assert np.abs(k_g - k_c).max() <= tol * np.abs(k_c).max() and np.abs(v_g - v_c).max() <= tol * np.abs(v_c).max()
+    vt = v_g.reshape(Lm, E, n_ctx)
+    assert np.abs(vt[:, :, n_past:n_past + T]).max() > 0 and np.array_equal(vt[:, :, :n_past], v_c.reshape(Lm, E, n_ctx)[:, :, :n_past])
     h.gh_model_free(m)

@@ -221,3 +221,29 @@ def test_mul_mat_q6_K_extreme_blocks(eb):
     want = po.oracle().mul_mat(po.Q6_K, raw.reshape(-1), N, K, X)
     assert np.abs(want).max() > 1e3                                                # rows 1, 2: |isum| = 1.3e8 per super-block
     assert rel_max(got, want) < 2e-6
+
+
+def test_fa_off_operator_surface(eb):
+    """SOFT_MAX (ggml_soft_max_ext), MUL_MAT with an f16 src0 batched over heads (with broadcast), CPY over strides — the ops of
+    llm_build_kqv without flash attention (R/src/llama.cpp:762-812) — against plain numpy restatements of the CPU kernels"""
+    rng = np.random.default_rng(21)
+    B, T, n = 4, 9, 301
+    x = rng.normal(0, 3, (B, T, n)).astype(np.float32)
+    mask = np.where(rng.random((12, n)) < 0.3, -np.inf, 0.0).astype(np.float32); mask[:, 0] = 0
+    for m in (mask.astype(np.float16), mask, None):
+        got = eb.soft_max_ext(x, m, 0.25)
+        w = x * np.float32(0.25) + (0 if m is None else m[:T].astype(np.float32)[None])
+        e = np.exp(w - w.max(-1, keepdims=True)); want = (e / e.sum(-1, keepdims=True)).astype(np.float32)
+        assert np.abs(got - want).max() < 2e-6 and np.abs(got.sum(-1) - 1).max() < 1e-5
+    Ba, Bx, N, K = 2, 6, 37, 128
+    a = rng.normal(0, 1, (Ba, N, K)).astype(np.float16); xx = rng.normal(0, 1, (Bx, T, K)).astype(np.float32)
+    got = eb.mul_mat_dense(a, xx)
+    want = np.einsum("btk,bnk->btn", xx.astype(np.float16).astype(np.float32), np.repeat(a.astype(np.float32), Bx // Ba, 0))
+    assert np.abs(got - want).max() < 1e-4 * np.abs(want).max()
+    # transposed store: src f32 [E][T] read as its transpose [T][E] -> f16 rows of a cache laid out [E][n_ctx] at column kv_head
+    E, Tt, n_ctx, kv_head = 16, 5, 12, 4
+    v = rng.normal(0, 1, (Tt, E)).astype(np.float32)                      # ggml: ne = [E, T]; transpose -> ne [T, E], nb [E*4, 4]
+    raw = eb.copy_strided(v, [Tt, E, 1, 1], [E * 4, 4, Tt * E * 4, Tt * E * 4], np.float16, [Tt, E, 1, 1], [2, n_ctx * 2, 0, 0], E * n_ctx * 2 + kv_head * 2)
+    cache = raw[:E * n_ctx * 2].view(np.float16).reshape(E, n_ctx)
+    # the call wrote relative to the buffer start: column 0..T-1
+    assert np.array_equal(cache[:, :Tt], v.T.astype(np.float16)) and not cache[:, Tt:].any()
