@@ -24,7 +24,9 @@ static thread_local const int *g_gate = nullptr;
 const int *eb_gate() { return g_gate; }
 void eb_gate_set(const int *g) { g_gate = g; }
 
-int eb_pdl_enabled() { static const int on = getenv("EB_NO_PDL") ? 0 : 1; return on; }
+static thread_local int g_pdl_scope = 1;
+void eb_pdl_scope(int on) { g_pdl_scope = on; }
+int eb_pdl_enabled() { static const int on = getenv("EB_NO_PDL") ? 0 : 1; return on && g_pdl_scope; }
 
 extern "C" {
 

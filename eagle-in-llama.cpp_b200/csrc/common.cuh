@@ -73,6 +73,7 @@ static inline int64_t cdiv(int64_t a, int64_t b) { return (a + b - 1) / b; }
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 int eb_pdl_enabled();
+void eb_pdl_scope(int on);     // host side, per thread: launches issued while the scope is off carry no PDL attribute
 template <typename... KArgs, typename... Args>
 static inline cudaError_t eb_launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args... args) {
     cudaLaunchConfig_t cfg = {};

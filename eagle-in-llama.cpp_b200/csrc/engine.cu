@@ -285,6 +285,10 @@ static int forward_dev(const eb_model *m, KVCache &kv, Workspace &w, const int32
     // gate_fwd / gate_lm (draft levels of a captured round): device words that switch the whole forward / its lm_head off
     // when the tree stopped growing (common.cuh "launch gate"); the caller clears the gate after the call
     eb_gate_set(gate_fwd);
+    // T <= 8 (draft head, single-token decode): measured slower with programmatic dependent launch (verify_only(8): 2.91 ms with,
+    // 2.80 ms without; EB_PDL_SMALL=1 keeps it on)
+    static const bool pdl_small = getenv("EB_PDL_SMALL") != nullptr;
+    struct PdlScope { bool off; PdlScope(bool o) : off(o) { if (off) eb_pdl_scope(0); } ~PdlScope() { if (off) eb_pdl_scope(1); } } pdl_scope_(T <= 8 && !pdl_small);
     // spec != null (draft level): hidden rows are gathered from root_feat / node_feat by the state's dft_src, and the result
     // features are scattered to node_feat, inside the kernels that read / produce them
     const int E = m->E, H = m->H, F = m->F, D = E / H;
