@@ -24,9 +24,9 @@ static thread_local const int *g_gate = nullptr;
 const int *eb_gate() { return g_gate; }
 void eb_gate_set(const int *g) { g_gate = g; }
 
-static thread_local int g_pdl_scope = 1;
-void eb_pdl_scope(int on) { g_pdl_scope = on; }
-int eb_pdl_enabled() { static const int on = getenv("EB_NO_PDL") ? 0 : 1; return on && g_pdl_scope; }
+static thread_local int g_pdl_scope = EB_PDL_ALL;
+void eb_pdl_scope(int mask) { g_pdl_scope = mask; }
+int eb_pdl_enabled(int cls) { static const int on = getenv("EB_NO_PDL") ? 0 : 1; return on && (g_pdl_scope & cls) != 0; }
 
 extern "C" {
 

@@ -72,15 +72,16 @@ static inline int64_t cdiv(int64_t a, int64_t b) { return (a + b - 1) / b; }
 // In a kernel launched the ordinary way both are no-ops.  EB_NO_PDL=1 turns the launch attribute off.
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
-int eb_pdl_enabled();
-void eb_pdl_scope(int on);     // host side, per thread: launches issued while the scope is off carry no PDL attribute
+enum { EB_PDL_GEMM = 1, EB_PDL_RESID = 2, EB_PDL_ROPE = 4, EB_PDL_ATTN = 8, EB_PDL_COMBINE = 16, EB_PDL_SWIGLU = 32, EB_PDL_CONCAT = 64, EB_PDL_TOPK = 128, EB_PDL_EXPAND = 256, EB_PDL_ALL = 511 };
+int eb_pdl_enabled(int cls = EB_PDL_ALL);
+void eb_pdl_scope(int mask);   // host side, per thread: kernel classes whose launches carry the PDL attribute (EB_PDL_ALL by default)
 template <typename... KArgs, typename... Args>
-static inline cudaError_t eb_launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args... args) {
+static inline cudaError_t eb_launch_pdl_c(int cls, void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args... args) {
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
     cudaLaunchAttribute at[1];
     at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization; at[0].val.programmaticStreamSerializationAllowed = 1;
-    cfg.attrs = at; cfg.numAttrs = eb_pdl_enabled() ? 1 : 0;
+    cfg.attrs = at; cfg.numAttrs = eb_pdl_enabled(cls) ? 1 : 0;
     return cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);
 }
 

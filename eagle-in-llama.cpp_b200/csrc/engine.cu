@@ -285,10 +285,14 @@ static int forward_dev(const eb_model *m, KVCache &kv, Workspace &w, const int32
     // gate_fwd / gate_lm (draft levels of a captured round): device words that switch the whole forward / its lm_head off
     // when the tree stopped growing (common.cuh "launch gate"); the caller clears the gate after the call
     eb_gate_set(gate_fwd);
-    // T <= 8 (draft head, single-token decode): measured slower with programmatic dependent launch (verify_only(8): 2.91 ms with,
-    // 2.80 ms without; EB_PDL_SMALL=1 keeps it on)
-    static const bool pdl_small = getenv("EB_PDL_SMALL") != nullptr;
-    struct PdlScope { bool off; PdlScope(bool o) : off(o) { if (off) eb_pdl_scope(0); } ~PdlScope() { if (off) eb_pdl_scope(1); } } pdl_scope_(T <= 8 && !pdl_small);
+    // Which launches carry the programmatic-dependent-launch attribute.  Only the kernels with a long prologue that does not depend
+    // on the predecessor (GEMMs: barrier init, TMEM, weight TMA ring; attention: TMEM, tensor maps) gain from starting early.  With the
+    // attribute on the glue kernels as well, launches chain several kernels deep (every kernel triggers at its start): CTAs of kernels
+    // two or three steps ahead park on SMs the running persistent GEMM needs.  Measured (tools/pdl_big_sweep.sh, pdl_small_sweep.sh):
+    // verify 3.447 ms with every class, 3.540 with none, 3.165 with GEMM | ROPE | ATTN; draft levels: round -0.11 ms with GEMM only.
+    static const int pdl_small_mask = getenv("EB_PDL_SMALL_MASK") ? atoi(getenv("EB_PDL_SMALL_MASK")) : EB_PDL_GEMM;
+    static const int pdl_big_mask = getenv("EB_PDL_BIG_MASK") ? atoi(getenv("EB_PDL_BIG_MASK")) : (EB_PDL_GEMM | EB_PDL_ROPE | EB_PDL_ATTN);
+    struct PdlScope { PdlScope(int m) { eb_pdl_scope(m); } ~PdlScope() { eb_pdl_scope(EB_PDL_ALL); } } pdl_scope_(T <= 8 ? pdl_small_mask : pdl_big_mask);
     // spec != null (draft level): hidden rows are gathered from root_feat / node_feat by the state's dft_src, and the result
     // features are scattered to node_feat, inside the kernels that read / produce them
     const int E = m->E, H = m->H, F = m->F, D = E / H;

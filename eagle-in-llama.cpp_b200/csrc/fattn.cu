@@ -281,7 +281,7 @@ __global__ void fattn_combine_quant_kernel(const float *__restrict__ part_o, con
                    a.h16 ? a.h16 + (int64_t)r * K + b * 256 : nullptr, (a.dT && r < EB_DT_PITCH) ? a.dT + (int64_t)b * EB_DT_PITCH + r : nullptr);
 }
 void eb_fattn_combine_quant(const float *part_o, const float *part_ml, int T, int H, int nsplit, const ActQ &a, cudaStream_t st) {
-    eb_launch_pdl(fattn_combine_quant_kernel, dim3((unsigned)cdiv((int64_t)T * (H / 2), 8)), dim3(256), 0, st, part_o, part_ml, T, H, nsplit, a, eb_gate());
+    eb_launch_pdl_c(EB_PDL_COMBINE, fattn_combine_quant_kernel, dim3((unsigned)cdiv((int64_t)T * (H / 2), 8)), dim3(256), 0, st, part_o, part_ml, T, H, nsplit, a, eb_gate());
 }
 void eb_fattn_combine(const float *part_o, const float *part_ml, float *out, int T, int H, int nsplit, cudaStream_t st) {
     fattn_combine_kernel<<<(unsigned)cdiv((int64_t)T * H, 8), 256, 0, st>>>(part_o, part_ml, out, T, H, nsplit);

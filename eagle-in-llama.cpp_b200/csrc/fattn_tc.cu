@@ -311,7 +311,7 @@ int eb_fattn_tc(const __half *q16, const void *k, const void *v, int64_t kv_stri
     if ((rc = eb_tc_map_2d_f16(&tmQ, q16, (uint64_t)H * 128, (uint64_t)T, (uint64_t)H * 128 * 2, 64, 128))) return rc;
     if ((rc = eb_tc_map_2d_f16(&tmK, k, (uint64_t)H * 128, (uint64_t)n_cells, (uint64_t)kv_stride * 2, 64, 128))) return rc;
     if ((rc = eb_tc_map_2d_f16(&tmV, v, (uint64_t)H * 128, (uint64_t)n_cells, (uint64_t)kv_stride * 2, 64, 128))) return rc;
-    eb_launch_pdl(fattn_tc_kernel, dim3(H, p.nsplit), dim3(256), FT_SMEM, st, tmQ, tmK, tmV, p);
+    eb_launch_pdl_c(EB_PDL_ATTN, fattn_tc_kernel, dim3(H, p.nsplit), dim3(256), FT_SMEM, st, tmQ, tmK, tmV, p);
     EB_CHECK_LAUNCH();
     if (want_prof) {
         long long h[16]; cudaStreamSynchronize(st); cudaMemcpy(h, prof_buf, sizeof(h), cudaMemcpyDeviceToHost);

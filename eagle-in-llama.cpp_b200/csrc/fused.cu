@@ -216,8 +216,8 @@ int eb_resid_norm_quant(float *x, const float *part, int ks, const float *w, flo
     if (T == 0) return EB_OK;
     Parts p{part, ks, (int64_t)T * n, n};
     if (n % 256 == 0 && n <= 8192 && (!aq.qs || (aq.kq && aq.K == n)))
-        if (n <= 4096) eb_launch_pdl(resid_norm_quant_regs_kernel<512>, dim3(T), dim3(n / 8), 0, st, x, p, w, eps, n, aq, feat, bias, spec, node_feat, eb_gate());
-        else eb_launch_pdl(resid_norm_quant_regs_kernel<1024>, dim3(T), dim3(n / 8), 0, st, x, p, w, eps, n, aq, feat, bias, spec, node_feat, eb_gate());
+        if (n <= 4096) eb_launch_pdl_c(EB_PDL_RESID, resid_norm_quant_regs_kernel<512>, dim3(T), dim3(n / 8), 0, st, x, p, w, eps, n, aq, feat, bias, spec, node_feat, eb_gate());
+        else eb_launch_pdl_c(EB_PDL_RESID, resid_norm_quant_regs_kernel<1024>, dim3(T), dim3(n / 8), 0, st, x, p, w, eps, n, aq, feat, bias, spec, node_feat, eb_gate());
     else {
         if (spec) return eb_set_err(EB_ERR_UNSUPPORTED, "resid_norm_quant: node-feature scatter needs the register kernel (n %% 256 == 0, n <= 8192, K-quant grid)");
         resid_norm_quant_kernel<<<T, 256, (size_t)n * 4, st>>>(x, p, w, eps, n, aq, feat, bias);
@@ -239,7 +239,7 @@ int eb_rope_kv_store_fused(PlaneRef qp, PlaneRef kp, PlaneRef vp, float *q, void
     if (D > 256 || D % 4) return eb_set_err(EB_ERR_ARG, "rope: D=%d", D);
     const int E = n_head * D;
     const int threads = 512, gy = (int)cdiv(E / 4, threads);
-    eb_launch_pdl(rope_kv_store_fused_kernel, dim3(T, gy), dim3(threads), 0, st, parts_of(qp, T), parts_of(kp, T), parts_of(vp, T), q, (__half *)q16, (const float2 *)tab,
+    eb_launch_pdl_c(EB_PDL_ROPE, rope_kv_store_fused_kernel, dim3(T, gy), dim3(threads), 0, st, parts_of(qp, T), parts_of(kp, T), parts_of(vp, T), q, (__half *)q16, (const float2 *)tab,
                   (__half *)kc, (__half *)vc, ctl, D, n_head, pos, powf(freq_base, -2.0f / D), eb_gate());
     EB_CHECK_LAUNCH();
     return EB_OK;
@@ -248,7 +248,7 @@ int eb_swiglu_quant(PlaneRef gate, PlaneRef up, int n, int T, const ActQ &aq, cu
     if (T == 0) return EB_OK;
     const int per = aq.kq ? 256 : 128;
     if (n % per || aq.K != n) return eb_set_err(EB_ERR_ARG, "swiglu: n=%d", n);
-    eb_launch_pdl(swiglu_quant_kernel, dim3((unsigned)cdiv(n / per, 8), T), dim3(256), 0, st, parts_of(gate, T), parts_of(up, T), n, aq, eb_gate());
+    eb_launch_pdl_c(EB_PDL_SWIGLU, swiglu_quant_kernel, dim3((unsigned)cdiv(n / per, 8), T), dim3(256), 0, st, parts_of(gate, T), parts_of(up, T), n, aq, eb_gate());
     EB_CHECK_LAUNCH();
     return EB_OK;
 }

@@ -273,8 +273,8 @@ int eb_mmq_small_parts(int type, const void *W, int64_t N, int64_t K, const ActQ
     p.W = W; p.N = N; p.nb_total = N * nbr; p.nbr = nbr; p.n_rb = n_rb; p.spp = (int)cdiv(nbr, best); p.n_items = n_rb * best; p.a = a; p.out = planes; p.gate = eb_gate();
     *ks_out = best;
     const int grid = std::min(p.n_items, G);
-    if (type == EB_Q4_K) eb_launch_pdl(mmq_small_kernel<0>, dim3(grid), dim3(SM_THREADS), small_smem<0>(nbr), st, p);
-    else eb_launch_pdl(mmq_small_kernel<1>, dim3(grid), dim3(SM_THREADS), small_smem<1>(nbr), st, p);
+    if (type == EB_Q4_K) eb_launch_pdl_c(EB_PDL_GEMM, mmq_small_kernel<0>, dim3(grid), dim3(SM_THREADS), small_smem<0>(nbr), st, p);
+    else eb_launch_pdl_c(EB_PDL_GEMM, mmq_small_kernel<1>, dim3(grid), dim3(SM_THREADS), small_smem<1>(nbr), st, p);
     EB_CHECK_LAUNCH();
     return EB_OK;
 }

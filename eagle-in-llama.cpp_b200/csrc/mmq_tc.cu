@@ -669,10 +669,10 @@ int eb_mmq_tc_parts(int type, const void *W, int64_t N, int64_t K, const ActQ &a
     const int grid = std::min(p.n_items, eb_sm_count());
     if (type == EB_Q4_K) {
         if (want_prof) mmq_tc_kernel<0, true><<<grid, TC_THREADS, SMEM_BYTES, st>>>(tmW, tmB, tmBS, tmQH, tmSC, p);
-        else eb_launch_pdl(mmq_tc_kernel<0, false>, dim3(grid), dim3(TC_THREADS), SMEM_BYTES, st, tmW, tmB, tmBS, tmQH, tmSC, p);
+        else eb_launch_pdl_c(EB_PDL_GEMM, mmq_tc_kernel<0, false>, dim3(grid), dim3(TC_THREADS), SMEM_BYTES, st, tmW, tmB, tmBS, tmQH, tmSC, p);
     } else {
         if (want_prof) mmq_tc_kernel<1, true><<<grid, TC_THREADS, SMEM_BYTES, st>>>(tmW, tmB, tmBS, tmQH, tmSC, p);
-        else eb_launch_pdl(mmq_tc_kernel<1, false>, dim3(grid), dim3(TC_THREADS), SMEM_BYTES, st, tmW, tmB, tmBS, tmQH, tmSC, p);
+        else eb_launch_pdl_c(EB_PDL_GEMM, mmq_tc_kernel<1, false>, dim3(grid), dim3(TC_THREADS), SMEM_BYTES, st, tmW, tmB, tmBS, tmQH, tmSC, p);
     }
     EB_CHECK_LAUNCH();
     *ks_out = ks;

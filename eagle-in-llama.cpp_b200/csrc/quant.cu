@@ -147,7 +147,7 @@ int eb_concat_quant(const float *x, const float *hid, int E, const ActQ &a, cuda
     if (a.K != 2 * (int64_t)E || E % per) return eb_set_err(EB_ERR_ARG, "concat_quant: E=%d K=%lld", E, (long long)a.K);
     const int64_t warps = a.K / per * a.T;
     if (warps == 0) return EB_OK;
-    eb_launch_pdl(concat_quant_kernel, dim3((unsigned)cdiv(warps, 8)), dim3(256), 0, st, x, hid, E, a, spec, root_feat, node_feat, eb_gate());
+    eb_launch_pdl_c(EB_PDL_CONCAT, concat_quant_kernel, dim3((unsigned)cdiv(warps, 8)), dim3(256), 0, st, x, hid, E, a, spec, root_feat, node_feat, eb_gate());
     EB_CHECK_LAUNCH();
     return EB_OK;
 }

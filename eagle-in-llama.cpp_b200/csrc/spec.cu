@@ -200,11 +200,11 @@ int eb_top_k_impl(const float *logits, int rows, int V, int k, int32_t *ids, flo
     static const bool no_split = getenv("EB_NO_TOPK_SPLIT") != nullptr;
     if (scratch && !no_split && V >= TK_S * 64 && V <= TK_S * TK_THREADS * TK_PER && rows <= 128) {
         unsigned *cnt = (unsigned *)scratch; float *sv = (float *)((char *)scratch + 512); int *si = (int *)(sv + (size_t)rows * TK_S * 16);
-        eb_launch_pdl(top_k_split_kernel, dim3(rows, TK_S), dim3(TK_THREADS), 0, st, logits, ks, plane, V, k, ids, vals, probs, eb_gate(), sv, si, cnt);
+        eb_launch_pdl_c(EB_PDL_TOPK, top_k_split_kernel, dim3(rows, TK_S), dim3(TK_THREADS), 0, st, logits, ks, plane, V, k, ids, vals, probs, eb_gate(), sv, si, cnt);
         EB_CHECK_LAUNCH();
         return EB_OK;
     }
-    eb_launch_pdl(top_k_kernel, dim3(rows), dim3(1024), (size_t)V * 4, st, logits, ks, plane, V, k, ids, vals, probs, eb_gate());
+    eb_launch_pdl_c(EB_PDL_TOPK, top_k_kernel, dim3(rows), dim3(1024), (size_t)V * 4, st, logits, ks, plane, V, k, ids, vals, probs, eb_gate());
     EB_CHECK_LAUNCH();
     return EB_OK;
 }
@@ -441,7 +441,7 @@ int eb_spec_scatter_feat(const SpecState *s, const float *feat, float *node_feat
 }
 int eb_spec_expand(SpecState *s, const SpecCfg &c, const int32_t *cand_ids, const float *cand_p, cudaStream_t st) {
     if (c.n_branch * c.top_k > 256) return eb_set_err(EB_ERR_ARG, "expand: n_branch * top_k > 256");
-    eb_launch_pdl(tree_expand_kernel, dim3(1), dim3(256), 0, st, s, c, cand_ids, cand_p); EB_CHECK_LAUNCH(); return EB_OK;
+    eb_launch_pdl_c(EB_PDL_EXPAND, tree_expand_kernel, dim3(1), dim3(256), 0, st, s, c, cand_ids, cand_p); EB_CHECK_LAUNCH(); return EB_OK;
 }
 int eb_spec_accept(SpecState *s, const SpecCfg &c, const int32_t *best, cudaStream_t st) { accept_kernel<<<1, 32, 0, st>>>(s, c, best); EB_CHECK_LAUNCH(); return EB_OK; }
 int eb_spec_compact(SpecState *s, void *kc, void *vc, void *stage, int64_t layer_stride, int E, int L, int max_acc, cudaStream_t st) {
