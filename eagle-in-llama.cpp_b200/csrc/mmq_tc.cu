@@ -56,7 +56,7 @@ static_assert(S_W6 * W6_STAGE <= S_W * W_STAGE, "Q6_K weight ring must fit the Q
 constexpr int D6_STRIDE = 80, A6_OFF = 192, A6_HALF = 128, A6_SECOND = 64;
 
 struct TcArgs {
-    const float *dT; float *out; int64_t N; int nbr, T, npad, n_rb, n_items, spp; long long *prof;
+    const float *dT; float *out; int64_t N; int nbr, T, npad, n_rb, n_items, spp, early_trigger; long long *prof;
     uint32_t k_lo, k_hi, k_magic;    // 0x000f000f, 0x00f000f0, 0x64006400 passed as data: kept in registers so that (x & m) | c is ONE LOP3
     uint32_t k_q2;                   // 0x03000300
     const __half *w_d;               // Q6_K: per-block d plane [N][nbr]
@@ -439,7 +439,7 @@ mmq_tc_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ C
     tc::fence_after();
     const uint32_t tmem = *tmem_slot;
     if (threadIdx.x == 0) TCP_STAMP(1);
-    pdl_trigger();                                  // the next kernel may start its own prologue on SMs this grid has left
+    if (p.early_trigger) pdl_trigger();             // the next kernel may start its own prologue on SMs this grid has left
 
     if (warp < 4) {
         // ------------------------------------------------------------ weight producer (warp 0): the first tile goes out
@@ -649,6 +649,8 @@ int eb_mmq_tc_parts(int type, const void *W, int64_t N, int64_t K, const ActQ &a
     p.dT = a.dT; p.out = planes; p.N = N; p.nbr = nbr; p.T = a.T; p.npad = (a.T + 15) / 16 * 16;
     p.k_lo = 0x000f000fu; p.k_hi = 0x00f000f0u; p.k_magic = 0x64006400u; p.k_q2 = 0x03000300u; p.w_d = nullptr;
     p.n_rb = (int)cdiv(N, 128); p.spp = (int)cdiv(nbr, ks); p.n_items = p.n_rb * ks;
+    static const int early = getenv("EB_TC_LATE_TRIGGER") ? 0 : 1;
+    p.early_trigger = early;
     CUtensorMap tmW, tmB, tmBS, tmQH, tmSC;
     int rc;
     if (type == EB_Q4_K) {
