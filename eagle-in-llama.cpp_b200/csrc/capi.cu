@@ -44,7 +44,7 @@ int eb_device_init(int device) {
     EB_CUDA(cudaSetDevice(device));
     g_sm_count = prop.multiProcessorCount; g_device = device;
     int rc;
-    if ((rc = eb_mmq_init()) || (rc = eb_mmq_small_init()) || (rc = eb_mmq_tc_init()) || (rc = eb_fattn_tc_init()) || (rc = eb_fattn_init()) || (rc = eb_spec_init()) || (rc = eb_fused_init())) return rc;
+    if ((rc = eb_mmq_init()) || (rc = eb_mmq32_init()) || (rc = eb_mmq_small_init()) || (rc = eb_mmq_tc_init()) || (rc = eb_fattn_tc_init()) || (rc = eb_fattn_init()) || (rc = eb_spec_init()) || (rc = eb_fused_init())) return rc;
     return EB_OK;
 }
 int eb_device_sm_count(void) { return g_sm_count; }
@@ -188,7 +188,7 @@ int eb_bench_mul_mat_kernel(int type, int64_t N, int64_t K, int T, int n_bufs, i
     const int ks = use_mmq ? eb_mmq_pick_ksplit(type, N, K, T) : 1;
     const bool use_tc = eb_mmq_tc_supported(type, N, K, T);
     const bool use_small = T > 1 && eb_mmq_small_supported(type, N, K, T);
-    auto one = [&](int i) { int k2; return use_small ? eb_mmq_small_parts(type, w[i % n_bufs], N, K, a, partial, &k2, st) : use_tc ? eb_mmq_tc_parts(type, w[i % n_bufs], N, K, a, partial, &k2, st) : use_mmq ? eb_mmq(type, w[i % n_bufs], N, K, a, y, partial, ks, st) : eb_mmvq(type, w[i % n_bufs], N, K, a, y, st); };
+    auto one = [&](int i) { int k2; return use_small ? eb_mmq_small_parts(type, w[i % n_bufs], N, K, a, partial, &k2, st) : use_tc ? eb_mmq_tc_parts(type, w[i % n_bufs], N, K, a, partial, &k2, st) : use_mmq ? eb_mmq(type, w[i % n_bufs], N, K, a, y, partial, ks, st) : eb_mmq32_supported(type, N, K, T) ? eb_mmq32_parts(type, w[i % n_bufs], N, K, a, partial, &k2, st) : eb_mmvq(type, w[i % n_bufs], N, K, a, y, st); };
     for (int i = 0; i < 3 && !rc; i++) rc = one(i);
     if (!rc) {
         // the timed launches are replayed from a CUDA graph: host-side work per launch (tensor-map

@@ -61,7 +61,9 @@ int eb_set_err(int code, const char *fmt, ...);
 void eb_count_launch();
 long eb_launches_now(); void eb_launches_add(long n);   // kernels recorded in a CUDA graph are counted per replay
 int eb_sm_count();
-int eb_mmq_init(); int eb_fattn_init(); int eb_spec_init();
+int eb_mmq_init(); int eb_fattn_init(); int eb_spec_init(); int eb_mmq32_init();
+int eb_mmq32_supported(int type, int64_t N, int64_t K, int T);
+int eb_mmq32_parts(int type, const void *W, int64_t N, int64_t K, const struct ActQ &a, float *planes, int *ks_out, cudaStream_t st);
 
 static inline int64_t cdiv(int64_t a, int64_t b) { return (a + b - 1) / b; }
 

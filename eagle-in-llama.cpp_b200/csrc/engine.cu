@@ -177,6 +177,11 @@ int eb_mul_mat_impl(int type, const void *W, int64_t N, int64_t K, const float *
         return eb_splitk_reduce(partial, y, (int64_t)T * N, ks, st);
     }
     if (eb_mmq_supported(type, N, K, T)) return eb_mmq(type, W, N, K, a, y, partial, eb_mmq_pick_ksplit(type, N, K, T), st);
+    if (eb_mmq32_supported(type, N, K, T)) {
+        int ks = 1;
+        rc = eb_mmq32_parts(type, W, N, K, a, partial, &ks, st); if (rc) return rc;
+        return eb_splitk_reduce(partial, y, (int64_t)T * N, ks, st);
+    }
     return eb_mmvq(type, W, N, K, a, y, st);
 }
 
@@ -268,6 +273,7 @@ static int mm_parts(const DTensor &w, const ActQ &a, float *planes, int *ks, cud
     if (eb_mmq_tc_supported(w.type, w.rows, w.cols, a.T)) return eb_mmq_tc_parts(w.type, w.data, w.rows, w.cols, a, planes, ks, st);
     if (eb_mmq_small_supported(w.type, w.rows, w.cols, a.T)) return eb_mmq_small_parts(w.type, w.data, w.rows, w.cols, a, planes, ks, st);
     if (eb_mmq_supported(w.type, w.rows, w.cols, a.T)) return eb_mmq_parts(w.type, w.data, w.rows, w.cols, a, planes, ks, st);
+    if (eb_mmq32_supported(w.type, w.rows, w.cols, a.T)) return eb_mmq32_parts(w.type, w.data, w.rows, w.cols, a, planes, ks, st);
     *ks = 1;
     return eb_mmvq(w.type, w.data, w.rows, w.cols, a, planes, st);
 }
@@ -380,7 +386,10 @@ static int forward_dev(const eb_model *m, KVCache &kv, Workspace &w, const int32
             RC(eb_splitk_reduce(w.partial, w.logits, (int64_t)T * o.rows, kl_, st));
         } else if (eb_mmq_supported(o.type, o.rows, o.cols, T) && eb_mmq_pick_ksplit(o.type, o.rows, o.cols, T) > 1)
             RC(eb_mmq(o.type, o.data, o.rows, o.cols, al, w.logits, w.partial, eb_mmq_pick_ksplit(o.type, o.rows, o.cols, T), st));
-        else
+        else if (eb_mmq32_supported(o.type, o.rows, o.cols, T)) {
+            RC(eb_mmq32_parts(o.type, o.data, o.rows, o.cols, al, w.partial, &kl_, st));
+            RC(eb_splitk_reduce(w.partial, w.logits, (int64_t)T * o.rows, kl_, st));
+        } else
             RC(mm_parts(o, al, w.logits, &kl_, st));
     }
 #undef RC
