@@ -7,7 +7,7 @@
 // CTA = 4 warps x 16 weight rows = 64 rows, all T columns (NT tiles of 8), a K range of the split.  Activations (Q8_0 grid: int8
 // quants + f32 block scales) ride a double-buffered cp.async ring in shared memory, one chunk = 8 blocks = 256 values per column;
 // weights go HBM -> registers (one chunk ahead) in the device planes layout (common.cuh WPlanes).  Bound: HBM; the scale
-// application (4 I2F + 4 FMUL + 4 FFMA per MMA) keeps the issue slots at ~1.5x the HBM time for T = 65.
+// application is 2 FADD2 + 2 FMUL2 + 2 FFMA2 per MMA (magic-number accumulator init instead of I2F, packed f32x2 arithmetic).
 #include "common.cuh"
 #include <algorithm>
 
@@ -21,12 +21,26 @@ template <int FMT> struct L32 {
 __device__ __forceinline__ void cp16(void *smem, const void *gmem) {
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(smem)), "l"(gmem));
 }
-__device__ __forceinline__ void mma_s8_k32(int (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1) {
-    asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.s8.s8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
-                 : "+r"(c[0]), "+r"(c[1]), "+r"(c[2]), "+r"(c[3]) : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+__device__ __forceinline__ void cp4(void *smem, const void *gmem) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((uint32_t)__cvta_generic_to_shared(smem)), "l"(gmem));
 }
+// int8 MMA whose accumulator starts at the bit pattern of 1.5 * 2^23: the s32 result, read as f32, is 12582912 + dot exactly
+// (|dot| <= 32 * 127 * 128 < 2^22, Q4_0's 16x-scaled nibbles included), so the int -> float conversion is one FADD instead of an I2F per output.
+constexpr int MAGIC_I = 0x4B400000;
+__device__ __forceinline__ void mma_s8_k32(uint64_t &c01, uint64_t &c23, uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1) {
+    int c0, c1, c2, c3;
+    asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.s8.s8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%10,%10,%10,%10};"
+                 : "=r"(c0), "=r"(c1), "=r"(c2), "=r"(c3) : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1), "r"(MAGIC_I));
+    asm("mov.b64 %0, {%1,%2};" : "=l"(c01) : "r"(c0), "r"(c1));
+    asm("mov.b64 %0, {%1,%2};" : "=l"(c23) : "r"(c2), "r"(c3));
+}
+// packed f32x2 arithmetic (FADD2 / FMUL2 / FFMA2): two outputs per issue slot
+__device__ __forceinline__ uint64_t pack2(float lo, float hi) { uint64_t r; asm("mov.b64 %0, {%1,%2};" : "=l"(r) : "f"(lo), "f"(hi)); return r; }
+__device__ __forceinline__ uint64_t add2(uint64_t a, uint64_t b) { uint64_t r; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ uint64_t mul2(uint64_t a, uint64_t b) { uint64_t r; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ void fma2(uint64_t &acc, uint64_t a, uint64_t b) { asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(acc) : "l"(a), "l"(b)); }
 
-struct WChunk { uint32_t a[KC][4]; __half d0[KC], d1[KC]; };
+struct WChunk { uint32_t a[KC][4]; uint4 d0, d1; };      // d0 / d1: the chunk's 8 f16 block scales of rows g / g + 8, one 16-byte load each
 
 // A fragments of one chunk for rows r0 (= g) and r1 (= g + 8).  Q8_0: the lane takes 8 contiguous bytes per (row, block) —
 // k-slots of the MMA are permuted consistently on the B side, the dot over the 32 values is the same.  Q4_0: 4 bytes per
@@ -39,14 +53,20 @@ __device__ __forceinline__ void load_chunk(WChunk &w, const WPlanes &p, int64_t 
         if (FMT == 1) {
             const uint2 x = __ldg((const uint2 *)(p.q80_qs() + k0 * 32 + 8 * t)), y = __ldg((const uint2 *)(p.q80_qs() + k1 * 32 + 8 * t));
             w.a[bb][0] = x.x; w.a[bb][1] = y.x; w.a[bb][2] = x.y; w.a[bb][3] = y.y;
-            w.d0[bb] = p.q80_d()[k0]; w.d1[bb] = p.q80_d()[k1];
         } else {
             const uint32_t x = __ldg((const uint32_t *)(p.q40_qs() + k0 * 16 + 4 * t)), y = __ldg((const uint32_t *)(p.q40_qs() + k1 * 16 + 4 * t));
-            w.a[bb][0] = __vsubss4(x & 0x0F0F0F0Fu, 0x08080808u); w.a[bb][1] = __vsubss4(y & 0x0F0F0F0Fu, 0x08080808u);
-            w.a[bb][2] = __vsubss4((x >> 4) & 0x0F0F0F0Fu, 0x08080808u); w.a[bb][3] = __vsubss4((y >> 4) & 0x0F0F0F0Fu, 0x08080808u);
-            w.d0[bb] = p.q40_d()[k0]; w.d1[bb] = p.q40_d()[k1];
+            // nibble n in the high half of a byte, top bit flipped, is the s8 value 16 * (n - 8): one LOP3 per register (plus a
+            // shift for the low nibbles); the factor 16 is taken out of the block scale (exact: a power of two)
+            w.a[bb][0] = ((x << 4) & 0xF0F0F0F0u) ^ 0x80808080u; w.a[bb][1] = ((y << 4) & 0xF0F0F0F0u) ^ 0x80808080u;
+            w.a[bb][2] = (x & 0xF0F0F0F0u) ^ 0x80808080u; w.a[bb][3] = (y & 0xF0F0F0F0u) ^ 0x80808080u;
         }
     }
+    const __half *dp = FMT == 1 ? p.q80_d() : p.q40_d();
+    w.d0 = __ldg((const uint4 *)(dp + r0 * nbr + b0)); w.d1 = __ldg((const uint4 *)(dp + r1 * nbr + b0));
+}
+__device__ __forceinline__ float scale_of(const uint4 &v, int bb) {
+    const uint32_t w = bb < 2 ? v.x : bb < 4 ? v.y : bb < 6 ? v.z : v.w;
+    return __half2float(__ushort_as_half((unsigned short)((bb & 1) ? (w >> 16) : (w & 0xFFFFu))));
 }
 
 template <int FMT, int NT>
@@ -67,15 +87,16 @@ __global__ void __launch_bounds__(128) mmq32_kernel(WPlanes wp, int64_t N, int n
             const int col = i >> 4, pc = i & 15;
             cp16(st + col * PITCH + pc * 16, a.qs + (int64_t)col * a.K + (int64_t)c * (KC * 32) + pc * 16);
         }
-        for (int i = tid; i < a.T * 2; i += 128) {                         // block scales: KC floats = 2 pieces per column
-            const int col = i >> 1, pc = i & 1;
-            cp16(st + TP * PITCH + col * (KC * 4) + pc * 16, a.d + (int64_t)col * nbr + c * KC + pc * 4);
+        for (int i = tid; i < a.T * KC; i += 128) {                        // block scales, transposed to [block][col]: (x0, x1) is one 8-byte load
+            const int col = i >> 3, bb = i & 7;
+            cp4(st + TP * PITCH + (bb * TP + col) * 4, a.d + (int64_t)col * nbr + c * KC + bb);
         }
         asm volatile("cp.async.commit_group;");
     };
-    float acc[NT][4];
+    uint64_t acc01[NT], acc23[NT];                                          // (row g: cols 2t, 2t+1), (row g + 8: same cols)
 #pragma unroll
-    for (int nt = 0; nt < NT; nt++) { acc[nt][0] = acc[nt][1] = acc[nt][2] = acc[nt][3] = 0.f; }
+    for (int nt = 0; nt < NT; nt++) { acc01[nt] = acc23[nt] = pack2(0.f, 0.f); }
+    const uint64_t neg_magic = pack2(-12582912.f, -12582912.f);
     WChunk nxt;
     if (c0 < c1) { stage_act(0, c0); load_chunk<FMT>(nxt, wp, r0, r1, nbr, c0 * KC, t); }
     for (int c = c0; c < c1; c++) {
@@ -88,18 +109,20 @@ __global__ void __launch_bounds__(128) mmq32_kernel(WPlanes wp, int64_t N, int n
         const float *dx = (const float *)(st + TP * PITCH);
 #pragma unroll
         for (int bb = 0; bb < KC; bb++) {
-            const float dw0 = __half2float(cur.d0[bb]), dw1 = __half2float(cur.d1[bb]);
+            constexpr float WS = FMT == 0 ? 0.0625f : 1.f;
+            const float dw0f = scale_of(cur.d0, bb) * WS, dw1f = scale_of(cur.d1, bb) * WS;
+            const uint64_t dw0 = pack2(dw0f, dw0f), dw1 = pack2(dw1f, dw1f);
 #pragma unroll
             for (int nt = 0; nt < NT; nt++) {
                 const uint8_t *br = st + (nt * 8 + g) * PITCH + bb * 32;
                 uint32_t b0, b1;
                 if (FMT == 1) { const uint2 v = *(const uint2 *)(br + 8 * t); b0 = v.x; b1 = v.y; }
                 else { b0 = *(const uint32_t *)(br + 4 * t); b1 = *(const uint32_t *)(br + 16 + 4 * t); }
-                int cc[4] = {0, 0, 0, 0};
-                mma_s8_k32(cc, cur.a[bb][0], cur.a[bb][1], cur.a[bb][2], cur.a[bb][3], b0, b1);
-                const float x0 = dx[(nt * 8 + 2 * t) * KC + bb], x1 = dx[(nt * 8 + 2 * t + 1) * KC + bb];
-                acc[nt][0] += (float)cc[0] * (dw0 * x0); acc[nt][1] += (float)cc[1] * (dw0 * x1);
-                acc[nt][2] += (float)cc[2] * (dw1 * x0); acc[nt][3] += (float)cc[3] * (dw1 * x1);
+                uint64_t c01, c23;
+                mma_s8_k32(c01, c23, cur.a[bb][0], cur.a[bb][1], cur.a[bb][2], cur.a[bb][3], b0, b1);
+                const uint64_t x01 = *(const uint64_t *)(dx + bb * TP + nt * 8 + 2 * t);
+                fma2(acc01[nt], add2(c01, neg_magic), mul2(dw0, x01));
+                fma2(acc23[nt], add2(c23, neg_magic), mul2(dw1, x01));
             }
         }
         __syncthreads();                                                    // the stage is overwritten two iterations later
@@ -108,8 +131,11 @@ __global__ void __launch_bounds__(128) mmq32_kernel(WPlanes wp, int64_t N, int n
 #pragma unroll
     for (int nt = 0; nt < NT; nt++) {
         const int col = nt * 8 + 2 * t;
-        if (col < a.T) { if (row0 < N) o[(int64_t)col * N + row0] = acc[nt][0]; if (row0 + 8 < N) o[(int64_t)col * N + row0 + 8] = acc[nt][2]; }
-        if (col + 1 < a.T) { if (row0 < N) o[(int64_t)(col + 1) * N + row0] = acc[nt][1]; if (row0 + 8 < N) o[(int64_t)(col + 1) * N + row0 + 8] = acc[nt][3]; }
+        float v0, v1, v2, v3;
+        asm("mov.b64 {%0,%1}, %2;" : "=f"(v0), "=f"(v1) : "l"(acc01[nt]));
+        asm("mov.b64 {%0,%1}, %2;" : "=f"(v2), "=f"(v3) : "l"(acc23[nt]));
+        if (col < a.T) { if (row0 < N) o[(int64_t)col * N + row0] = v0; if (row0 + 8 < N) o[(int64_t)col * N + row0 + 8] = v2; }
+        if (col + 1 < a.T) { if (row0 < N) o[(int64_t)(col + 1) * N + row0] = v1; if (row0 + 8 < N) o[(int64_t)(col + 1) * N + row0 + 8] = v3; }
     }
 }
 
@@ -146,7 +172,9 @@ int eb_mmq32_parts(int type, const void *W, int64_t N, int64_t K, const ActQ &a,
     const int64_t rb = cdiv(N, 64);
     // enough CTAs to fill the machine ~3x over (each CTA walks its chunks serially), at least 2 chunks per split, at most 8 planes
     int ks = (int)std::min<int64_t>(8, std::max<int64_t>(1, cdiv(3 * (int64_t)eb_sm_count(), rb)));
+    if (n_chunks >= 8) ks = std::max(ks, 2);            // measured: two K halves beat one pass even at 500 row blocks (lm_head 98.6 -> 83.7 us)
     ks = std::max(1, std::min(ks, n_chunks / 2));
+    if (const char *e = getenv("EB_MMQ32_KS")) ks = std::max(1, std::min(std::min(8, n_chunks), atoi(e)));   // tuning sweeps
     int cps = (int)cdiv(n_chunks, ks); ks = (int)cdiv(n_chunks, cps);
     *ks_out = ks;
     WPlanes wp{(const uint8_t *)W, N * nbr};
