@@ -257,8 +257,21 @@ __global__ void splitk_reduce_kernel(const float *__restrict__ partial, float *_
     *(float4 *)(y + i) = s;
 }
 
+// the same sum, one element per thread: n % 4 != 0 (ragged operator-layer shapes) leaves the planes unaligned for float4
+__global__ void splitk_reduce_scalar_kernel(const float *__restrict__ partial, float *__restrict__ y, int64_t n, int ksplit) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float s = partial[i];
+    for (int k = 1; k < ksplit; k++) s += partial[(int64_t)k * n + i];
+    y[i] = s;
+}
+
 int eb_splitk_reduce(const float *partial, float *y, int64_t n, int ksplit, cudaStream_t st) {
-    if (n % 4) return eb_set_err(EB_ERR_ARG, "splitk_reduce: n %% 4");
+    if (n % 4) {
+        splitk_reduce_scalar_kernel<<<(unsigned)cdiv(n, 256), 256, 0, st>>>(partial, y, n, ksplit);
+        EB_CHECK_LAUNCH();
+        return EB_OK;
+    }
     splitk_reduce_kernel<<<(unsigned)cdiv(n / 4, 256), 256, 0, st>>>(partial, y, n, ksplit);
     EB_CHECK_LAUNCH();
     return EB_OK;

@@ -104,6 +104,23 @@ def test_mul_mat_draft_shapes(eb, t, N, K, T):
     assert rel_max(got, want) < 2e-5
 
 
+@pytest.mark.parametrize("t", [po.Q4_0, po.Q8_0])
+@pytest.mark.parametrize("T", [2, 17, 40, 65, 72, 128])
+def test_mul_mat_32block_gemm_ragged(eb, t, T):
+    """the int8 tensor-core GEMM for the 32-element block formats (mmq32.cu): K = 11008 (43 chunks of 8 blocks: uneven K
+    splits, a last split of one chunk), a row count that is not a multiple of the 64-row CTA tile or the 16-row warp tile,
+    every column-tile instantiation (T 2..128), random quant bytes (the -128 corner included), zero activation blocks."""
+    rng = np.random.default_rng(7 * t + T)
+    N, K = 1003, 11008
+    raw = fx.random_blocks(t, N * K, rng)
+    X = rng.normal(0, 1, (T, K)).astype(np.float32)
+    X[1, 256:512] = 0; X[T - 1, :32] = 0
+    got = eb.mul_mat(eb.Weights(t, raw, N, K), X)
+    want = po.oracle().mul_mat(t, raw, N, K, X)
+    assert got.shape == want.shape
+    assert rel_max(got, want) < 2e-5
+
+
 def test_mul_mat_linearity_full_size(eb):
     """size-independent property at the BASELINE shape (lm_head 32000 x 4096, Q6_K, T = 65):
     a column that is an exact copy of another must give identical outputs, zero columns zero."""
