@@ -152,8 +152,12 @@ int dispatch32(const WPlanes &wp, int64_t N, int nbr, const ActQ &a, float *plan
     const int nt = (a.T + 7) / 8;
     if (nt <= 1) return launch32<FMT, 1>(wp, N, nbr, a, planes, ks, cps, st);
     if (nt <= 2) return launch32<FMT, 2>(wp, N, nbr, a, planes, ks, cps, st);
+    if (nt <= 3) return launch32<FMT, 3>(wp, N, nbr, a, planes, ks, cps, st);      // 16-node tree + root
     if (nt <= 4) return launch32<FMT, 4>(wp, N, nbr, a, planes, ks, cps, st);
-    if (nt <= 9) return launch32<FMT, 9>(wp, N, nbr, a, planes, ks, cps, st);
+    if (nt <= 5) return launch32<FMT, 5>(wp, N, nbr, a, planes, ks, cps, st);      // 32-node tree + root
+    if (nt <= 7) return launch32<FMT, 7>(wp, N, nbr, a, planes, ks, cps, st);
+    if (nt <= 9) return launch32<FMT, 9>(wp, N, nbr, a, planes, ks, cps, st);      // 64-node tree + root
+    if (nt <= 12) return launch32<FMT, 12>(wp, N, nbr, a, planes, ks, cps, st);
     return launch32<FMT, 16>(wp, N, nbr, a, planes, ks, cps, st);
 }
 
@@ -185,7 +189,9 @@ int eb_mmq32_parts(int type, const void *W, int64_t N, int64_t K, const ActQ &a,
 template <int FMT, int NT> static int init32() { EB_CUDA(cudaFuncSetAttribute(mmq32_kernel<FMT, NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem32<FMT, NT>())); return EB_OK; }
 int eb_mmq32_init() {
     int rc;
-    if ((rc = init32<0, 1>()) || (rc = init32<0, 2>()) || (rc = init32<0, 4>()) || (rc = init32<0, 9>()) || (rc = init32<0, 16>())) return rc;
-    if ((rc = init32<1, 1>()) || (rc = init32<1, 2>()) || (rc = init32<1, 4>()) || (rc = init32<1, 9>()) || (rc = init32<1, 16>())) return rc;
+    if ((rc = init32<0, 1>()) || (rc = init32<0, 2>()) || (rc = init32<0, 3>()) || (rc = init32<0, 4>()) || (rc = init32<0, 5>()) || (rc = init32<0, 7>()) ||
+        (rc = init32<0, 9>()) || (rc = init32<0, 12>()) || (rc = init32<0, 16>())) return rc;
+    if ((rc = init32<1, 1>()) || (rc = init32<1, 2>()) || (rc = init32<1, 3>()) || (rc = init32<1, 4>()) || (rc = init32<1, 5>()) || (rc = init32<1, 7>()) ||
+        (rc = init32<1, 9>()) || (rc = init32<1, 12>()) || (rc = init32<1, 16>())) return rc;
     return EB_OK;
 }
