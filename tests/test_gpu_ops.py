@@ -121,12 +121,14 @@ def test_mul_mat_32block_gemm_ragged(eb, t, T):
     assert rel_max(got, want) < 2e-5
 
 
-def test_mul_mat_linearity_full_size(eb):
-    """size-independent property at the BASELINE shape (lm_head 32000 x 4096, Q6_K, T = 65):
-    a column that is an exact copy of another must give identical outputs, zero columns zero."""
+@pytest.mark.parametrize("t", [po.Q6_K, po.Q8_0, po.Q4_0])
+def test_mul_mat_linearity_full_size(eb, t):
+    """size-independent property at the BASELINE shape (lm_head 32000 x 4096, T = 65; Q6_K for config 2 on the tcgen05 GEMM,
+    Q8_0 / Q4_0 for configs 3 / 1 on the int8 mma.sync GEMM): a column that is an exact copy of another must give identical
+    outputs, zero columns zero."""
     rng = np.random.default_rng(9)
     N, K, T = 32000, 4096, 65
-    w = eb.Weights(po.Q6_K, fx.random_blocks(po.Q6_K, N * K, rng), N, K)
+    w = eb.Weights(t, fx.random_blocks(t, N * K, rng), N, K)
     X = rng.normal(0, 1, (T, K)).astype(np.float32)
     X[10] = X[3]; X[64] = X[3]; X[20] = 0
     Y = eb.mul_mat(w, X)
