@@ -82,6 +82,7 @@ def lib():
         "eb_session_forward": ([vp, i32, vp, vp, vp, vp, i32, vp, vp], i32),
         "eb_tree_bits_from_batch": ([i32, vp, vp, vp, vp], i32),
         "eb_session_forward_batch": ([vp, i32, vp, vp, vp, vp, vp, i32, vp, vp], i32),
+        "eb_session_set_tap": ([vp, vp, sz], i32), "eb_session_tap_state": ([vp, C.POINTER(sz), C.POINTER(i32)], i32),
         "eb_session_commit": ([vp, i32, i32], i32), "eb_session_n_past": ([vp, i32], i32),
         "eb_session_synth_kv": ([vp, i32, C.c_uint64], i32), "eb_session_set_root": ([vp, C.c_int32, vp], i32),
         "eb_session_round": ([vp, C.POINTER(RoundResult)], i32),
@@ -425,6 +426,30 @@ class Session:
         feat = np.empty((T, m.E), np.float32)
         _ck(lib().eb_session_forward_batch(self.h, model, _hp(tokens), _hp(pos), _hp(n_seq), C.cast(ptrs, C.c_void_p), _hp(hid), T, _hp(logits), _hp(feat)))
         return logits, feat
+
+    def forward_tapped(self, model, tokens, pos, parent=None, hidden=None):
+        """forward + the int8 activation plane of every quantisation site (eb_session_set_tap: the counterpart of llama.cpp's
+        cb_eval callback).  -> logits, feat, [plane [T][K] int8, ...] in site order."""
+        m = self.head if model else self.target
+        T = int(np.asarray(tokens).size)
+        cap = T * ((2 * m.E if m.is_eagle else 0) + m.L * (3 * m.E + m.F) + m.E) + 1024
+        buf = DeviceBuffer(cap)
+        _ck(lib().eb_session_set_tap(self.h, buf.ptr, cap))
+        try:
+            logits, feat = self.forward(model, tokens, pos, parent=parent, hidden=hidden)
+            n, sites = C.c_size_t(), C.c_int()
+            _ck(lib().eb_session_tap_state(self.h, C.byref(n), C.byref(sites)))
+            raw = np.empty(n.value, np.int8)
+            _ck(lib().eb_download(_hp(raw), buf.ptr, n.value, None))
+        finally:
+            _ck(lib().eb_session_set_tap(self.h, None, 0))
+            buf.free()
+        widths = ([2 * m.E] if m.is_eagle else []) + [m.E, m.E, m.E, m.F] * m.L + [m.E]
+        assert sites.value == len(widths) and n.value == T * sum(widths), (sites.value, len(widths), n.value)
+        planes, off = [], 0
+        for w in widths:
+            planes.append(raw[off:off + T * w].reshape(T, w)); off += T * w
+        return logits, feat, planes
 
     def commit(self, model, n):
         _ck(lib().eb_session_commit(self.h, model, n))

@@ -142,12 +142,23 @@ int eb_soft_max_ext(const float *x, const void *mask, int mask_type, int64_t mas
 int eb_concat2(const float *a, const float *b, float *y, int E, int T, void *st) { NEED_DEV(); return eb_concat2_impl(a, b, y, E, T, S(st)); }
 int eb_cpy_f32_f16(const float *x, void *y, int64_t n, void *st) { NEED_DEV(); return eb_cpy_f32_f16_impl(x, y, n, S(st)); }
 
-size_t eb_flash_attn_ws_size(int T, int H, int D, int n_kv) { return std::max(eb_flash_attn_ws_size_impl(T, H, D, n_kv), eb_fattn_tc_ws_size(T, H, n_kv)); }
+size_t eb_flash_attn_ws_size(int T, int H, int D, int n_kv) { T = std::min(T, 128); return std::max(eb_flash_attn_ws_size_impl(T, H, D, n_kv), eb_fattn_tc_ws_size(T, H, n_kv)); }
 int eb_flash_attn(const float *q, const void *k, const void *v, int64_t kv_stride, const void *mask, int64_t mask_stride,
                   const uint32_t *tree_bits, int n_prefix, int T, int H, int D, int n_kv, float scale, float *out, void *ws, void *st) {
     NEED_DEV();
     if (!mask && tree_bits && eb_fattn_tc_supported(T, D) && kv_stride % 8 == 0)      // compact tree mask: tcgen05 kernel
         return eb_fattn_tc_f32q(q, k, v, kv_stride, tree_bits, n_prefix, n_kv, T, H, scale, out, ws, S(st));
+    if (mask && T > 128) {
+        // prompt-sized batches (llama_decode_impl_init, R/src/llama.cpp:10512: T = 512): query rows in chunks of one verify tile,
+        // each with its own mask rows; the chunks run back to back on the stream and share the workspace
+        for (int t0 = 0; t0 < T; t0 += 128) {
+            const int tc = std::min(128, T - t0);
+            int rc = eb_flash_attn_impl(q + (size_t)t0 * H * D, k, v, kv_stride, (const __half *)mask + (size_t)t0 * mask_stride, mask_stride, nullptr, 0,
+                                        tc, H, D, n_kv, scale, out + (size_t)t0 * H * D, ws, S(st));
+            if (rc) return rc;
+        }
+        return EB_OK;
+    }
     return eb_flash_attn_impl(q, k, v, kv_stride, mask, mask_stride, tree_bits, n_prefix, T, H, D, n_kv, scale, out, ws, S(st));
 }
 int eb_top_k(const float *logits, int rows, int V, int k, int32_t *ids, float *vals, float *probs, void *st) { NEED_DEV(); return eb_top_k_impl(logits, rows, V, k, ids, vals, probs, S(st), 1, 0, rows <= 128 ? eb_top_k_default_scratch() : nullptr); }

@@ -267,7 +267,16 @@ extern "C" void eb_session_free(eb_session *s) {
 // All inputs are device-resident: tokens/pos/bits [T], hidden [T][E] (head), ctl (n_prefix,
 // node_base, n_tree).  K/V rows go to cells n_prefix + node_base + t.
 // GEMM into split-K planes (T > 8, K-quants) or a single plane (matvec path)
-static bool skip_class(const char *name);
+// EB_SKIP=resid,rope,attn,swiglu,gemm elides a kernel class to measure its marginal in-graph cost (results are garbage).  The knob
+// exists only in a library built with -DEB_TIMING_KNOBS (tools/skip_sweep.sh builds one); the shipped .so has no such switch.
+#ifdef EB_TIMING_KNOBS
+static bool skip_class(const char *name) {
+    static const char *e = getenv("EB_SKIP");
+    return e && strstr(e, name);
+}
+#else
+static constexpr bool skip_class(const char *) { return false; }
+#endif
 static int mm_parts(const DTensor &w, const ActQ &a, float *planes, int *ks, cudaStream_t st) {
     if (skip_class("gemm")) { *ks = 1; return EB_OK; }
     if (eb_mmq_tc_supported(w.type, w.rows, w.cols, a.T)) return eb_mmq_tc_parts(w.type, w.data, w.rows, w.cols, a, planes, ks, st);
@@ -277,17 +286,26 @@ static int mm_parts(const DTensor &w, const ActQ &a, float *planes, int *ks, cud
     *ks = 1;
     return eb_mmvq(w.type, w.data, w.rows, w.cols, a, planes, st);
 }
-// EB_SKIP=resid,rope,attn,swiglu,gemm: timing experiments only (results are garbage): the marginal in-graph cost of a kernel class
-static bool skip_class(const char *name) {
-    static const char *e = getenv("EB_SKIP");
-    return e && strstr(e, name);
-}
 static int grid_of(const DTensor &w) { return w.type == EB_Q4_K || w.type == EB_Q6_K; }
+
+// Activation tap (eb_session_set_tap): the analogue of the reference's per-node eval callback (cparams.cb_eval ->
+// ggml_backend_sched_set_eval_callback, R/src/llama.cpp:9562): after every activation-quantisation site of an eager forward the
+// int8 plane [T][K] that the following GEMM(s) consume is appended to the caller's device buffer.  Site order per layer: attn_norm
+// (input of wq|wk|wv), attention output (input of wo), ffn_norm (input of gate|up), SwiGLU (input of ffn_down); then output_norm
+// (input of the lm_head) when logits are requested; the EAGLE head starts with the [embd | hidden] input of fc.
+static int tap_site(ActTap *tap, const ActQ &a, cudaStream_t st) {
+    if (!tap || !tap->buf || !a.qs) return EB_OK;
+    const size_t n = (size_t)a.T * a.K;
+    if (tap->off + n > tap->cap) return eb_set_err(EB_ERR_ARG, "tap buffer too small (%zu + %zu > %zu)", tap->off, n, tap->cap);
+    EB_CUDA(cudaMemcpyAsync(tap->buf + tap->off, a.qs, n, cudaMemcpyDeviceToDevice, st));
+    tap->off += n; tap->sites++;
+    return EB_OK;
+}
 
 static int forward_dev(const eb_model *m, KVCache &kv, Workspace &w, const int32_t *tokens, const int32_t *pos, const uint32_t *bits,
                        const float *hidden, const FwdCtl *ctl, int T, bool want_logits, cudaStream_t st, int *logit_ks = nullptr,
                        const SpecState *spec = nullptr, const float *root_feat = nullptr, float *node_feat = nullptr,
-                       const int *gate_fwd = nullptr, const int *gate_lm = nullptr) {
+                       const int *gate_fwd = nullptr, const int *gate_lm = nullptr, ActTap *tap = nullptr) {
     // gate_fwd / gate_lm (draft levels of a captured round): device words that switch the whole forward / its lm_head off
     // when the tree stopped growing (common.cuh "launch gate"); the caller clears the gate after the call
     eb_gate_set(gate_fwd);
@@ -314,6 +332,7 @@ static int forward_dev(const eb_model *m, KVCache &kv, Workspace &w, const int32
         const DTensor &fc = m->g[EB_T_FC];
         ActQ ac = eb_actq_carve(w.actq2, grid_of(fc), 2 * E, T);
         RC(eb_concat_quant(w.x, hidden, E, ac, st, spec, root_feat, node_feat));
+        RC(tap_site(tap, ac, st));
         RC(mm_parts(fc, ac, w.pup, &pend_ks, st));
         pend = w.pup; pend_bias = (const float *)m->g[EB_T_FC_BIAS].data;
     }
@@ -326,6 +345,7 @@ static int forward_dev(const eb_model *m, KVCache &kv, Workspace &w, const int32
         ActQ a = eb_actq_carve(w.actq, gq, E, T);
         if (!skip_class("resid")) RC(eb_resid_norm_quant(w.x, pend, pend_ks, (const float *)t[EB_L_ATTN_NORM].data, m->eps, E, T, a, nullptr, st, pend_bias));
         pend_bias = nullptr;
+        RC(tap_site(tap, a, st));
         if (grid_of(t[EB_L_WK]) != gq || grid_of(t[EB_L_WV]) != gq) return eb_set_err(EB_ERR_UNSUPPORTED, "layer %d: wq/wk/wv mix K-quant and 32-block formats", l);
         const LayerFuse &fu = m->fuse[l];
         PlaneRef rq, rk, rv;
@@ -346,6 +366,7 @@ static int forward_dev(const eb_model *m, KVCache &kv, Workspace &w, const int32
         else if (fa_tc) RC(eb_fattn_tc(w.q16, kc, vc, E, kv.n_ctx, bits, ctl, 0, 0, T, H, 1.0f / sqrtf((float)D), w.att, w.fa_ws, st, &ao, &att_quantized));
         else RC(eb_flash_attn_ctl(w.q, kc, vc, E, bits, ctl, T, H, D, kv.n_ctx, 1.0f / sqrtf((float)D), w.att, w.fa_ws, st));
         if (!att_quantized) RC(eb_quantize_act(w.att, ao, st));
+        RC(tap_site(tap, ao, st));
         int ko_;
         RC(mm_parts(t[EB_L_WO], ao, w.po, &ko_, st));
         // ffn_inp = wo.att + x ; cur = rms_norm(ffn_inp) * ffn_norm -> grid of up/gate
@@ -353,6 +374,7 @@ static int forward_dev(const eb_model *m, KVCache &kv, Workspace &w, const int32
         if (grid_of(t[EB_L_GATE]) != gu) return eb_set_err(EB_ERR_UNSUPPORTED, "layer %d: ffn_up/ffn_gate mix formats", l);
         ActQ af = eb_actq_carve(w.actq, gu, E, T);
         if (!skip_class("resid")) RC(eb_resid_norm_quant(w.x, w.po, ko_, (const float *)t[EB_L_FFN_NORM].data, m->eps, E, T, af, nullptr, st));
+        RC(tap_site(tap, af, st));
         PlaneRef rg, ru;
         {
             int ks_;
@@ -367,6 +389,7 @@ static int forward_dev(const eb_model *m, KVCache &kv, Workspace &w, const int32
         }
         ActQ ad = eb_actq_carve(w.actq2, grid_of(t[EB_L_DOWN]), F, T);
         if (!skip_class("swiglu")) RC(eb_swiglu_quant(rg, ru, F, T, ad, st));
+        RC(tap_site(tap, ad, st));
         RC(mm_parts(t[EB_L_DOWN], ad, w.pq, &pend_ks, st));       // pq is free again: holds the down planes
         pend = w.pq;
     }
@@ -375,6 +398,7 @@ static int forward_dev(const eb_model *m, KVCache &kv, Workspace &w, const int32
     ActQ al = eb_actq_carve(w.actq, grid_of(o), E, T);
     if (!want_logits) al.qs = nullptr;
     RC(eb_resid_norm_quant(w.x, pend, pend_ks, (const float *)m->g[EB_T_OUTPUT_NORM].data, m->eps, E, T, al, w.feat, st, nullptr, spec, node_feat));
+    RC(tap_site(tap, al, st));
     if (gate_lm) eb_gate_set(gate_lm);
     if (want_logits && logit_ks) {
         // the caller's top-k / argmax sums the lm_head's split-K planes [ks][T][V] (w.partial) itself
@@ -449,7 +473,8 @@ static int forward_bits(eb_session *s, int model, const int32_t *h_tokens, const
         if (!h_hidden) return eb_set_err(EB_ERR_ARG, "forward: the head needs hidden input");
         EB_CUDA(cudaMemcpyAsync(w.hidden, h_hidden, (size_t)T * m->E * 4, cudaMemcpyHostToDevice, s->st));
     }
-    rc = forward_dev(m, kv, w, w.tokens, w.pos, w.bits, w.hidden, w.ctl, T, h_logits != nullptr, s->st); if (rc) return rc;
+    ActTap *tap = s->tap.buf ? &s->tap : nullptr;
+    rc = forward_dev(m, kv, w, w.tokens, w.pos, w.bits, w.hidden, w.ctl, T, h_logits != nullptr, s->st, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, tap); if (rc) return rc;
     if (h_logits) EB_CUDA(cudaMemcpyAsync(h_logits, w.logits, (size_t)T * m->V * 4, cudaMemcpyDeviceToHost, s->st));
     if (h_feat) EB_CUDA(cudaMemcpyAsync(h_feat, w.feat, (size_t)T * m->E * 4, cudaMemcpyDeviceToHost, s->st));
     EB_CUDA(cudaStreamSynchronize(s->st));
@@ -477,6 +502,16 @@ extern "C" int eb_session_forward_batch(eb_session *s, int model, const int32_t 
     uint32_t bits[128 * 4];
     const int rc = eb_tree_bits_from_batch(T, h_pos, n_seq_id, seq_id, bits); if (rc) return rc;
     return forward_bits(s, model, h_tokens, h_pos, bits, h_hidden, T, h_logits, h_feat);
+}
+
+extern "C" int eb_session_set_tap(eb_session *s, void *d_buf, size_t bytes) {
+    s->tap.buf = (int8_t *)d_buf; s->tap.cap = d_buf ? bytes : 0; s->tap.off = 0; s->tap.sites = 0;
+    return EB_OK;
+}
+extern "C" int eb_session_tap_state(const eb_session *s, size_t *bytes_written, int *n_sites) {
+    if (bytes_written) *bytes_written = s->tap.off;
+    if (n_sites) *n_sites = s->tap.sites;
+    return EB_OK;
 }
 
 __global__ void set_n_past_kernel(SpecState *s, int n) { s->n_past = n; }

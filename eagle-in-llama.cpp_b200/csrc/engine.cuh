@@ -30,7 +30,10 @@ struct Workspace {
     __half *q16;                                  // f16 copy of the rotated queries (TMA source of the tcgen05 attention)
 };
 
+struct ActTap { int8_t *buf = nullptr; size_t cap = 0, off = 0; int sites = 0; };
+
 struct eb_session {
+    ActTap tap;
     eb_model *tgt, *head; eb_session_params p; SpecCfg cfg;
     KVCache kv_t, kv_h; Workspace ws_t, ws_h;
     SpecState *state; float *root_feat, *node_feat; int32_t *cand_ids; float *cand_vals, *cand_p; void *topk_scr; int32_t *best;

@@ -133,12 +133,12 @@ static bool b200_dev_supports_op(ggml_backend_dev_t, const ggml_tensor *op) {
             return b->type == GGML_TYPE_F32 && op->type == GGML_TYPE_F32 && a->nb[0] == ggml_type_size(a->type) && b->nb[0] == 4 && a->ne[3] == 1 && b->ne[3] == 1 &&
                    a->ne[2] >= 1 && b->ne[2] % a->ne[2] == 0 && ggml_is_contiguous(op);
         return b200_weight_type(a->type) && ggml_is_contiguous(a) && a->ne[2] == 1 && a->ne[3] == 1 && b->type == GGML_TYPE_F32 && ggml_is_contiguous(b) &&
-               b->ne[2] == 1 && b->ne[3] == 1 && a->ne[0] % (a->type == GGML_TYPE_Q4_K || a->type == GGML_TYPE_Q6_K ? 256 : 32) == 0 && op->type == GGML_TYPE_F32;
+               b->ne[2] == 1 && b->ne[3] == 1 && a->ne[0] % (a->type == GGML_TYPE_Q4_K || a->type == GGML_TYPE_Q6_K ? 256 : 128) == 0 && op->type == GGML_TYPE_F32;   // 128: the Q8_0-grid quantiser works on 128-value groups
     case GGML_OP_FLASH_ATTN_EXT: {
         const ggml_tensor *v = op->src[2], *m = op->src[3];
         float max_bias = op_f32(op, 1), softcap = op_f32(op, 2);
         return a->ne[0] == 128 && fa_q_layout_ok(a) && fa_kv_layout_ok(b, a) && fa_kv_layout_ok(v, a) && b->nb[1] == v->nb[1] && b->ne[1] == v->ne[1] && m && m->type == GGML_TYPE_F16 &&
-               ggml_is_contiguous(m) && m->ne[0] == b->ne[1] && max_bias == 0.0f && softcap == 0.0f && a->ne[1] <= 128;
+               ggml_is_contiguous(m) && m->ne[0] == b->ne[1] && m->ne[1] >= a->ne[1] && max_bias == 0.0f && softcap == 0.0f;
     }
     case GGML_OP_GET_ROWS:
         return (b200_weight_type(a->type) || a->type == GGML_TYPE_F16 || a->type == GGML_TYPE_F32) && ggml_is_contiguous(a) && a->ne[2] == 1 && b->type == GGML_TYPE_I32 && ggml_is_contiguous(b) && b->ne[1] == 1;

@@ -186,6 +186,13 @@ EB_API int eb_session_forward(eb_session *s, int model, const int32_t *h_tokens,
 EB_API int eb_tree_bits_from_batch(int n_tokens, const int32_t *h_pos, const int32_t *h_n_seq_id, const int32_t *const *h_seq_id, uint32_t *bits_out);
 EB_API int eb_session_forward_batch(eb_session *s, int model, const int32_t *h_tokens, const int32_t *h_pos, const int32_t *h_n_seq_id,
                                     const int32_t *const *h_seq_id, const float *h_hidden, int T, float *h_logits, float *h_feat);
+/* Activation tap — the counterpart of the reference's per-node eval callback (llama_context_params.cb_eval ->
+ * ggml_backend_sched_set_eval_callback, R/src/llama.cpp:9562; demo R/examples/eval-callback/eval-callback.cpp:161): while a tap
+ * buffer is set, every eb_session_forward / _forward_batch appends the int8 activation plane [T][K] of each quantisation site
+ * (per layer: input of wq|wk|wv, of wo, of gate|up, of ffn_down; then the lm_head input; the head's fc input first) to d_buf.
+ * d_buf = NULL turns it off.  eb_session_tap_state reports bytes / sites written since set_tap.  Not used inside eb_session_round. */
+EB_API int eb_session_set_tap(eb_session *s, void *d_buf, size_t bytes);
+EB_API int eb_session_tap_state(const eb_session *s, size_t *bytes_written, int *n_sites);
 /* commit the first n of the T tokens of the last forward of `model` (chain prefill) */
 EB_API int eb_session_commit(eb_session *s, int model, int n);
 EB_API int eb_session_n_past(const eb_session *s, int model);

@@ -483,6 +483,33 @@ uint16_t *eo_kv_v(eo_kv *kv, int l) { return kv->v[l]; }
 
 static void mm(const eo_tensor *w, int64_t N, int64_t K, const float *x, int T, float *y) { eo_mul_mat(w->type, w->data, N, K, x, T, y); }
 
+/* Activation tap (checker for rounding flips, tests only): when set, eo_forward appends the int8 quants [T][K] of every
+ * activation-quantisation site, on the grid the following mul_mat uses (from_float of its vec_dot_type, ggml-cpu.c:254-419,
+ * 7588-7623), in the order: [fc input] ; per layer wq|wk|wv input, wo input, gate|up input, ffn_down input ; lm_head input. */
+static int8_t *g_tap; static size_t g_tap_cap, g_tap_off;
+void eo_set_tap(int8_t *buf, size_t cap) { g_tap = buf; g_tap_cap = buf ? cap : 0; g_tap_off = 0; }
+size_t eo_tap_bytes(void) { return g_tap_off; }
+static void tap_site(int wtype, const float *x, int64_t K, int T) {
+    if (!g_tap || g_tap_off + (size_t)T * K > g_tap_cap) return;
+    const int kq = (wtype == EO_Q4_K || wtype == EO_Q6_K);
+    if (!kq && wtype != EO_Q4_0 && wtype != EO_Q8_0) { g_tap_off += (size_t)T * K; return; }
+    for (int t = 0; t < T; t++) {
+        int8_t *dst = g_tap + g_tap_off + (size_t)t * K;
+        if (kq) {
+            blk_q8_K *b = malloc((size_t)(K / QK_K) * sizeof(blk_q8_K));
+            eo_quantize_row_q8_K(x + (size_t)t * K, b, K);
+            for (int64_t i = 0; i < K / QK_K; i++) memcpy(dst + i * QK_K, b[i].qs, QK_K);
+            free(b);
+        } else {
+            blk_q8_0 *b = malloc((size_t)(K / QK) * sizeof(blk_q8_0));
+            eo_quantize_row_q8_0(x + (size_t)t * K, b, K);
+            for (int64_t i = 0; i < K / QK; i++) memcpy(dst + i * QK, b[i].qs, QK);
+            free(b);
+        }
+    }
+    g_tap_off += (size_t)T * K;
+}
+
 /* build_llama R/src/llama.cpp:1647-1811 and build_eagle :1839-2019 (FA on, f16 KV, no biases
  * except fc_bias, rope type NORM, kq_scale 1/sqrt(D)).  Differences of the eagle head, all the
  * reference's behaviour: input = relu(fc([embd ; hidden]) + fc_bias) (:1863-1869, :367-420);
@@ -503,6 +530,7 @@ void eo_forward(const eo_model *m, eo_kv *kv, const int32_t *tokens, const int32
             memcpy(cat + (size_t)t * 2 * E, x + (size_t)t * E, (size_t)E * 4);
             memcpy(cat + (size_t)t * 2 * E + E, hidden_in + (size_t)t * E, (size_t)E * 4);
         }
+        tap_site(m->g[EO_T_FC].type, cat, 2 * E, T);
         mm(&m->g[EO_T_FC], E, 2 * E, cat, T, x);
         const float *b = m->g[EO_T_FC_BIAS].data;
         for (int t = 0; t < T; t++) for (int i = 0; i < E; i++) {
@@ -515,6 +543,7 @@ void eo_forward(const eo_model *m, eo_kv *kv, const int32_t *tokens, const int32
         const eo_tensor *w = m->layers[l];
         eo_rms_norm(x, cur, E, T, m->eps);
         if (w[EO_L_ATTN_NORM].data) { const float *g = w[EO_L_ATTN_NORM].data; for (size_t i = 0; i < TE; i++) cur[i] *= g[i % E]; }
+        tap_site(w[EO_L_WQ].type, cur, E, T);
         mm(&w[EO_L_WQ], E, E, cur, T, q); mm(&w[EO_L_WK], E, E, cur, T, k); mm(&w[EO_L_WV], E, E, cur, T, v);
         eo_rope_norm(q, pos, D, H, T, m->freq_base);
         eo_rope_norm(k, pos, D, H, T, m->freq_base);
@@ -523,21 +552,25 @@ void eo_forward(const eo_model *m, eo_kv *kv, const int32_t *tokens, const int32
             kv->v[l][(size_t)kv_head * E + i] = eo_f32_to_f16(v[i]);
         }
         eo_flash_attn(q, kv->k[l], kv->v[l], vis, T, H, D, n_kv, 1.0f / sqrtf((float)D), att);
+        tap_site(w[EO_L_WO].type, att, E, T);
         mm(&w[EO_L_WO], E, E, att, T, cur);
         for (size_t i = 0; i < TE; i++) x[i] = cur[i] + x[i];          /* ffn_inp = cur + inpSA */
         eo_rms_norm(x, cur, E, T, m->eps);
         if (w[EO_L_FFN_NORM].data) { const float *g = w[EO_L_FFN_NORM].data; for (size_t i = 0; i < TE; i++) cur[i] *= g[i % E]; }
+        tap_site(w[EO_L_UP].type, cur, E, T);
         mm(&w[EO_L_UP], F, E, cur, T, up); mm(&w[EO_L_GATE], F, E, cur, T, gate);
         for (size_t i = 0; i < (size_t)T * F; i++) {        /* ggml_silu_f32: x/(1+expf(-x)), ggml-cpu.c:1838; then mul */
             const float g = gate[i];
             gate[i] = (g / (1.0f + expf(-g))) * up[i];
         }
+        tap_site(w[EO_L_DOWN].type, gate, F, T);
         mm(&w[EO_L_DOWN], E, F, gate, T, cur);
         for (size_t i = 0; i < TE; i++) x[i] = cur[i] + x[i];
     }
     eo_rms_norm(x, cur, E, T, m->eps);
     if (m->g[EO_T_OUTPUT_NORM].data) { const float *g = m->g[EO_T_OUTPUT_NORM].data; for (size_t i = 0; i < TE; i++) cur[i] *= g[i % E]; }
     if (feat) memcpy(feat, cur, TE * 4);                    /* "result_norm" */
+    tap_site(m->g[EO_T_OUTPUT].type, cur, E, T);
     if (logits) mm(&m->g[EO_T_OUTPUT], m->V, E, cur, T, logits);
     free(x); free(cur); free(q); free(k); free(v); free(att); free(gate); free(up);
 }

@@ -96,6 +96,9 @@ uint16_t *eo_kv_v(eo_kv *kv, int layer);
 /* Forward T tokens.  The new K/V rows are stored at cells [kv_head, kv_head+T); attention runs
  * over cells [0, n_kv) with visibility vis[T][n_kv].  hidden_in [T][E] is only read by eagle
  * heads.  Outputs: logits [T][V], feat [T][E] = result_norm (either may be NULL). */
+/* tests only: append the int8 activation quants of every quantisation site of eo_forward to buf (NULL = off) */
+void eo_set_tap(int8_t *buf, size_t cap);
+size_t eo_tap_bytes(void);
 void eo_forward(const eo_model *m, eo_kv *kv, const int32_t *tokens, const int32_t *pos,
                 const float *hidden_in, int T, int kv_head, int n_kv, const uint8_t *vis,
                 float *logits, float *feat);

@@ -80,6 +80,8 @@ class CpuPath:
             g("tree_vis").argtypes = [vp, i32, vp]
             g("accept_walk").argtypes = [vp, vp, i32, vp, vp, vp]
             g("kv_compact").argtypes = [vp, i32, vp, i32]
+            g("set_tap").argtypes = [vp, C.c_size_t]
+            g("tap_bytes").restype = C.c_size_t
         else:
             g("quantize").argtypes = [i32, vp, vp, i64, i64]
             g("quantize").restype = C.c_size_t
@@ -171,6 +173,22 @@ class CpuPath:
         self._g("forward")(m, kv, _ptr(tokens), _ptr(pos), _ptr(hid), T, kv_head, n_kv, _ptr(vis),
                            _ptr(logits), _ptr(feat))
         return logits, feat
+
+    def forward_tapped(self, m, kv, tokens, pos, hidden_in, kv_head, n_kv, vis, E, V, widths):
+        """eo_ only: forward + the int8 activation quants [T][K] of every quantisation site (widths = K per site, in order)"""
+        assert self.p == "eo_"
+        T = int(np.asarray(tokens).size)
+        buf = np.zeros(T * sum(widths), np.int8)
+        self._g("set_tap")(_ptr(buf), buf.size)
+        try:
+            logits, feat = self.forward(m, kv, tokens, pos, hidden_in, kv_head, n_kv, vis, E, V)
+            assert self._g("tap_bytes")() == buf.size, (self._g("tap_bytes")(), buf.size)
+        finally:
+            self._g("set_tap")(None, 0)
+        planes, off = [], 0
+        for w in widths:
+            planes.append(buf[off:off + T * w].reshape(T, w)); off += T * w
+        return logits, feat, planes
 
     def kv_arrays(self, kv, L, E, n_ctx):
         ks, vs = [], []

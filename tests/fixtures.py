@@ -125,6 +125,26 @@ def tree_parents(T, rng, n_branch=4):
     return par
 
 
+def tree_seq_ids(par):
+    """seq-id sets as the reference's tree driver assigns them (R/examples/speculative/speculative-eagle.cpp:556-625): one branch
+    per root-to-leaf path; a node's FIRST id is the branch that created it, followed by the branches that split off below it."""
+    T = len(par)
+    children = [[j for j in range(T) if par[j] == i] for i in range(T)]
+    seqs = [[] for _ in range(T)]; nxt = [1]
+
+    def walk(i, sid):
+        if not seqs[i]:
+            seqs[i].insert(0, sid)
+        for n, ch in enumerate(children[i]):
+            s = sid if n == 0 else nxt[0]
+            if n:
+                nxt[0] += 1
+            walk(ch, s)
+            seqs[i].extend(x for x in seqs[ch] if x not in seqs[i])
+    walk(0, 0)
+    return seqs, nxt[0]
+
+
 def tree_depths(par):
     d = np.zeros(len(par), np.int32)
     for i in range(1, len(par)):

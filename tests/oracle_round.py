@@ -69,15 +69,17 @@ class CpuStream:
                 if not drafting[b] or skip[b]:
                     continue
                 ids, vals, pr = po.top_k(lg[row[b]], top_k)
-                cand_log.append((ids.copy(), vals.copy()))
-                sa = [b]
+                sa = [b]; checked = []
                 for f in range(1, min(8, top_k)):
+                    if n_seq < n_branch:
+                        checked.append(f)                 # a p_split comparison that was actually evaluated
                     if n_seq < n_branch and pr[f] > p_split:
                         nb = n_seq; n_seq += 1
                         drafting[nb] = True; skip[nb] = True; last_node[nb] = last_node[b]; row[nb] = row[b]
                         sa.append(nb)
                     else:
                         break
+                cand_log.append((ids.copy(), vals.copy(), len(sa), checked))
                 for i, br in enumerate(sa):
                     if len(tokens) + len(new) >= max_nodes:
                         drafting[br] = False

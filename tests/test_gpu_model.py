@@ -8,6 +8,7 @@ import pytest
 
 import fixtures as fx
 import pyoracle as po
+import parity as pa
 from golden_io import load_tiny, nmse, rel_max
 from oracle_round import CpuStream
 
@@ -21,26 +22,30 @@ TIE_REL = 2e-3     # |top1 - top2| below this fraction of |top1| => flagged as a
 #                                     R/tests/test-backend-ops.cpp:3482) and max-rel <= 3e-2;
 #   vs the oracle in f32-accumulator mode (every other op the reference's): max-rel <= 1e-2,
 #                                     greedy ids identical, near-ties flagged.
-REF_NMSE, REF_REL, REF_TIE = 2e-3, 3e-2, 3e-2
+REF_NMSE, REF_REL, REF_TIE = 2e-3, 3e-2, pa.TIE_REL
 # Noise floor of ANY non-bit-identical implementation (measured in tools/ and DESIGN.md §numerics):
 # the activation quantisers (Q8_K / Q8_0, round-to-nearest on a 127-level grid) turn a relative
 # perturbation eps of their input into ~0.17*sqrt(eps) relative output noise (rounding flips), so
 # after a few layers any 1e-7 summation-order difference saturates near 1e-2 of the logit range.
 # Per-op parity is therefore asserted tightly (tests/test_gpu_ops.py: 1e-5 / bit-exact) and
 # whole-model parity with the reference's own whole-graph bar (NMSE 2e-3) + max-rel 3e-2.
-MODEL_NMSE, MODEL_REL = 2e-3, 3e-2
+MODEL_NMSE = 2e-3
+# vs the oracle in f32-accumulator mode the bar is parity.check_forward: rows without a DETECTED rounding flip (identical int8
+# activation planes at every quantisation site, engine tap vs oracle tap) must meet CLEAN_REL — two orders below the north star's
+# 1e-2, they measure ~1e-6 —, flipped rows are counted, bounded (MAX_FLIP) and held to parity.FLIP_REL.
+CLEAN_REL, MAX_FLIP = 1e-4, 0.35
 
 
-def greedy_agree(a, b, tie=TIE_REL):
-    """-> (mismatches on clear rows, number of tie rows)"""
-    bad = ties = 0
-    for ra, rb in zip(a, b):
-        top = np.sort(rb)[-2:]
-        if top[1] - top[0] <= tie * abs(top[1]):
-            ties += 1
-        elif ra.argmax() != rb.argmax():
-            bad += 1
+def greedy_agree(a, b, tie=TIE_REL, tag="greedy"):
+    """-> (mismatches on decided rows, number of flagged tie rows); the tie share is printed and bounded (parity.MAX_TIE_FRAC)"""
+    bad, ties, n = pa.greedy_report(a, b, tie)
+    print(f"[parity] {tag}: {n} rows, {ties} flagged ties ({100.0 * ties / max(n, 1):.1f} %), {bad} mismatches on decided rows")
+    assert ties <= max(1, pa.MAX_TIE_FRAC * n), (ties, n)
     return bad, ties
+
+
+def oracle_tapped(o, mo, kv, hp, tokens, pos, hidden, kv_head, n_ctx, vis):
+    return o.forward_tapped(mo, kv, tokens, pos, hidden, kv_head, n_ctx, vis, hp["E"], hp["V"], pa.site_widths(hp))
 
 
 def test_tiny_model_vs_golden(eb):
@@ -67,10 +72,15 @@ def test_tiny_model_vs_golden(eb):
     with po.fattn_acc_f32():
         mo = fx.to_cpu_model(o, tgt); kvo = o._g("kv_new")(2, 256, 64)
         vis = np.zeros((P, 64), np.uint8); vis[:, :P] = np.tril(np.ones((P, P), np.uint8))
-        lo, fo = o.forward(mo, kvo, prompt, np.arange(P), None, 0, 64, vis, 256, 512)
-        lo_t, _ = o.forward(mo, kvo, z["tree_tokens"], z["tree_pos"], None, P, 64, fx.vis_matrix(z["tree_parent"], P, 64), 256, 512)
-    assert rel_max(lg, lo) < MODEL_REL and nmse(lg, lo) < MODEL_NMSE and rel_max(lg_t, lo_t) < MODEL_REL
-    assert greedy_agree(lg, lo, REF_TIE)[0] == 0 and greedy_agree(lg_t, lo_t, REF_TIE)[0] == 0
+        lo, fo, pl_o = oracle_tapped(o, mo, kvo, tgt["hparams"], prompt, np.arange(P), None, 0, 64, vis)
+        lo_t, _, pl_ot = oracle_tapped(o, mo, kvo, tgt["hparams"], z["tree_tokens"], z["tree_pos"], None, P, 64, fx.vis_matrix(z["tree_parent"], P, 64))
+    s2 = eb.Session(mt, None, n_ctx=64, max_nodes=16, use_graph=False)
+    lg2, _, pl_g = s2.forward_tapped(0, prompt, np.arange(P)); s2.commit(0, P)
+    lg2_t, _, pl_gt = s2.forward_tapped(0, z["tree_tokens"], z["tree_pos"], parent=z["tree_parent"])
+    assert np.array_equal(lg2, lg) and np.array_equal(lg2_t, lg_t)          # the tap does not change the forward
+    pa.check_forward("tiny prefill vs oracle(f32 acc)", lg, lo, pl_g, pl_o, MAX_FLIP, CLEAN_REL)
+    pa.check_forward("tiny tree vs oracle(f32 acc)", lg_t, lo_t, pl_gt, pl_ot, MAX_FLIP, CLEAN_REL)
+    s2.free()
     # get_tensor returns the GGUF bytes that were uploaded (bit-exact weights)
     for which, (t, raw) in tgt["layers"][0].items():
         assert np.array_equal(mt.get_tensor(0, which, raw.size), raw.view(np.uint8).reshape(-1))
@@ -78,29 +88,29 @@ def test_tiny_model_vs_golden(eb):
 
 
 def test_independent_rows_rounding_flips(eb):
-    """A batch of INDEPENDENT first tokens (parent = -1) is a pure GEMM chain per row: no attention mixing, so the
-    only source of deviation from the oracle is an activation-quantisation rounding flip (an f32 value within 1 ulp of
-    a .5 boundary of the Q8_K grid rounds the other way because the f32 summation ORDER differs).  Measured on B200:
-    ~5-6 % of rows flip, identically for the mma.sync and the tcgen05 GEMM; a flipped row deviates ~1e-2, all other
-    rows agree to f32 rounding.  Bound the flip rate and the unflipped error."""
+    """A batch of INDEPENDENT first tokens (parent = -1) is a pure GEMM chain per row: no attention mixing, so the only source of
+    deviation from the oracle is an activation-quantisation rounding flip.  The flip is DETECTED (int8 planes of every site, engine
+    tap vs oracle tap): rows without one agree to f32 rounding (1e-5), rows with one stay under parity.FLIP_REL, and the flip rate
+    is bounded (measured on B200: ~5 % of rows per 3-layer forward)."""
     hp = dict(E=512, H=4, F=1024, V=2048, L=3)
     tgt = fx.make_model(**hp, ftype="q4_k_m", seed=21)
     o = po.oracle(); n_ctx = 256
     mo = fx.to_cpu_model(o, tgt); mg = fx.to_gpu_model(eb, tgt)
-    P, clean, total = 40, 0, 0
+    P, flips, total = 40, 0, 0
     po.set_fattn_acc_f32(1)
     for seed in range(4):
         kv = o._g("kv_new")(hp["L"], hp["E"], n_ctx)
         s = eb.Session(mg, None, n_ctx=n_ctx, max_nodes=65, use_graph=False)
         prompt = np.random.default_rng(1000 + seed).integers(3, hp["V"], P).astype(np.int32)
         vis = np.zeros((P, n_ctx), np.uint8); vis[np.arange(P), np.arange(P)] = 1
-        lo, _ = o.forward(mo, kv, prompt, np.zeros(P, np.int32), None, 0, n_ctx, vis, hp["E"], hp["V"])
-        lg, _ = s.forward(0, prompt, np.zeros(P, np.int32), parent=np.full(P, -1, np.int32))
-        err = np.abs(lg - lo).max(1) / np.abs(lo).max()
-        assert err.max() < MODEL_REL
-        clean += int((err < 1e-5).sum()); total += P
+        lo, _, pl_o = oracle_tapped(o, mo, kv, tgt["hparams"], prompt, np.zeros(P, np.int32), None, 0, n_ctx, vis)
+        lg, _, pl_g = s.forward_tapped(0, prompt, np.zeros(P, np.int32), parent=np.full(P, -1, np.int32))
+        rep = pa.check_forward(f"independent rows seed {seed}", lg, lo, pl_g, pl_o, 0.25, 1e-5)
+        flips += rep["flipped"]; total += P
         s.free()
-    assert clean >= 0.8 * total, (clean, total)
+    po.set_fattn_acc_f32(0)
+    print(f"[parity] independent rows: {flips} of {total} rows flipped ({100.0 * flips / total:.1f} %)")
+    assert flips <= 0.15 * total, (flips, total)
 
 
 @pytest.mark.parametrize("ftype", ["q4_k_m", po.Q4_0, po.Q8_0])
@@ -118,62 +128,75 @@ def test_forward_vs_oracle(eb, ftype, T):
     prompt = rng.integers(3, hp["V"], P).astype(np.int32)
     vis = np.zeros((P, n_ctx), np.uint8); vis[:, :P] = np.tril(np.ones((P, P), np.uint8))
     po.set_fattn_acc_f32(1)
-    lo, fo = o.forward(mo, kv, prompt, np.arange(P), None, 0, n_ctx, vis, hp["E"], hp["V"])
-    lg, fg = s.forward(0, prompt, np.arange(P))
-    assert rel_max(lg, lo) < MODEL_REL and nmse(lg, lo) < MODEL_NMSE
+    lo, fo, pl_o = oracle_tapped(o, mo, kv, tgt["hparams"], prompt, np.arange(P), None, 0, n_ctx, vis)
+    lg, fg, pl_g = s.forward_tapped(0, prompt, np.arange(P))
+    pa.check_forward(f"prefill {ftype} vs oracle(f32 acc)", lg, lo, pl_g, pl_o, MAX_FLIP, CLEAN_REL)
+    assert nmse(lg, lo) < MODEL_NMSE
     s.commit(0, P)
     par = fx.tree_parents(T, rng, 6)
     toks = rng.integers(3, hp["V"], T).astype(np.int32); pos = (P + fx.tree_depths(par)).astype(np.int32)
-    lo, fo = o.forward(mo, kv, toks, pos, None, P, n_ctx, fx.vis_matrix(par, P, n_ctx), hp["E"], hp["V"])
+    lo, fo, pl_o = oracle_tapped(o, mo, kv, tgt["hparams"], toks, pos, None, P, n_ctx, fx.vis_matrix(par, P, n_ctx))
     po.set_fattn_acc_f32(0)
-    lg, fg = s.forward(0, toks, pos, parent=par)
-    assert rel_max(lg, lo) < MODEL_REL and nmse(lg, lo) < MODEL_NMSE and nmse(fg, fo) < MODEL_NMSE
-    bad, ties = greedy_agree(lg, lo, REF_TIE)
-    assert bad == 0, (bad, ties)
+    lg, fg, pl_g = s.forward_tapped(0, toks, pos, parent=par)
+    pa.check_forward(f"tree T={T} {ftype} vs oracle(f32 acc)", lg, lo, pl_g, pl_o, MAX_FLIP, CLEAN_REL)
+    assert nmse(lg, lo) < MODEL_NMSE and nmse(fg, fo) < MODEL_NMSE
     s.free()
 
 
 @pytest.mark.parametrize("head_ftype", [po.Q4_0, "q4_k_m"])
 @pytest.mark.parametrize("use_graph", [False, True])
-def test_spec_rounds_vs_oracle(eb, use_graph, head_ftype):
-    """multi-round greedy decoding: draft-tree token ids, accepted paths and bonus tokens must be
-    identical to the oracle composition round after round (KV compaction feeds the next round)."""
+@pytest.mark.parametrize("inert_caps", [True, False])
+def test_spec_rounds_vs_oracle(eb, use_graph, head_ftype, inert_caps):
+    """multi-round greedy decoding: draft-tree token ids, parents, accepted paths and bonus tokens identical to the oracle composition
+    round after round (KV compaction and the feature hand-off feed the next round).  At least one of 8 prompts must run >= 4 full
+    rounds from the start with every round identical (6 are attempted); a prompt may only drop out at a round where the oracle's own
+    closest decision (parity.round_margin: used candidates' order, evaluated p_split comparisons, argmax on the accepted path) was
+    nearer than the north star's logits tolerance 1e-2 — "ties within tolerance flagged" —; a divergence at a clearer margin fails.  inert_caps: max_depth >= n_draft and
+    max_nodes >= n_draft + n_branch + 1, i.e. the engine's two capacity rules never fire and the expansion is the reference loop's
+    (R/examples/speculative/speculative-eagle.cpp:527-642) rule for rule."""
     hp = dict(E=256, H=2, F=512, V=1024, L=2)
     tgt = fx.make_model(**hp, ftype="q4_k_m", seed=31)
     head = fx.make_model(**{**hp, "L": 1}, ftype=head_ftype, seed=32, is_eagle=True)
-    cfg = dict(n_branch=4, n_draft=12, max_depth=5, top_k=10, p_split=0.1, max_nodes=16)
-    n_ctx = 128
-    cpu = CpuStream(po.oracle(), tgt, head, n_ctx)
+    cfg = dict(n_branch=4, n_draft=12, max_depth=12, top_k=10, p_split=0.1, max_nodes=17) if inert_caps else \
+          dict(n_branch=4, n_draft=12, max_depth=5, top_k=10, p_split=0.1, max_nodes=16)
+    n_ctx, n_rounds = 160, 6
     po.set_fattn_acc_f32(1)
     mt = fx.to_gpu_model(eb, tgt); mh = fx.to_gpu_model(eb, head, target=mt)
-    s = eb.Session(mt, mh, n_ctx=n_ctx, use_graph=use_graph, **cfg)
-    prompt = np.random.default_rng(1).integers(3, hp["V"], 12).astype(np.int32)
-    lg_c, ft_c = cpu.prefill(prompt)
-    lg, ft = s.forward(0, prompt, np.arange(len(prompt)))
-    hid = np.zeros((len(prompt), hp["E"]), np.float32); hid[1:] = ft[:-1]
-    s.forward(1, prompt, np.arange(len(prompt)), hidden=hid)
-    s.commit(0, len(prompt))
-    assert int(lg[-1].argmax()) == cpu.root_token
-    s.set_root(cpu.root_token, ft[-1])
-    flagged = 0
-    for rnd in range(6):
-        want = cpu.round(**cfg)
-        got = s.round()
-        n = got.n_nodes
-        near_tie = any((v[0] - v[min(len(v) - 1, 9)]) < TIE_REL * abs(v[0]) or np.min(-np.diff(v)) < TIE_REL * abs(v[0]) for _, v in want["cand"])
-        same_tree = n == len(want["tokens"]) and list(got.tokens[:n]) == want["tokens"].tolist() and list(got.parent[:n]) == want["parent"].tolist()
-        if not same_tree and near_tie:
-            flagged += 1
-            break                                            # streams diverged on a flagged tie: stop comparing
-        assert same_tree, (rnd, list(got.tokens[:n]), want["tokens"].tolist())
-        lgw = want["logits"]
-        bad, ties = greedy_agree(lgw, lgw)
-        assert list(got.path[:got.n_accept]) == want["path"].tolist() or ties, (rnd, list(got.path[:got.n_accept]), want["path"].tolist())
-        assert got.bonus == want["bonus"] or ties
-        assert s.n_past() == cpu.n_past
+    full, log = 0, []
+    for seed in range(1, 9):
+        cpu = CpuStream(po.oracle(), tgt, head, n_ctx)
+        s = eb.Session(mt, mh, n_ctx=n_ctx, use_graph=use_graph, **cfg)
+        prompt = np.random.default_rng(seed).integers(3, hp["V"], 12).astype(np.int32)
+        lg_c, ft_c = cpu.prefill(prompt)
+        lg, ft = s.forward(0, prompt, np.arange(len(prompt)))
+        hid = np.zeros((len(prompt), hp["E"]), np.float32); hid[1:] = ft[:-1]
+        s.forward(1, prompt, np.arange(len(prompt)), hidden=hid)
+        s.commit(0, len(prompt))
+        if int(lg[-1].argmax()) != cpu.root_token:
+            top = np.sort(lg_c[-1])[-2:]
+            assert top[1] - top[0] <= pa.NORTH_STAR_REL * abs(top[1]), "root token differs at a clear margin"
+            log.append((seed, 0, "root near-tie")); s.free(); continue
+        s.set_root(cpu.root_token, ft[-1])
+        ok = 0
+        for rnd in range(n_rounds):
+            want = cpu.round(**cfg); got = s.round()
+            if pa.same_round(got, want):
+                assert s.n_past() == cpu.n_past
+                ok += 1
+                continue
+            margin = pa.round_margin(want, cfg["p_split"])
+            assert margin <= pa.NORTH_STAR_REL, (seed, rnd, margin, list(got.tokens[:got.n_nodes]), want["tokens"].tolist(), list(got.path[:got.n_accept]), want["path"].tolist())
+            log.append((seed, rnd, f"near-tie, margin {margin:.2e}"))
+            break
+        full += ok >= 4
+        if ok == n_rounds:
+            log.append((seed, n_rounds, "identical"))
+        s.free()
+        if full >= 2:
+            break
     po.set_fattn_acc_f32(0)
-    assert flagged <= 1
-    s.free()
+    print(f"[parity] spec rounds (graph={use_graph}, head={head_ftype}, inert_caps={inert_caps}): {log}")
+    assert full >= 1, log
 
 
 def test_fixed_accept_round_properties(eb):
@@ -246,11 +269,11 @@ def test_forward_7b_width_one_layer(eb):
         s.forward(0, ids, np.arange(c0, c0 + n)); s.commit(0, n)
     par = fx.tree_parents(T, rng, 6)
     toks = rng.integers(3, V, T).astype(np.int32); pos = (P + fx.tree_depths(par)).astype(np.int32)
-    lo, fo = o.forward(mo, kv, toks, pos, None, P, n_ctx, fx.vis_matrix(par, P, n_ctx), E, V)
+    lo, fo, pl_o = oracle_tapped(o, mo, kv, tgt["hparams"], toks, pos, None, P, n_ctx, fx.vis_matrix(par, P, n_ctx))
     po.set_fattn_acc_f32(0)
-    lg, fg = s.forward(0, toks, pos, parent=par)
-    assert rel_max(lg, lo) < MODEL_REL and nmse(lg, lo) < MODEL_NMSE and nmse(fg, fo) < MODEL_NMSE
-    assert greedy_agree(lg, lo, REF_TIE)[0] == 0
+    lg, fg, pl_g = s.forward_tapped(0, toks, pos, parent=par)
+    pa.check_forward("7B-width layer, 65-row tree vs oracle(f32 acc)", lg, lo, pl_g, pl_o, MAX_FLIP, CLEAN_REL)
+    assert nmse(lg, lo) < MODEL_NMSE and nmse(fg, fo) < MODEL_NMSE
     s.free()
 
 
