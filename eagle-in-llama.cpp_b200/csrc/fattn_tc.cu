@@ -6,8 +6,12 @@
 // is read from HBM exactly once per layer.  Per 128-cell tile:
 //     S = Q K^T    tcgen05.mma SS   (Q, K K-major 128B-swizzled smem)           -> TMEM S[b]  (128 lanes x 128 f32 columns)
 //     softmax      one thread per query row: tcgen05.ld S row -> registers, mask, running max (rescale of O only when the
-//                  max grows by more than 2^8), P = exp2 -> f16 pairs -> tcgen05.st over the first 64 columns of S[b]
-//     O += P V     tcgen05.mma TS   (P from TMEM, V MN-major smem: the cache layout [cell][dim] needs no transpose)
+//                  max grows by more than 2^8), P = exp2 as TWO f16 addends (hi = f16(P), lo = f16(P - hi): ~22 significant
+//                  bits, i.e. the f32 P of the CPU kernel, R/ggml/src/ggml-cpu/ggml-cpu.c:11135-11170) -> tcgen05.st over S[b]
+//                  (hi pairs in columns 0..63, lo pairs in columns 64..127)
+//     O += P V     tcgen05.mma TS x 2 (P_hi, then P_lo on the same accumulator; V MN-major smem: the cache layout [cell][dim]
+//                  needs no transpose).  Products f16 x f16 are exact, accumulation is f32: the only difference left against
+//                  the reference is its f16 V accumulator (documented deviation)
 // S is double-buffered so QK^T of tile i+2 and PV of tile i run on the tensor pipe while the softmax warps work on tile i+1.
 // Roles: warp 0 TMA producer (3-stage K ring + 3-stage V ring, 32 KB tiles), warp 1 MMA issuer, warp 2 TMEM allocator,
 // warps 4-7 softmax / correction / epilogue (warp 4+q owns TMEM lanes 32q..32q+31 = query rows).
@@ -142,6 +146,7 @@ fattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
                 const uint32_t vb = sbase + FT_OFF_V + s * FT_STAGE;
                 if (elect_one()) {
                     mma_f16_ts_x8_rows(tmem + FT_COL_O, tmem + b * 128, smem_desc_sw128_mn(vb, FT_BOX), id_o, i > 0);
+                    mma_f16_ts_x8_rows(tmem + FT_COL_O, tmem + b * 128 + 64, smem_desc_sw128_mn(vb, FT_BOX), id_o, 1);      // P_lo
                     mma_commit(bars + (FB_V_EMPTY + s) * 8);
                     mma_commit(bars + FB_O_DONE * 8);
                 }
@@ -213,18 +218,22 @@ fattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
             FA_CK(3);
             const float base = m == -INFINITY ? 0.f : m * c;
             float rs[4] = {0.f, 0.f, 0.f, 0.f};                                // independent partial row sums (ILP)
-            uint32_t pk[2][32];
 #pragma unroll
-            for (int ch = 0; ch < 4; ch++)
+            for (int ch = 0; ch < 4; ch++) {                                   // 32 cells at a time: their hi and lo pairs live together
+                uint32_t ph[16], pl[16];
 #pragma unroll
                 for (int k = 0; k < 32; k += 2) {
                     const float p0 = ex2(fmaf(__uint_as_float(sr[ch][k]), c, -base)), p1 = ex2(fmaf(__uint_as_float(sr[ch][k + 1]), c, -base));
                     rs[(k >> 1) & 3] += p0 + p1;
-                    pk[ch >> 1][(ch & 1) * 16 + (k >> 1)] = pack_h2(p0, p1);
+                    const __half2 hi = __floats2half2_rn(p0, p1);
+                    const float2 hf2 = __half22float2(hi);
+                    ph[k >> 1] = *(const uint32_t *)&hi;
+                    pl[k >> 1] = pack_h2(p0 - hf2.x, p1 - hf2.y);
                 }
+                tmem_st16(ts + ch * 16, ph); tmem_st16(ts + 64 + ch * 16, pl);
+            }
             l += (rs[0] + rs[1]) + (rs[2] + rs[3]);
             FA_CK(4);
-            tmem_st32(ts, pk[0]); tmem_st32(ts + 32, pk[1]);
             wait_st();
             fence_before();
             __syncwarp();

@@ -213,11 +213,7 @@ __device__ __forceinline__ void dequant_group_q6(uint32_t (&r1)[16], uint32_t (&
         r2[2 * w + 1] = h2u(__hfma2(u2h(and_or(b2, k_q2, k_magic)), m, c2));
     }
 }
-__device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t (&r)[16]) {
-    asm volatile("tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16};"
-                 ::"r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]),
-                   "r"(r[8]), "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]) : "memory");
-}
+using tc::tmem_st16;
 // dequant role for Q6_K: MEMBER m handles groups m and m + 2 of each half (same 32 ql bytes: low / high nibbles)
 template <int MEMBER, bool PROF>
 __device__ __forceinline__ void dequant_q6_K(const TcArgs &p, uint8_t *smem, uint32_t bar0, uint32_t tmem, int q, int lane) {
