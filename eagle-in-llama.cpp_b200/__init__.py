@@ -83,6 +83,9 @@ def lib():
         "eb_tree_bits_from_batch": ([i32, vp, vp, vp, vp], i32),
         "eb_session_forward_batch": ([vp, i32, vp, vp, vp, vp, vp, i32, vp, vp], i32),
         "eb_session_set_tap": ([vp, vp, sz], i32), "eb_session_tap_state": ([vp, C.POINTER(sz), C.POINTER(i32)], i32),
+        "eb_session_prefill": ([vp, vp, i32, vp, vp], i32),
+        "eb_session_kv_write": ([vp, i32, i32, i32, i32, i32, vp], i32), "eb_session_kv_read": ([vp, i32, i32, i32, i32, i32, vp], i32),
+        "eb_session_set_n_past": ([vp, i32], i32),
         "eb_session_commit": ([vp, i32, i32], i32), "eb_session_n_past": ([vp, i32], i32),
         "eb_session_synth_kv": ([vp, i32, C.c_uint64], i32), "eb_session_set_root": ([vp, C.c_int32, vp], i32),
         "eb_session_round": ([vp, C.POINTER(RoundResult)], i32),
@@ -450,6 +453,26 @@ class Session:
         for w in widths:
             planes.append(raw[off:off + T * w].reshape(T, w)); off += T * w
         return logits, feat, planes
+
+    def prefill(self, tokens):
+        """prompt of any length through target (+ head): -> (logits [V], feature [E]) of the last token; both caches committed"""
+        tokens = np.ascontiguousarray(tokens, np.int32)
+        lg = np.empty(self.target.V, np.float32); ft = np.empty(self.target.E, np.float32)
+        _ck(lib().eb_session_prefill(self.h, _hp(tokens), tokens.size, _hp(lg), _hp(ft)))
+        return lg, ft
+
+    def kv_write(self, model, layer, which, cell0, rows):
+        rows = np.ascontiguousarray(rows).view(np.uint16)
+        _ck(lib().eb_session_kv_write(self.h, model, layer, which, cell0, rows.shape[0], _hp(rows)))
+
+    def kv_read(self, model, layer, which, cell0, n_cells):
+        m = self.head if model else self.target
+        out = np.empty((n_cells, m.E), np.uint16)
+        _ck(lib().eb_session_kv_read(self.h, model, layer, which, cell0, n_cells, _hp(out)))
+        return out
+
+    def set_n_past(self, n):
+        _ck(lib().eb_session_set_n_past(self.h, n))
 
     def commit(self, model, n):
         _ck(lib().eb_session_commit(self.h, model, n))

@@ -5,6 +5,8 @@
 #include "engine.cuh"
 #include <cmath>
 #include <cstring>
+#include <vector>
+#include <algorithm>
 
 static int tensor_shape(const eb_model *m, int layer, int which, int64_t &rows, int64_t &cols) {
     const int64_t E = m->E, F = m->F, V = m->V;
@@ -526,6 +528,72 @@ extern "C" int eb_session_commit(eb_session *s, int model, int n) {
     EB_CUDA(cudaStreamSynchronize(s->st));
     return EB_OK;
 }
+// ---- prompt prefill (llama_decode_init + llama_decode_initial of the chain driver, R/examples/speculative-simple/speculative-eagle.cpp:150,194;
+// R/src/llama.cpp:10512,10256): the prompt goes through the target in chunks of one verify tile (128 rows, causal inside the chunk,
+// the committed cells as prefix), and through the draft head with the target feature of the PREVIOUS token as its hidden input
+// (SURVEY F4/F5), both caches advancing together.
+extern "C" int eb_session_prefill(eb_session *s, const int32_t *h_tokens, int n, float *h_logits_last, float *h_feat_last) {
+    if (n < 1 || !h_tokens) return eb_set_err(EB_ERR_ARG, "prefill: n=%d", n);
+    const int E = s->tgt->E, V = s->tgt->V;
+    const int n_past0 = eb_session_n_past(s, 0);
+    if (n_past0 + n > s->p.n_ctx) return eb_set_err(EB_ERR_ARG, "prefill: %d + %d tokens exceed n_ctx %d", n_past0, n, s->p.n_ctx);
+    std::vector<float> feat((size_t)128 * E), hid((size_t)128 * E), prev((size_t)E, 0.f), logits;
+    std::vector<int32_t> pos(128);
+    uint32_t bits[128 * 4];
+    for (int c0 = 0; c0 < n; c0 += 128) {
+        const int T = std::min(128, n - c0);
+        const bool last = c0 + T == n;
+        memset(bits, 0, sizeof(bits));
+        for (int t = 0; t < T; t++) {
+            pos[t] = n_past0 + c0 + t;
+            for (int j = 0; j <= t; j++) bits[t * 4 + (j >> 5)] |= 1u << (j & 31);
+        }
+        if (last && h_logits_last) logits.resize((size_t)T * V);
+        int rc = forward_bits(s, 0, h_tokens + c0, pos.data(), bits, nullptr, T, last && h_logits_last ? logits.data() : nullptr, feat.data());
+        if (rc) return rc;
+        if (s->head) {
+            memcpy(hid.data(), prev.data(), (size_t)E * 4);
+            if (T > 1) memcpy(hid.data() + E, feat.data(), (size_t)(T - 1) * E * 4);
+            rc = forward_bits(s, 1, h_tokens + c0, pos.data(), bits, hid.data(), T, nullptr, nullptr);
+            if (rc) return rc;
+        }
+        memcpy(prev.data(), feat.data() + (size_t)(T - 1) * E, (size_t)E * 4);
+        rc = eb_session_commit(s, 0, T); if (rc) return rc;
+        if (last && h_logits_last) memcpy(h_logits_last, logits.data() + (size_t)(T - 1) * V, (size_t)V * 4);
+    }
+    if (h_feat_last) memcpy(h_feat_last, prev.data(), (size_t)E * 4);
+    return EB_OK;
+}
+
+// ---- KV cache access (what llama_state_* / ggml_backend_tensor_get|set do on the reference's cache tensors, R/src/llama-context.cpp:1229-2190):
+// f16 rows [n_cells][E] of one layer's K (which = 0) or V (which = 1), starting at cell0
+static int kv_span(eb_session *s, int model, int layer, int which, int cell0, int n_cells, __half **p) {
+    if (model && !s->head) return eb_set_err(EB_ERR_ARG, "kv: session has no draft head");
+    KVCache &kv = model ? s->kv_h : s->kv_t;
+    if (layer < 0 || layer >= kv.L || cell0 < 0 || n_cells < 0 || cell0 + n_cells > kv.n_ctx || (which != 0 && which != 1))
+        return eb_set_err(EB_ERR_ARG, "kv: layer %d cells [%d, %d) of %d", layer, cell0, cell0 + n_cells, kv.n_ctx);
+    *p = (which ? kv.v : kv.k) + (int64_t)layer * kv.layer_stride + (int64_t)cell0 * kv.E;
+    return EB_OK;
+}
+extern "C" int eb_session_kv_write(eb_session *s, int model, int layer, int which, int cell0, int n_cells, const void *h_f16) {
+    __half *p; int rc = kv_span(s, model, layer, which, cell0, n_cells, &p); if (rc) return rc;
+    EB_CUDA(cudaMemcpyAsync(p, h_f16, (size_t)n_cells * (model ? s->kv_h : s->kv_t).E * 2, cudaMemcpyHostToDevice, s->st));
+    EB_CUDA(cudaStreamSynchronize(s->st));
+    return EB_OK;
+}
+extern "C" int eb_session_kv_read(eb_session *s, int model, int layer, int which, int cell0, int n_cells, void *h_f16) {
+    __half *p; int rc = kv_span(s, model, layer, which, cell0, n_cells, &p); if (rc) return rc;
+    EB_CUDA(cudaMemcpyAsync(h_f16, p, (size_t)n_cells * (model ? s->kv_h : s->kv_t).E * 2, cudaMemcpyDeviceToHost, s->st));
+    EB_CUDA(cudaStreamSynchronize(s->st));
+    return EB_OK;
+}
+extern "C" int eb_session_set_n_past(eb_session *s, int n_past) {
+    if (n_past < 0 || n_past > s->p.n_ctx) return eb_set_err(EB_ERR_ARG, "set_n_past: %d", n_past);
+    set_n_past_kernel<<<1, 1, 0, s->st>>>(s->state, n_past); EB_CHECK_LAUNCH();
+    EB_CUDA(cudaStreamSynchronize(s->st));
+    return EB_OK;
+}
+
 extern "C" int eb_session_set_root(eb_session *s, int32_t id_last, const float *h_feat) {
     set_root_kernel<<<1, 1, 0, s->st>>>(s->state, id_last); EB_CHECK_LAUNCH();
     if (h_feat) EB_CUDA(cudaMemcpyAsync(s->root_feat, h_feat, (size_t)s->tgt->E * 4, cudaMemcpyHostToDevice, s->st));

@@ -196,6 +196,17 @@ EB_API int eb_session_tap_state(const eb_session *s, size_t *bytes_written, int 
 /* commit the first n of the T tokens of the last forward of `model` (chain prefill) */
 EB_API int eb_session_commit(eb_session *s, int model, int n);
 EB_API int eb_session_n_past(const eb_session *s, int model);
+/* Prompt prefill of any length — llama_decode_init + llama_decode_initial of the chain driver (R/examples/speculative-simple/
+ * speculative-eagle.cpp:150,194; R/src/llama.cpp:10512,10256), SURVEY §8(f) N1: the tokens go through the target in chunks of
+ * one verify tile and through the draft head with the previous token's target feature as hidden input; both caches are committed.
+ * h_logits_last [V] / h_feat_last [E]: logits and feature (result_norm) of the LAST prompt token (either may be NULL). */
+EB_API int eb_session_prefill(eb_session *s, const int32_t *h_tokens, int n, float *h_logits_last, float *h_feat_last);
+/* KV cache rows as raw f16 [n_cells][E] of one layer (which: 0 = K, 1 = V; model: 0 = target, 1 = head): what the reference's
+ * session save / load does through ggml_backend_tensor_get / _set on the cache tensors (R/src/llama-context.cpp:1229-2190).
+ * eb_session_set_n_past declares how many leading cells are the committed prefix (after writing a cache). */
+EB_API int eb_session_kv_write(eb_session *s, int model, int layer, int which, int cell0, int n_cells, const void *h_f16);
+EB_API int eb_session_kv_read(eb_session *s, int model, int layer, int which, int cell0, int n_cells, void *h_f16);
+EB_API int eb_session_set_n_past(eb_session *s, int n_past);
 /* fill both KV caches with n_past cells of synthetic N(0,1) K/V (bench: 4K context) */
 EB_API int eb_session_synth_kv(eb_session *s, int n_past, uint64_t seed);
 /* start decoding: last committed token id + the target feature (result_norm) that produced it */

@@ -205,6 +205,25 @@ int rr_kv_read_row(void *c, int layer, int which, int cell, uint16_t *out, int n
     return 0;
 }
 
+// synthetic committed prefix (full-size parity runs and the timed CPU arm: a 4K-token CPU prefill of a 7B model would take minutes):
+// raw f16 rows [n][n_embd] written into one layer's K / V cache tensor from cell0, and the cell metadata of a prefix of n cells at
+// positions 0..n-1 that belongs to sequences 0..n_seq-1 (what the cache looks like after the driver's seq_cp 0 -> s, speculative-eagle.cpp:648-652)
+int rr_kv_write_rows(void *c, int layer, int which, int cell0, int n, const uint16_t *rows, int n_embd) {
+    const llama_kv_cache &kv = ((rr_ctx *)c)->ctx->kv_self;
+    ggml_tensor *t = which ? kv.v_l[layer] : kv.k_l[layer];
+    if (t->type != GGML_TYPE_F16 || (which && kv.v_trans)) return -1;
+    ggml_backend_tensor_set(t, rows, (size_t)cell0 * n_embd * 2, (size_t)n * n_embd * 2);
+    return 0;
+}
+int rr_kv_set_prefix(void *c, int n, int n_seq) {
+    llama_kv_cache &kv = ((rr_ctx *)c)->ctx->kv_self;
+    if ((uint32_t)n > kv.size) return -1;
+    for (uint32_t i = 0; i < kv.size; i++) { kv.cells[i].pos = -1; kv.cells[i].seq_id.clear(); kv.cells[i].delta = 0; }
+    for (int i = 0; i < n; i++) { kv.cells[i].pos = i; for (int s = 0; s < n_seq; s++) kv.cells[i].seq_id.insert(s); }
+    kv.head = n; kv.used = n;
+    return 0;
+}
+
 // time one llama_decode of a tree batch (the CPU arm of bench.py): returns microseconds (ggml_time_us), < 0 on failure
 int64_t rr_time_decode(void *c, int n, const int32_t *tok, const int32_t *pos, const int32_t *n_seq, const int32_t *seq, int max_seq) {
     rr_ctx *r = (rr_ctx *)c;

@@ -45,6 +45,7 @@ def lib(native=False):
         l.rr_kv_defrag.argtypes = [vp]
         l.rr_kv_cells.argtypes = [vp, vp, vp, i32]
         l.rr_kv_read_row.argtypes = [vp, i32, i32, i32, vp, i32]
+        l.rr_kv_write_rows.argtypes = [vp, i32, i32, i32, i32, vp, i32]; l.rr_kv_set_prefix.argtypes = [vp, i32, i32]
         l.rr_time_decode.argtypes = [vp, i32, vp, vp, vp, vp, i32]; l.rr_time_decode.restype = i64
         _lib = l
     return _lib
@@ -155,6 +156,15 @@ class Context:
         if self.l.rr_kv_read_row(self.h, layer, which, cell, _p(out), E) != 0:
             raise RuntimeError("kv_read_row: cache is not f16 / V is transposed")
         return out
+
+    def kv_write(self, layer, which, cell0, rows):
+        rows = np.ascontiguousarray(rows).view(np.uint16)
+        if self.l.rr_kv_write_rows(self.h, layer, which, cell0, rows.shape[0], _p(rows), rows.shape[1]) != 0:
+            raise RuntimeError("kv_write: cache is not f16 / V is transposed")
+
+    def kv_set_prefix(self, n, n_seq=1):
+        if self.l.rr_kv_set_prefix(self.h, n, n_seq) != 0:
+            raise RuntimeError("kv_set_prefix")
 
     def seq_rm(self, s, p0, p1): self.l.rr_kv_seq_rm(self.h, s, p0, p1)
     def seq_cp(self, a, b, p0=-1, p1=-1): self.l.rr_kv_seq_cp(self.h, a, b, p0, p1)

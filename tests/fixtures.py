@@ -125,6 +125,23 @@ def tree_parents(T, rng, n_branch=4):
     return par
 
 
+def driver_like_tree(T, n_branch, rng):
+    """a verify tree shaped like the reference tree driver's (-np n_branch): the root, branches that split off within the first
+    levels (p_split), then every branch extends as a chain, one node per branch per depth level, until T nodes exist"""
+    par = [-1]; tips = [0]
+    while len(par) < T:
+        nxt = []
+        n_now = len(tips)                                  # branches alive at this depth (+ the ones opened below)
+        for tip in tips:
+            if len(par) >= T:
+                break
+            par.append(tip); nxt.append(len(par) - 1)
+            if n_now < n_branch and len(par) < T and rng.random() < 0.5:
+                par.append(tip); nxt.append(len(par) - 1); n_now += 1
+        tips = nxt
+    return np.array(par[:T], np.int32)
+
+
 def tree_seq_ids(par):
     """seq-id sets as the reference's tree driver assigns them (R/examples/speculative/speculative-eagle.cpp:556-625): one branch
     per root-to-leaf path; a node's FIRST id is the branch that created it, followed by the branches that split off below it."""

@@ -32,6 +32,7 @@ def site_widths(hp, logits=True):
 
 
 def flipped_rows(planes_a, planes_b):
+    # (simple form, used where both sides are whole-model reference runs)
     """-> bool [T]: row t has at least one differing int8 value at any site; and the per-site count of differing rows"""
     T = planes_a[0].shape[0]
     bad = np.zeros(T, bool); per_site = []
@@ -87,25 +88,51 @@ def greedy_report(a, b, tie=TIE_REL):
     return bad, ties, len(a)
 
 
-def check_forward(tag, lg, lo, planes_g=None, planes_o=None, max_flip_frac=0.5, clean_rel=NORTH_STAR_REL, flip_rel=FLIP_REL):
-    """the model-level bar.  Returns a dict of the numbers (also printed: `pytest -s` / the driver's log shows them)."""
+def classify_rows(planes_g, planes_o, vis=None, is_eagle=False):
+    """-> (dirty [T], primary [T], per-site differing-row counts).  dirty: the row has a differing int8 value at some site.
+    primary: the row's FIRST difference is a rounding flip of its own — not explained by attention over an already-dirty row
+    (attention mixes rows: once row r differs, layer l+1's K/V of r differ and every row that sees r inherits a perturbation at
+    its wo input; that is propagation of r's flip, not a new one).  vis [T][T]: row t sees row r (None: rows are independent)."""
+    T = planes_g[0].shape[0]
+    dirty = np.zeros(T, bool); primary = np.zeros(T, bool); per_site = []
+    off = 1 if is_eagle else 0
+    for si, (a, b) in enumerate(zip(planes_g, planes_o)):
+        assert a.shape == b.shape, (a.shape, b.shape)
+        d = (a != b).any(1)
+        per_site.append(int(d.sum()))
+        new = d & ~dirty
+        attn_site = si >= off and (si - off) % 4 == 1 and si < len(planes_g) - 1
+        if attn_site and vis is not None:
+            others = np.array(vis, bool).copy(); np.fill_diagonal(others, False)
+            contaminated = (others & dirty[None, :]).any(1)
+            primary |= new & ~contaminated
+        else:
+            primary |= new
+        dirty |= d
+    return dirty, primary, per_site
+
+
+def check_forward(tag, lg, lo, planes_g=None, planes_o=None, max_flip_frac=0.2, clean_rel=NORTH_STAR_REL, flip_rel=FLIP_REL, vis=None, is_eagle=False):
+    """the model-level bar.  Rows whose int8 activation planes are identical on both sides at every site must agree to clean_rel;
+    rows with a difference (a detected rounding flip of their own, or one inherited through attention) to flip_rel; the share of
+    rows with a PRIMARY flip is bounded by max_flip_frac.  Returns the numbers (also printed: `pytest -s` shows them)."""
     rel = row_rel(lg, lo)
     T = len(rel)
     if planes_g is not None:
-        flipped, per_site = flipped_rows(planes_g, planes_o)
+        dirty, primary, per_site = classify_rows(planes_g, planes_o, vis, is_eagle)
     else:
-        flipped, per_site = np.zeros(T, bool), []
-    clean = ~flipped
+        dirty, primary, per_site = np.zeros(T, bool), np.zeros(T, bool), []
+    clean = ~dirty
     bad, ties, _ = greedy_report(lg, lo)
-    rep = dict(tag=tag, rows=T, flipped=int(flipped.sum()), clean_max_rel=float(rel[clean].max()) if clean.any() else 0.0,
-               flipped_max_rel=float(rel[flipped].max()) if flipped.any() else 0.0, greedy_bad=bad, ties=ties)
-    print(f"[parity] {tag}: rows {T}, flipped {rep['flipped']} ({100.0 * rep['flipped'] / T:.1f} %), clean max rel {rep['clean_max_rel']:.2e}, "
-          f"flipped max rel {rep['flipped_max_rel']:.2e}, greedy mismatches {bad}, flagged ties {ties}" + (f", first flips per site {per_site}" if per_site else ""))
+    rep = dict(tag=tag, rows=T, dirty=int(dirty.sum()), flipped=int(primary.sum()), clean_max_rel=float(rel[clean].max()) if clean.any() else 0.0,
+               flipped_max_rel=float(rel[dirty].max()) if dirty.any() else 0.0, greedy_bad=bad, ties=ties)
+    print(f"[parity] {tag}: rows {T}, primary flips {rep['flipped']} ({100.0 * rep['flipped'] / T:.1f} %), rows with differing planes {rep['dirty']}, "
+          f"clean max rel {rep['clean_max_rel']:.2e}, differing-row max rel {rep['flipped_max_rel']:.2e}, greedy mismatches {bad}, undecided at {TIE_REL:.0e}: {ties}"
+          + (f", differing rows per site {per_site}" if per_site else ""))
     assert rep["clean_max_rel"] <= clean_rel, rep
     assert rep["flipped_max_rel"] <= flip_rel, rep
-    assert rep["flipped"] <= max_flip_frac * T, rep
-    assert ties <= max(1, MAX_TIE_FRAC * T), rep
-    # greedy ids: identical on every decided row that did not flip; a flipped row may legitimately move a near-decision
+    assert rep["flipped"] <= max(2, max_flip_frac * T), rep
+    # greedy ids: identical on every decided row whose planes are identical; a differing row may legitimately move a near-decision
     bad_clean, _, _ = greedy_report(lg[clean], lo[clean]) if clean.any() else (0, 0, 0)
     assert bad_clean == 0, rep
     return rep

@@ -33,7 +33,7 @@ MODEL_NMSE = 2e-3
 # vs the oracle in f32-accumulator mode the bar is parity.check_forward: rows without a DETECTED rounding flip (identical int8
 # activation planes at every quantisation site, engine tap vs oracle tap) must meet CLEAN_REL — two orders below the north star's
 # 1e-2, they measure ~1e-6 —, flipped rows are counted, bounded (MAX_FLIP) and held to parity.FLIP_REL.
-CLEAN_REL, MAX_FLIP = 1e-4, 0.35
+CLEAN_REL, MAX_FLIP = 1e-4, 0.2
 
 
 def greedy_agree(a, b, tie=TIE_REL, tag="greedy"):
@@ -79,8 +79,8 @@ def test_tiny_model_vs_golden(eb):
     lg2, _, pl_g = s2.forward_tapped(0, prompt, np.arange(P)); s2.commit(0, P)
     lg2_t, _, pl_gt = s2.forward_tapped(0, z["tree_tokens"], z["tree_pos"], parent=z["tree_parent"])
     assert np.array_equal(lg2, lg) and np.array_equal(lg2_t, lg_t)          # the tap does not change the forward
-    pa.check_forward("tiny prefill vs oracle(f32 acc)", lg, lo, pl_g, pl_o, MAX_FLIP, CLEAN_REL)
-    pa.check_forward("tiny tree vs oracle(f32 acc)", lg_t, lo_t, pl_gt, pl_ot, MAX_FLIP, CLEAN_REL)
+    pa.check_forward("tiny prefill vs oracle(f32 acc)", lg, lo, pl_g, pl_o, MAX_FLIP, CLEAN_REL, vis=np.tril(np.ones((P, P), bool)))
+    pa.check_forward("tiny tree vs oracle(f32 acc)", lg_t, lo_t, pl_gt, pl_ot, MAX_FLIP, CLEAN_REL, vis=po.tree_vis(z["tree_parent"]))
     s2.free()
     # get_tensor returns the GGUF bytes that were uploaded (bit-exact weights)
     for which, (t, raw) in tgt["layers"][0].items():
@@ -106,7 +106,7 @@ def test_independent_rows_rounding_flips(eb):
         vis = np.zeros((P, n_ctx), np.uint8); vis[np.arange(P), np.arange(P)] = 1
         lo, _, pl_o = oracle_tapped(o, mo, kv, tgt["hparams"], prompt, np.zeros(P, np.int32), None, 0, n_ctx, vis)
         lg, _, pl_g = s.forward_tapped(0, prompt, np.zeros(P, np.int32), parent=np.full(P, -1, np.int32))
-        rep = pa.check_forward(f"independent rows seed {seed}", lg, lo, pl_g, pl_o, 0.25, 1e-5)
+        rep = pa.check_forward(f"independent rows seed {seed}", lg, lo, pl_g, pl_o, 0.25, 1e-5, vis=np.eye(P, dtype=bool))
         flips += rep["flipped"]; total += P
         s.free()
     po.set_fattn_acc_f32(0)
@@ -131,7 +131,7 @@ def test_forward_vs_oracle(eb, ftype, T):
     po.set_fattn_acc_f32(1)
     lo, fo, pl_o = oracle_tapped(o, mo, kv, tgt["hparams"], prompt, np.arange(P), None, 0, n_ctx, vis)
     lg, fg, pl_g = s.forward_tapped(0, prompt, np.arange(P))
-    pa.check_forward(f"prefill {ftype} vs oracle(f32 acc)", lg, lo, pl_g, pl_o, MAX_FLIP, CLEAN_REL)
+    pa.check_forward(f"prefill {ftype} vs oracle(f32 acc)", lg, lo, pl_g, pl_o, MAX_FLIP, CLEAN_REL, vis=np.tril(np.ones((P, P), bool)))
     assert nmse(lg, lo) < MODEL_NMSE
     s.commit(0, P)
     par = fx.tree_parents(T, rng, 6)
@@ -139,7 +139,8 @@ def test_forward_vs_oracle(eb, ftype, T):
     lo, fo, pl_o = oracle_tapped(o, mo, kv, tgt["hparams"], toks, pos, None, P, n_ctx, fx.vis_matrix(par, P, n_ctx))
     po.set_fattn_acc_f32(0)
     lg, fg, pl_g = s.forward_tapped(0, toks, pos, parent=par)
-    pa.check_forward(f"tree T={T} {ftype} vs oracle(f32 acc)", lg, lo, pl_g, pl_o, MAX_FLIP, CLEAN_REL)
+    # the prefix may already carry flipped rows (their K/V differ), which every tree row sees: no primary / inherited split here
+    pa.check_forward(f"tree T={T} {ftype} vs oracle(f32 acc)", lg, lo, pl_g, pl_o, 1.0, CLEAN_REL)
     assert nmse(lg, lo) < MODEL_NMSE and nmse(fg, fo) < MODEL_NMSE
     s.free()
 
@@ -273,7 +274,7 @@ def test_forward_7b_width_one_layer(eb):
     lo, fo, pl_o = oracle_tapped(o, mo, kv, tgt["hparams"], toks, pos, None, P, n_ctx, fx.vis_matrix(par, P, n_ctx))
     po.set_fattn_acc_f32(0)
     lg, fg, pl_g = s.forward_tapped(0, toks, pos, parent=par)
-    pa.check_forward("7B-width layer, 65-row tree vs oracle(f32 acc)", lg, lo, pl_g, pl_o, MAX_FLIP, CLEAN_REL)
+    pa.check_forward("7B-width layer, 65-row tree vs oracle(f32 acc)", lg, lo, pl_g, pl_o, 1.0, CLEAN_REL)
     assert nmse(lg, lo) < MODEL_NMSE and nmse(fg, fo) < MODEL_NMSE
     s.free()
 
