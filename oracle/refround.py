@@ -14,13 +14,22 @@ def have():
     return os.path.exists(os.path.join(REF, "libref_round.so"))
 
 
-def lib(native=False):
-    """native=True loads the -march=native ggml build under libllama (timed CPU arm only)"""
-    global _lib
+VARIANTS = {"ref": "libggml-ref.so",          # the reference's ggml-cpu, deterministic flags: THE parity oracle
+            "native": "libggml-native.so",    # same sources, -march=native + llamafile + repack: the timed CPU arm only
+            "f32acc": "libggml-f32acc.so"}    # attribution instrument: f32 flash-attention V accumulator, nothing else changed
+_variant = None
+
+
+def lib(native=False, variant=None):
+    """One ggml build per process (all three carry the soname libggml-ref.so; the first one loaded serves libllama-ref.so).
+    variant: "ref" (default) | "native" | "f32acc"; the environment variable EB_REF_GGML overrides the default."""
+    global _lib, _variant
+    want = variant or ("native" if native else os.environ.get("EB_REF_GGML", "ref"))
+    if _lib is not None and want != _variant and (variant or native):
+        raise RuntimeError(f"refround: ggml variant {_variant!r} is already loaded in this process, cannot switch to {want!r}")
     if _lib is None:
-        ggml = "libggml-native.so" if native else "libggml-ref.so"
-        # libllama-ref.so names libggml-ref.so as a dependency: for the native arm the symbols are provided first, globally
-        C.CDLL(os.path.join(REF, ggml), mode=C.RTLD_GLOBAL)
+        _variant = want
+        C.CDLL(os.path.join(REF, VARIANTS[want]), mode=C.RTLD_GLOBAL)
         l = C.CDLL(os.path.join(REF, "libref_round.so"), mode=C.RTLD_GLOBAL)
         vp, i32, i64 = C.c_void_p, C.c_int, C.c_int64
         l.rr_load_backend.argtypes = [C.c_char_p]
@@ -65,8 +74,8 @@ def seq_arrays(seq_sets, max_seq=8):
 
 
 class Model:
-    def __init__(self, path, n_gpu_layers=0, native=False):
-        self.l = lib(native)
+    def __init__(self, path, n_gpu_layers=0, native=False, variant=None):
+        self.l = lib(native, variant)
         self.h = self.l.rr_model_load(path.encode(), n_gpu_layers)
         if not self.h:
             raise RuntimeError(f"reference loader rejected {path}")
