@@ -218,9 +218,8 @@ fattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
             FA_CK(3);
             const float base = m == -INFINITY ? 0.f : m * c;
             float rs[4] = {0.f, 0.f, 0.f, 0.f};                                // independent partial row sums (ILP)
-#pragma unroll
-            for (int ch = 0; ch < 4; ch++) {                                   // 32 cells at a time: their hi and lo pairs live together
-                uint32_t ph[16], pl[16];
+            // 32 cells at a time: their hi and lo pairs live together
+            auto exp_chunk = [&](int ch, uint32_t (&ph)[16], uint32_t (&pl)[16]) {
 #pragma unroll
                 for (int k = 0; k < 32; k += 2) {
                     const float p0 = ex2(fmaf(__uint_as_float(sr[ch][k]), c, -base)), p1 = ex2(fmaf(__uint_as_float(sr[ch][k + 1]), c, -base));
@@ -230,6 +229,22 @@ fattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
                     ph[k >> 1] = *(const uint32_t *)&hi;
                     pl[k >> 1] = pack_h2(p0 - hf2.x, p1 - hf2.y);
                 }
+            };
+            {
+                uint32_t ph0[16], pl0[16], ph1[16], pl1[16];
+                exp_chunk(0, ph0, pl0); exp_chunk(1, ph1, pl1);
+                // P(i) is written only after PV(i-1) has completed, for EVERY warp (not just the ones that rescaled above).  Measured
+                // (tools/diag_attn.py, 4K cells, score std 3): with 16 PV MMAs per tile the softmax of a warp that did not rescale
+                // can reach its tcgen05.st while PV(i-1) is still executing, and the outputs then differ from run to run (1e-2 ..
+                // 3e-1 off); with this wait they are deterministic and within 4e-6 of float64.  Half of the exponentials are
+                // computed before the wait so that it overlaps the tensor pipe.
+                if (i > 0) { mbar_wait(bars + FB_O_DONE * 8, (i - 1) & 1); fence_after(); }
+                tmem_st16(ts, ph0); tmem_st16(ts + 64, pl0); tmem_st16(ts + 16, ph1); tmem_st16(ts + 64 + 16, pl1);
+            }
+#pragma unroll
+            for (int ch = 2; ch < 4; ch++) {
+                uint32_t ph[16], pl[16];
+                exp_chunk(ch, ph, pl);
                 tmem_st16(ts + ch * 16, ph); tmem_st16(ts + 64 + ch * 16, pl);
             }
             l += (rs[0] + rs[1]) + (rs[2] + rs[3]);

@@ -100,6 +100,18 @@ def run(cfg_id, variant, tmp_dir):
                greedy_identical=int(T - undecided - bad), greedy_undecided=int(undecided), greedy_mismatch=int(bad),
                kv_layer0_bit_identical=[float((k_g == k_o).mean()), float((v_g == v_o).mean())],
                setup_s=round(t1 - t0, 1), reference_decode_s=round(t2 - t1, 2), host_threads=os.cpu_count())
+    if os.environ.get("EB_FULLSIZE_DEBUG"):
+        print("per_site[:16]", per_site[:16], "rel per row", np.round(rel, 4).tolist(), file=sys.stderr)
+        d0 = (pl_g[0] != pl_o[0])
+        print("site0 differing rows", np.nonzero(d0.any(1))[0].tolist(), "elements", int(d0.sum()), file=sys.stderr)
+        r0 = int(np.nonzero(d0.any(1))[0][0]) if d0.any() else 0
+        cols = np.nonzero(d0[r0])[0][:8]
+        print("row", r0, "cols", cols.tolist(), "gpu", pl_g[0][r0, cols].tolist(), "ref", pl_o[0][r0, cols].tolist(), "ref x", taps[0][1][r0, cols].tolist(), file=sys.stderr)
+        t, raw = tgt["globals"][po.T_TOK_EMBD]
+        emb = po.ref().get_rows(t, raw, hp["E"], hp["V"], tokens)
+        x = po.ref().rms_norm(emb, 1e-5) * tgt["layers"][0][po.L_ATTN_NORM][1].view(np.float32)[None, :]
+        print("reference tap site0 == recomputed norm(embedding):", np.array_equal(x.astype(np.float32), taps[0][1]), float(np.abs(x - taps[0][1]).max()), file=sys.stderr)
+        print("tap names[:8]", [n for n, _ in taps[:8]], file=sys.stderr)
     s.free(); c.free(); m.free()
     return out
 
