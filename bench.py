@@ -30,7 +30,17 @@ N_PAST0 = 4096 - 65                                       # KV cells committed b
 TREE = dict(max_nodes=65, n_branch=8, n_draft=64, max_depth=10, top_k=10, p_split=0.1)
 FIXED_ACCEPT = 3
 Q4_K_BPW, Q6_K_BPW = 144 / 256, 210 / 256
-ROOFLINE_TRAFFIC_BYTES = 51.65e6   # profiles/r1c_summary.md: ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum per launch, N=22016 K=4096 T=65
+
+
+def roofline_traffic():
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel at the bench shape, from the committed
+    `ncu --set full` capture of the SHIPPED kernel (profiles/r2_ncu_traffic.json, written by tools/ncu_extract.py); null without it"""
+    try:
+        d = json.load(open(os.path.join(ROOT, "profiles", "r2_ncu_traffic.json")))
+        return float(d["dram_bytes_per_launch"])
+    except Exception:
+        return None
+
 
 
 def q4_k_m_more_bits(l, n):                               # R/src/llama-quant.cpp:129-131
@@ -135,12 +145,16 @@ def run_gpu(args, rank, world, local_rank):
         torch.cuda.set_device(local_rank)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     tgt, head = build_gpu_models(eb)
-    s = eb.Session(tgt, head, n_ctx=4096 + 256, fixed_accept=FIXED_ACCEPT, use_graph=True, **TREE)
+    # room for every timed round (4 committed tokens each) after the 4K prefix, + one tree
+    n_ctx = (N_PAST0 + (FIXED_ACCEPT + 1) * (args.steps + 1) + TREE["max_nodes"] + TREE["n_branch"] + 255) // 256 * 256
+    s = eb.Session(tgt, head, n_ctx=max(n_ctx, 4096 + 256), fixed_accept=FIXED_ACCEPT, use_graph=True, **TREE)
     s.synth_kv(N_PAST0, seed=replica_seed(rank))
     s.set_root(1)
     tok = 1
     res = None
-    for _ in range(max(args.warmup, 3)):
+    for w in range(max(args.warmup, 3)):
+        if w and w % 16 == 0:
+            s.synth_kv(N_PAST0, seed=replica_seed(rank))     # long warm-ups stay inside the context
         s.set_root(tok); res = s.round(); tok = res.bonus
     # rewind the KV length so that the timed rounds sit around the 4K mark
     s.synth_kv(N_PAST0, seed=replica_seed(rank)); s.set_root(tok)
@@ -156,17 +170,20 @@ def run_gpu(args, rank, world, local_rank):
     t0 = time.perf_counter()
     gpu_ms = 0.0
     nodes = []
+    committed = 0
     for _ in range(args.steps):
         s.set_root(tok)                      # H2D: the step's input (last accepted token id), 4 bytes
         res = s.round()                      # D2H: eb_round_result (accepted ids, tree) — the step's result
         tok = res.bonus; gpu_ms += res.gpu_ms; nodes.append(res.n_nodes)
+        committed += res.n_accept            # accepted nodes incl. the root = tokens this round committed (fixed_accept drafted + bonus)
+    assert committed == (FIXED_ACCEPT + 1) * args.steps, f"rounds committed {committed} tokens, expected {(FIXED_ACCEPT + 1) * args.steps}: the synthetic tree is shallower than fixed_accept"
     eb.lib().eb_synchronize(None)
     t1 = time.perf_counter()
     launches = eb.launch_count()
     wall_ms = (t1 - t0) * 1e3
     wall_ms, gpu_ms = max_over_ranks(dist, [wall_ms, gpu_ms], "cuda")
     clocks = sampler.summary()
-    tokens = job_tokens(args.steps, world)
+    tokens = committed * world               # every replica runs the same fixed-acceptance schedule (asserted above on each rank)
     out = None
     if rank == 0:
         hbm, peak_src = peaks()
@@ -181,16 +198,14 @@ def run_gpu(args, rank, world, local_rank):
         k_bytes = kN * kK * Q4_K_BPW
         achieved = k_bytes / (k_ms * 1e-3) / 1e9
         mv_ms = eb.bench_mul_mat_kernel(eb.Q4_K, kN, kK, 1, n_bufs=8, iters=200)
-        traffic = ROOFLINE_TRAFFIC_BYTES      # dram bytes per launch of the same kernel/shape from the committed ncu capture (profiles/)
+        traffic = roofline_traffic()
         out = {
             "metric": "eagle_decode_tok_per_s", "value": tokens / (gpu_ms * 1e-3), "unit": "tok/s",
             "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": gpu_ms / args.steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int8xq4_K/q6_K dot, f32 accumulate, f16 KV",
             "data": "synthetic (random-init Q4_K_M blocks, N(0,1) f16 KV prefill, fixed accept length 3)",
-            "config": {"workload": "vicuna-7b Q4_K_M + EAGLE head, 64-node tree (65-row verify batch), KV ~4096, batch 1, fixed_accept=3",
-                       "tree": TREE, "n_kv_at_verify": 4096, "tree_nodes_median": int(np.median(nodes)),
-                       "l2": "weights (4.0 GB) + KV (2.1 GB) per step exceed L2 (126 MB): no flush needed",
-                       "parallelism": f"replicas x{world}, no collective"},
+            "config": config_dict(f"replicas x{world}, no collective", int(np.median(nodes)),
+                                  "weights (4.0 GB) + KV (2.1 GB) per step exceed L2 (126 MB): no flush needed"),
             "e2e": {"value": tokens / (wall_ms * 1e-3), "unit": "tok/s", "h2d_bytes_per_step": 4, "d2h_bytes_per_step": 1552},
             "gpu_launches": launches,
             "verify_step_us": verify_us,
@@ -203,7 +218,7 @@ def run_gpu(args, rank, world, local_rank):
         }
         if world == 1 and not args.no_cpu_baseline:
             try:
-                out["cpu_baseline"] = cpu_baseline(budget_s=25.0)
+                out["cpu_baseline"] = cpu_baseline(n_rounds=3)
             except Exception as e:                     # the baseline is a reported number, never the product path
                 out["cpu_baseline"] = {"error": str(e)}
     s.free()
@@ -213,127 +228,151 @@ def run_gpu(args, rank, world, local_rank):
 
 
 # ------------------------------------------------------------------------------------------ CPU arm
-def _rand_blocks(t, n_elems, rng):
-    sys.path.insert(0, os.path.join(ROOT, "tests"))
-    import fixtures as fx
-    return fx.random_blocks(t, n_elems, rng)
+WORKLOAD = "vicuna-7b Q4_K_M + EAGLE head, 64-node tree (65-row verify batch), KV ~4096, batch 1, fixed_accept=3"
 
 
-class CpuSlice:
-    """The reference's ggml-cpu path (or the oracle port) on a slice of the 7B workload."""
+def config_dict(parallelism, nodes_median, l2):
+    """the same key set in both arms (the driver compares them)"""
+    return {"workload": WORKLOAD, "tree": TREE, "n_kv_at_verify": 4096, "tree_nodes_median": nodes_median, "l2": l2, "parallelism": parallelism}
+
+
+def native_cpu_ok():
+    """oracle/_ref/libggml-native.so was built with -march=native where the repository was built; it may only run on a host whose
+    ISA covers that machine's (oracle/_ref/native.cpuflags, written by oracle/Makefile)"""
+    f = os.path.join(ROOT, "oracle", "_ref", "native.cpuflags")
+    if not os.path.exists(f) or not os.path.exists(os.path.join(ROOT, "oracle", "_ref", "libggml-native.so")):
+        return False
+    need = set(open(f).read().split())
+    have = set()
+    for line in open("/proc/cpuinfo"):
+        if line.startswith("flags"):
+            have = set(line.split(":", 1)[1].split()); break
+    isa = {x for x in need if x.startswith(("avx", "amx", "fma", "f16c", "bmi", "sse4", "gfni", "vaes", "vpclmul"))}
+    return isa <= have
+
+
+class CpuRound:
+    """The reference's own CPU implementation of one round, measured, not extrapolated: the tree-verify forward is ONE llama_decode
+    (R/src/llama.cpp:11916) of the reference's libllama over the 65-token tree batch on a 32-layer Vicuna-7B-shaped Q4_K_M GGUF with
+    4031 committed KV cells; the draft side is the reference's build_eagle graph (oracle/ref_harness.cpp, same ggml-cpu) run for
+    every one of the max_depth + 1 levels.  ggml build: -march=native + llamafile + repack (the reference's default cmake
+    configuration) when this host's ISA allows it, else the deterministic AVX2 build — named in `kind_detail`."""
 
     def __init__(self):
-        sys.path.insert(0, os.path.join(ROOT, "oracle"))
+        import tempfile
+        sys.path.insert(0, os.path.join(ROOT, "oracle")); sys.path.insert(0, os.path.join(ROOT, "tests"))
+        import fixtures as fx
+        import fullsize_run as fr
+        import gguf_fixture as gf
         import pyoracle as po
-        self.po = po
-        if po.have_ref():
-            self.path = po.ref()
-            flags = open("/proc/cpuinfo").read()
-            self.cores = len(os.sched_getaffinity(0))
-            self.path._g("set_threads")(self.cores)
-            assert "avx2" in flags and "fma" in flags, "oracle/_ref needs AVX2+FMA"
-        else:
-            self.path = po.oracle()
-            self.cores = len(os.sched_getaffinity(0))
-        self.kind = self.path.kind
-        rng = np.random.default_rng(0)
-        E, F, V = HP["E"], HP["F"], HP["V"]
-        self.keep = []
-
-        def blocks(t, n):
-            a = _rand_blocks(t, n, rng); self.keep.append(a); return a
-
-        self.emb = blocks(po.Q4_K, V * E); self.out = blocks(po.Q6_K, V * E)
-        self.norm = np.ones(E, np.float32)
-        self.layer = {po.L_ATTN_NORM: (po.F32, self.norm), po.L_FFN_NORM: (po.F32, self.norm),
-                      po.L_WQ: (po.Q4_K, blocks(po.Q4_K, E * E)), po.L_WK: (po.Q4_K, blocks(po.Q4_K, E * E)),
-                      po.L_WV: (po.Q6_K, blocks(po.Q6_K, E * E)), po.L_WO: (po.Q4_K, blocks(po.Q4_K, E * E)),
-                      po.L_GATE: (po.Q4_K, blocks(po.Q4_K, F * E)), po.L_UP: (po.Q4_K, blocks(po.Q4_K, F * E)),
-                      po.L_DOWN: (po.Q4_K, blocks(po.Q4_K, E * F))}
-        self.fc = blocks(po.Q4_K, 2 * E * E); self.fc_b = np.zeros(E, np.float32)
-        self.n_ctx = 4096 + 64
-        self.models = {}
-
-    def model(self, L, eagle):
-        key = (L, eagle)
-        if key in self.models:
-            return self.models[key]
-        po, p = self.po, self.path
-        m = p.model_new(HP["E"], HP["H"], HP["F"], HP["V"], L, 1e-5, 10000.0, eagle)
-        p._g("model_set_global")(m, po.T_TOK_EMBD, po.Q4_K, po._ptr(self.emb))
-        p._g("model_set_global")(m, po.T_OUTPUT, po.Q6_K, po._ptr(self.out))
-        if eagle:
-            p._g("model_set_global")(m, po.T_FC, po.Q4_K, po._ptr(self.fc)); p._g("model_set_global")(m, po.T_FC_BIAS, po.F32, po._ptr(self.fc_b))
-        else:
-            p._g("model_set_global")(m, po.T_OUTPUT_NORM, po.F32, po._ptr(self.norm))
-        for l in range(L):
-            for which, (t, raw) in self.layer.items():
-                if eagle and which == po.L_ATTN_NORM:
-                    continue
-                p._g("model_set_layer")(m, l, which, t, po._ptr(raw))
-        kv = p._g("kv_new")(max(L, 1), HP["E"], self.n_ctx)
-        ks, vs = p.kv_arrays(kv, max(L, 1), HP["E"], self.n_ctx)
-        rng = np.random.default_rng(1)
-        for a in ks + vs:
-            a[:N_PAST0] = rng.normal(0, 1, (N_PAST0, HP["E"])).astype(np.float16).view(np.uint16)
-        self.models[key] = (m, kv)
-        return self.models[key]
-
-    def forward_s(self, L, eagle, T):
-        m, kv = self.model(L, eagle)
-        tokens = (np.arange(T) * 37 % 1000).astype(np.int32)
-        pos = (N_PAST0 + np.arange(T)).astype(np.int32)
-        vis = np.zeros((T, self.n_ctx), np.uint8); vis[:, :N_PAST0] = 1
-        vis[:, N_PAST0:N_PAST0 + T] = np.tril(np.ones((T, T), np.uint8))
-        hid = np.zeros((T, HP["E"]), np.float32) if eagle else None
+        import refround as rr
+        if not rr.have():
+            raise RuntimeError("oracle/_ref (the reference build) is missing")
+        self.variant = "native" if native_cpu_ok() else "ref"
+        self.cores = len(os.sched_getaffinity(0))
+        rr.lib(variant=self.variant)                       # the ggml build of this process, loaded before anything else links ggml
+        self.po, self.fx = po, fx
         t0 = time.perf_counter()
-        self.path.forward(m, kv, tokens, pos, hid, N_PAST0, self.n_ctx, vis, HP["E"], HP["V"])
+        tgt = fr.random_model(HP, "q4_k_m", 7)
+        tmp = tempfile.mkdtemp(prefix="eb_bench_")
+        path = gf.write_gguf(tgt, os.path.join(tmp, "vicuna7b_q4_k_m_random.gguf"), n_ctx_train=8192)
+        self.m = rr.Model(path, variant=self.variant)
+        os.remove(path); os.rmdir(tmp)
+        rng = np.random.default_rng(11)
+        self.par = fx.driver_like_tree(65, TREE["n_branch"], rng); self.depth = fx.tree_depths(self.par)
+        self.seqs, n_seq = fx.tree_seq_ids(self.par)
+        self.c = rr.Context(self.m, 4096 + 256, n_batch=512, n_seq_max=max(8, n_seq), n_threads=self.cores)
+        for l in range(HP["L"]):
+            for which in (0, 1):
+                self.c.kv_write(l, which, 0, rng.standard_normal((N_PAST0, HP["E"]), np.float32).astype(np.float16))
+        self.n_seq = n_seq
+        self.tokens = rng.integers(3, HP["V"], 65).astype(np.int32)
+        # draft head: build_eagle on the same ggml-cpu (lm_head = the target's output matrix)
+        self.ref = po.ref(); self.ref._g("set_threads")(self.cores)
+        E, F, V = HP["E"], HP["F"], HP["V"]
+        self.keep = [tgt]
+        hm = self.ref.model_new(E, HP["H"], F, V, 1, 1e-5, 10000.0, True)
+        hr = np.random.default_rng(12)
+        def blocks(t, n):
+            a = fx.random_blocks(t, n, hr); self.keep.append(a); return a
+        fcb = np.zeros(E, np.float32); ones = np.ones(E, np.float32); self.keep += [fcb, ones]
+        g = self.ref._g
+        g("model_set_global")(hm, po.T_TOK_EMBD, po.Q4_K, po._ptr(tgt["globals"][po.T_TOK_EMBD][1]))
+        g("model_set_global")(hm, po.T_OUTPUT, po.Q6_K, po._ptr(tgt["globals"][po.T_OUTPUT][1]))
+        g("model_set_global")(hm, po.T_FC, po.Q4_K, po._ptr(blocks(po.Q4_K, 2 * E * E))); g("model_set_global")(hm, po.T_FC_BIAS, po.F32, po._ptr(fcb))
+        for which, (t, n) in {po.L_WQ: (po.Q4_K, E * E), po.L_WK: (po.Q4_K, E * E), po.L_WV: (po.Q6_K, E * E), po.L_WO: (po.Q4_K, E * E),
+                              po.L_GATE: (po.Q4_K, F * E), po.L_UP: (po.Q4_K, F * E), po.L_DOWN: (po.Q6_K, E * F)}.items():
+            g("model_set_layer")(hm, 0, which, t, po._ptr(blocks(t, n)))
+        g("model_set_layer")(hm, 0, po.L_FFN_NORM, po.F32, po._ptr(ones))
+        self.hm = hm
+        self.h_ctx = 4096 + 64
+        self.hkv = g("kv_new")(1, E, self.h_ctx)
+        ks, vs = self.ref.kv_arrays(self.hkv, 1, E, self.h_ctx)
+        for a in ks + vs:
+            a[:N_PAST0] = hr.standard_normal((N_PAST0, E), np.float32).astype(np.float16).view(np.uint16)
+        self.setup_s = time.perf_counter() - t0
+
+    def verify_s(self):
+        """one llama_decode of the 65-token tree batch at n_kv = 4096 (the tree's cells are released again afterwards)"""
+        self.c.kv_set_prefix(N_PAST0, self.n_seq)
+        us = self.c.time_decode(self.tokens, N_PAST0 + self.depth, self.seqs)
+        return us * 1e-6
+
+    def head_level_s(self):
+        """one draft level: the head over n_branch rows + (host) top-k is negligible next to it"""
+        T = TREE["n_branch"]
+        tokens = (np.arange(T) * 37 % 1000).astype(np.int32); pos = np.full(T, N_PAST0, np.int32)
+        vis = np.zeros((T, self.h_ctx), np.uint8); vis[:, :N_PAST0] = 1; vis[np.arange(T), N_PAST0 + np.arange(T)] = 1
+        hid = np.zeros((T, HP["E"]), np.float32)
+        t0 = time.perf_counter()
+        self.ref.forward(self.hm, self.hkv, tokens, pos, hid, N_PAST0, self.h_ctx, vis, HP["E"], HP["V"])
         return time.perf_counter() - t0
 
-    def round_seconds(self, t_layer_plus, t_overhead, t_head):
-        per_layer = max(t_layer_plus - t_overhead, 1e-9)
-        verify = HP["L"] * per_layer + t_overhead
-        return verify + (TREE["max_depth"] + 1) * t_head, verify
+    def round_s(self):
+        v = self.verify_s()
+        h = sum(self.head_level_s() for _ in range(TREE["max_depth"] + 1))
+        return v + h, v
+
+    def describe(self):
+        return {"cores": self.cores, "kind": "reference",
+                "kind_detail": ("reference libllama + ggml-cpu, -march=native + llamafile sgemm + runtime repack" if self.variant == "native"
+                                else "reference libllama + ggml-cpu, deterministic AVX2/FMA build (this host's ISA does not cover the native build's)")}
 
 
-def cpu_baseline(budget_s=12.0):
-    """reference CPU path on the host cores: a bounded sample (about budget_s seconds of CPU work) of the same workload"""
-    c = CpuSlice()
-    c.forward_s(1, False, 65)                                # warm the thread pool and the page cache
-    t_first = c.forward_s(1, False, 65)
-    reps = int(min(64, max(3, budget_s * 0.8 / max(t_first, 1e-3))))
-    t_l1 = float(np.median([c.forward_s(1, False, 65) for _ in range(reps)]))      # one decoder layer at n_kv = 4096 (+ lm_head slice)
-    t_over = float(np.median([c.forward_s(0, False, 65) for _ in range(5)]))       # embeddings + final norm + lm_head
-    t_head = float(np.median([c.forward_s(1, True, 8) for _ in range(5)]))         # one draft level: head forward over 8 branches
-    rnd, ver = c.round_seconds(t_l1, t_over, t_head)
-    return {"value": (FIXED_ACCEPT + 1) / rnd, "unit": "tok/s", "cores": c.cores, "kind": c.kind,
-            "verify_step_us": ver * 1e6,
-            "sample": f"1 of 32 target layers (T=65, n_kv=4096) timed {reps}x + lm_head slice 5x + one 8-row draft-head level 5x "
-                      f"(medians {t_l1:.2f}s, {t_over:.2f}s, {t_head:.2f}s; {reps * t_l1 + 5 * (t_over + t_head):.0f}s of CPU work), "
-                      f"scaled to 32 layers + {TREE['max_depth'] + 1} draft levels"}
+def cpu_baseline(n_rounds=3):
+    """reference CPU path on the host cores: n_rounds whole rounds (each ~3 s of a 16-thread host), nothing scaled"""
+    c = CpuRound()
+    c.round_s()                                              # warm the thread pool and the page cache
+    rs = [c.round_s() for _ in range(n_rounds)]
+    rnd = float(np.median([r[0] for r in rs])); ver = float(np.median([r[1] for r in rs]))
+    d = c.describe()
+    d.update({"value": (FIXED_ACCEPT + 1) / rnd, "unit": "tok/s", "verify_step_us": ver * 1e6,
+              "sample": f"{n_rounds} whole rounds after 1 warm-up: llama_decode of the 65-token tree batch over all 32 layers at n_kv 4096 "
+                        f"(median {ver:.2f} s) + {TREE['max_depth'] + 1} draft-head levels of {TREE['n_branch']} rows (median round {rnd:.2f} s); "
+                        f"model + KV set-up {c.setup_s:.0f} s outside the timing"})
+    return d
 
 
 def run_reference(args, rank, world):
     if rank != 0:
         return None
-    c = CpuSlice()
-    t_over = c.forward_s(0, False, 65)
-    t_head = c.forward_s(1, True, 8)
-    for _ in range(min(args.warmup, 2)):
-        c.forward_s(1, False, 65)
-    ts = [c.forward_s(1, False, 65) for _ in range(args.steps)]
-    t_l1 = float(np.median(ts))
-    rnd, ver = c.round_seconds(t_l1, t_over, t_head)
+    c = CpuRound()
+    for _ in range(max(1, min(args.warmup, 2))):
+        c.round_s()
+    t0 = time.perf_counter()
+    rs = [c.round_s() for _ in range(args.steps)]
+    wall = time.perf_counter() - t0
+    rnd = float(np.mean([r[0] for r in rs])); ver = float(np.median([r[1] for r in rs]))
     val = (FIXED_ACCEPT + 1) / rnd
-    sample = (f"each step = 1 of 32 target layers + lm_head slice at T=65, n_kv=4096 on {c.cores} host threads "
-              f"(median {t_l1:.2f}s; lm_head slice {t_over:.2f}s, draft level {t_head:.2f}s), scaled to the full round")
+    d = c.describe()
+    d.update({"value": val, "unit": "tok/s",
+              "sample": f"each step = one whole round on {c.cores} host threads: llama_decode of the 65-token tree batch over all 32 layers at n_kv 4096 "
+                        f"(median {ver:.2f} s) + {TREE['max_depth'] + 1} draft-head levels; {args.steps} steps in {wall:.0f} s, nothing scaled"})
     return {"impl": "reference", "metric": "eagle_decode_tok_per_s", "value": val, "unit": "tok/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": rnd * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "int8xq4_K/q6_K dot, f32 accumulate, f16 KV", "data": "synthetic (random-init Q4_K_M blocks)",
-            "config": {"workload": "vicuna-7b Q4_K_M + EAGLE head, 64-node tree (65-row verify batch), KV ~4096, batch 1, fixed_accept=3",
-                       "tree": TREE, "parallelism": "host cores only"},
-            "verify_step_us": ver * 1e6,
-            "cpu_baseline": {"value": val, "unit": "tok/s", "cores": c.cores, "kind": c.kind, "sample": sample},
+            "dtype": "int8xq4_K/q6_K dot, f32 accumulate, f16 KV", "data": "synthetic (random-init Q4_K_M blocks, N(0,1) f16 KV prefill, fixed accept length 3)",
+            "config": config_dict("host cores only", 65, "n/a (host arm)"),
+            "verify_step_us": ver * 1e6, "cpu_baseline": d,
             "e2e": {"value": val, "unit": "tok/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
 
 

@@ -435,9 +435,8 @@ static int check_model(eb_model *m) {
 }
 
 extern "C" int eb_session_n_past(const eb_session *s, int model) {
-    (void)model; int n = -1;
-    if (cudaMemcpy(&n, &s->state->n_past, 4, cudaMemcpyDeviceToHost) != cudaSuccess) return -1;
-    return n;
+    (void)model;
+    return s->n_past_h;          // host mirror: every entry point that moves SpecState.n_past updates it (no device read)
 }
 
 // Visibility among the tokens of a tree-shaped llama_batch (R/include/llama.h:247-257), by the rule of the reference's KQ-mask
@@ -591,6 +590,7 @@ extern "C" int eb_session_set_n_past(eb_session *s, int n_past) {
     if (n_past < 0 || n_past > s->p.n_ctx) return eb_set_err(EB_ERR_ARG, "set_n_past: %d", n_past);
     set_n_past_kernel<<<1, 1, 0, s->st>>>(s->state, n_past); EB_CHECK_LAUNCH();
     EB_CUDA(cudaStreamSynchronize(s->st));
+    s->n_past_h = n_past;
     return EB_OK;
 }
 
@@ -613,6 +613,7 @@ extern "C" int eb_session_synth_kv(eb_session *s, int n_past, uint64_t seed) {
     set_n_past_kernel<<<1, 1, 0, s->st>>>(s->state, n_past); EB_CHECK_LAUNCH();
     int rc = eb_synth_impl(EB_F32, s->root_feat, s->tgt->E, seed + 77, 1.0f, 0, s->st); if (rc) return rc;
     EB_CUDA(cudaStreamSynchronize(s->st));
+    s->n_past_h = n_past;
     return EB_OK;
 }
 
@@ -692,6 +693,7 @@ extern "C" int eb_session_round(eb_session *s, eb_round_result *h_out) {
     EB_CUDA(cudaStreamSynchronize(s->st));
     float ms = 0; EB_CUDA(cudaEventElapsedTime(&ms, s->ev0, s->ev1));
     s->h_res->gpu_ms = ms;
+    s->n_past_h += s->h_res->n_accept;                          // round_end commits the accepted path: n_past += n_accept
     if (h_out) *h_out = *s->h_res;
     return EB_OK;
 }

@@ -43,6 +43,7 @@ struct eb_session {
     cudaGraphExec_t graph_round = nullptr, graph_verify = nullptr; int graph_verify_T = 0;
     long graph_round_kernels = 0, graph_verify_kernels = 0;
     int last_T[2] = {0, 0};
+    int n_past_h = 0;      // host mirror of SpecState.n_past (advanced from the round result): no extra D2H per round
 };
 
 // ops implemented in the other translation units

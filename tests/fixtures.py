@@ -18,8 +18,21 @@ def random_blocks(t, n_elems, rng, scale=0.02):
     raw = rng.integers(0, 256, (nb, bb), dtype=np.uint8)
     d = (scale * (2.2 + 0.6 * rng.random(nb))).astype(np.float32)
     if t == po.Q4_K:
-        raw[:, 0:2] = (d / (7.5 * 48)).astype(np.float16).view(np.uint8).reshape(nb, 2)
-        raw[:, 2:4] = (d / 48).astype(np.float16).view(np.uint8).reshape(nb, 2)
+        # centred sub-blocks, as a quantiser produces them for zero-mean weights: value = d*sc*q - dmin*m with dmin = 8 d and
+        # m = round(7.5 sc / 8), i.e. ~ d*sc*(q - 7.5).  (Independent random sc and m give every 32-weight sub-block its own large
+        # offset; a 32-layer model of such matrices amplifies an f32 rounding difference ~4x per layer — chaotic, useless for parity.)
+        sc = rng.integers(24, 64, (nb, 8), dtype=np.uint8)
+        m = np.rint(sc * (7.5 / 8)).astype(np.uint8)
+        dd = (d / (100 * 4.6)).astype(np.float16)          # dequantised std ~ 0.022, like the other formats
+        raw[:, 0:2] = dd.view(np.uint8).reshape(nb, 2)
+        raw[:, 2:4] = (dd.astype(np.float32) * 8).astype(np.float16).view(np.uint8).reshape(nb, 2)
+        # 6-bit packing of get_scale_min_k4 (R/ggml/src/ggml-quants.c:631): j < 4: sc = q[j] & 63, m = q[j+4] & 63;
+        # j >= 4: sc = (q[j+4] & 15) | (q[j-4] >> 6) << 4, m = (q[j+4] >> 4) | (q[j] >> 6) << 4
+        q = np.zeros((nb, 12), np.uint8)
+        q[:, 0:4] = (sc[:, 0:4] & 63) | ((sc[:, 4:8] >> 4) << 6)
+        q[:, 4:8] = (m[:, 0:4] & 63) | ((m[:, 4:8] >> 4) << 6)
+        q[:, 8:12] = (sc[:, 4:8] & 15) | ((m[:, 4:8] & 15) << 4)
+        raw[:, 4:16] = q
     elif t == po.Q6_K:
         raw[:, 208:210] = (d / (32 * 96)).astype(np.float16).view(np.uint8).reshape(nb, 2)
     elif t == po.Q4_0:

@@ -28,17 +28,29 @@ HP7B = dict(E=4096, H=32, F=11008, V=32000, L=32)
 CONFIGS = {
     "config1": dict(name="config 1: Vicuna-7B shape Q4_0, 26-node tree, 512-token prompt", ftype=po.Q4_0, T=27, n_prefix=512, n_ctx=1024, seed=101),
     "config2": dict(name="config 2: Vicuna-7B shape Q4_K_M, 64-node tree, 4K KV", ftype="q4_k_m", T=65, n_prefix=4031, n_ctx=4352, seed=102),
+    # diagnostics (not part of the test suite): one factor of config 2 at a time
+    "diagA": dict(name="diag A: Q4_K_M, T 65, 512-token prompt", ftype="q4_k_m", T=65, n_prefix=512, n_ctx=1024, seed=102),
+    "diagB": dict(name="diag B: Q4_0, T 65, 4K KV", ftype=po.Q4_0, T=65, n_prefix=4031, n_ctx=4352, seed=102),
+    "diagC": dict(name="diag C: Q4_K_M, T 27, 4K KV", ftype="q4_k_m", T=27, n_prefix=4031, n_ctx=4352, seed=102),
 }
 
 
-def random_model(hp, ftype, seed):
+def random_model(hp, ftype, seed, branch_gain=None):
     """well-formed random blocks of the config's type mixture (quantising 6.7e9 Gaussian weights with the reference quantiser would
-    take minutes; any block bytes are a valid tensor for both sides)"""
+    take minutes; any block bytes are a valid tensor for both sides).  Conditioning: a deep stack of i.i.d. random layers is
+    chaotic — with std-0.02 embeddings and std-0.02 output projections every layer rewrites the residual stream, and ANY 1e-7
+    difference (a different f32 summation order, one activation rounding flip) grows ~1.3x per layer: the reference's own two
+    accumulator variants then disagree by 1e-1 on the logits of a 32-layer model (tests/test_fullsize.py reports that number).  So
+    the fixture is initialised the way deep transformers are: unit-scale embeddings and residual-branch output projections
+    (attn_output, ffn_down) scaled by branch_gain = 1/sqrt(2 L) (GPT-2 / Megatron init), which keeps the per-layer update a
+    fraction of the stream — as it is in a trained checkpoint."""
     rng = np.random.default_rng(seed)
     E, F, V, L = hp["E"], hp["F"], hp["V"], hp["L"]
+    if branch_gain is None:
+        branch_gain = 1.0 / np.sqrt(2.0 * L)
 
-    def mat(rows, cols, t):
-        return (t, fx.random_blocks(t, rows * cols, rng))
+    def mat(rows, cols, t, scale=0.02):
+        return (t, fx.random_blocks(t, rows * cols, rng, scale))
 
     def vec(n):
         return (po.F32, (1 + rng.normal(0, 0.02, n)).astype(np.float32).view(np.uint8).reshape(-1).copy())
@@ -48,12 +60,12 @@ def random_model(hp, ftype, seed):
 
     base = po.Q4_K if ftype == "q4_k_m" else ftype
     out_t = po.Q6_K if ftype in ("q4_k_m", po.Q4_0) else ftype
-    g = {po.T_TOK_EMBD: mat(V, E, base), po.T_OUTPUT_NORM: vec(E), po.T_OUTPUT: mat(V, E, out_t)}
+    g = {po.T_TOK_EMBD: mat(V, E, base, 1.0), po.T_OUTPUT_NORM: vec(E), po.T_OUTPUT: mat(V, E, out_t)}
     layers = []
     for l in range(L):
         layers.append({po.L_ATTN_NORM: vec(E), po.L_WQ: mat(E, E, lt(po.L_WQ, l)), po.L_WK: mat(E, E, lt(po.L_WK, l)), po.L_WV: mat(E, E, lt(po.L_WV, l)),
-                       po.L_WO: mat(E, E, lt(po.L_WO, l)), po.L_FFN_NORM: vec(E), po.L_GATE: mat(F, E, lt(po.L_GATE, l)),
-                       po.L_UP: mat(F, E, lt(po.L_UP, l)), po.L_DOWN: mat(E, F, lt(po.L_DOWN, l))})
+                       po.L_WO: mat(E, E, lt(po.L_WO, l), 0.02 * branch_gain), po.L_FFN_NORM: vec(E), po.L_GATE: mat(F, E, lt(po.L_GATE, l)),
+                       po.L_UP: mat(F, E, lt(po.L_UP, l)), po.L_DOWN: mat(E, F, lt(po.L_DOWN, l), 0.02 * branch_gain)})
     return {"hparams": dict(**hp, eps=1e-5, freq_base=10000.0, is_eagle=False), "globals": g, "layers": layers}
 
 
@@ -101,7 +113,10 @@ def run(cfg_id, variant, tmp_dir):
                kv_layer0_bit_identical=[float((k_g == k_o).mean()), float((v_g == v_o).mean())],
                setup_s=round(t1 - t0, 1), reference_decode_s=round(t2 - t1, 2), host_threads=os.cpu_count())
     if os.environ.get("EB_FULLSIZE_DEBUG"):
-        print("per_site[:16]", per_site[:16], "rel per row", np.round(rel, 4).tolist(), file=sys.stderr)
+        frac = [float((a != b).mean()) for a, b in zip(pl_g, pl_o)]
+        big = [float((np.abs(a.astype(np.int32) - b) > 1).mean()) for a, b in zip(pl_g, pl_o)]
+        print("element fraction differing per site:", np.round(frac, 4).tolist(), file=sys.stderr)
+        print("element fraction differing by more than 1:", np.round(big, 4).tolist(), file=sys.stderr)
         d0 = (pl_g[0] != pl_o[0])
         print("site0 differing rows", np.nonzero(d0.any(1))[0].tolist(), "elements", int(d0.sum()), file=sys.stderr)
         r0 = int(np.nonzero(d0.any(1))[0][0]) if d0.any() else 0
