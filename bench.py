@@ -237,18 +237,9 @@ def config_dict(parallelism, nodes_median, l2):
 
 
 def native_cpu_ok():
-    """oracle/_ref/libggml-native.so was built with -march=native where the repository was built; it may only run on a host whose
-    ISA covers that machine's (oracle/_ref/native.cpuflags, written by oracle/Makefile)"""
-    f = os.path.join(ROOT, "oracle", "_ref", "native.cpuflags")
-    if not os.path.exists(f) or not os.path.exists(os.path.join(ROOT, "oracle", "_ref", "libggml-native.so")):
-        return False
-    need = set(open(f).read().split())
-    have = set()
-    for line in open("/proc/cpuinfo"):
-        if line.startswith("flags"):
-            have = set(line.split(":", 1)[1].split()); break
-    isa = {x for x in need if x.startswith(("avx", "amx", "fma", "f16c", "bmi", "sse4", "gfni", "vaes", "vpclmul"))}
-    return isa <= have
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import refround as rr
+    return rr.native_ok()
 
 
 class CpuRound:

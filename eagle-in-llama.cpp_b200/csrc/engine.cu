@@ -525,6 +525,7 @@ extern "C" int eb_session_commit(eb_session *s, int model, int n) {
     const int n_past = eb_session_n_past(s, model);
     set_n_past_kernel<<<1, 1, 0, s->st>>>(s->state, n_past + n); EB_CHECK_LAUNCH();
     EB_CUDA(cudaStreamSynchronize(s->st));
+    s->n_past_h = n_past + n;
     return EB_OK;
 }
 // ---- prompt prefill (llama_decode_init + llama_decode_initial of the chain driver, R/examples/speculative-simple/speculative-eagle.cpp:150,194;

@@ -14,6 +14,21 @@ def have():
     return os.path.exists(os.path.join(REF, "libref_round.so"))
 
 
+def native_ok():
+    """libggml-native.so was built with -march=native on the build machine; it may only be loaded on a host whose ISA covers that
+    machine's (oracle/_ref/native.cpuflags, written by oracle/Makefile)"""
+    f = os.path.join(REF, "native.cpuflags")
+    if not os.path.exists(f) or not os.path.exists(os.path.join(REF, "libggml-native.so")):
+        return False
+    need = set(open(f).read().split())
+    have_ = set()
+    for line in open("/proc/cpuinfo"):
+        if line.startswith("flags"):
+            have_ = set(line.split(":", 1)[1].split()); break
+    isa = {x for x in need if x.startswith(("avx", "amx", "fma", "f16c", "bmi", "sse4", "gfni", "vaes", "vpclmul"))}
+    return isa <= have_
+
+
 VARIANTS = {"ref": "libggml-ref.so",          # the reference's ggml-cpu, deterministic flags: THE parity oracle
             "native": "libggml-native.so",    # same sources, -march=native + llamafile + repack: the timed CPU arm only
             "f32acc": "libggml-f32acc.so"}    # attribution instrument: f32 flash-attention V accumulator, nothing else changed

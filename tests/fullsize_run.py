@@ -127,6 +127,7 @@ def run(cfg_id, variant, tmp_dir):
         x = po.ref().rms_norm(emb, 1e-5) * tgt["layers"][0][po.L_ATTN_NORM][1].view(np.float32)[None, :]
         print("reference tap site0 == recomputed norm(embedding):", np.array_equal(x.astype(np.float32), taps[0][1]), float(np.abs(x - taps[0][1]).max()), file=sys.stderr)
         print("tap names[:8]", [n for n, _ in taps[:8]], file=sys.stderr)
+    np.savez(os.path.join(tmp_dir, f"logits_{cfg_id}_{variant}.npz"), engine=lg, reference=lo)
     s.free(); c.free(); m.free()
     return out
 
