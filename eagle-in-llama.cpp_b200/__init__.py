@@ -73,6 +73,7 @@ def lib():
         "eb_flash_attn_ws_size": ([i32, i32, i32, i32], sz),
         "eb_flash_attn": ([vp, vp, vp, i64, vp, i64, vp, i32, i32, i32, i32, i32, f32, vp, vp, vp], i32),
         "eb_top_k": ([vp, i32, i32, i32, vp, vp, vp, vp], i32), "eb_argmax": ([vp, i32, i32, vp, vp], i32),
+        "eb_top_k_noalloc": ([vp, i32, i32, i32, vp, vp, vp, vp], i32),
         "eb_model_create": ([i32, i32, i32, i32, i32, f32, f32, i32], vp), "eb_model_free": ([vp], None),
         "eb_model_set_tensor": ([vp, i32, i32, i32, vp], i32),
         "eb_model_synth_tensor": ([vp, i32, i32, i32, C.c_uint64, f32], i32),

@@ -457,8 +457,55 @@ int eb_spec_round_end(SpecState *s, const float *tgt_feat, float *root_feat, int
 
 static void *g_topk_scr = nullptr;      // scratch of the operator-layer eb_top_k (sessions own theirs)
 void *eb_top_k_default_scratch() { return g_topk_scr; }
+
+// ---- eb_top_k_noalloc: the 16-slice top-k with its scratch in a file-scope device array, for callers that cannot allocate
+// (CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc); no
+// counterpart in the reference.  The array is part of the module image: every GPU that loads the library holds these 66 048 bytes
+// until the process exits.  In HOST code the name `g_topk_static` is only a stand-in for the symbol, not a device address (a kernel
+// given it would fault, or quietly use host memory where the GPU can reach it): its device address is taken once per device, with
+// that device current, by cudaGetSymbolAddress in eb_spec_init() and kept in g_topk_static_ptr[device].
+#define EB_TOPK_NOALLOC_BYTES (512 + (size_t)EB_TOP_K_NOALLOC_MAX_ROWS * TK_S * 16 * 8)      // arrival counters | slice lists (vals, ids)
+static_assert(EB_TOP_K_NOALLOC_MAX_ROWS * 4 <= 512, "one arrival counter per row in the first 512 bytes");
+static __device__ __align__(256) unsigned char g_topk_static[EB_TOPK_NOALLOC_BYTES];
+constexpr int EB_MAX_DEVICES = 64;
+static void *g_topk_static_ptr[EB_MAX_DEVICES] = {};
+
 int eb_spec_init() {
     EB_CUDA(cudaFuncSetAttribute(top_k_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 56000 * 4));
     if (!g_topk_scr) { EB_CUDA(cudaMalloc(&g_topk_scr, eb_top_k_scratch_bytes(128))); EB_CUDA(cudaMemset(g_topk_scr, 0, eb_top_k_scratch_bytes(128))); }
+    int dev = -1;
+    EB_CUDA(cudaGetDevice(&dev));
+    if (dev >= 0 && dev < EB_MAX_DEVICES && !g_topk_static_ptr[dev]) {
+        void *ptr = nullptr;
+        EB_CUDA(cudaGetSymbolAddress(&ptr, g_topk_static));          // device address of the array on THIS device
+        EB_CUDA(cudaMemset(ptr, 0, EB_TOPK_NOALLOC_BYTES));
+        g_topk_static_ptr[dev] = ptr;
+    }
+    return EB_OK;
+}
+
+// Allocation-free entry point: inputs and outputs are the caller's device buffers; nothing here calls cudaMalloc / cudaFree or an
+// allocating library routine (the kernel launch and a 512-byte cudaMemsetAsync are the only CUDA calls, both legal under stream
+// capture).  Every call on a device shares g_topk_static, which keeps the previous call's slice lists: the lists are fully
+// rewritten before they are read (each slice writes its 16 slots, the last arriver reads them), the arrival counters must start at
+// zero and are cleared on the stream before the launch.  Two calls that overlap on the GPU (different streams, or concurrent graph
+// branches) race on the array: serialise them.
+extern "C" int eb_top_k_noalloc(const float *d_logits, int rows, int V, int k, int32_t *d_ids, float *d_vals, float *d_probs, void *stream) {
+    int dev = -1;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= EB_MAX_DEVICES || !g_topk_static_ptr[dev])
+        return eb_set_err(EB_ERR_CUDA, "top_k_noalloc: call eb_device_init(device) for the current device first (this entry point sets nothing up itself)");
+    if (!d_logits || !d_ids || !d_vals) return eb_set_err(EB_ERR_ARG, "top_k_noalloc: null buffer");
+    if (rows < 0 || rows > EB_TOP_K_NOALLOC_MAX_ROWS)
+        return eb_set_err(EB_ERR_ARG, "top_k_noalloc: rows=%d exceeds the static scratch (EB_TOP_K_NOALLOC_MAX_ROWS = %d): use eb_top_k", rows, EB_TOP_K_NOALLOC_MAX_ROWS);
+    if (k < 1 || k > 16) return eb_set_err(EB_ERR_ARG, "top_k_noalloc: k=%d (1..16)", k);
+    if (V < TK_S * 64 || V > TK_S * TK_THREADS * TK_PER)
+        return eb_set_err(EB_ERR_ARG, "top_k_noalloc: V=%d outside the 16-slice kernel's range [%d, %d]: use eb_top_k", V, TK_S * 64, TK_S * TK_THREADS * TK_PER);
+    if (rows == 0) return EB_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    unsigned char *scr = (unsigned char *)g_topk_static_ptr[dev];
+    unsigned *cnt = (unsigned *)scr; float *sv = (float *)(scr + 512); int *si = (int *)(sv + (size_t)rows * TK_S * 16);
+    EB_CUDA(cudaMemsetAsync(cnt, 0, 512, st));                       // counters start at zero whatever an earlier (aborted) call left
+    top_k_split_kernel<<<dim3(rows, TK_S), dim3(TK_THREADS), 0, st>>>(d_logits, 1, 0, V, k, d_ids, d_vals, d_probs, nullptr, sv, si, cnt);
+    EB_CHECK_LAUNCH();
     return EB_OK;
 }

@@ -133,6 +133,15 @@ EB_API int eb_flash_attn(const float *d_q, const void *d_k, const void *d_v, int
  * must not overlap in time (sessions own their scratch). */
 EB_API int eb_top_k(const float *d_logits, int rows, int V, int k, int32_t *d_ids, float *d_vals, float *d_probs, void *stream);
 EB_API int eb_argmax(const float *d_logits, int rows, int V, int32_t *d_ids, void *stream);
+/* eb_top_k without any allocation.  NO COUNTERPART IN THE REFERENCE: added for callers that
+ * cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same results as
+ * eb_top_k (the 16-slice kernel); its scratch is a file-scope `static __device__` array of EB_TOP_K_NOALLOC_MAX_ROWS rows
+ * (66 048 bytes, held by every GPU that loads the library until exit).  Limits: rows <= EB_TOP_K_NOALLOC_MAX_ROWS, 1024 <= V <=
+ * 32768, k <= 16; anything else is refused with EB_ERR_ARG.  The device must have been set up with eb_device_init() beforehand
+ * (this call sets nothing up and calls no cudaMalloc / cudaFree).  All calls on a device share the array: calls that overlap on
+ * the GPU (different streams) race — serialise them. */
+#define EB_TOP_K_NOALLOC_MAX_ROWS 32
+EB_API int eb_top_k_noalloc(const float *d_logits, int rows, int V, int k, int32_t *d_ids, float *d_vals, float *d_probs, void *stream);
 
 /* ---- engine layer -------------------------------------------------------------------- */
 typedef struct eb_model eb_model;      /* weights of one GGUF model resident in HBM */
