@@ -348,6 +348,8 @@ __device__ void tree_expand_serial(SpecState *s, const SpecCfg &c, const int32_t
             new_tok[n_new] = ids[is]; new_src[n_new] = s->br_last_node[br]; new_br[n_new] = br; n_new++;
             if (s->n_nodes + n_new > c.n_draft) s->br_drafting[br] = 0;               // batch_tgt.n_tokens > n_draft
         }
+        // chain driver's confidence stop (R/common/speculative.cpp:283): the token just drafted stays, the branch that drew it stops
+        if (c.p_min > 0.f && pr[0] < c.p_min) s->br_drafting[b] = 0;
     }
     for (int i = 0; i < n_new; i++) {
         const int node = first_new + i, par = new_src[i];

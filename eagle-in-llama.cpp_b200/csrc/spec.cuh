@@ -5,7 +5,7 @@
 
 struct FwdCtl { int n_prefix; int node_base; int n_tree; };   // read by the engine kernels on device
 
-struct SpecCfg { int max_nodes, n_branch, n_draft, max_depth, top_k, fixed_accept; float p_split; };
+struct SpecCfg { int max_nodes, n_branch, n_draft, max_depth, top_k, fixed_accept; float p_split; float p_min; };
 
 struct SpecState {
     // committed state

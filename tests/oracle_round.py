@@ -42,7 +42,7 @@ class CpuStream:
         self.root_feat = ft[-1].copy()
         return lg, ft
 
-    def round(self, n_branch, n_draft, max_depth, top_k, p_split, max_nodes, fixed_accept=-1):
+    def round(self, n_branch, n_draft, max_depth, top_k, p_split, max_nodes, fixed_accept=-1, p_min=0.0):
         E = self.hp["E"]
         tokens, parent, depth = [self.root_token], [-1], [0]
         drafting = [False] * n_branch; last_node = [0] * n_branch; row = [0] * n_branch
@@ -87,6 +87,8 @@ class CpuStream:
                     new.append((int(ids[i]), last_node[br], br))
                     if len(tokens) + len(new) > n_draft:
                         drafting[br] = False
+                if p_min > 0 and pr[0] < p_min:               # R/common/speculative.cpp:283
+                    drafting[b] = False
             first = len(tokens)
             for i, (tok, par, br) in enumerate(new):
                 tokens.append(tok); parent.append(par); depth.append(depth[par] + 1)

@@ -201,6 +201,43 @@ def test_spec_rounds_vs_oracle(eb, use_graph, head_ftype, inert_caps):
     assert full >= 1, log
 
 
+def test_spec_round_p_min_stops_branches(eb):
+    """--draft-p-min (R/common/speculative.cpp:283, :445 — the chain drafter): a branch stops drafting after a token whose draft
+    probability is below p_min.  With one branch (the chain the reference applies it to) and p_min above any probability a softmax of
+    random logits reaches, the draft is the root plus ONE token; in a tree the branches split off at that level still draft their
+    own next token once before they stop too (depth <= 2).  A moderate p_min gives the oracle composition's tree, and p_min = 0 is
+    the tree driver's behaviour (no stop)."""
+    hp = dict(E=256, H=2, F=512, V=1024, L=2)
+    tgt = fx.make_model(**hp, ftype="q4_k_m", seed=31)
+    head = fx.make_model(**{**hp, "L": 1}, ftype=po.Q4_0, seed=32, is_eagle=True)
+    base = dict(n_branch=4, n_draft=12, max_depth=12, top_k=10, p_split=0.1, max_nodes=17)
+    mt = fx.to_gpu_model(eb, tgt); mh = fx.to_gpu_model(eb, head, target=mt)
+    po.set_fattn_acc_f32(1)
+    sizes = {}
+    for n_branch, p_min in ((4, 0.0), (4, 0.2), (4, 0.9999), (1, 0.0), (1, 0.9999)):
+        cfg = dict(base, p_min=p_min, n_branch=n_branch)
+        cpu = CpuStream(po.oracle(), tgt, head, 128)
+        s = eb.Session(mt, mh, n_ctx=128, use_graph=True, **cfg)
+        prompt = np.random.default_rng(2).integers(3, hp["V"], 12).astype(np.int32)
+        cpu.prefill(prompt)
+        lg, ft = s.forward(0, prompt, np.arange(12))
+        hid = np.zeros((12, hp["E"]), np.float32); hid[1:] = ft[:-1]
+        s.forward(1, prompt, np.arange(12), hidden=hid); s.commit(0, 12); s.set_root(cpu.root_token, ft[-1])
+        want, got = cpu.round(**cfg), s.round()
+        n = got.n_nodes
+        sizes[(n_branch, p_min)] = n
+        if not pa.same_round(got, want):
+            assert pa.round_margin(want, cfg["p_split"]) <= pa.NORTH_STAR_REL, (p_min, list(got.tokens[:n]), want["tokens"].tolist())
+        depth = fx.tree_depths(np.array(got.parent[:n], np.int32))
+        assert n == len(want["tokens"]), (n_branch, p_min, n, len(want["tokens"]))
+        if p_min > 0.99:
+            assert (n == 2 and depth.max() == 1) if n_branch == 1 else depth.max() <= 2, (n_branch, n, depth.tolist())
+        s.free()
+    po.set_fattn_acc_f32(0)
+    print(f"[parity] p_min: tree sizes by (n_branch, p_min) {sizes}")
+    assert sizes[(4, 0.9999)] < sizes[(4, 0.0)] and sizes[(1, 0.9999)] < sizes[(1, 0.0)]
+
+
 def test_fixed_accept_round_properties(eb):
     """bench mode: accept exactly `a` draft nodes per round; n_past advances by a+1, trees stay
     well-formed, and re-running from the same state is deterministic."""
