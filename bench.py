@@ -367,6 +367,30 @@ def run_reference(args, rank, world):
             "e2e": {"value": val, "unit": "tok/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
 
 
+def run_config4(args, rank, world):
+    """BASELINE config 4: one tree-verify step of a LLaMA-2-13B-shaped Q4_K_M target (40 layers, E 5120, 40 heads, F 13824), 65 rows at
+    n_kv 4096, tensor parallel over the ranks (N-split wq|wk|wv|gate|up, K-split wo|down, one peer-memory all-reduce after each
+    K-split GEMM: csrc/tp.cu).  STRONG scaling: the same step on 1, 2, 4, 8 GPUs; time-like metric (tools/tp_run.py does the work)."""
+    if args.impl == "reference":
+        return {"impl": "reference", "unavailable": "config 4 is a latency table of this repo's tensor-parallel path; the reference arm covers the metric's own config"} if rank == 0 else None
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import tp_run
+    sampler = ClockSampler(int(os.environ.get("LOCAL_RANK", "0"))); sampler.start()
+    r = tp_run.bench("13b", args.steps, args.warmup, quiet=True)
+    clocks = sampler.summary()
+    tp_run.shutdown()
+    if rank != 0:
+        return None
+    return {"metric": "verify_step_us", "value": r["verify_step_us"], "unit": "us", "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup),
+            "ms_per_step": r["verify_step_us"] / 1e3, "higher_is_better": False, "scaling": "strong", "vs_baseline": None,
+            "dtype": "int8xq4_K/q6_K dot, f32 accumulate, f16 KV", "data": "synthetic (random-init Q4_K_M blocks, N(0,1) f16 KV prefill)",
+            "config": {"workload": "config 4: llama-2-13b-shaped Q4_K_M target, 65-row tree verify step at n_kv 4096, batch 1",
+                       "parallelism": f"tp{world}: N-split wq|wk|wv|gate|up, K-split wo|down, {r['allreduces_per_step']} peer-memory all-reduces of [65][5120] f32 per step",
+                       "l2": "weights per rank exceed L2: no flush needed"},
+            "gpu_launches": r["launches"], "weight_bytes_per_rank": r["weight_bytes_per_rank"], "tp_error_word": r["tp_error_word"],
+            "clocks": clocks}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -374,9 +398,13 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--config", type=int, default=2, choices=[2, 4],
+                    help="BASELINE.json config: 2 = the metric's own (default, the driver's run); 4 = LLaMA-2-13B verify step, tensor parallel over --gpus")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1")); local = int(os.environ.get("LOCAL_RANK", "0"))
-    if args.impl == "reference":
+    if args.config == 4:
+        out = run_config4(args, rank, world)
+    elif args.impl == "reference":
         out = run_reference(args, rank, world)
     else:
         out = run_gpu(args, rank, world, local)

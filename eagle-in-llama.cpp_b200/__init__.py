@@ -31,7 +31,7 @@ class EagleB200Error(RuntimeError):
 class SessionParams(C.Structure):
     _fields_ = [("n_ctx", C.c_int), ("max_nodes", C.c_int), ("n_branch", C.c_int), ("n_draft", C.c_int),
                 ("max_depth", C.c_int), ("top_k", C.c_int), ("p_split", C.c_float), ("fixed_accept", C.c_int),
-                ("use_graph", C.c_int)]
+                ("use_graph", C.c_int), ("p_min", C.c_float)]
 
 
 class RoundResult(C.Structure):
@@ -83,6 +83,10 @@ def lib():
         "eb_session_forward": ([vp, i32, vp, vp, vp, vp, i32, vp, vp], i32),
         "eb_tree_bits_from_batch": ([i32, vp, vp, vp, vp], i32),
         "eb_session_forward_batch": ([vp, i32, vp, vp, vp, vp, vp, i32, vp, vp], i32),
+        "eb_model_create_tp": ([i32, i32, i32, i32, i32, i32, f32, f32], vp),
+        "eb_tp_create": ([i32, i32, i64], vp), "eb_tp_handle": ([vp, vp], i32), "eb_tp_open_peer": ([vp, i32, vp], i32),
+        "eb_tp_free": ([vp], None), "eb_tp_error": ([vp], i32), "eb_tp_allreduce": ([vp, vp, i32, i64, vp, vp], i32),
+        "eb_session_set_tp": ([vp, vp], i32),
         "eb_session_set_tap": ([vp, vp, sz], i32), "eb_session_tap_state": ([vp, C.POINTER(sz), C.POINTER(i32)], i32),
         "eb_session_prefill": ([vp, vp, i32, vp, vp], i32),
         "eb_session_kv_write": ([vp, i32, i32, i32, i32, i32, vp], i32), "eb_session_kv_read": ([vp, i32, i32, i32, i32, i32, vp], i32),
@@ -396,13 +400,96 @@ class Model:
             self.h = None
 
 
+class ShardModel(Model):
+    """One rank's shard of a target model for tensor parallelism (eb_model_create_tp): n_head_local heads of size D, F_local ffn rows"""
+
+    def __init__(self, E, D, n_head_local, F_local, V, L, eps=1e-5, freq_base=10000.0):
+        self.E, self.H, self.F, self.V, self.L, self.is_eagle = E, n_head_local, F_local, V, L, False
+        self.D, self.Ea = D, n_head_local * D
+        self.eps, self.freq_base = eps, freq_base
+        self.h = lib().eb_model_create_tp(E, D, n_head_local, F_local, V, L, eps, freq_base)
+        if not self.h:
+            raise EagleB200Error(lib().eb_last_error().decode())
+
+
+def tp_partition(H, F, size):
+    """(head0, n_heads, f0, n_f) per rank: heads in pairs (256-element blocks of the K-split wo), ffn rows in 256-row super-blocks,
+    as even as the block granularity allows (13B at 8 ranks: 6,6,6,6,4,4,4,4 heads; 7,7,7,7,7,7,6,6 ffn blocks)"""
+    def split(n_units):
+        base, extra = divmod(n_units, size)
+        cnt = [base + (r < extra) for r in range(size)]
+        off = [sum(cnt[:r]) for r in range(size)]
+        return off, cnt
+    assert H % 2 == 0 and F % 256 == 0 and H // 2 >= size and F // 256 >= size
+    ho, hc = split(H // 2); fo, fc = split(F // 256)
+    return [(2 * ho[r], 2 * hc[r], 256 * fo[r], 256 * fc[r]) for r in range(size)]
+
+
+def tp_shard_tensor(which, t, raw, E, F, D, part):
+    """this rank's slice of one per-layer tensor (raw ggml blocks, row-major [rows][cols/block]): wq|wk|wv and gate|up are split by
+    output rows (N-split: whole heads / 256-row ffn super-blocks), wo and ffn_down by input columns (K-split, block aligned), the
+    norms are replicated.  part = one entry of tp_partition()."""
+    h0, nh, f0, nf = part
+
+    def rows_of(rows, cols, r0, n):
+        return np.ascontiguousarray(np.asarray(raw).reshape(rows, row_size(t, cols))[r0:r0 + n]).reshape(-1)
+
+    def cols_of(rows, cols, c0, n):
+        be, bb = BLOCK[t]
+        assert c0 % be == 0 and n % be == 0, (c0, n, be)
+        return np.ascontiguousarray(np.asarray(raw).reshape(rows, cols // be, bb)[:, c0 // be:(c0 + n) // be]).reshape(-1)
+
+    if which in (L_WQ, L_WK, L_WV):
+        return rows_of(E, E, h0 * D, nh * D)
+    if which == L_WO:
+        return cols_of(E, E, h0 * D, nh * D)
+    if which in (L_GATE, L_UP):
+        return rows_of(F, E, f0, nf)
+    if which == L_DOWN:
+        return cols_of(E, F, f0, nf)
+    return raw
+
+
+class TpGroup:
+    """peer-memory communicator (csrc/tp.cu).  exchange(fn): fn(handle_bytes) -> list of every rank's handle bytes (the host program's
+    transport, e.g. torch.distributed.all_gather_object)"""
+
+    def __init__(self, rank, size, max_elems, exchange):
+        self.rank, self.size = rank, size
+        self.h = lib().eb_tp_create(rank, size, int(max_elems))
+        if not self.h:
+            raise EagleB200Error(lib().eb_last_error().decode())
+        mine = C.create_string_buffer(64)
+        _ck(lib().eb_tp_handle(self.h, mine))
+        handles = exchange(bytes(mine.raw))
+        for r, hb in enumerate(handles):
+            if r != rank:
+                _ck(lib().eb_tp_open_peer(self.h, r, C.create_string_buffer(hb, 64)))
+
+    def allreduce(self, planes):
+        """planes f32 [ks][n] (host) -> sum over ranks and planes [n] (host); test helper"""
+        planes = np.ascontiguousarray(planes, np.float32)
+        ks, n = planes.shape
+        dp, do = DeviceBuffer.from_host(planes), DeviceBuffer(n * 4)
+        _ck(lib().eb_tp_allreduce(self.h, dp.ptr, ks, n, do.ptr, None))
+        _ck(lib().eb_synchronize(None))
+        return do.to_host(np.float32, n)
+
+    def error(self):
+        return lib().eb_tp_error(self.h)
+
+    def free(self):
+        if self.h:
+            lib().eb_tp_free(self.h); self.h = None
+
+
 class Session:
     """One decoding stream: target + draft head + both KV caches + device-side tree state."""
 
     def __init__(self, target, head=None, n_ctx=4096, max_nodes=65, n_branch=8, n_draft=64, max_depth=8, top_k=10,
-                 p_split=0.1, fixed_accept=-1, use_graph=True):
+                 p_split=0.1, fixed_accept=-1, use_graph=True, p_min=0.0):
         self.target, self.head = target, head
-        self.params = SessionParams(n_ctx, max_nodes, n_branch, n_draft, max_depth, top_k, p_split, fixed_accept, int(use_graph))
+        self.params = SessionParams(n_ctx, max_nodes, n_branch, n_draft, max_depth, top_k, p_split, fixed_accept, int(use_graph), p_min)
         self.h = lib().eb_session_create(target.h, head.h if head else None, C.byref(self.params))
         if not self.h:
             raise EagleB200Error(lib().eb_last_error().decode())
@@ -454,6 +541,9 @@ class Session:
         for w in widths:
             planes.append(raw[off:off + T * w].reshape(T, w)); off += T * w
         return logits, feat, planes
+
+    def set_tp(self, tp):
+        _ck(lib().eb_session_set_tp(self.h, tp.h if tp else None))
 
     def prefill(self, tokens):
         """prompt of any length through target (+ head): -> (logits [V], feature [E]) of the last token; both caches committed"""

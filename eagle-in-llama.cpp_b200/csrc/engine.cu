@@ -9,7 +9,7 @@
 #include <algorithm>
 
 static int tensor_shape(const eb_model *m, int layer, int which, int64_t &rows, int64_t &cols) {
-    const int64_t E = m->E, F = m->F, V = m->V;
+    const int64_t E = m->E, F = m->F, V = m->V, Ea = m->Ea;
     if (layer < 0) {
         switch (which) {
             case EB_T_TOK_EMBD: rows = V; cols = E; return 0;
@@ -22,7 +22,8 @@ static int tensor_shape(const eb_model *m, int layer, int which, int64_t &rows, 
     }
     switch (which) {
         case EB_L_ATTN_NORM: case EB_L_FFN_NORM: rows = 1; cols = E; return 0;
-        case EB_L_WQ: case EB_L_WK: case EB_L_WV: case EB_L_WO: rows = E; cols = E; return 0;
+        case EB_L_WQ: case EB_L_WK: case EB_L_WV: rows = Ea; cols = E; return 0;      // N-split across a TP group (all of E otherwise)
+        case EB_L_WO: rows = E; cols = Ea; return 0;                                  // K-split
         case EB_L_GATE: case EB_L_UP: rows = F; cols = E; return 0;
         case EB_L_DOWN: rows = E; cols = F; return 0;
     }
@@ -40,6 +41,23 @@ extern "C" eb_model *eb_model_create(int E, int H, int F, int V, int L, float ep
     if (E <= 0 || H <= 0 || E % H || E % 256 || F % 256 || L <= 0) { eb_set_err(EB_ERR_ARG, "model_create: E=%d H=%d F=%d L=%d (E,F must be multiples of 256)", E, H, F, L); return nullptr; }
     eb_model *m = new eb_model();
     m->E = E; m->H = H; m->F = F; m->V = V; m->L = L; m->eps = eps; m->freq_base = freq_base; m->is_eagle = is_eagle;
+    m->D = E / H; m->Ea = E;
+    m->layers.assign(L, std::vector<DTensor>(EB_L_COUNT));
+    m->fuse.assign(L, LayerFuse());
+    return m;
+}
+// One rank's shard of a target model for row-split tensor parallelism (the reference's --split-mode row,
+// R/ggml/src/ggml-cuda/ggml-cuda.cu:735-748,1359-1668, re-done as N-split wq|wk|wv|gate|up + K-split wo|down): this rank holds
+// n_head_local heads (rows of wq/wk/wv, columns of wo) and F_local ffn rows (rows of gate/up, columns of down); embeddings, norms
+// and the lm_head are replicated.  Shards may be uneven (13B at 8 ranks: 6,6,6,6,4,4,4,4 heads); n_head_local * D and F_local must
+// be multiples of 256 (quantisation super-blocks are not split).
+extern "C" eb_model *eb_model_create_tp(int E, int D, int n_head_local, int F_local, int V, int L, float eps, float freq_base) {
+    if (E <= 0 || D != 128 || n_head_local <= 0 || E % 256 || (n_head_local * D) % 256 || F_local <= 0 || F_local % 256 || L <= 0) {
+        eb_set_err(EB_ERR_ARG, "model_create_tp: E=%d D=%d heads=%d F_local=%d L=%d (head block and F_local must be multiples of 256)", E, D, n_head_local, F_local, L); return nullptr;
+    }
+    eb_model *m = new eb_model();
+    m->E = E; m->H = n_head_local; m->F = F_local; m->V = V; m->L = L; m->eps = eps; m->freq_base = freq_base; m->is_eagle = 0;
+    m->D = D; m->Ea = n_head_local * D;
     m->layers.assign(L, std::vector<DTensor>(EB_L_COUNT));
     m->fuse.assign(L, LayerFuse());
     return m;
@@ -202,7 +220,7 @@ static int ws_alloc(Workspace &w, const eb_model *m, int Tmax, int n_ctx) {
     EB_CUDA(cudaMalloc(&w.actq, w.actq_bytes)); EB_CUDA(cudaMalloc(&w.actq2, w.actq_bytes));
     w.partial_bytes = (size_t)8 * T * Nmax * 4;
     EB_CUDA(cudaMalloc((void **)&w.partial, w.partial_bytes));
-    w.fa_bytes = std::max(eb_flash_attn_ws_size_impl(Tmax, m->H, m->E / m->H, n_ctx), eb_fattn_tc_ws_size(Tmax, m->H, n_ctx));
+    w.fa_bytes = std::max(eb_flash_attn_ws_size_impl(Tmax, m->H, m->D, n_ctx), eb_fattn_tc_ws_size(Tmax, m->H, n_ctx));
     EB_CUDA(fa(&w.rope_tab, T * 256));
     EB_CUDA(cudaMalloc((void **)&w.q16, T * E * 2)); EB_CUDA(cudaMemset(w.q16, 0, T * E * 2));
     EB_CUDA(cudaMalloc(&w.fa_ws, w.fa_bytes));
@@ -216,7 +234,7 @@ static void ws_free(Workspace &w) {
         cudaFree(p);
 }
 static int kv_alloc(KVCache &kv, const eb_model *m, int n_ctx) {
-    kv.L = m->L; kv.E = m->E; kv.n_ctx = n_ctx; kv.layer_stride = (int64_t)n_ctx * m->E;
+    kv.L = m->L; kv.E = m->Ea; kv.n_ctx = n_ctx; kv.layer_stride = (int64_t)n_ctx * m->Ea;
     const size_t bytes = (size_t)kv.L * kv.layer_stride * 2;
     EB_CUDA(cudaMalloc((void **)&kv.k, bytes)); EB_CUDA(cudaMalloc((void **)&kv.v, bytes));
     EB_CUDA(cudaMemset(kv.k, 0, bytes)); EB_CUDA(cudaMemset(kv.v, 0, bytes));
@@ -230,7 +248,7 @@ extern "C" eb_session *eb_session_create(eb_model *target, eb_model *head, const
     if (head && (head->E != target->E || head->V != target->V)) { eb_set_err(EB_ERR_ARG, "session_create: head/target shape mismatch"); return nullptr; }
     eb_session *s = new eb_session();
     s->tgt = target; s->head = head; s->p = *p;
-    s->cfg = SpecCfg{p->max_nodes, p->n_branch, p->n_draft, p->max_depth, p->top_k, p->fixed_accept, p->p_split};
+    s->cfg = SpecCfg{p->max_nodes, p->n_branch, p->n_draft, p->max_depth, p->top_k, p->fixed_accept, p->p_split, p->p_min};
     const int E = target->E;
     auto fail = [&]() { eb_session_free(s); return (eb_session *)nullptr; };
     if (cudaStreamCreateWithFlags(&s->st, cudaStreamNonBlocking) != cudaSuccess) { eb_set_err(EB_ERR_CUDA, "stream"); delete s; return nullptr; }
@@ -258,6 +276,7 @@ extern "C" void eb_session_free(eb_session *s) {
     if (s->graph_verify) cudaGraphExecDestroy(s->graph_verify);
     ws_free(s->ws_t); cudaFree(s->kv_t.k); cudaFree(s->kv_t.v);
     if (s->head) { ws_free(s->ws_h); cudaFree(s->kv_h.k); cudaFree(s->kv_h.v); }
+    cudaFree(s->tp_buf);
     for (void *p : {(void *)s->state, (void *)s->root_feat, (void *)s->node_feat, (void *)s->cand_ids, (void *)s->cand_vals, (void *)s->cand_p, s->topk_scr, (void *)s->best, (void *)s->stage, (void *)s->d_res})
         cudaFree(p);
     if (s->h_res) cudaFreeHost(s->h_res);
@@ -307,7 +326,7 @@ static int tap_site(ActTap *tap, const ActQ &a, cudaStream_t st) {
 static int forward_dev(const eb_model *m, KVCache &kv, Workspace &w, const int32_t *tokens, const int32_t *pos, const uint32_t *bits,
                        const float *hidden, const FwdCtl *ctl, int T, bool want_logits, cudaStream_t st, int *logit_ks = nullptr,
                        const SpecState *spec = nullptr, const float *root_feat = nullptr, float *node_feat = nullptr,
-                       const int *gate_fwd = nullptr, const int *gate_lm = nullptr, ActTap *tap = nullptr) {
+                       const int *gate_fwd = nullptr, const int *gate_lm = nullptr, ActTap *tap = nullptr, eb_tp *tp = nullptr, float *tp_buf = nullptr) {
     // gate_fwd / gate_lm (draft levels of a captured round): device words that switch the whole forward / its lm_head off
     // when the tree stopped growing (common.cuh "launch gate"); the caller clears the gate after the call
     eb_gate_set(gate_fwd);
@@ -321,7 +340,7 @@ static int forward_dev(const eb_model *m, KVCache &kv, Workspace &w, const int32
     struct PdlScope { PdlScope(int m) { eb_pdl_scope(m); } ~PdlScope() { eb_pdl_scope(EB_PDL_ALL); } } pdl_scope_(T <= 8 ? pdl_small_mask : pdl_big_mask);
     // spec != null (draft level): hidden rows are gathered from root_feat / node_feat by the state's dft_src, and the result
     // features are scattered to node_feat, inside the kernels that read / produce them
-    const int E = m->E, H = m->H, F = m->F, D = E / H;
+    const int E = m->E, H = m->H, F = m->F, D = m->D, Ea = m->Ea;      // Ea = H * D: the attention width held here (= E unless sharded)
     int rc;
 #define RC(x) do { rc = (x); if (rc) return rc; } while (0)
     const DTensor &emb = m->g[EB_T_TOK_EMBD];
@@ -352,30 +371,34 @@ static int forward_dev(const eb_model *m, KVCache &kv, Workspace &w, const int32
         const LayerFuse &fu = m->fuse[l];
         PlaneRef rq, rk, rv;
         {
-            DTensor wqkv = t[EB_L_WQ]; wqkv.rows = (int64_t)fu.n_qkv * E;          // fused view: n_qkv matrices of E rows back to back
+            DTensor wqkv = t[EB_L_WQ]; wqkv.rows = (int64_t)fu.n_qkv * Ea;         // fused view: n_qkv matrices of Ea rows back to back
             int ks_;
             RC(mm_parts(wqkv, a, w.pq, &ks_, st));
             rq = PlaneRef{w.pq, ks_, wqkv.rows};
-            if (fu.n_qkv >= 2) rk = PlaneRef{w.pq + E, ks_, wqkv.rows}; else { RC(mm_parts(t[EB_L_WK], a, w.pk, &ks_, st)); rk = PlaneRef{w.pk, ks_, E}; }
-            if (fu.n_qkv >= 3) rv = PlaneRef{w.pq + 2 * E, ks_, wqkv.rows}; else { RC(mm_parts(t[EB_L_WV], a, w.pv, &ks_, st)); rv = PlaneRef{w.pv, ks_, E}; }
+            if (fu.n_qkv >= 2) rk = PlaneRef{w.pq + Ea, ks_, wqkv.rows}; else { RC(mm_parts(t[EB_L_WK], a, w.pk, &ks_, st)); rk = PlaneRef{w.pk, ks_, Ea}; }
+            if (fu.n_qkv >= 3) rv = PlaneRef{w.pq + 2 * Ea, ks_, wqkv.rows}; else { RC(mm_parts(t[EB_L_WV], a, w.pv, &ks_, st)); rv = PlaneRef{w.pv, ks_, Ea}; }
         }
         __half *kc = kv.k + (int64_t)l * kv.layer_stride, *vc = kv.v + (int64_t)l * kv.layer_stride;
         const bool fa_tc = eb_fattn_tc_supported(T, D);
         if (!skip_class("rope")) RC(eb_rope_kv_store_fused(rq, rk, rv, w.q, fa_tc ? w.q16 : nullptr, use_tab ? w.rope_tab : nullptr, kc, vc, ctl, D, H, T, st, pos, m->freq_base));
-        ActQ ao = eb_actq_carve(w.actq, grid_of(t[EB_L_WO]), E, T);
+        ActQ ao = eb_actq_carve(w.actq, grid_of(t[EB_L_WO]), Ea, T);
         int att_quantized = 0;
         if (skip_class("attn")) att_quantized = 1;
-        else if (fa_tc) RC(eb_fattn_tc(w.q16, kc, vc, E, kv.n_ctx, bits, ctl, 0, 0, T, H, 1.0f / sqrtf((float)D), w.att, w.fa_ws, st, &ao, &att_quantized));
-        else RC(eb_flash_attn_ctl(w.q, kc, vc, E, bits, ctl, T, H, D, kv.n_ctx, 1.0f / sqrtf((float)D), w.att, w.fa_ws, st));
+        else if (fa_tc) RC(eb_fattn_tc(w.q16, kc, vc, Ea, kv.n_ctx, bits, ctl, 0, 0, T, H, 1.0f / sqrtf((float)D), w.att, w.fa_ws, st, &ao, &att_quantized));
+        else RC(eb_flash_attn_ctl(w.q, kc, vc, Ea, bits, ctl, T, H, D, kv.n_ctx, 1.0f / sqrtf((float)D), w.att, w.fa_ws, st));
         if (!att_quantized) RC(eb_quantize_act(w.att, ao, st));
         RC(tap_site(tap, ao, st));
         int ko_;
         RC(mm_parts(t[EB_L_WO], ao, w.po, &ko_, st));
+        const float *po_planes = w.po;
+        // tensor parallel: wo is K-split over the ranks' heads; the partial [T][E] sums (this rank's split-K planes included) are
+        // summed over the group by one peer-memory kernel (tp.cu), every rank ends up with the same bits
+        if (tp) { RC(eb_tp_allreduce_planes(tp, w.po, ko_, (int64_t)T * E, tp_buf, st)); po_planes = tp_buf; ko_ = 1; }
         // ffn_inp = wo.att + x ; cur = rms_norm(ffn_inp) * ffn_norm -> grid of up/gate
         const int gu = grid_of(t[EB_L_UP]);
         if (grid_of(t[EB_L_GATE]) != gu) return eb_set_err(EB_ERR_UNSUPPORTED, "layer %d: ffn_up/ffn_gate mix formats", l);
         ActQ af = eb_actq_carve(w.actq, gu, E, T);
-        if (!skip_class("resid")) RC(eb_resid_norm_quant(w.x, w.po, ko_, (const float *)t[EB_L_FFN_NORM].data, m->eps, E, T, af, nullptr, st));
+        if (!skip_class("resid")) RC(eb_resid_norm_quant(w.x, po_planes, ko_, (const float *)t[EB_L_FFN_NORM].data, m->eps, E, T, af, nullptr, st));
         RC(tap_site(tap, af, st));
         PlaneRef rg, ru;
         {
@@ -394,6 +417,7 @@ static int forward_dev(const eb_model *m, KVCache &kv, Workspace &w, const int32
         RC(tap_site(tap, ad, st));
         RC(mm_parts(t[EB_L_DOWN], ad, w.pq, &pend_ks, st));       // pq is free again: holds the down planes
         pend = w.pq;
+        if (tp) { RC(eb_tp_allreduce_planes(tp, w.pq, pend_ks, (int64_t)T * E, tp_buf, st)); pend = tp_buf; pend_ks = 1; }   // ffn_down is K-split too
     }
     // x += pending; result_norm = rms_norm(x) * output_norm  (-> feat, and the lm_head's grid)
     const DTensor &o = m->g[EB_T_OUTPUT];
@@ -475,7 +499,8 @@ static int forward_bits(eb_session *s, int model, const int32_t *h_tokens, const
         EB_CUDA(cudaMemcpyAsync(w.hidden, h_hidden, (size_t)T * m->E * 4, cudaMemcpyHostToDevice, s->st));
     }
     ActTap *tap = s->tap.buf ? &s->tap : nullptr;
-    rc = forward_dev(m, kv, w, w.tokens, w.pos, w.bits, w.hidden, w.ctl, T, h_logits != nullptr, s->st, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, tap); if (rc) return rc;
+    rc = forward_dev(m, kv, w, w.tokens, w.pos, w.bits, w.hidden, w.ctl, T, h_logits != nullptr, s->st, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, tap,
+                     model ? nullptr : s->tp, s->tp_buf); if (rc) return rc;
     if (h_logits) EB_CUDA(cudaMemcpyAsync(h_logits, w.logits, (size_t)T * m->V * 4, cudaMemcpyDeviceToHost, s->st));
     if (h_feat) EB_CUDA(cudaMemcpyAsync(h_feat, w.feat, (size_t)T * m->E * 4, cudaMemcpyDeviceToHost, s->st));
     EB_CUDA(cudaStreamSynchronize(s->st));
@@ -505,6 +530,14 @@ extern "C" int eb_session_forward_batch(eb_session *s, int model, const int32_t 
     return forward_bits(s, model, h_tokens, h_pos, bits, h_hidden, T, h_logits, h_feat);
 }
 
+// tensor-parallel group of the TARGET forward (eb_session_forward / _forward_batch / _prefill / _verify_only with a shard model from
+// eb_model_create_tp); NULL detaches.  The draft head is not sharded (240 MB per level: nothing to gain).
+extern "C" int eb_session_set_tp(eb_session *s, eb_tp *tp) {
+    if (tp && !s->tp_buf) EB_CUDA(cudaMalloc((void **)&s->tp_buf, (size_t)128 * s->tgt->E * 4));
+    s->tp = tp;
+    if (s->graph_verify) { cudaGraphExecDestroy(s->graph_verify); s->graph_verify = nullptr; }
+    return EB_OK;
+}
 extern "C" int eb_session_set_tap(eb_session *s, void *d_buf, size_t bytes) {
     s->tap.buf = (int8_t *)d_buf; s->tap.cap = d_buf ? bytes : 0; s->tap.off = 0; s->tap.sites = 0;
     return EB_OK;
@@ -623,7 +656,8 @@ static int verify_dev(eb_session *s, int T, cudaStream_t st) {
     SpecState *d = s->state;
     // tree-verify forward + per-node greedy token; the argmax sums the lm_head's split-K planes, so it belongs to the step
     int ks = 1;
-    int rc = forward_dev(s->tgt, s->kv_t, s->ws_t, d->tokens, d->pos, d->tree_bits, nullptr, &d->ctl_tgt, T, true, st, &ks);
+    int rc = forward_dev(s->tgt, s->kv_t, s->ws_t, d->tokens, d->pos, d->tree_bits, nullptr, &d->ctl_tgt, T, true, st, &ks,
+                         nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, s->tp, s->tp_buf);
     if (rc) return rc;
     return eb_argmax_impl(s->ws_t.partial, T, s->tgt->V, s->best, st, ks, (int64_t)T * s->tgt->V);
 }

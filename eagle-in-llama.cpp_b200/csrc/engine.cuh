@@ -11,6 +11,9 @@ struct LayerFuse { int n_qkv = 1; bool gate_up = false; };
 
 struct eb_model {
     int E, H, F, V, L, is_eagle; float eps, freq_base;
+    // tensor-parallel shard (eb_model_create_tp): H = heads held by this rank, D = head size, Ea = H * D = rows of wq/wk/wv and
+    // columns of wo held here, F = ffn rows held here.  Unsharded models: D = E / H, Ea = E.
+    int D = 0, Ea = 0;
     DTensor g[EB_T_GLOBAL_COUNT];
     std::vector<std::vector<DTensor>> layers;
     std::vector<LayerFuse> fuse; std::vector<void *> fused_bufs; bool finalized = false;
@@ -30,6 +33,9 @@ struct Workspace {
     __half *q16;                                  // f16 copy of the rotated queries (TMA source of the tcgen05 attention)
 };
 
+struct eb_tp;      // tp.cu: peer-memory communicator of a tensor-parallel group
+int eb_tp_allreduce_planes(eb_tp *tp, const float *planes, int ks, int64_t n, float *out, cudaStream_t st);
+
 struct ActTap { int8_t *buf = nullptr; size_t cap = 0, off = 0; int sites = 0; };
 
 struct eb_session {
@@ -43,6 +49,8 @@ struct eb_session {
     cudaGraphExec_t graph_round = nullptr, graph_verify = nullptr; int graph_verify_T = 0;
     long graph_round_kernels = 0, graph_verify_kernels = 0;
     int last_T[2] = {0, 0};
+    eb_tp *tp = nullptr;   // tensor-parallel group of the target forward (eb_session_set_tp), or null
+    float *tp_buf = nullptr;
     int n_past_h = 0;      // host mirror of SpecState.n_past (advanced from the round result): no extra D2H per round
 };
 

@@ -165,6 +165,25 @@ EB_API int eb_model_get_tensor(const eb_model *m, int layer, int which, void *h_
 EB_API int eb_model_share_lm_head(eb_model *head, const eb_model *target);   /* R/src/llama.cpp:2016 */
 EB_API size_t eb_model_weight_bytes(const eb_model *m);   /* bytes one forward streams */
 
+/* ---- tensor parallelism of the target's verify forward (BASELINE config 4).  Replaces the reference's --split-mode row
+ * (ggml_backend_cuda_split_buffer_type / ggml_cuda_op_mul_mat, R/ggml/src/ggml-cuda/ggml-cuda.cu:735-748,1359-1668: weight rows
+ * split across GPUs, partial rows gathered to the main device by cudaMemcpyPeerAsync) with N-split wq|wk|wv|gate|up + K-split
+ * wo|down and ONE peer-memory all-reduce kernel per K-split output (csrc/tp.cu), one process per GPU.
+ * eb_model_create_tp: this rank's shard (n_head_local heads of size D = 128, F_local ffn rows, both * may be uneven across ranks,
+ * multiples of 256 elements); tensors are set with eb_model_set_tensor in the shard's own shapes: wq/wk/wv [n_head_local*D][E],
+ * wo [E][n_head_local*D], gate/up [F_local][E], down [E][F_local]; embeddings, norms and output are replicated.
+ * eb_tp_create / _handle / _open_peer: the communicator; the host program carries the 64-byte handles between the processes.
+ * eb_session_set_tp attaches it to a session whose target is a shard model; every rank must then make the same forward calls. */
+typedef struct eb_tp eb_tp;
+EB_API eb_model *eb_model_create_tp(int E, int D, int n_head_local, int F_local, int V, int L, float eps, float freq_base);
+EB_API eb_tp *eb_tp_create(int rank, int size, int64_t max_elems);
+EB_API int  eb_tp_handle(eb_tp *tp, void *out64);
+EB_API int  eb_tp_open_peer(eb_tp *tp, int peer_rank, const void *handle64);
+EB_API void eb_tp_free(eb_tp *tp);
+EB_API int  eb_tp_error(eb_tp *tp);      /* 1 after a wait for a peer timed out */
+/* out[i] = sum over ranks of sum over the ks planes [ks][n] of every rank; identical bits on all ranks; n % 4 == 0 */
+EB_API int  eb_tp_allreduce(eb_tp *tp, const float *d_planes, int ks, int64_t n, float *d_out, void *stream);
+
 typedef struct {
     int n_ctx;          /* KV cells per cache */
     int max_nodes;      /* verify batch capacity incl. root (<= 128) */
@@ -175,6 +194,8 @@ typedef struct {
     float p_split;      /* --draft-p-split, R/common/common.h:183 */
     int fixed_accept;   /* >= 0: accept exactly this many draft nodes per round (bench mode) */
     int use_graph;      /* capture the round in a CUDA graph */
+    float p_min;        /* --draft-p-min (R/common/speculative.cpp:283, default 0.75 R/common/common.h:184): a branch stops drafting after a
+                         * token whose draft probability (softmax over the kept top-k) is below p_min; 0 = off, as in the tree driver */
 } eb_session_params;
 
 EB_API eb_session *eb_session_create(eb_model *target, eb_model *head, const eb_session_params *p);
@@ -200,6 +221,7 @@ EB_API int eb_session_forward_batch(eb_session *s, int model, const int32_t *h_t
  * buffer is set, every eb_session_forward / _forward_batch appends the int8 activation plane [T][K] of each quantisation site
  * (per layer: input of wq|wk|wv, of wo, of gate|up, of ffn_down; then the lm_head input; the head's fc input first) to d_buf.
  * d_buf = NULL turns it off.  eb_session_tap_state reports bytes / sites written since set_tap.  Not used inside eb_session_round. */
+EB_API int eb_session_set_tp(eb_session *s, eb_tp *tp);
 EB_API int eb_session_set_tap(eb_session *s, void *d_buf, size_t bytes);
 EB_API int eb_session_tap_state(const eb_session *s, size_t *bytes_written, int *n_sites);
 /* commit the first n of the T tokens of the last forward of `model` (chain prefill) */
