@@ -218,7 +218,10 @@ def run_gpu(args, rank, world, local_rank):
         }
         if world == 1 and not args.no_cpu_baseline:
             try:
-                out["cpu_baseline"] = cpu_baseline(n_rounds=3)
+                out["cpu_baseline"] = cpu_baseline(n_rounds=3, with_plugin=True)
+                # the same verify step through the reference's own llama_decode -> ggml_backend_sched -> ggml_backend_graph_compute of
+                # libggml-b200.so (unfused ggml ops, host-side graph build and launches included), next to the engine's fused step
+                out["plugin_verify_step_us"] = out["cpu_baseline"].pop("plugin_verify_step_us", None)
             except Exception as e:                     # the baseline is a reported number, never the product path
                 out["cpu_baseline"] = {"error": str(e)}
     s.free()
@@ -249,7 +252,7 @@ class CpuRound:
     every one of the max_depth + 1 levels.  ggml build: -march=native + llamafile + repack (the reference's default cmake
     configuration) when this host's ISA allows it, else the deterministic AVX2 build — named in `kind_detail`."""
 
-    def __init__(self):
+    def __init__(self, with_plugin=False):
         import tempfile
         sys.path.insert(0, os.path.join(ROOT, "oracle")); sys.path.insert(0, os.path.join(ROOT, "tests"))
         import fixtures as fx
@@ -268,7 +271,6 @@ class CpuRound:
         tmp = tempfile.mkdtemp(prefix="eb_bench_")
         path = gf.write_gguf(tgt, os.path.join(tmp, "vicuna7b_q4_k_m_random.gguf"), n_ctx_train=8192)
         self.m = rr.Model(path, variant=self.variant)
-        os.remove(path); os.rmdir(tmp)
         rng = np.random.default_rng(11)
         self.par = fx.driver_like_tree(65, TREE["n_branch"], rng); self.depth = fx.tree_depths(self.par)
         self.seqs, n_seq = fx.tree_seq_ids(self.par)
@@ -278,6 +280,28 @@ class CpuRound:
                 self.c.kv_write(l, which, 0, rng.standard_normal((N_PAST0, HP["E"]), np.float32).astype(np.float16))
         self.n_seq = n_seq
         self.tokens = rng.integers(3, HP["V"], 65).astype(np.int32)
+        # the same GGUF through the reference's loader with every layer on libggml-b200.so (the CPU context above was created before
+        # the plug-in was registered, so its scheduler holds the CPU backend only)
+        self.plugin_us = None; self.plugin_err = None
+        if with_plugin:
+            try:
+                plug = os.path.join(ROOT, "eagle-in-llama.cpp_b200", "ggml_backend", "libggml-b200.so")
+                if rr.lib().rr_load_backend(plug.encode()) < 2:
+                    raise RuntimeError("ggml_backend_load(libggml-b200.so) failed")
+                mp = rr.Model(path, n_gpu_layers=99, variant=self.variant)
+                cp = rr.Context(mp, 4096 + 256, n_batch=512, n_seq_max=max(8, n_seq), n_threads=self.cores)
+                for l in range(HP["L"]):
+                    for which in (0, 1):
+                        cp.kv_write(l, which, 0, rng.standard_normal((N_PAST0, HP["E"]), np.float32).astype(np.float16))
+                ts = []
+                for _ in range(8):
+                    cp.kv_set_prefix(N_PAST0, n_seq)
+                    ts.append(cp.time_decode(self.tokens, N_PAST0 + self.depth, self.seqs))
+                self.plugin_us = float(np.median(ts[3:]))
+                cp.free(); mp.free()
+            except Exception as e:                           # reported, never fatal for the bench line
+                self.plugin_err = str(e)
+        os.remove(path); os.rmdir(tmp)
         # draft head: build_eagle on the same ggml-cpu (lm_head = the target's output matrix)
         self.ref = po.ref(); self.ref._g("set_threads")(self.cores)
         E, F, V = HP["E"], HP["F"], HP["V"]
@@ -330,9 +354,9 @@ class CpuRound:
                                 else "reference libllama + ggml-cpu, deterministic AVX2/FMA build (this host's ISA does not cover the native build's)")}
 
 
-def cpu_baseline(n_rounds=3):
+def cpu_baseline(n_rounds=3, with_plugin=False):
     """reference CPU path on the host cores: n_rounds whole rounds (each ~3 s of a 16-thread host), nothing scaled"""
-    c = CpuRound()
+    c = CpuRound(with_plugin=with_plugin)
     c.round_s()                                              # warm the thread pool and the page cache
     rs = [c.round_s() for _ in range(n_rounds)]
     rnd = float(np.median([r[0] for r in rs])); ver = float(np.median([r[1] for r in rs]))
@@ -341,6 +365,8 @@ def cpu_baseline(n_rounds=3):
               "sample": f"{n_rounds} whole rounds after 1 warm-up: llama_decode of the 65-token tree batch over all 32 layers at n_kv 4096 "
                         f"(median {ver:.2f} s) + {TREE['max_depth'] + 1} draft-head levels of {TREE['n_branch']} rows (median round {rnd:.2f} s); "
                         f"model + KV set-up {c.setup_s:.0f} s outside the timing"})
+    if with_plugin:
+        d["plugin_verify_step_us"] = c.plugin_us if c.plugin_us is not None else {"error": c.plugin_err}
     return d
 
 

@@ -72,6 +72,13 @@ def lib():
         "eb_cpy_f32_f16": ([vp, vp, i64, vp], i32),
         "eb_flash_attn_ws_size": ([i32, i32, i32, i32], sz),
         "eb_flash_attn": ([vp, vp, vp, i64, vp, i64, vp, i32, i32, i32, i32, i32, f32, vp, vp, vp], i32),
+        "eb_mask_bits_size": ([i32, i32], sz), "eb_mask_to_bits": ([vp, i64, i32, i32, vp, C.POINTER(i32), vp], i32),
+        "eb_flash_attn_bits_supported": ([i32, i32, i32, i64], i32),
+        "eb_flash_attn_bits": ([vp, vp, vp, i64, vp, i32, i32, i32, i32, f32, vp, vp, vp], i32),
+        "eb_stream_create": ([C.POINTER(vp)], i32), "eb_stream_destroy": ([vp], i32), "eb_device_synchronize": ([], i32),
+        "eb_upload_async": ([vp, vp, sz, vp], i32), "eb_download_async": ([vp, vp, sz, vp], i32),
+        "eb_event_create": ([C.POINTER(vp)], i32), "eb_event_destroy": ([vp], i32), "eb_event_record": ([vp, vp], i32),
+        "eb_stream_wait_event": ([vp, vp], i32), "eb_event_synchronize": ([vp], i32),
         "eb_top_k": ([vp, i32, i32, i32, vp, vp, vp, vp], i32), "eb_argmax": ([vp, i32, i32, vp, vp], i32),
         "eb_top_k_noalloc": ([vp, i32, i32, i32, vp, vp, vp, vp], i32),
         "eb_model_create": ([i32, i32, i32, i32, i32, f32, f32, i32], vp), "eb_model_free": ([vp], None),
@@ -346,6 +353,26 @@ def flash_attn_ext(q, k, v, scale, mask_f16=None, tree_bits=None, n_prefix=0):
     _ck(lib().eb_flash_attn(dq.ptr, dk.ptr, dv.ptr, H * D, dm.ptr if dm else None, stride, db.ptr if db else None,
                             n_prefix, T, H, D, n_kv, scale, do.ptr, ws.ptr, None))
     return do.to_host(np.float32, q.shape)
+
+
+def flash_attn_ext_bits(q, k, v, scale, mask_f16, stream=None):
+    """GGML_OP_FLASH_ATTN_EXT through eb_mask_to_bits + eb_flash_attn_bits (tcgen05 kernel, any 0 / -inf mask, any T).
+    -> (out, general): general = True means the mask held other values and `out` is None (use flash_attn_ext)."""
+    q = np.ascontiguousarray(q, np.float32)
+    T, H, D = q.shape
+    k = np.ascontiguousarray(k).view(np.uint16); v = np.ascontiguousarray(v).view(np.uint16)
+    n_kv = k.shape[0]
+    m = np.ascontiguousarray(mask_f16, np.float16)
+    dq, dk, dv, do = DeviceBuffer.from_host(q), DeviceBuffer.from_host(k), DeviceBuffer.from_host(v), DeviceBuffer(q.nbytes)
+    dm = DeviceBuffer.from_host(m.view(np.uint16))
+    ws = DeviceBuffer(lib().eb_flash_attn_ws_size(T, H, D, n_kv)); bits = DeviceBuffer(lib().eb_mask_bits_size(T, n_kv))
+    general = C.c_int(-1)
+    _ck(lib().eb_mask_to_bits(dm.ptr, m.shape[1], T, n_kv, bits.ptr, C.byref(general), stream))
+    if general.value:
+        return None, True
+    _ck(lib().eb_flash_attn_bits(dq.ptr, dk.ptr, dv.ptr, H * D, bits.ptr, T, H, D, n_kv, scale, do.ptr, ws.ptr, stream))
+    _ck(lib().eb_synchronize(stream))
+    return do.to_host(np.float32, q.shape), False
 
 
 def top_k(logits, k):

@@ -161,6 +161,37 @@ int eb_flash_attn(const float *q, const void *k, const void *v, int64_t kv_strid
     }
     return eb_flash_attn_impl(q, k, v, kv_stride, mask, mask_stride, tree_bits, n_prefix, T, H, D, n_kv, scale, out, ws, S(st));
 }
+// the ggml mask in bit form (any mask whose values are 0 or -inf): lets the tcgen05 kernel serve GGML_OP_FLASH_ATTN_EXT
+size_t eb_mask_bits_size(int T, int n_kv) { return eb_mask_bits_size_impl(T, n_kv); }
+int eb_mask_to_bits(const void *mask, int64_t mask_stride, int T, int n_kv, void *bits, int *h_general, void *st) {
+    NEED_DEV();
+    if (T < 1 || n_kv < 1 || !mask || !bits) return eb_set_err(EB_ERR_ARG, "mask_to_bits: T %d n_kv %d", T, n_kv);
+    int rc = eb_mask_to_bits_impl(mask, mask_stride, T, n_kv, bits, S(st)); if (rc) return rc;
+    if (h_general) {                                    // the caller decides on the host which kernel runs: one 4-byte read per mask
+        EB_CUDA(cudaMemcpyAsync(h_general, eb_mask_bits_flag(bits, T, n_kv), 4, cudaMemcpyDeviceToHost, S(st)));
+        EB_CUDA(cudaStreamSynchronize(S(st)));
+    }
+    return EB_OK;
+}
+int eb_flash_attn_bits_supported(int T, int H, int D, int64_t kv_stride) { (void)H; return T >= 1 && eb_fattn_tc_supported(std::min(T, 128), D) && kv_stride % 8 == 0; }
+int eb_flash_attn_bits(const float *q, const void *k, const void *v, int64_t kv_stride, const void *bits, int T, int H, int D, int n_kv, float scale, float *out,
+                       void *ws, void *st) {
+    NEED_DEV();
+    if (!eb_flash_attn_bits_supported(T, H, D, kv_stride)) return eb_set_err(EB_ERR_UNSUPPORTED, "flash_attn_bits: T %d D %d kv_stride %lld", T, D, (long long)kv_stride);
+    return eb_fattn_tc_bits(q, k, v, kv_stride, bits, T, H, n_kv, scale, out, ws, S(st));
+}
+// streams and events for hosts that own several execution contexts (one ggml_backend_t = one stream)
+int eb_stream_create(void **st) { NEED_DEV(); cudaStream_t s; EB_CUDA(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking)); *st = (void *)s; return EB_OK; }
+int eb_stream_destroy(void *st) { if (st) EB_CUDA(cudaStreamDestroy(S(st))); return EB_OK; }
+int eb_device_synchronize(void) { NEED_DEV(); EB_CUDA(cudaDeviceSynchronize()); return EB_OK; }
+int eb_upload_async(void *d, const void *h, size_t bytes, void *st) { NEED_DEV(); EB_CUDA(cudaMemcpyAsync(d, h, bytes, cudaMemcpyHostToDevice, S(st))); return EB_OK; }
+int eb_download_async(void *h, const void *d, size_t bytes, void *st) { NEED_DEV(); EB_CUDA(cudaMemcpyAsync(h, d, bytes, cudaMemcpyDeviceToHost, S(st))); return EB_OK; }
+int eb_event_create(void **ev) { NEED_DEV(); cudaEvent_t e; EB_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming)); *ev = (void *)e; return EB_OK; }
+int eb_event_destroy(void *ev) { if (ev) EB_CUDA(cudaEventDestroy((cudaEvent_t)ev)); return EB_OK; }
+int eb_event_record(void *ev, void *st) { EB_CUDA(cudaEventRecord((cudaEvent_t)ev, S(st))); return EB_OK; }
+int eb_stream_wait_event(void *st, void *ev) { EB_CUDA(cudaStreamWaitEvent(S(st), (cudaEvent_t)ev, 0)); return EB_OK; }
+int eb_event_synchronize(void *ev) { EB_CUDA(cudaEventSynchronize((cudaEvent_t)ev)); return EB_OK; }
+
 int eb_top_k(const float *logits, int rows, int V, int k, int32_t *ids, float *vals, float *probs, void *st) { NEED_DEV(); return eb_top_k_impl(logits, rows, V, k, ids, vals, probs, S(st), 1, 0, rows <= 128 ? eb_top_k_default_scratch() : nullptr); }
 int eb_argmax(const float *logits, int rows, int V, int32_t *ids, void *st) { NEED_DEV(); return eb_argmax_impl(logits, rows, V, ids, S(st)); }
 

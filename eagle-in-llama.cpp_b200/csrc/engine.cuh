@@ -87,7 +87,13 @@ int eb_rope_kv_store_fused(PlaneRef qp, PlaneRef kp, PlaneRef vp, float *q, void
 // fattn_tc.cu: tcgen05 tree attention
 int eb_fattn_tc_init(); int eb_fattn_tc_supported(int T, int D); size_t eb_fattn_tc_ws_size(int T, int H, int n_kv);
 int eb_fattn_tc(const __half *q16, const void *k, const void *v, int64_t kv_stride, int64_t n_cells, const uint32_t *tree_bits, const FwdCtl *ctl,
-                int n_prefix, int n_kv, int T, int H, float scale, float *out, void *ws, cudaStream_t st, const ActQ *aq, int *quantized);
+                int n_prefix, int n_kv, int T, int H, float scale, float *out, void *ws, cudaStream_t st, const ActQ *aq, int *quantized,
+                const uint32_t *mask_bits = nullptr, int mask_words = 0, const uint8_t *tile_kind = nullptr);
+size_t eb_mask_bits_size_impl(int T, int n_kv);
+int eb_mask_to_bits_impl(const void *mask, int64_t mask_stride, int T, int n_kv, void *bits, cudaStream_t st);
+const int *eb_mask_bits_flag(const void *bits, int T, int n_kv);
+int eb_fattn_tc_bits(const float *q, const void *k, const void *v, int64_t kv_stride, const void *bits, int T, int H, int n_kv, float scale, float *out, void *ws,
+                     cudaStream_t st);
 int eb_fattn_tc_f32q(const float *q, const void *k, const void *v, int64_t kv_stride, const uint32_t *tree_bits, int n_prefix, int n_kv,
                      int T, int H, float scale, float *out, void *ws, cudaStream_t st);
 int eb_swiglu_quant(PlaneRef gate, PlaneRef up, int n, int T, const ActQ &aq, cudaStream_t st);

@@ -38,6 +38,7 @@ constexpr uint32_t FT_COL_O = 256;                      // TMEM: S[0] 0..127, S[
 
 struct FtArgs {
     const uint32_t *tree_bits; const FwdCtl *ctl;
+    const uint32_t *mask_bits; const uint8_t *tile_kind; int mask_words;     // general 0 / -inf mask as bits (operator layer), or null
     int n_prefix, n_kv, n_ctx;
     int T, H, nsplit;
     float scale_log2;
@@ -160,7 +161,7 @@ fattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         const bool live = row < p.T;
         const uint32_t lane_base = tmem + ((uint32_t)(q * 32) << 16);
         uint32_t tb[4] = {0, 0, 0, 0};
-        if (live) { const uint4 w = *(const uint4 *)(p.tree_bits + row * 4); tb[0] = w.x; tb[1] = w.y; tb[2] = w.z; tb[3] = w.w; }
+        if (live && p.tree_bits) { const uint4 w = *(const uint4 *)(p.tree_bits + row * 4); tb[0] = w.x; tb[1] = w.y; tb[2] = w.z; tb[3] = w.w; }
         const float c = p.scale_log2;
         float m = -INFINITY, l = 0.f;                                       // m in raw score units (before the scale)
         const bool prof = p.prof && blockIdx.x == 0 && blockIdx.y == 0 && warp == 4 && lane == 0;
@@ -177,7 +178,19 @@ fattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
             wait_ld();
             FA_CK(1);
             const int cb0 = (t0 + i) * FT_TILE;
-            if (cb0 + FT_TILE > n_prefix) {                                  // tile touches the tree cells (or the cache tail)
+            if (p.mask_bits) {                                               // any 0 / -inf mask: one bit per (row, cell), tiles that hide nothing are flagged 0
+                if (p.tile_kind[t0 + i]) {
+                    uint4 w = make_uint4(0u, 0u, 0u, 0u);
+                    if (live) w = *(const uint4 *)(p.mask_bits + (size_t)row * p.mask_words + (cb0 >> 5));
+                    const uint32_t vws[4] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+                    for (int ch = 0; ch < 4; ch++) {
+                        const uint32_t vw = vws[ch];
+#pragma unroll
+                        for (int k = 0; k < 32; k++) if (!((vw >> k) & 1u)) sr[ch][k] = 0xff800000u;   // -inf
+                    }
+                }
+            } else if (cb0 + FT_TILE > n_prefix) {                           // tile touches the tree cells (or the cache tail)
 #pragma unroll
                 for (int ch = 0; ch < 4; ch++) {
                     const uint32_t vw = vis_word(cb0 + ch * 32, n_prefix, tb);
@@ -318,10 +331,13 @@ void eb_fattn_combine_quant(const float *part_o, const float *part_ml, int T, in
 // q16: f16 copy of the (rotated) queries [T][H*128]; k, v: f16 cells with kv_stride elements between cells.
 // ctl != null: lengths are read on the device (engine); otherwise n_prefix / n_kv are used.
 int eb_fattn_tc(const __half *q16, const void *k, const void *v, int64_t kv_stride, int64_t n_cells, const uint32_t *tree_bits, const FwdCtl *ctl,
-                int n_prefix, int n_kv, int T, int H, float scale, float *out, void *ws, cudaStream_t st, const ActQ *aq, int *quantized) {
+                int n_prefix, int n_kv, int T, int H, float scale, float *out, void *ws, cudaStream_t st, const ActQ *aq, int *quantized,
+                const uint32_t *mask_bits, int mask_words, const uint8_t *tile_kind) {
     FtArgs p;
     if (quantized) *quantized = 0;
     p.tree_bits = tree_bits; p.ctl = ctl; p.n_prefix = n_prefix; p.n_kv = n_kv; p.n_ctx = (int)n_cells;
+    p.mask_bits = mask_bits; p.mask_words = mask_words; p.tile_kind = tile_kind;
+    if (!mask_bits && !tree_bits) return eb_set_err(EB_ERR_ARG, "flash_attn: no mask form given");
     p.T = T; p.H = H; p.scale_log2 = scale * 1.44269504f;
     const int n_tiles_max = (int)cdiv(n_cells, FT_TILE);     // the split count depends on the buffer size only (workspace bound)
     p.nsplit = eb_fattn_tc_nsplit(H, n_tiles_max);
@@ -365,7 +381,67 @@ int eb_fattn_tc_f32q(const float *q, const void *k, const void *v, int64_t kv_st
     const int64_t nq = (int64_t)T * H * 128;
     q_to_f16_kernel<<<(unsigned)cdiv(nq / 4, 256), 256, 0, st>>>(q, q16, nq);
     EB_CHECK_LAUNCH();
-    return eb_fattn_tc(q16, k, v, kv_stride, n_kv, tree_bits, nullptr, n_prefix, std::min(n_kv, n_prefix + T), T, H, scale, out, ws, st, nullptr, nullptr);
+    return eb_fattn_tc(q16, k, v, kv_stride, n_kv, tree_bits, nullptr, n_prefix, std::min(n_kv, n_prefix + T), T, H, scale, out, ws, st, nullptr, nullptr, nullptr, 0, nullptr);
+}
+// ---- general 0 / -inf masks (the ggml f16 mask of GGML_OP_FLASH_ATTN_EXT, R/ggml/include/ggml.h:1778-1793) as bits
+// layout of the bits buffer: uint32 [T][words] (words = 4 per 128-cell tile, bit = visible) | uint8 [n_tiles] tile kinds (0 = every
+// row sees every cell of the tile, else 2) | int flag (1 = some mask value is neither 0 nor -inf: the bit form does not apply)
+static int mask_words_of(int n_kv) { return 4 * (int)cdiv(n_kv, FT_TILE); }
+size_t eb_mask_bits_size_impl(int T, int n_kv) { return (size_t)T * mask_words_of(n_kv) * 4 + (((size_t)cdiv(n_kv, FT_TILE) + 15) & ~(size_t)15) + 16; }
+// one CTA per tile, one warp per row at a time: lane l reads cells l, l+32, l+64, l+96 (coalesced), four ballots = the four words
+__global__ void __launch_bounds__(128) mask_to_bits_kernel(const __half *__restrict__ mask, int64_t mask_stride, int T, int n_kv, uint32_t *__restrict__ bits, int words,
+                                                           uint8_t *__restrict__ kind, int *__restrict__ flag) {
+    const int tile = blockIdx.x, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    bool all = true, general = false;
+    for (int r = warp; r < T; r += 4) {
+        const __half *mr = mask + (size_t)r * mask_stride + (size_t)tile * FT_TILE;
+        uint32_t w[4];
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const int c = tile * FT_TILE + 32 * k + lane;
+            float v = -INFINITY;
+            if (c < n_kv) v = __half2float(mr[32 * k + lane]);
+            general |= !(v == 0.f || v == -INFINITY);
+            w[k] = __ballot_sync(0xffffffffu, v == 0.f);
+            all &= w[k] == 0xffffffffu;
+        }
+        if (lane == 0) *(uint4 *)(bits + (size_t)r * words + 4 * tile) = make_uint4(w[0], w[1], w[2], w[3]);
+    }
+    const int every = __syncthreads_and(all ? 1 : 0);
+    if (threadIdx.x == 0) kind[tile] = every ? 0 : 2;
+    if (__any_sync(0xffffffffu, general) && lane == 0) atomicOr(flag, 1);
+}
+int eb_mask_to_bits_impl(const void *mask, int64_t mask_stride, int T, int n_kv, void *bits, cudaStream_t st) {
+    const int words = mask_words_of(n_kv), n_tiles = (int)cdiv(n_kv, FT_TILE);
+    uint8_t *kind = (uint8_t *)bits + (size_t)T * words * 4;
+    int *flag = (int *)(kind + ((n_tiles + 15) & ~15));
+    EB_CUDA(cudaMemsetAsync(flag, 0, 4, st));
+    mask_to_bits_kernel<<<n_tiles, 128, 0, st>>>((const __half *)mask, mask_stride, T, n_kv, (uint32_t *)bits, words, kind, flag);
+    EB_CHECK_LAUNCH();
+    return EB_OK;
+}
+const int *eb_mask_bits_flag(const void *bits, int T, int n_kv) {
+    const int n_tiles = (int)cdiv(n_kv, FT_TILE);
+    return (const int *)((const uint8_t *)bits + (size_t)T * mask_words_of(n_kv) * 4 + ((n_tiles + 15) & ~15));
+}
+// operator-layer entry with the bit mask: query rows in chunks of one 128-row tile (prompt-sized batches), f32 q -> f16 as above
+int eb_fattn_tc_bits(const float *q, const void *k, const void *v, int64_t kv_stride, const void *bits, int T, int H, int n_kv, float scale, float *out, void *ws,
+                     cudaStream_t st) {
+    if (!ws) return eb_set_err(EB_ERR_ARG, "flash_attn: workspace required");
+    const int words = mask_words_of(n_kv);
+    const uint8_t *kind = (const uint8_t *)bits + (size_t)T * words * 4;
+    const int ns = eb_fattn_tc_nsplit(H, (int)cdiv(n_kv, FT_TILE));
+    for (int t0 = 0; t0 < T; t0 += 128) {
+        const int tc = std::min(128, T - t0);
+        __half *q16 = (__half *)((uint8_t *)ws + (((size_t)H * ns * tc * (128 + 2) * 4 + 255) & ~(size_t)255));
+        const int64_t nq = (int64_t)tc * H * 128;
+        q_to_f16_kernel<<<(unsigned)cdiv(nq / 4, 256), 256, 0, st>>>(q + (size_t)t0 * H * 128, q16, nq);
+        EB_CHECK_LAUNCH();
+        int rc = eb_fattn_tc(q16, k, v, kv_stride, n_kv, nullptr, nullptr, n_kv, n_kv, tc, H, scale, out + (size_t)t0 * H * 128, ws, st, nullptr, nullptr,
+                             (const uint32_t *)bits + (size_t)t0 * words, words, kind);
+        if (rc) return rc;
+    }
+    return EB_OK;
 }
 int eb_fattn_tc_init() {
     EB_CUDA(cudaFuncSetAttribute(fattn_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FT_SMEM));

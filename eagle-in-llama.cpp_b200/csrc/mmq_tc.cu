@@ -628,7 +628,9 @@ static int tc_pick_ksplit(int64_t N, int nbr) {
         const int spp = (int)cdiv(nbr, ks), eff_ks = (int)cdiv(nbr, spp);
         if (eff_ks != ks) continue;
         const int rounds = (int)cdiv((int64_t)n_rb * ks, G);
-        static const double c_item = getenv("EB_TC_CITEM") ? atof(getenv("EB_TC_CITEM")) : 2.0;   // per-item fill in super-block units
+        // per-item cost in super-block units.  Fit of the EB_TC_KS sweep of 22016 x 4096 (profiles/r2_summary.md):
+        // t = 0.74 us + 0.835 us per super-block + 0.82 us per item, i.e. one item ~ one super-block
+        static const double c_item = getenv("EB_TC_CITEM") ? atof(getenv("EB_TC_CITEM")) : 1.0;
         const double cost = rounds * (spp + c_item) + 0.25 * ks;
         if (cost < best_cost) { best_cost = cost; best = ks; }
     }

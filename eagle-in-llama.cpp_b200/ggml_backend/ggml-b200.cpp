@@ -30,6 +30,7 @@
 #include <cmath>
 #include <cstdint>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <string>
@@ -52,11 +53,15 @@ static void b200_buf_init_tensor(ggml_backend_buffer_t, ggml_tensor *t) {
     if (t->view_src && b200_repacked(t->type) && !(t->view_offs == 0 && ggml_nbytes(t) == ggml_nbytes(t->view_src)))
         GGML_ABORT("ggml-b200: partial views of %s tensors are not supported", ggml_type_name(t->type));
 }
+// The buffer interface is blocking and knows no backend: compute runs on per-backend non-blocking streams, so these calls first
+// wait for the whole device (ggml_backend_cuda_buffer_set_tensor does the same with cudaStreamPerThread + synchronize, ggml-cuda.cu:571-590)
 static void b200_buf_memset_tensor(ggml_backend_buffer_t, ggml_tensor *t, uint8_t v, size_t off, size_t size) {
+    B200_OK(eb_device_synchronize());
     B200_OK(eb_memset((char *)t->data + off, v, size, nullptr)); B200_OK(eb_synchronize(nullptr));
 }
 // host -> device, blocking (ggml_backend_cuda_buffer_set_tensor, ggml-cuda.cu:571)
 static void b200_buf_set_tensor(ggml_backend_buffer_t, ggml_tensor *t, const void *data, size_t off, size_t size) {
+    B200_OK(eb_device_synchronize());
     if (!b200_repacked(t->type)) { B200_OK(eb_upload((char *)t->data + off, data, size, nullptr)); return; }
     const size_t total = ggml_nbytes(t);
     void *stage = nullptr; B200_OK(eb_malloc(&stage, total));
@@ -66,7 +71,7 @@ static void b200_buf_set_tensor(ggml_backend_buffer_t, ggml_tensor *t, const voi
     B200_OK(eb_synchronize(nullptr)); B200_OK(eb_free(stage));
 }
 static void b200_buf_get_tensor(ggml_backend_buffer_t, const ggml_tensor *t, void *data, size_t off, size_t size) {
-    B200_OK(eb_synchronize(nullptr));
+    B200_OK(eb_device_synchronize());
     if (!b200_repacked(t->type)) { B200_OK(eb_download(data, (const char *)t->data + off, size, nullptr)); return; }
     void *stage = nullptr; B200_OK(eb_malloc(&stage, ggml_nbytes(t)));
     B200_OK(eb_unpack((int)t->type, t->data, stage, ggml_nelements(t), nullptr));
@@ -75,11 +80,12 @@ static void b200_buf_get_tensor(ggml_backend_buffer_t, const ggml_tensor *t, voi
 static ggml_backend_buffer_type_t b200_buffer_type();
 static bool b200_buf_cpy_tensor(ggml_backend_buffer_t, const ggml_tensor *src, ggml_tensor *dst) {
     if (!src->buffer || src->buffer->buft != b200_buffer_type() || !ggml_is_contiguous(src) || !ggml_is_contiguous(dst)) return false;
+    B200_OK(eb_device_synchronize());
     B200_OK(eb_copy(dst->data, src->data, ggml_nbytes(src), nullptr)); B200_OK(eb_synchronize(nullptr));
     return true;
 }
 static void b200_buf_clear(ggml_backend_buffer_t b, uint8_t v) {
-    auto *c = (b200_buffer_ctx *)b->context; B200_OK(eb_memset(c->base, v, c->size, nullptr)); B200_OK(eb_synchronize(nullptr));
+    auto *c = (b200_buffer_ctx *)b->context; B200_OK(eb_device_synchronize()); B200_OK(eb_memset(c->base, v, c->size, nullptr)); B200_OK(eb_synchronize(nullptr));
 }
 static const ggml_backend_buffer_i b200_buffer_iface = {
     b200_buf_free, b200_buf_base, b200_buf_init_tensor, b200_buf_memset_tensor, b200_buf_set_tensor, b200_buf_get_tensor,
@@ -98,17 +104,60 @@ static size_t b200_buft_alloc_size(ggml_backend_buffer_type_t, const ggml_tensor
 static bool b200_buft_is_host(ggml_backend_buffer_type_t) { return false; }
 
 // ---------------------------------------------------------------------------------- backend
+// one ggml_backend_t = one stream (ggml_backend_cuda_context::stream(), R/ggml/src/ggml-cuda/common.cuh): graphs, async copies and
+// events of one backend are ordered on it; two backends of the same device overlap
 struct b200_backend_ctx {
+    void *stream = nullptr;
     void *ws = nullptr; size_t ws_size = 0;      // scratch of eb_mul_mat / eb_flash_attn, grown on demand
     void *scratch(size_t need) {
-        if (need > ws_size) { if (ws) { eb_synchronize(nullptr); eb_free(ws); } ws = nullptr; ws_size = 0; if (eb_malloc(&ws, need) != EB_OK) return nullptr; ws_size = need; }
+        if (need > ws_size) { if (ws) { eb_synchronize(stream); eb_free(ws); } ws = nullptr; ws_size = 0; if (eb_malloc(&ws, need) != EB_OK) return nullptr; ws_size = need; }
         return ws;
     }
+    // FLASH_ATTN_EXT: the mask of a graph in bit form (every layer uses the same KQ_mask tensor), valid for one graph_compute
+    void *bits = nullptr; size_t bits_size = 0;
+    const void *mask_data = nullptr; int mask_T = 0, mask_kv = 0; bool mask_bits_ok = false;
 };
 
 static const char *b200_be_name(ggml_backend_t) { return B200_NAME; }
-static void b200_be_free(ggml_backend_t be) { auto *c = (b200_backend_ctx *)be->context; if (c->ws) eb_free(c->ws); delete c; delete be; }
-static void b200_be_sync(ggml_backend_t) { B200_OK(eb_synchronize(nullptr)); }
+static void b200_be_free(ggml_backend_t be) {
+    auto *c = (b200_backend_ctx *)be->context;
+    eb_synchronize(c->stream);
+    if (c->ws) eb_free(c->ws);
+    if (c->bits) eb_free(c->bits);
+    eb_stream_destroy(c->stream);
+    delete c; delete be;
+}
+static void b200_be_sync(ggml_backend_t be) { B200_OK(eb_synchronize(((b200_backend_ctx *)be->context)->stream)); }
+// stream-ordered copies (ggml_backend_cuda_set_tensor_async / get_tensor_async, R/ggml/src/ggml-cuda/ggml-cuda.cu:2390-2410); weights in
+// plane layout go through the blocking repack path
+static void b200_be_set_tensor_async(ggml_backend_t be, ggml_tensor *t, const void *data, size_t off, size_t size) {
+    ggml_backend_buffer_t buf = t->view_src ? t->view_src->buffer : t->buffer;
+    if (b200_repacked(t->type)) { buf->iface.set_tensor(buf, t, data, off, size); return; }
+    B200_OK(eb_upload_async((char *)t->data + off, data, size, ((b200_backend_ctx *)be->context)->stream));
+}
+static void b200_be_get_tensor_async(ggml_backend_t be, const ggml_tensor *t, void *data, size_t off, size_t size) {
+    ggml_backend_buffer_t buf = t->view_src ? t->view_src->buffer : t->buffer;
+    if (b200_repacked(t->type)) { buf->iface.get_tensor(buf, t, data, off, size); return; }
+    B200_OK(eb_download_async(data, (const char *)t->data + off, size, ((b200_backend_ctx *)be->context)->stream));
+}
+static ggml_backend_buffer_type_t b200_buffer_type();
+static bool b200_be_cpy_tensor_async(ggml_backend_t src_be, ggml_backend_t dst_be, const ggml_tensor *src, ggml_tensor *dst) {
+    // both ends on this device type, contiguous, not in plane layout: a device copy on the destination's stream after the source's work
+    if (src_be->iface.get_name != b200_be_name || dst_be->iface.get_name != b200_be_name) return false;
+    ggml_backend_buffer_t sb = src->view_src ? src->view_src->buffer : src->buffer, db = dst->view_src ? dst->view_src->buffer : dst->buffer;
+    if (!sb || !db || sb->buft != b200_buffer_type() || db->buft != b200_buffer_type()) return false;
+    if (!ggml_is_contiguous(src) || !ggml_is_contiguous(dst) || ggml_nbytes(src) != ggml_nbytes(dst)) return false;
+    auto *sc = (b200_backend_ctx *)src_be->context; auto *dc = (b200_backend_ctx *)dst_be->context;
+    if (sc != dc) {
+        void *ev = nullptr;
+        B200_OK(eb_event_create(&ev)); B200_OK(eb_event_record(ev, sc->stream)); B200_OK(eb_stream_wait_event(dc->stream, ev)); B200_OK(eb_event_destroy(ev));
+    }
+    B200_OK(eb_copy(dst->data, src->data, ggml_nbytes(src), dc->stream));
+    return true;
+}
+// events (ggml_backend_cuda_event_record / event_wait, ggml-cuda.cu:2790-2815)
+static void b200_be_event_record(ggml_backend_t be, ggml_backend_event_t ev) { B200_OK(eb_event_record(ev->context, ((b200_backend_ctx *)be->context)->stream)); }
+static void b200_be_event_wait(ggml_backend_t be, ggml_backend_event_t ev) { B200_OK(eb_stream_wait_event(((b200_backend_ctx *)be->context)->stream, ev->context)); }
 
 static float op_f32(const ggml_tensor *t, int i) { float v; memcpy(&v, (const int32_t *)t->op_params + i, 4); return v; }
 static bool same_shape_contig(const ggml_tensor *a, const ggml_tensor *b) { return ggml_are_same_shape(a, b) && ggml_is_contiguous(a) && ggml_is_contiguous(b); }
@@ -173,61 +222,83 @@ static bool b200_dev_supports_op(ggml_backend_dev_t, const ggml_tensor *op) {
 
 static int b200_compute_node(b200_backend_ctx *ctx, ggml_tensor *d) {
     const ggml_tensor *a = d->src[0], *b = d->src[1];
+    void *st = ctx->stream;
     switch (d->op) {
     case GGML_OP_NONE: case GGML_OP_RESHAPE: case GGML_OP_VIEW: case GGML_OP_PERMUTE: case GGML_OP_TRANSPOSE: return EB_OK;
     case GGML_OP_MUL_MAT: {     // a = weights [K, N], b = activations f32 [K, T] -> d f32 [N, T]
         if (a->type == GGML_TYPE_F16 || a->type == GGML_TYPE_F32)
             return eb_mul_mat_dense((int)a->type, a->data, (int64_t)a->nb[1], (int64_t)a->nb[2], a->ne[2], (const float *)b->data, (int64_t)b->nb[1], (int64_t)b->nb[2],
-                                    (float *)d->data, a->ne[1], a->ne[0], b->ne[1], b->ne[2], nullptr);
+                                    (float *)d->data, a->ne[1], a->ne[0], b->ne[1], b->ne[2], st);
         void *ws = ctx->scratch(eb_mul_mat_ws_size((int)a->type, a->ne[1], a->ne[0], b->ne[1]));
         if (!ws) return EB_ERR_OOM;
-        return eb_mul_mat((int)a->type, a->data, a->ne[1], a->ne[0], (const float *)b->data, b->ne[1], (float *)d->data, ws, nullptr);
+        return eb_mul_mat((int)a->type, a->data, a->ne[1], a->ne[0], (const float *)b->data, b->ne[1], (float *)d->data, ws, st);
     }
     case GGML_OP_FLASH_ATTN_EXT: {
         const ggml_tensor *v = d->src[2], *m = d->src[3];
         const int D = (int)a->ne[0], T = (int)a->ne[1], H = (int)a->ne[2], n_kv = (int)b->ne[1];
+        const int64_t kv_stride = (int64_t)(b->nb[1] / 2);
         void *ws = ctx->scratch(eb_flash_attn_ws_size(T, H, D, n_kv));
         if (!ws) return EB_ERR_OOM;
-        return eb_flash_attn((const float *)a->data, b->data, v->data, (int64_t)(b->nb[1] / 2), m->data, (int64_t)(m->nb[1] / 2), nullptr, 0,
-                             T, H, D, n_kv, op_f32(d, 0), (float *)d->data, ws, nullptr);
+        // llama_set_inputs writes 0 / -inf masks (R/src/llama-context.cpp:136-201): those run on the tcgen05 kernel through the mask's
+        // bit form, built once per graph (all layers share KQ_mask); anything else (ALiBi, test masks) takes the generic kernel
+        static const bool generic_only = getenv("GGML_B200_FA_GENERIC") != nullptr;      // A/B switch: always take the f16-mask kernel
+        if (!generic_only && eb_flash_attn_bits_supported(T, H, D, kv_stride) && m->nb[1] == (size_t)m->ne[0] * 2) {
+            if (ctx->mask_data != m->data || ctx->mask_T != T || ctx->mask_kv != n_kv) {
+                const size_t need = eb_mask_bits_size(T, n_kv);
+                if (need > ctx->bits_size) {
+                    if (ctx->bits) { eb_synchronize(st); eb_free(ctx->bits); }
+                    ctx->bits = nullptr; ctx->bits_size = 0;
+                    if (eb_malloc(&ctx->bits, need) != EB_OK) return EB_ERR_OOM;
+                    ctx->bits_size = need;
+                }
+                int general = 1;
+                int rc = eb_mask_to_bits(m->data, (int64_t)(m->nb[1] / 2), T, n_kv, ctx->bits, &general, st); if (rc) return rc;
+                ctx->mask_data = m->data; ctx->mask_T = T; ctx->mask_kv = n_kv; ctx->mask_bits_ok = general == 0;
+            }
+            if (ctx->mask_bits_ok)
+                return eb_flash_attn_bits((const float *)a->data, b->data, v->data, kv_stride, ctx->bits, T, H, D, n_kv, op_f32(d, 0), (float *)d->data, ws, st);
+        }
+        return eb_flash_attn((const float *)a->data, b->data, v->data, kv_stride, m->data, (int64_t)(m->nb[1] / 2), nullptr, 0,
+                             T, H, D, n_kv, op_f32(d, 0), (float *)d->data, ws, st);
     }
-    case GGML_OP_GET_ROWS: return eb_get_rows_n((int)a->type, a->data, a->ne[1], a->ne[0], (const int32_t *)b->data, (int)b->ne[0], (float *)d->data, nullptr);
-    case GGML_OP_RMS_NORM: return eb_rms_norm((const float *)a->data, nullptr, (float *)d->data, a->ne[0], ggml_nrows(a), op_f32(d, 0), nullptr);
+    case GGML_OP_GET_ROWS: return eb_get_rows_n((int)a->type, a->data, a->ne[1], a->ne[0], (const int32_t *)b->data, (int)b->ne[0], (float *)d->data, st);
+    case GGML_OP_RMS_NORM: return eb_rms_norm((const float *)a->data, nullptr, (float *)d->data, a->ne[0], ggml_nrows(a), op_f32(d, 0), st);
     case GGML_OP_ROPE: {        // the library rotates in place; ggml's dst may or may not alias src0 (ggml-alloc inplace)
-        int rc = eb_copy(d->data, a->data, ggml_nbytes(a), nullptr); if (rc) return rc;
-        return eb_rope_norm((float *)d->data, (const int32_t *)b->data, (int)a->ne[0], (int)a->ne[1], (int)a->ne[2], op_f32(d, 5), nullptr);
+        int rc = eb_copy(d->data, a->data, ggml_nbytes(a), st); if (rc) return rc;
+        return eb_rope_norm((float *)d->data, (const int32_t *)b->data, (int)a->ne[0], (int)a->ne[1], (int)a->ne[2], op_f32(d, 5), st);
     }
-    case GGML_OP_ADD: return eb_add((const float *)a->data, (const float *)b->data, (float *)d->data, ggml_nelements(d), ggml_nelements(b), nullptr);
-    case GGML_OP_MUL: return eb_mul((const float *)a->data, (const float *)b->data, (float *)d->data, ggml_nelements(d), ggml_nelements(b), nullptr);
+    case GGML_OP_ADD: return eb_add((const float *)a->data, (const float *)b->data, (float *)d->data, ggml_nelements(d), ggml_nelements(b), st);
+    case GGML_OP_MUL: return eb_mul((const float *)a->data, (const float *)b->data, (float *)d->data, ggml_nelements(d), ggml_nelements(b), st);
     case GGML_OP_UNARY:
-        return ggml_get_unary_op(d) == GGML_UNARY_OP_SILU ? eb_silu((const float *)a->data, (float *)d->data, ggml_nelements(d), nullptr)
-                                                          : eb_relu((const float *)a->data, (float *)d->data, ggml_nelements(d), nullptr);
-    case GGML_OP_CONCAT: return eb_concat2((const float *)a->data, (const float *)b->data, (float *)d->data, (int)a->ne[0], (int)a->ne[1], nullptr);
+        return ggml_get_unary_op(d) == GGML_UNARY_OP_SILU ? eb_silu((const float *)a->data, (float *)d->data, ggml_nelements(d), st)
+                                                          : eb_relu((const float *)a->data, (float *)d->data, ggml_nelements(d), st);
+    case GGML_OP_CONCAT: return eb_concat2((const float *)a->data, (const float *)b->data, (float *)d->data, (int)a->ne[0], (int)a->ne[1], st);
     case GGML_OP_CPY: case GGML_OP_DUP: case GGML_OP_CONT: {
         const ggml_tensor *dst = d->op == GGML_OP_CPY ? d->src[1] : d;     // ggml_cpy: the node is a view of src[1]
         if (ggml_is_contiguous(a) && ggml_is_contiguous(dst)) {
-            if (a->type == GGML_TYPE_F32 && dst->type == GGML_TYPE_F16) return eb_cpy_f32_f16((const float *)a->data, dst->data, ggml_nelements(a), nullptr);   // KV store, mask cast
-            if (a->type == dst->type) return eb_copy(dst->data, a->data, ggml_nbytes(a), nullptr);
+            if (a->type == GGML_TYPE_F32 && dst->type == GGML_TYPE_F16) return eb_cpy_f32_f16((const float *)a->data, dst->data, ggml_nelements(a), st);   // KV store, mask cast
+            if (a->type == dst->type) return eb_copy(dst->data, a->data, ggml_nbytes(a), st);
         }
         const int64_t nbs[4] = {(int64_t)a->nb[0], (int64_t)a->nb[1], (int64_t)a->nb[2], (int64_t)a->nb[3]};
         const int64_t nbd[4] = {(int64_t)dst->nb[0], (int64_t)dst->nb[1], (int64_t)dst->nb[2], (int64_t)dst->nb[3]};
-        return eb_copy_strided((int)a->type, (int)dst->type, a->data, dst->data, a->ne, nbs, dst->ne, nbd, nullptr);
+        return eb_copy_strided((int)a->type, (int)dst->type, a->data, dst->data, a->ne, nbs, dst->ne, nbd, st);
     }
     case GGML_OP_SOFT_MAX: {
         const ggml_tensor *m = d->src[1];
         return eb_soft_max_ext((const float *)a->data, m ? m->data : nullptr, m ? (int)m->type : 0, m ? (int64_t)(m->nb[1] / ggml_type_size(m->type)) : 0,
-                               (float *)d->data, a->ne[0], ggml_nrows(a), a->ne[1], op_f32(d, 0), nullptr);
+                               (float *)d->data, a->ne[0], ggml_nrows(a), a->ne[1], op_f32(d, 0), st);
     }
-    case GGML_OP_ARGMAX: return eb_argmax((const float *)a->data, (int)ggml_nrows(a), (int)a->ne[0], (int32_t *)d->data, nullptr);
+    case GGML_OP_ARGMAX: return eb_argmax((const float *)a->data, (int)ggml_nrows(a), (int)a->ne[0], (int32_t *)d->data, st);
     default: return EB_ERR_UNSUPPORTED;
     }
 }
 
-// graph_compute (ggml_backend_cuda_graph_compute, ggml-cuda.cu:2693): asynchronous on the library stream;
+// graph_compute (ggml_backend_cuda_graph_compute, ggml-cuda.cu:2693): asynchronous on the backend's stream;
 // a failing op fails the graph (-> llama_decode returns -3, R/src/llama.cpp:9610-9617)
 static ggml_status b200_be_graph_compute(ggml_backend_t be, ggml_cgraph *g) {
     auto *ctx = (b200_backend_ctx *)be->context;
     const int n = ggml_graph_n_nodes(g);
+    ctx->mask_data = nullptr;                    // the mask's contents change between graphs even when its address does not
     for (int i = 0; i < n; i++) {
         ggml_tensor *d = ggml_graph_node(g, i);
         if (ggml_is_empty(d)) continue;
@@ -239,8 +310,8 @@ static ggml_status b200_be_graph_compute(ggml_backend_t be, ggml_cgraph *g) {
 }
 
 static const ggml_backend_i b200_backend_iface = {
-    b200_be_name, b200_be_free, /* set_tensor_async */ nullptr, /* get_tensor_async */ nullptr, /* cpy_tensor_async */ nullptr, b200_be_sync,
-    nullptr, nullptr, nullptr, nullptr, b200_be_graph_compute, /* event_record */ nullptr, /* event_wait */ nullptr,
+    b200_be_name, b200_be_free, b200_be_set_tensor_async, b200_be_get_tensor_async, b200_be_cpy_tensor_async, b200_be_sync,
+    nullptr, nullptr, nullptr, nullptr, b200_be_graph_compute, b200_be_event_record, b200_be_event_wait,
 };
 static ggml_guid_t b200_guid() { static ggml_guid g = {0xb2, 0x00, 0xea, 0x61, 0x1e, 0x5b, 0x10, 0x0a, 0x73, 0xc9, 0x05, 0x7a, 0x4d, 0x11, 0x20, 0x26}; return &g; }
 
@@ -253,20 +324,31 @@ static enum ggml_backend_dev_type b200_dev_type(ggml_backend_dev_t) { return GGM
 static void b200_dev_props(ggml_backend_dev_t d, ggml_backend_dev_props *p) {
     p->name = b200_dev_name(d); p->description = b200_dev_desc(d); p->type = GGML_BACKEND_DEVICE_TYPE_GPU;
     b200_dev_memory(d, &p->memory_free, &p->memory_total);
-    p->caps = { /* async */ true, /* host_buffer */ false, /* buffer_from_host_ptr */ false, /* events */ false };
+    p->caps = { /* async */ true, /* host_buffer */ false, /* buffer_from_host_ptr */ false, /* events */ true };
 }
 static ggml_backend_t b200_dev_init_backend(ggml_backend_dev_t dev, const char *) {
     if (eb_device_init(((b200_device_ctx *)dev->context)->device) != EB_OK) { b200_log_err("init_backend"); return nullptr; }   // refuses anything that is not sm_100
-    return new ggml_backend{ b200_guid(), b200_backend_iface, dev, new b200_backend_ctx() };
+    auto *c = new b200_backend_ctx();
+    if (eb_stream_create(&c->stream) != EB_OK) { b200_log_err("init_backend: stream"); delete c; return nullptr; }
+    return new ggml_backend{ b200_guid(), b200_backend_iface, dev, c };
 }
 static ggml_backend_buffer_type_t b200_dev_buffer_type(ggml_backend_dev_t) { return b200_buffer_type(); }
 static bool b200_dev_supports_buft(ggml_backend_dev_t, ggml_backend_buffer_type_t buft) { return buft == b200_buffer_type(); }
 static bool b200_dev_offload_op(ggml_backend_dev_t, const ggml_tensor *) { return false; }    // weights are resident: nothing is offloaded per op
 
+// events (ggml_backend_cuda_device_event_new / free / synchronize, ggml-cuda.cu:3161-3198)
+static ggml_backend_event_t b200_dev_event_new(ggml_backend_dev_t dev) {
+    void *ev = nullptr;
+    if (eb_event_create(&ev) != EB_OK) { b200_log_err("event_new"); return nullptr; }
+    return new ggml_backend_event{ dev, ev };
+}
+static void b200_dev_event_free(ggml_backend_dev_t, ggml_backend_event_t ev) { eb_event_destroy(ev->context); delete ev; }
+static void b200_dev_event_sync(ggml_backend_dev_t, ggml_backend_event_t ev) { B200_OK(eb_event_synchronize(ev->context)); }
+
 static const ggml_backend_device_i b200_device_iface = {
     b200_dev_name, b200_dev_desc, b200_dev_memory, b200_dev_type, b200_dev_props, b200_dev_init_backend, b200_dev_buffer_type,
     /* get_host_buffer_type */ nullptr, /* buffer_from_host_ptr */ nullptr, b200_dev_supports_op, b200_dev_supports_buft, b200_dev_offload_op,
-    /* event_new */ nullptr, /* event_free */ nullptr, /* event_synchronize */ nullptr,
+    b200_dev_event_new, b200_dev_event_free, b200_dev_event_sync,
 };
 
 // ---------------------------------------------------------------------------------- reg

@@ -47,6 +47,20 @@ EB_API int eb_memset(void *d_ptr, int value, size_t bytes, void *stream);
 EB_API int eb_upload(void *d_dst, const void *h_src, size_t bytes, void *stream);    /* set_tensor */
 EB_API int eb_download(void *h_dst, const void *d_src, size_t bytes, void *stream);  /* get_tensor */
 EB_API int eb_synchronize(void *stream);
+/* One stream per execution context and stream-ordered copies / events between them: what ggml_backend_i asks of an
+ * asynchronous backend (R/ggml/src/ggml-backend-impl.h:87-124; CUDA backend: set/get_tensor_async
+ * R/ggml/src/ggml-cuda/ggml-cuda.cu:2390-2440, event_record / event_wait :2790-2815, event_new / free / synchronize
+ * :3161-3198).  Streams are non-blocking (no implicit ordering with the NULL stream). */
+EB_API int eb_stream_create(void **stream);
+EB_API int eb_stream_destroy(void *stream);
+EB_API int eb_device_synchronize(void);
+EB_API int eb_upload_async(void *d_dst, const void *h_src, size_t bytes, void *stream);
+EB_API int eb_download_async(void *h_dst, const void *d_src, size_t bytes, void *stream);
+EB_API int eb_event_create(void **event);
+EB_API int eb_event_destroy(void *event);
+EB_API int eb_event_record(void *event, void *stream);
+EB_API int eb_stream_wait_event(void *stream, void *event);
+EB_API int eb_event_synchronize(void *event);
 /* device-to-device copy: GGML_OP_CPY / CONT / DUP of a contiguous same-type tensor and buffer_i::cpy_tensor
  * (R/ggml/src/ggml-cuda/cpy.cu:526, ggml-cuda.cu:603) */
 EB_API int eb_copy(void *d_dst, const void *d_src, size_t bytes, void *stream);
@@ -126,6 +140,18 @@ EB_API int eb_flash_attn(const float *d_q, const void *d_k, const void *d_v, int
                          const void *d_mask_f16, int64_t mask_stride,
                          const uint32_t *d_tree_bits, int n_prefix,
                          int T, int H, int D, int n_kv, float scale, float *d_out, void *d_ws, void *stream);
+
+/* The same operator on the tcgen05 kernel for ANY mask whose values are 0 or -inf (what llama_set_inputs writes,
+ * R/src/llama-context.cpp:136-201): the f16 mask is first turned into one bit per (row, cell) plus a per-tile summary
+ * (eb_mask_to_bits, once per mask: every layer of a graph shares it), then eb_flash_attn_bits runs the attention for T of
+ * any size (128-row chunks).  *h_general (optional, host) = 1 when some mask value is neither 0 nor -inf (ALiBi slopes, the
+ * random masks of R/tests/test-backend-ops.cpp): the bit form does not apply and the caller uses eb_flash_attn.  Reading
+ * it synchronises the stream once.  d_bits: eb_mask_bits_size(T, n_kv) bytes.  kv_stride must be a multiple of 8. */
+EB_API size_t eb_mask_bits_size(int T, int n_kv);
+EB_API int eb_mask_to_bits(const void *d_mask_f16, int64_t mask_stride, int T, int n_kv, void *d_bits, int *h_general, void *stream);
+EB_API int eb_flash_attn_bits_supported(int T, int H, int D, int64_t kv_stride);
+EB_API int eb_flash_attn_bits(const float *d_q, const void *d_k, const void *d_v, int64_t kv_stride, const void *d_bits,
+                              int T, int H, int D, int n_kv, float scale, float *d_out, void *d_ws, void *stream);
 
 /* GGML_OP_ARGMAX / top-k (R/ggml/src/ggml-cuda/argmax.cu:8, argsort.cu:11; host sampler
  * R/src/llama-sampling.cpp:228-302): per row top-k by logit, ties to the lower id; probs =

@@ -241,3 +241,46 @@ GH_API int gh_forward(int which, const GModel *m, uint16_t *kv_k, uint16_t *kv_v
     ggml_backend_buffer_free(wbuf); ggml_free(c); ggml_free(cw);
     return rc;
 }
+
+// Two ggml_backend_t of the plugin's device = two streams, chained the way ggml_backend_sched chains pipeline copies
+// (R/ggml/src/ggml-backend.cpp: event_record after a split, event_wait + tensor_copy_async before the next): backend A uploads x
+// (set_tensor_async) and runs a long chain y = (chain + 1) * x, records an event; backend B waits for it, takes y with
+// cpy_tensor_async, computes z = y * y and hands it back with get_tensor_async.  Without stream ordering B would read y before A wrote it.
+GH_API int gh_two_backends(int64_t n, int chain, const float *x_host, float *z_host, int *caps_out) {
+    if (!g_reg) { snprintf(g_err, sizeof g_err, "plugin not loaded"); return -1; }
+    ggml_backend_dev_t dev = ggml_backend_reg_dev_get(g_reg, 0);
+    ggml_backend_dev_props props; ggml_backend_dev_get_props(dev, &props);
+    if (caps_out) *caps_out = (props.caps.async ? 1 : 0) | (props.caps.events ? 2 : 0);
+    if (!props.caps.async || !props.caps.events) { snprintf(g_err, sizeof g_err, "device reports async %d events %d", props.caps.async, props.caps.events); return -2; }
+    ggml_backend_t A = ggml_backend_dev_init(dev, nullptr), B = ggml_backend_dev_init(dev, nullptr);
+    ggml_backend_event_t ev = ggml_backend_event_new(dev);
+    if (!A || !B || !ev || A == B) { snprintf(g_err, sizeof g_err, "could not create two backends + an event"); return -3; }
+    ggml_init_params p = {ggml_tensor_overhead() * (size_t)(chain + 8) + ggml_graph_overhead() * 2, nullptr, true};
+    ggml_context *ca = ggml_init(p), *cb = ggml_init(p);
+    ggml_tensor *x = ggml_new_tensor_1d(ca, GGML_TYPE_F32, n), *y = x;
+    for (int i = 0; i < chain; i++) y = ggml_add(ca, y, x);
+    ggml_cgraph *ga = ggml_new_graph(ca); ggml_build_forward_expand(ga, y);
+    ggml_tensor *y2 = ggml_new_tensor_1d(cb, GGML_TYPE_F32, n), *z = ggml_mul(cb, y2, y2);
+    ggml_cgraph *gb = ggml_new_graph(cb); ggml_build_forward_expand(gb, z);
+    ggml_backend_buffer_t ba = ggml_backend_alloc_ctx_tensors(ca, A), bb = ggml_backend_alloc_ctx_tensors(cb, B);
+    int rc = 0;
+    if (!ba || !bb) { snprintf(g_err, sizeof g_err, "alloc failed"); rc = -4; }
+    if (!rc) {
+        ggml_backend_tensor_set_async(A, x, x_host, 0, (size_t)n * 4);
+        if (ggml_backend_graph_compute_async(A, ga) != GGML_STATUS_SUCCESS) { snprintf(g_err, sizeof g_err, "graph A failed"); rc = -5; }
+        ggml_backend_event_record(ev, A);
+        ggml_backend_event_wait(B, ev);
+        ggml_backend_tensor_copy_async(A, B, y, y2);
+        if (!rc && ggml_backend_graph_compute_async(B, gb) != GGML_STATUS_SUCCESS) { snprintf(g_err, sizeof g_err, "graph B failed"); rc = -6; }
+        ggml_backend_tensor_get_async(B, z, z_host, 0, (size_t)n * 4);
+        ggml_backend_synchronize(B);
+        ggml_backend_event_synchronize(ev);
+        ggml_backend_synchronize(A);
+    }
+    if (ba) ggml_backend_buffer_free(ba);
+    if (bb) ggml_backend_buffer_free(bb);
+    ggml_backend_event_free(ev);
+    ggml_backend_free(A); ggml_backend_free(B);
+    ggml_free(ca); ggml_free(cb);
+    return rc;
+}

@@ -166,6 +166,26 @@ def test_set_get_tensor_roundtrip(plugin, t):
 
 
 @pytest.mark.gpu
+def test_two_backends_streams_events_async_copies(plugin):
+    """ggml_backend_i's asynchronous half (R/ggml/src/ggml-backend-impl.h:87-124): each ggml_backend_t owns a stream; set/get/cpy_tensor_async
+    and event_record / event_wait order two of them the way ggml_backend_sched's pipeline does.  The producer graph is a chain of 96 adds
+    over 8 MB (~0.5 ms): a consumer that did not wait would square stale data."""
+    import ctypes as C
+    n, chain = 2 * 1024 * 1024, 96
+    x = np.random.default_rng(7).normal(0, 1, n).astype(np.float32); z = np.zeros(n, np.float32)
+    caps = C.c_int(0)
+    plugin.gh_two_backends.argtypes = [C.c_int64, C.c_int, C.c_void_p, C.c_void_p, C.POINTER(C.c_int)]
+    for rep in range(3):
+        z[:] = 0
+        assert plugin.gh_two_backends(n, chain, po._ptr(x), po._ptr(z), C.byref(caps)) == 0, plugin.gh_last_error().decode()
+        assert caps.value == 3                                   # async and events are both advertised (get_props)
+        y = x.copy()
+        for _ in range(chain):
+            y = y + x                                            # the same f32 chain
+        np.testing.assert_array_equal(z, y * y)
+
+
+@pytest.mark.gpu
 @pytest.mark.parametrize("ftype,is_eagle,T", [("q4_k_m", False, 27), ("q4_k_m", False, 65), (po.Q4_0, False, 16), (po.Q8_0, False, 5),
                                               ("q4_k_m", True, 8), (po.Q4_0, True, 27)])
 def test_plugin_graph_matches_reference_cpu_backend(plugin, ftype, is_eagle, T):

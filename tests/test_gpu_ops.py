@@ -185,6 +185,39 @@ def test_flash_attn_vs_oracle(eb, T, n_past, H):
     assert np.isfinite(got).all()
 
 
+@pytest.mark.parametrize("T,n_kv,H", [(1, 96, 2), (27, 256, 2), (65, 4096, 4), (65, 1000, 3), (128, 384, 1), (200, 512, 2), (300, 300, 2)])
+def test_flash_attn_bit_mask_form_vs_oracle(eb, T, n_kv, H):
+    """eb_mask_to_bits + eb_flash_attn_bits: the tcgen05 kernel under ANY 0 / -inf f16 mask — holes inside the committed prefix (cells of
+    rejected branches, R/src/llama-kv-cache.cpp:368-420), an unused cache tail, n_kv that is not a multiple of the 128-cell tile, prompt
+    batches beyond one 128-row tile — against the oracle's attention over the same visibility matrix"""
+    rng = np.random.default_rng(T * 13 + n_kv)
+    D = 128
+    q = rng.normal(0, 1, (T, H, D)).astype(np.float32)
+    k = rng.normal(0, 1, (n_kv, H, D)).astype(np.float16); v = rng.normal(0, 1, (n_kv, H, D)).astype(np.float16)
+    vis = np.zeros((T, n_kv), bool)
+    used = max(T, int(0.8 * n_kv))
+    prefix = used - min(T, used)
+    alive = rng.random(prefix) > 0.15                     # ~15 % of the prefix cells are empty
+    vis[:, :prefix] = alive[None, :]
+    for t in range(T):                                    # batch cells: causal over a random subset (tree-like)
+        cells = prefix + np.arange(min(T, used))
+        vis[t, cells[:t + 1]] = rng.random(min(t + 1, len(cells))) > 0.4
+        vis[t, cells[min(t, len(cells) - 1)]] = True      # every row sees at least itself
+    Tp = (T + 63) // 64 * 64
+    mask = np.full((Tp, n_kv), -np.inf, np.float16); mask[:T][vis] = 0
+    got, general = eb.flash_attn_ext_bits(q, k, v, 1 / np.sqrt(D), mask)
+    assert not general
+    want = po.oracle().flash_attn(q, k.view(np.uint16), v.view(np.uint16), vis.astype(np.uint8), 1 / np.sqrt(D))
+    assert np.isfinite(got).all()
+    assert nmse(got, want) < 5e-4, nmse(got, want)         # the bar of R/tests/test-backend-ops.cpp for FLASH_ATTN_EXT
+    if T <= 128:                                          # and the generic f16-mask kernel on the same input
+        got2 = eb.flash_attn_ext(q, k, v, 1 / np.sqrt(D), mask_f16=mask)
+        assert np.abs(got - got2).max() < 2e-3
+    # a mask with other values (ALiBi-like) must be reported, not mis-read
+    mask2 = mask.copy(); mask2[0, 0] = np.float16(-0.5)
+    assert eb.flash_attn_ext_bits(q, k, v, 1 / np.sqrt(D), mask2) == (None, True)
+
+
 def test_top_k_argmax(eb):
     rng = np.random.default_rng(4)
     x = rng.normal(0, 2, (9, 32000)).astype(np.float32)
