@@ -393,6 +393,44 @@ def run_reference(args, rank, world):
             "e2e": {"value": val, "unit": "tok/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
 
 
+def run_config3(args, rank, world, local_rank):
+    """BASELINE config 3: Vicuna-7B Q8_0 target + Q8_0 EAGLE head, 64 concurrent request streams on 8 GPUs = 8 streams per GPU over ONE
+    resident copy of the weights (each stream: its own KV caches, tree state and CUDA graph).  A step = one round of every stream of the
+    rank, issued round-robin; the streams of a GPU are NOT batched into one weight pass (that needs a T >= 512 Q8_0 tensor-core GEMM,
+    DESIGN.md section 7), so the aggregate equals the single-stream rate per GPU.  Weak scaling: 8 streams per GPU whatever N."""
+    if args.impl == "reference":
+        return {"impl": "reference", "unavailable": "the reference arm covers the metric's own config (2)"} if rank == 0 else None
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import config3_streams as c3
+    from __graft_entry__ import load_package
+    eb = load_package(); eb.init(local_rank)
+    dist = None
+    if world > 1:
+        import torch
+        import torch.distributed as dist
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    per_gpu = 8
+    sampler = ClockSampler(local_rank); sampler.start()
+    r = c3.run(eb, per_gpu, args.steps, eb.Q8_0, warm=max(3, args.warmup), barrier=(dist.barrier if dist else None), seed0=100 + 1000 * rank)
+    clocks = sampler.summary()
+    ms = max_over_ranks(dist, [r["gpu_ms"]], "cuda")[0] if dist else r["gpu_ms"]
+    tokens = r["tokens"] * world
+    if dist:
+        dist.destroy_process_group()
+    if rank != 0:
+        return None
+    return {"metric": "eagle_decode_tok_per_s", "value": tokens / (ms * 1e-3), "unit": "tok/s", "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup),
+            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "int8xq8_0 dot, f32 accumulate, f16 KV", "data": "synthetic (random-init Q8_0 blocks, N(0,1) f16 KV prefill, fixed accept length 3)",
+            "config": {"workload": f"config 3: vicuna-7b Q8_0 + Q8_0 EAGLE head, {per_gpu * world} request streams ({per_gpu} per GPU, one resident weight copy per GPU), "
+                                   "64-node tree, KV ~4096 per stream", "parallelism": f"{world} GPU(s) x {per_gpu} streams, round-robin, no batching across streams, no collective",
+                       "l2": "weights (7.0 GB) per verify exceed L2: no flush needed"},
+            "round_ms_per_stream": r["round_ms"], "verify_step_us": 1e3 * r["verify_ms"],
+            "verify_step_hbm_frac": algorithmic_bytes(r["weight_bytes"], r["n_past"], r["T"]) / (r["verify_ms"] * 1e-3) / 1e9 / peaks()[0],
+            "gpu_launches": r["launches"], "clocks": clocks}
+
+
 def run_config4(args, rank, world):
     """BASELINE config 4: one tree-verify step of a LLaMA-2-13B-shaped Q4_K_M target (40 layers, E 5120, 40 heads, F 13824), 65 rows at
     n_kv 4096, tensor parallel over the ranks (N-split wq|wk|wv|gate|up, K-split wo|down, one peer-memory all-reduce after each
@@ -424,12 +462,15 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--config", type=int, default=2, choices=[2, 4],
-                    help="BASELINE.json config: 2 = the metric's own (default, the driver's run); 4 = LLaMA-2-13B verify step, tensor parallel over --gpus")
+    ap.add_argument("--config", type=int, default=2, choices=[2, 3, 4],
+                    help="BASELINE.json config: 2 = the metric's own (default, the driver's run); 3 = Q8_0 target, 8 request streams per GPU; "
+                         "4 = LLaMA-2-13B verify step, tensor parallel over --gpus")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1")); local = int(os.environ.get("LOCAL_RANK", "0"))
     if args.config == 4:
         out = run_config4(args, rank, world)
+    elif args.config == 3:
+        out = run_config3(args, rank, world, local)
     elif args.impl == "reference":
         out = run_reference(args, rank, world)
     else:
