@@ -75,6 +75,7 @@ def lib():
         "eb_mask_bits_size": ([i32, i32], sz), "eb_mask_to_bits": ([vp, i64, i32, i32, vp, C.POINTER(i32), vp], i32),
         "eb_flash_attn_bits_supported": ([i32, i32, i32, i64], i32),
         "eb_flash_attn_bits": ([vp, vp, vp, i64, vp, i32, i32, i32, i32, f32, vp, vp, vp], i32),
+        "eb_malloc_host": ([C.POINTER(vp), sz], i32), "eb_free_host": ([vp], i32),
         "eb_stream_create": ([C.POINTER(vp)], i32), "eb_stream_destroy": ([vp], i32), "eb_device_synchronize": ([], i32),
         "eb_upload_async": ([vp, vp, sz, vp], i32), "eb_download_async": ([vp, vp, sz, vp], i32),
         "eb_event_create": ([C.POINTER(vp)], i32), "eb_event_destroy": ([vp], i32), "eb_event_record": ([vp, vp], i32),

@@ -181,6 +181,9 @@ int eb_flash_attn_bits(const float *q, const void *k, const void *v, int64_t kv_
     return eb_fattn_tc_bits(q, k, v, kv_stride, bits, T, H, n_kv, scale, out, ws, S(st));
 }
 // streams and events for hosts that own several execution contexts (one ggml_backend_t = one stream)
+// pinned host memory (ggml_backend_cuda_host_buffer_type, ggml-cuda.cu:1048-1108): inputs and the logits buffer of a host program
+int eb_malloc_host(void **p, size_t bytes) { NEED_DEV(); if (cudaMallocHost(p, bytes ? bytes : 1) != cudaSuccess) { cudaGetLastError(); *p = nullptr; return eb_set_err(EB_ERR_OOM, "cudaMallocHost(%zu)", bytes); } return EB_OK; }
+int eb_free_host(void *p) { if (p) EB_CUDA(cudaFreeHost(p)); return EB_OK; }
 int eb_stream_create(void **st) { NEED_DEV(); cudaStream_t s; EB_CUDA(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking)); *st = (void *)s; return EB_OK; }
 int eb_stream_destroy(void *st) { if (st) EB_CUDA(cudaStreamDestroy(S(st))); return EB_OK; }
 int eb_device_synchronize(void) { NEED_DEV(); EB_CUDA(cudaDeviceSynchronize()); return EB_OK; }

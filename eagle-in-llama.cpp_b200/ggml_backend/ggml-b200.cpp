@@ -103,6 +103,28 @@ static size_t b200_buft_alignment(ggml_backend_buffer_type_t) { return 256; }   
 static size_t b200_buft_alloc_size(ggml_backend_buffer_type_t, const ggml_tensor *t) { return (ggml_nbytes(t) + 255) & ~(size_t)255; }
 static bool b200_buft_is_host(ggml_backend_buffer_type_t) { return false; }
 
+// ---------------------------------------------------------------------------------- host (pinned) buffer type
+// What libllama asks a GPU device for so that inputs and the logits / embeddings output buffer live in page-locked memory
+// (llama_output_reserve, R/src/llama-context.cpp:884-958; ggml_backend_cuda_host_buffer_type, ggml-cuda.cu:1048-1108): a CPU buffer over
+// cudaMallocHost memory, so stream-ordered copies to and from it are real DMA transfers.  Falls back to a plain CPU buffer when pinning fails.
+static const char *b200_host_buft_name(ggml_backend_buffer_type_t) { return B200_NAME "_Host"; }
+static void b200_host_buf_free(ggml_backend_buffer_t b) { eb_free_host(b->context); }
+static ggml_backend_buffer_t b200_host_buft_alloc(ggml_backend_buffer_type_t buft, size_t size) {
+    void *p = nullptr;
+    if (getenv("GGML_B200_NO_PINNED") || eb_malloc_host(&p, size) != EB_OK || !p) return ggml_backend_buft_alloc_buffer(ggml_backend_cpu_buffer_type(), size);
+    ggml_backend_buffer_t b = ggml_backend_cpu_buffer_from_ptr(p, size);
+    b->buft = buft; b->iface.free_buffer = b200_host_buf_free;
+    return b;
+}
+static ggml_backend_dev_t b200_the_device();
+static ggml_backend_buffer_type_t b200_host_buffer_type() {
+    static ggml_backend_buffer_type t = {
+        { b200_host_buft_name, b200_host_buft_alloc, ggml_backend_cpu_buffer_type()->iface.get_alignment, /* get_max_size */ nullptr,
+          ggml_backend_cpu_buffer_type()->iface.get_alloc_size, ggml_backend_cpu_buffer_type()->iface.is_host },
+        b200_the_device(), nullptr };
+    return &t;
+}
+
 // ---------------------------------------------------------------------------------- backend
 // one ggml_backend_t = one stream (ggml_backend_cuda_context::stream(), R/ggml/src/ggml-cuda/common.cuh): graphs, async copies and
 // events of one backend are ordered on it; two backends of the same device overlap
@@ -324,7 +346,7 @@ static enum ggml_backend_dev_type b200_dev_type(ggml_backend_dev_t) { return GGM
 static void b200_dev_props(ggml_backend_dev_t d, ggml_backend_dev_props *p) {
     p->name = b200_dev_name(d); p->description = b200_dev_desc(d); p->type = GGML_BACKEND_DEVICE_TYPE_GPU;
     b200_dev_memory(d, &p->memory_free, &p->memory_total);
-    p->caps = { /* async */ true, /* host_buffer */ false, /* buffer_from_host_ptr */ false, /* events */ true };
+    p->caps = { /* async */ true, /* host_buffer */ true, /* buffer_from_host_ptr */ false, /* events */ true };
 }
 static ggml_backend_t b200_dev_init_backend(ggml_backend_dev_t dev, const char *) {
     if (eb_device_init(((b200_device_ctx *)dev->context)->device) != EB_OK) { b200_log_err("init_backend"); return nullptr; }   // refuses anything that is not sm_100
@@ -333,6 +355,8 @@ static ggml_backend_t b200_dev_init_backend(ggml_backend_dev_t dev, const char *
     return new ggml_backend{ b200_guid(), b200_backend_iface, dev, c };
 }
 static ggml_backend_buffer_type_t b200_dev_buffer_type(ggml_backend_dev_t) { return b200_buffer_type(); }
+static ggml_backend_buffer_type_t b200_dev_host_buffer_type(ggml_backend_dev_t) { return b200_host_buffer_type(); }
+// tensors in the pinned host type are computed on by the CPU backend (it is a host buffer), not by this device
 static bool b200_dev_supports_buft(ggml_backend_dev_t, ggml_backend_buffer_type_t buft) { return buft == b200_buffer_type(); }
 static bool b200_dev_offload_op(ggml_backend_dev_t, const ggml_tensor *) { return false; }    // weights are resident: nothing is offloaded per op
 
@@ -347,7 +371,7 @@ static void b200_dev_event_sync(ggml_backend_dev_t, ggml_backend_event_t ev) { B
 
 static const ggml_backend_device_i b200_device_iface = {
     b200_dev_name, b200_dev_desc, b200_dev_memory, b200_dev_type, b200_dev_props, b200_dev_init_backend, b200_dev_buffer_type,
-    /* get_host_buffer_type */ nullptr, /* buffer_from_host_ptr */ nullptr, b200_dev_supports_op, b200_dev_supports_buft, b200_dev_offload_op,
+    b200_dev_host_buffer_type, /* buffer_from_host_ptr */ nullptr, b200_dev_supports_op, b200_dev_supports_buft, b200_dev_offload_op,
     b200_dev_event_new, b200_dev_event_free, b200_dev_event_sync,
 };
 
@@ -373,6 +397,7 @@ static ggml_backend_reg_t b200_reg() {
     static ggml_backend_reg reg = { GGML_BACKEND_API_VERSION, b200_reg_iface, nullptr };
     return &reg;
 }
+static ggml_backend_dev_t b200_the_device() { return b200_reg_device(b200_reg(), 0); }
 static ggml_backend_dev_t b200_reg_device(ggml_backend_reg_t reg, size_t i) {
     static b200_device_ctx dctx;
     static ggml_backend_device dev = { b200_device_iface, reg, &dctx };

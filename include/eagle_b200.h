@@ -51,6 +51,8 @@ EB_API int eb_synchronize(void *stream);
  * asynchronous backend (R/ggml/src/ggml-backend-impl.h:87-124; CUDA backend: set/get_tensor_async
  * R/ggml/src/ggml-cuda/ggml-cuda.cu:2390-2440, event_record / event_wait :2790-2815, event_new / free / synchronize
  * :3161-3198).  Streams are non-blocking (no implicit ordering with the NULL stream). */
+EB_API int eb_malloc_host(void **h_ptr, size_t bytes);   /* pinned: the host buffer type of the device (ggml-cuda.cu:1048-1108) */
+EB_API int eb_free_host(void *h_ptr);
 EB_API int eb_stream_create(void **stream);
 EB_API int eb_stream_destroy(void *stream);
 EB_API int eb_device_synchronize(void);

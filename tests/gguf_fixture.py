@@ -57,8 +57,25 @@ def _add(w, name, t, raw, shape, dequant=None):
     w.add_tensor(name, raw.reshape(rows, -1), raw_dtype=QT[t])
 
 
-def write_gguf(fx, path, n_ctx_train=4096, as_f16=False):
-    """fx: fixtures.make_model dict -> GGUF at `path` (arch llama or eagle by fx['hparams']['is_eagle'])"""
+def _add_spm_vocab(w, V):
+    """a minimal SentencePiece-style vocabulary with byte fallback (R/src/llama-vocab.cpp, tokenizer model "llama"): <unk>, <s>, </s>, the
+    256 byte tokens, then unique filler pieces — enough for the reference's drivers to tokenise any prompt and detokenise any id"""
+    assert V >= 259 + 16
+    toks, scores, types = ["<unk>", "<s>", "</s>"], [0.0, 0.0, 0.0], [2, 3, 3]          # UNKNOWN, CONTROL, CONTROL
+    for b in range(256):
+        toks.append("<0x%02X>" % b); scores.append(0.0); types.append(6)                 # BYTE
+    i = 0
+    while len(toks) < V:
+        toks.append("\u2581t%d" % i); scores.append(-1000.0 - i); types.append(1); i += 1   # NORMAL, never produced by the tokenizer
+    w.add_tokenizer_model("llama")
+    w.add_token_list(toks); w.add_token_scores(scores); w.add_token_types(types)
+    w.add_bos_token_id(1); w.add_eos_token_id(2); w.add_unk_token_id(0)
+    w.add_add_bos_token(True); w.add_add_eos_token(False)
+
+
+def write_gguf(fx, path, n_ctx_train=4096, as_f16=False, vocab=False):
+    """fx: fixtures.make_model dict -> GGUF at `path` (arch llama or eagle by fx['hparams']['is_eagle']); vocab=True adds a byte-fallback
+    SPM vocabulary so that the reference's command-line drivers can run on the file"""
     hp = fx["hparams"]
     arch = "eagle" if hp["is_eagle"] else "llama"
     w = gguf.GGUFWriter(path, arch)
@@ -73,7 +90,10 @@ def write_gguf(fx, path, n_ctx_train=4096, as_f16=False):
     w.add_uint32(f"{arch}.rope.dimension_count", hp["E"] // hp["H"])
     w.add_float32(f"{arch}.rope.freq_base", hp["freq_base"])
     w.add_uint32(f"{arch}.vocab_size", hp["V"])
-    w.add_string("tokenizer.ggml.model", "no_vocab")
+    if vocab:
+        _add_spm_vocab(w, hp["V"])
+    else:
+        w.add_string("tokenizer.ggml.model", "no_vocab")
     dq = None
     if as_f16:
         def dq(t, raw, out):
