@@ -64,6 +64,8 @@ def lib():
         "eb_dequantize": ([i32, vp, vp, i64, vp], i32),
         "eb_mul_mat_ws_size": ([i32, i64, i64, i64], sz),
         "eb_mul_mat": ([i32, vp, i64, i64, vp, i64, vp, vp, vp], i32),
+        "eb_mul_mat_ex": ([i32, vp, i64, i64, vp, i64, vp, vp, i32, vp], i32),
+        "eb_rope_norm_to": ([vp, vp, vp, i32, i32, i32, f32, vp], i32),
         "eb_rms_norm": ([vp, vp, vp, i64, i64, f32, vp], i32),
         "eb_rope_norm": ([vp, vp, i32, i32, i32, f32, vp], i32),
         "eb_get_rows_n": ([i32, vp, i64, i64, vp, i32, vp, vp], i32),

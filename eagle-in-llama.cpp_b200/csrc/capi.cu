@@ -103,14 +103,20 @@ size_t eb_mul_mat_ws_size(int type, int64_t N, int64_t K, int64_t T) {
     return 2 * eb_actq_bytes(1, K, (int)T) + (size_t)8 * T * N * 4 + 1024;
 }
 int eb_mul_mat(int type, const void *d_W, int64_t N, int64_t K, const float *d_x, int64_t T, float *d_y, void *d_ws, void *st) {
+    return eb_mul_mat_ex(type, d_W, N, K, d_x, T, d_y, d_ws, 0, st);
+}
+// reuse_activation != 0: the previous eb_mul_mat / eb_mul_mat_ex call on this workspace quantised the SAME d_x (same K, T <= 128, same
+// activation grid: K-quants share Q8_K, Q4_0 / Q8_0 share Q8_0) and nothing else touched the workspace since — the planes are reused
+int eb_mul_mat_ex(int type, const void *d_W, int64_t N, int64_t K, const float *d_x, int64_t T, float *d_y, void *d_ws, int reuse_activation, void *st) {
     NEED_DEV();
     if (T < 1) return EB_OK;
     if (!d_ws) return eb_set_err(EB_ERR_ARG, "mul_mat: workspace required");
+    if (reuse_activation && T > 128) return eb_set_err(EB_ERR_ARG, "mul_mat_ex: activation reuse needs T <= 128");
     const size_t aq = 2 * eb_actq_bytes(1, K, (int)T);
     // batches beyond one verify tile are processed in column chunks of 128
     for (int64_t t0 = 0; t0 < T; t0 += 128) {
         const int tc = (int)std::min<int64_t>(128, T - t0);
-        int rc = eb_mul_mat_impl(type, d_W, N, K, d_x + t0 * K, tc, d_y + t0 * N, d_ws, (float *)((char *)d_ws + ((aq + 255) & ~(size_t)255)), S(st));
+        int rc = eb_mul_mat_impl(type, d_W, N, K, d_x + t0 * K, tc, d_y + t0 * N, d_ws, (float *)((char *)d_ws + ((aq + 255) & ~(size_t)255)), S(st), reuse_activation != 0);
         if (rc) return rc;
     }
     return EB_OK;
@@ -123,7 +129,8 @@ int eb_quantize_act_planes(int kq, const float *d_x, int64_t K, int T, int8_t *d
 }
 
 int eb_rms_norm(const float *x, const float *w, float *y, int64_t n, int64_t rows, float eps, void *st) { NEED_DEV(); return eb_rms_norm_impl(x, w, y, n, rows, eps, S(st)); }
-int eb_rope_norm(float *x, const int32_t *pos, int D, int n_head, int T, float freq_base, void *st) { NEED_DEV(); return eb_rope_norm_impl(x, pos, D, n_head, T, freq_base, S(st)); }
+int eb_rope_norm(float *x, const int32_t *pos, int D, int n_head, int T, float freq_base, void *st) { NEED_DEV(); return eb_rope_norm_impl(x, x, pos, D, n_head, T, freq_base, S(st)); }
+int eb_rope_norm_to(const float *src, float *dst, const int32_t *pos, int D, int n_head, int T, float freq_base, void *st) { NEED_DEV(); return eb_rope_norm_impl(src, dst, pos, D, n_head, T, freq_base, S(st)); }
 int eb_get_rows_n(int type, const void *W, int64_t n_rows, int64_t K, const int32_t *ids, int n, float *out, void *st) { NEED_DEV(); return eb_get_rows_dev(type, W, n_rows, K, ids, n, out, S(st)); }
 int eb_add(const float *a, const float *b, float *y, int64_t n, int64_t nb, void *st) { NEED_DEV(); return eb_add_impl(a, b, y, n, nb, S(st)); }
 int eb_mul(const float *a, const float *b, float *y, int64_t n, int64_t nb, void *st) { NEED_DEV(); return eb_mul_impl(a, b, y, n, nb, S(st)); }

@@ -181,11 +181,12 @@ static int model_finalize(eb_model *m) {
 // ------------------------------------------------------------------ mul_mat dispatch
 // T <= 8: dequant-dot matvec (K1); T > 8: int8 tensor-core GEMM (K2) for K-quants, else K1 in
 // column chunks.  actq_ws holds the quantised activations.
-int eb_mul_mat_impl(int type, const void *W, int64_t N, int64_t K, const float *x, int T, float *y, void *actq_ws, float *partial, cudaStream_t st) {
+// reuse_act: the planes in actq_ws already hold the quantisation of this x on this grid (previous call, same x / K / T / grid class)
+int eb_mul_mat_impl(int type, const void *W, int64_t N, int64_t K, const float *x, int T, float *y, void *actq_ws, float *partial, cudaStream_t st, bool reuse_act) {
     const int kq = (type == EB_Q4_K || type == EB_Q6_K);
     if (!kq && type != EB_Q4_0 && type != EB_Q8_0) return eb_set_err(EB_ERR_UNSUPPORTED, "mul_mat: weight type %d", type);
     ActQ a = eb_actq_carve(actq_ws, kq, K, T);
-    int rc = eb_quantize_act(x, a, st); if (rc) return rc;
+    int rc = reuse_act ? EB_OK : eb_quantize_act(x, a, st); if (rc) return rc;
     if (eb_mmq_tc_supported(type, N, K, T)) {
         int ks = 1;
         rc = eb_mmq_tc_parts(type, W, N, K, a, partial, &ks, st); if (rc) return rc;

@@ -56,7 +56,7 @@ struct eb_session {
 
 // ops implemented in the other translation units
 int eb_rms_norm_impl(const float *x, const float *w, float *y, int64_t n, int64_t rows, float eps, cudaStream_t st);
-int eb_rope_norm_impl(float *x, const int32_t *pos, int D, int n_head, int T, float freq_base, cudaStream_t st);
+int eb_rope_norm_impl(const float *src, float *dst, const int32_t *pos, int D, int n_head, int T, float freq_base, cudaStream_t st);
 int eb_add_impl(const float *a, const float *b, float *y, int64_t n, int64_t nb, cudaStream_t st);
 int eb_mul_impl(const float *a, const float *b, float *y, int64_t n, int64_t nb, cudaStream_t st);
 int eb_silu_impl(const float *x, float *y, int64_t n, cudaStream_t st);
@@ -97,4 +97,4 @@ int eb_fattn_tc_bits(const float *q, const void *k, const void *v, int64_t kv_st
 int eb_fattn_tc_f32q(const float *q, const void *k, const void *v, int64_t kv_stride, const uint32_t *tree_bits, int n_prefix, int n_kv,
                      int T, int H, float scale, float *out, void *ws, cudaStream_t st);
 int eb_swiglu_quant(PlaneRef gate, PlaneRef up, int n, int T, const ActQ &aq, cudaStream_t st);
-int eb_mul_mat_impl(int type, const void *W, int64_t N, int64_t K, const float *x, int T, float *y, void *actq_ws, float *partial, cudaStream_t st);
+int eb_mul_mat_impl(int type, const void *W, int64_t N, int64_t K, const float *x, int T, float *y, void *actq_ws, float *partial, cudaStream_t st, bool reuse_act = false);

@@ -52,26 +52,33 @@ int eb_rms_norm_impl(const float *x, const float *w, float *y, int64_t n, int64_
 // ------------------------------------------------------------------ RoPE (NORM) [+ KV store]
 // ggml_compute_forward_rope_f32 (R/ggml/src/ggml-cpu/ggml-cpu.c:9449) with ggml_rope_cache_init
 // (:9376): theta_0 = pos, theta_{i+1} = theta_i * theta_scale (sequential f32 products, restated
-// exactly), pairs (2i, 2i+1).  One thread per (token, pair); heads looped inside so cos/sin are
-// computed once per (token, pair) like the reference's cache.
-__global__ void rope_norm_kernel(float *__restrict__ x, const int32_t *__restrict__ pos, int D, int n_head, int T, float theta_scale) {
-    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-    const int half = D / 2;
-    if (idx >= T * half) return;
-    const int t = idx / half, i = idx % half;
-    float theta = (float)pos[t];
-    for (int j = 0; j < i; j++) theta = __fmul_rn(theta, theta_scale);
-    const float c = cosf(theta), s = sinf(theta);
-    float *p = x + (int64_t)t * n_head * D + 2 * i;
-    for (int h = 0; h < n_head; h++, p += D) {
-        const float2 v = *(float2 *)p;
-        *(float2 *)p = make_float2(__fsub_rn(__fmul_rn(v.x, c), __fmul_rn(v.y, s)), __fadd_rn(__fmul_rn(v.x, s), __fmul_rn(v.y, c)));
+// exactly), pairs (2i, 2i+1).  One CTA per token: the first D/2 threads build the token's cos/sin
+// cache in shared memory (like the reference's per-row cache), then all threads rotate the
+// n_head * D/2 pairs of the row.  src may equal dst (in place) or not (ggml's ROPE node is not
+// always in place).
+__global__ void __launch_bounds__(256) rope_norm_kernel(const float *__restrict__ src, float *__restrict__ dst, const int32_t *__restrict__ pos, int D, int n_head, float theta_scale) {
+    __shared__ float2 cs[128];
+    const int t = blockIdx.x, half = D / 2;
+    for (int i = threadIdx.x; i < half; i += blockDim.x) {
+        float theta = (float)pos[t];
+        for (int j = 0; j < i; j++) theta = __fmul_rn(theta, theta_scale);
+        cs[i] = make_float2(cosf(theta), sinf(theta));
+    }
+    __syncthreads();
+    const int64_t row = (int64_t)t * n_head * D;
+    for (int idx = threadIdx.x; idx < n_head * half; idx += blockDim.x) {
+        const int h = idx / half, i = idx - h * half;
+        const float2 k = cs[i];
+        const int64_t o = row + (int64_t)h * D + 2 * i;
+        const float2 v = *(const float2 *)(src + o);
+        *(float2 *)(dst + o) = make_float2(__fsub_rn(__fmul_rn(v.x, k.x), __fmul_rn(v.y, k.y)), __fadd_rn(__fmul_rn(v.x, k.y), __fmul_rn(v.y, k.x)));
     }
 }
-int eb_rope_norm_impl(float *x, const int32_t *pos, int D, int n_head, int T, float freq_base, cudaStream_t st) {
+int eb_rope_norm_impl(const float *src, float *dst, const int32_t *pos, int D, int n_head, int T, float freq_base, cudaStream_t st) {
     if (T == 0) return EB_OK;
+    if (D > 256 || (D & 1)) return eb_set_err(EB_ERR_ARG, "rope: D=%d", D);
     const float theta_scale = powf(freq_base, -2.0f / D);
-    rope_norm_kernel<<<cdiv(T * (D / 2), 128), 128, 0, st>>>(x, pos, D, n_head, T, theta_scale);
+    rope_norm_kernel<<<T, 256, 0, st>>>(src, dst, pos, D, n_head, theta_scale);
     EB_CHECK_LAUNCH();
     return EB_OK;
 }

@@ -132,12 +132,16 @@ struct b200_backend_ctx {
     void *stream = nullptr;
     void *ws = nullptr; size_t ws_size = 0;      // scratch of eb_mul_mat / eb_flash_attn, grown on demand
     void *scratch(size_t need) {
-        if (need > ws_size) { if (ws) { eb_synchronize(stream); eb_free(ws); } ws = nullptr; ws_size = 0; if (eb_malloc(&ws, need) != EB_OK) return nullptr; ws_size = need; }
+        if (need > ws_size) { if (ws) { eb_synchronize(stream); eb_free(ws); } ws = nullptr; ws_size = 0; aq_src = nullptr; if (eb_malloc(&ws, need) != EB_OK) return nullptr; ws_size = need; }
         return ws;
     }
     // FLASH_ATTN_EXT: the mask of a graph in bit form (every layer uses the same KQ_mask tensor), valid for one graph_compute
     void *bits = nullptr; size_t bits_size = 0;
     const void *mask_data = nullptr; int mask_T = 0, mask_kv = 0; bool mask_bits_ok = false;
+    // MUL_MAT: the activation planes left in the scratch by the previous MUL_MAT (wq / wk / wv and ffn_gate / ffn_up read one tensor
+    // each).  Valid until a node writes into that tensor, another op takes the scratch, or the graph ends.
+    const char *aq_src = nullptr; size_t aq_bytes = 0; int64_t aq_K = 0, aq_T = 0; int aq_kq = -1; void *aq_ws = nullptr;
+    void aq_drop() { aq_src = nullptr; }
 };
 
 static const char *b200_be_name(ggml_backend_t) { return B200_NAME; }
@@ -253,7 +257,12 @@ static int b200_compute_node(b200_backend_ctx *ctx, ggml_tensor *d) {
                                     (float *)d->data, a->ne[1], a->ne[0], b->ne[1], b->ne[2], st);
         void *ws = ctx->scratch(eb_mul_mat_ws_size((int)a->type, a->ne[1], a->ne[0], b->ne[1]));
         if (!ws) return EB_ERR_OOM;
-        return eb_mul_mat((int)a->type, a->data, a->ne[1], a->ne[0], (const float *)b->data, b->ne[1], (float *)d->data, ws, st);
+        const int kq = a->type == GGML_TYPE_Q4_K || a->type == GGML_TYPE_Q6_K;
+        const int64_t K = a->ne[0], T = b->ne[1];
+        const bool reuse = T <= 128 && ctx->aq_src == (const char *)b->data && ctx->aq_K == K && ctx->aq_T == T && ctx->aq_kq == kq && ctx->aq_ws == ws;
+        const int rc = eb_mul_mat_ex((int)a->type, a->data, a->ne[1], K, (const float *)b->data, T, (float *)d->data, ws, reuse ? 1 : 0, st);
+        ctx->aq_src = T <= 128 && rc == EB_OK ? (const char *)b->data : nullptr; ctx->aq_bytes = (size_t)T * K * 4; ctx->aq_K = K; ctx->aq_T = T; ctx->aq_kq = kq; ctx->aq_ws = ws;
+        return rc;
     }
     case GGML_OP_FLASH_ATTN_EXT: {
         const ggml_tensor *v = d->src[2], *m = d->src[3];
@@ -261,6 +270,7 @@ static int b200_compute_node(b200_backend_ctx *ctx, ggml_tensor *d) {
         const int64_t kv_stride = (int64_t)(b->nb[1] / 2);
         void *ws = ctx->scratch(eb_flash_attn_ws_size(T, H, D, n_kv));
         if (!ws) return EB_ERR_OOM;
+        ctx->aq_drop();                                             // the attention workspace overlays the activation planes
         // llama_set_inputs writes 0 / -inf masks (R/src/llama-context.cpp:136-201): those run on the tcgen05 kernel through the mask's
         // bit form, built once per graph (all layers share KQ_mask); anything else (ALiBi, test masks) takes the generic kernel
         static const bool generic_only = getenv("GGML_B200_FA_GENERIC") != nullptr;      // A/B switch: always take the f16-mask kernel
@@ -285,10 +295,8 @@ static int b200_compute_node(b200_backend_ctx *ctx, ggml_tensor *d) {
     }
     case GGML_OP_GET_ROWS: return eb_get_rows_n((int)a->type, a->data, a->ne[1], a->ne[0], (const int32_t *)b->data, (int)b->ne[0], (float *)d->data, st);
     case GGML_OP_RMS_NORM: return eb_rms_norm((const float *)a->data, nullptr, (float *)d->data, a->ne[0], ggml_nrows(a), op_f32(d, 0), st);
-    case GGML_OP_ROPE: {        // the library rotates in place; ggml's dst may or may not alias src0 (ggml-alloc inplace)
-        int rc = eb_copy(d->data, a->data, ggml_nbytes(a), st); if (rc) return rc;
-        return eb_rope_norm((float *)d->data, (const int32_t *)b->data, (int)a->ne[0], (int)a->ne[1], (int)a->ne[2], op_f32(d, 5), st);
-    }
+    case GGML_OP_ROPE:          // ggml's dst may or may not alias src0 (ggml-alloc inplace): the kernel reads src and writes dst
+        return eb_rope_norm_to((const float *)a->data, (float *)d->data, (const int32_t *)b->data, (int)a->ne[0], (int)a->ne[1], (int)a->ne[2], op_f32(d, 5), st);
     case GGML_OP_ADD: return eb_add((const float *)a->data, (const float *)b->data, (float *)d->data, ggml_nelements(d), ggml_nelements(b), st);
     case GGML_OP_MUL: return eb_mul((const float *)a->data, (const float *)b->data, (float *)d->data, ggml_nelements(d), ggml_nelements(b), st);
     case GGML_OP_UNARY:
@@ -321,13 +329,24 @@ static ggml_status b200_be_graph_compute(ggml_backend_t be, ggml_cgraph *g) {
     auto *ctx = (b200_backend_ctx *)be->context;
     const int n = ggml_graph_n_nodes(g);
     ctx->mask_data = nullptr;                    // the mask's contents change between graphs even when its address does not
+    ctx->aq_drop();
+    static const bool timing = getenv("GGML_B200_TIMING") != nullptr;
+    const int64_t t0 = timing ? ggml_time_us() : 0;
     for (int i = 0; i < n; i++) {
         ggml_tensor *d = ggml_graph_node(g, i);
         if (ggml_is_empty(d)) continue;
+        // a node that writes into the tensor whose quantisation is cached ends the cache (views and reshapes compute nothing)
+        if (ctx->aq_src && d->op != GGML_OP_MUL_MAT && d->op != GGML_OP_NONE && d->op != GGML_OP_RESHAPE && d->op != GGML_OP_VIEW && d->op != GGML_OP_PERMUTE &&
+            d->op != GGML_OP_TRANSPOSE && d->data) {
+            const char *w0 = (const char *)d->data, *w1 = w0 + ggml_nbytes(d);
+            if (w0 < ctx->aq_src + ctx->aq_bytes && ctx->aq_src < w1) ctx->aq_drop();
+        }
         const int rc = b200_compute_node(ctx, d);
         if (rc == EB_ERR_OOM) { b200_log_err(ggml_op_name(d->op)); return GGML_STATUS_ALLOC_FAILED; }
         if (rc != EB_OK) { fprintf(stderr, "ggml-b200: %s (%s): %s\n", ggml_op_name(d->op), d->name, rc == EB_ERR_UNSUPPORTED ? "unsupported op" : eb_last_error()); return GGML_STATUS_FAILED; }
     }
+    ctx->aq_drop();
+    if (timing) fprintf(stderr, "ggml-b200: graph_compute issued %d nodes in %lld us (host side; the stream runs on)\n", n, (long long)(ggml_time_us() - t0));
     return GGML_STATUS_SUCCESS;
 }
 

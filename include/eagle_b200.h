@@ -94,12 +94,20 @@ EB_API int eb_dequantize(int type, const void *d_src, float *d_dst, int64_t n_el
 EB_API size_t eb_mul_mat_ws_size(int type, int64_t N, int64_t K, int64_t T);
 EB_API int eb_mul_mat(int type, const void *d_W, int64_t N, int64_t K, const float *d_x, int64_t T,
                       float *d_y, void *d_ws, void *stream);
+/* the same with the activation quantisation shared between consecutive calls on one workspace: reuse_activation != 0 says that the
+ * previous eb_mul_mat / eb_mul_mat_ex call quantised this very d_x (same K, same T <= 128, same grid: K-quants share Q8_K, Q4_0 / Q8_0
+ * share Q8_0) and nothing else used d_ws since.  wq / wk / wv and ffn_gate / ffn_up read one tensor each: the reference's CPU path
+ * quantises src1 once per MUL_MAT node too, into the same values (R/ggml/src/ggml-cpu/ggml-cpu.c:7590-7620), so results are unchanged. */
+EB_API int eb_mul_mat_ex(int w_type, const void *d_W, int64_t N, int64_t K, const float *d_x, int64_t T, float *d_y, void *d_ws,
+                         int reuse_activation, void *stream);
 
 /* GGML_OP_RMS_NORM (+ optional GGML_OP_MUL by a weight row): R/ggml/src/ggml-cuda/norm.cu:108 */
 EB_API int eb_rms_norm(const float *d_x, const float *d_weight_or_null, float *d_y, int64_t n,
                        int64_t rows, float eps, void *stream);
 /* GGML_OP_ROPE, mode NORM, in place on [T][n_head][D]: R/ggml/src/ggml-cuda/rope.cu:41 */
 EB_API int eb_rope_norm(float *d_x, const int32_t *d_pos, int D, int n_head, int T, float freq_base, void *stream);
+/* out of place: dst = rope(src); dst may equal src */
+EB_API int eb_rope_norm_to(const float *d_src, float *d_dst, const int32_t *d_pos, int D, int n_head, int T, float freq_base, void *stream);
 /* GGML_OP_GET_ROWS with dequantisation: R/ggml/src/ggml-cuda/getrows.cu:5-148 */
 EB_API int eb_get_rows_n(int type, const void *d_W, int64_t n_rows, int64_t K, const int32_t *d_ids, int n, float *d_out, void *stream);
 /* elementwise: R/ggml/src/ggml-cuda/binbcast.cu:26, unary.cu:45,201.  b is broadcast over rows
