@@ -218,6 +218,34 @@ def test_flash_attn_bit_mask_form_vs_oracle(eb, T, n_kv, H):
     assert eb.flash_attn_ext_bits(q, k, v, 1 / np.sqrt(D), mask2) == (None, True)
 
 
+def test_mul_mat_shared_activation_and_rope_out_of_place(eb):
+    """eb_mul_mat_ex: three weight matrices on ONE activation tensor (wq / wk / wv in a ggml graph) with the quantisation done once — bit-identical
+    to three independent eb_mul_mat calls; eb_rope_norm_to out of place == eb_rope_norm in place, source untouched"""
+    lib = eb.lib()
+    rng = np.random.default_rng(12)
+    K, N, T = 1024, 384, 27
+    X = rng.normal(0, 1, (T, K)).astype(np.float32)
+    for types in ((po.Q4_K, po.Q4_K, po.Q6_K), (po.Q4_0, po.Q8_0, po.Q4_0)):
+        ws = [eb.Weights(t, fx.random_blocks(t, N * K, rng), N, K) for t in types]
+        want = [eb.mul_mat(w, X) for w in ws]
+        dx = eb.DeviceBuffer.from_host(X); scratch = eb.DeviceBuffer(lib.eb_mul_mat_ws_size(types[0], N, K, T))
+        got = []
+        for i, w in enumerate(ws):
+            dy = eb.DeviceBuffer(T * N * 4)
+            assert lib.eb_mul_mat_ex(w.t, w.buf.ptr, N, K, dx.ptr, T, dy.ptr, scratch.ptr, 1 if i else 0, None) == 0, lib.eb_last_error().decode()
+            assert lib.eb_synchronize(None) == 0
+            got.append(dy.to_host(np.float32, (T, N)))
+        for a, b in zip(got, want):
+            assert np.array_equal(a, b)
+    dy = eb.DeviceBuffer(200 * N * 4); dx2 = eb.DeviceBuffer.from_host(np.zeros((200, K), np.float32))
+    assert lib.eb_mul_mat_ex(ws[0].t, ws[0].buf.ptr, N, K, dx2.ptr, 200, dy.ptr, scratch.ptr, 1, None) != 0       # reuse beyond one 128-row tile is refused
+    x = rng.normal(0, 1, (9, 4, 128)).astype(np.float32); pos = rng.integers(0, 4000, 9).astype(np.int32)
+    want = eb.rope_norm(x, pos, 10000.0)
+    ds, dd, dp = eb.DeviceBuffer.from_host(x), eb.DeviceBuffer(x.nbytes), eb.DeviceBuffer.from_host(pos)
+    assert lib.eb_rope_norm_to(ds.ptr, dd.ptr, dp.ptr, 128, 4, 9, 10000.0, None) == 0 and lib.eb_synchronize(None) == 0
+    assert np.array_equal(dd.to_host(np.float32, x.shape), want) and np.array_equal(ds.to_host(np.float32, x.shape), x)
+
+
 def test_top_k_argmax(eb):
     rng = np.random.default_rng(4)
     x = rng.normal(0, 2, (9, 32000)).astype(np.float32)
