@@ -410,9 +410,12 @@ def run_config3(args, rank, world, local_rank):
         import torch.distributed as dist
         torch.cuda.set_device(local_rank)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-    per_gpu = 8
+    c1 = args.config == 1                                   # config 1: the reference's CPU-runnable case — Q4_0 target + Q4_0 head, 26-node tree, 512-token prompt, one stream
+    per_gpu = 1 if c1 else 8
+    qt, qn = (eb.Q4_0, "Q4_0") if c1 else (eb.Q8_0, "Q8_0")
     sampler = ClockSampler(local_rank); sampler.start()
-    r = c3.run(eb, per_gpu, args.steps, eb.Q8_0, warm=max(3, args.warmup), barrier=(dist.barrier if dist else None), seed0=100 + 1000 * rank)
+    r = c3.run(eb, per_gpu, args.steps, qt, n_draft=26 if c1 else None, n_past=512 if c1 else None, warm=max(3, args.warmup),
+               barrier=(dist.barrier if dist else None), seed0=100 + 1000 * rank)
     clocks = sampler.summary()
     ms = max_over_ranks(dist, [r["gpu_ms"]], "cuda")[0] if dist else r["gpu_ms"]
     tokens = r["tokens"] * world
@@ -422,10 +425,12 @@ def run_config3(args, rank, world, local_rank):
         return None
     return {"metric": "eagle_decode_tok_per_s", "value": tokens / (ms * 1e-3), "unit": "tok/s", "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup),
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "int8xq8_0 dot, f32 accumulate, f16 KV", "data": "synthetic (random-init Q8_0 blocks, N(0,1) f16 KV prefill, fixed accept length 3)",
-            "config": {"workload": f"config 3: vicuna-7b Q8_0 + Q8_0 EAGLE head, {per_gpu * world} request streams ({per_gpu} per GPU, one resident weight copy per GPU), "
-                                   "64-node tree, KV ~4096 per stream", "parallelism": f"{world} GPU(s) x {per_gpu} streams, round-robin, no batching across streams, no collective",
-                       "l2": "weights (7.0 GB) per verify exceed L2: no flush needed"},
+            "dtype": f"int8x{qn.lower()} dot, f32 accumulate, f16 KV", "data": f"synthetic (random-init {qn} blocks, N(0,1) f16 KV prefill, fixed accept length 3)",
+            "config": {"workload": (f"config 1: vicuna-7b Q4_0 + Q4_0 EAGLE head, 26-node tree, 512-token prompt, {world} stream(s) (one per GPU)" if c1 else
+                                    f"config 3: vicuna-7b Q8_0 + Q8_0 EAGLE head, {per_gpu * world} request streams ({per_gpu} per GPU, one resident weight copy per GPU), "
+                                    "64-node tree, KV ~4096 per stream"),
+                       "parallelism": f"{world} GPU(s) x {per_gpu} stream(s), round-robin, no batching across streams, no collective",
+                       "l2": f"weights ({r['weight_bytes'] / 1e9:.1f} GB) per verify exceed L2: no flush needed"},
             "round_ms_per_stream": r["round_ms"], "verify_step_us": 1e3 * r["verify_ms"],
             "verify_step_hbm_frac": algorithmic_bytes(r["weight_bytes"], r["n_past"], r["T"]) / (r["verify_ms"] * 1e-3) / 1e9 / peaks()[0],
             "gpu_launches": r["launches"], "clocks": clocks}
@@ -462,14 +467,14 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--config", type=int, default=2, choices=[2, 3, 4],
-                    help="BASELINE.json config: 2 = the metric's own (default, the driver's run); 3 = Q8_0 target, 8 request streams per GPU; "
-                         "4 = LLaMA-2-13B verify step, tensor parallel over --gpus")
+    ap.add_argument("--config", type=int, default=2, choices=[1, 2, 3, 4],
+                    help="BASELINE.json config: 2 = the metric's own (default, the driver's run); 1 = Q4_0 target, 26-node tree, 512-token prompt, one stream; "
+                         "3 = Q8_0 target, 8 request streams per GPU; 4 = LLaMA-2-13B verify step, tensor parallel over --gpus")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1")); local = int(os.environ.get("LOCAL_RANK", "0"))
     if args.config == 4:
         out = run_config4(args, rank, world)
-    elif args.config == 3:
+    elif args.config in (1, 3):
         out = run_config3(args, rank, world, local)
     elif args.impl == "reference":
         out = run_reference(args, rank, world)

@@ -89,6 +89,9 @@ def lib():
         "eb_model_synth_tensor": ([vp, i32, i32, i32, C.c_uint64, f32], i32),
         "eb_model_get_tensor": ([vp, i32, i32, vp, sz], i32),
         "eb_model_share_lm_head": ([vp, vp], i32), "eb_model_weight_bytes": ([vp], sz),
+        "eb_model_get_hparams": ([vp, C.POINTER(i32), C.POINTER(C.c_float)], i32),
+        "eb_model_load_gguf": ([C.c_char_p, C.POINTER(vp), C.POINTER(C.c_double), C.POINTER(C.c_uint64)], i32),
+        "eb_gguf_probe": ([C.c_char_p, C.POINTER(i32), C.POINTER(C.c_float), C.POINTER(i32), C.POINTER(C.c_uint64)], i32),
         "eb_session_create": ([vp, vp, C.POINTER(SessionParams)], vp), "eb_session_free": ([vp], None),
         "eb_session_forward": ([vp, i32, vp, vp, vp, vp, i32, vp, vp], i32),
         "eb_tree_bits_from_batch": ([i32, vp, vp, vp, vp], i32),
@@ -406,6 +409,19 @@ class Model:
         if not self.h:
             raise EagleB200Error(lib().eb_last_error().decode())
 
+    @classmethod
+    def from_gguf(cls, path):
+        """eb_model_load_gguf: a GGUF file (arch llama or eagle) streamed into HBM -> Model; .load_seconds / .load_bytes report the upload"""
+        h, sec, nb = C.c_void_p(), C.c_double(), C.c_uint64()
+        _ck(lib().eb_model_load_gguf(os.fsencode(path), C.byref(h), C.byref(sec), C.byref(nb)))
+        hp, hf = (C.c_int32 * 6)(), (C.c_float * 2)()
+        _ck(lib().eb_model_get_hparams(h, hp, hf))
+        m = cls.__new__(cls)
+        m.E, m.H, m.F, m.V, m.L, m.is_eagle = hp[0], hp[1], hp[2], hp[3], hp[4], bool(hp[5])
+        m.eps, m.freq_base, m.h = float(hf[0]), float(hf[1]), h
+        m.load_seconds, m.load_bytes = sec.value, nb.value
+        return m
+
     def set_tensor(self, layer, which, t, raw):
         raw = np.ascontiguousarray(raw)
         _ck(lib().eb_model_set_tensor(self.h, layer, which, t, _hp(raw)))
@@ -651,6 +667,13 @@ def tree_bits_from_batch(pos, seq_ids):
     out = np.zeros((len(keep), 4), np.uint32)
     _ck(lib().eb_tree_bits_from_batch(len(keep), _hp(pos), _hp(n_seq), C.cast(ptrs, C.c_void_p), _hp(out)))
     return out
+
+
+def gguf_probe(path):
+    """header of a GGUF file, no device needed -> dict(E, H, F, V, L, is_eagle, eps, freq_base, n_tensors, bytes)"""
+    hp, hf, n, nb = (C.c_int32 * 6)(), (C.c_float * 2)(), C.c_int32(), C.c_uint64()
+    _ck(lib().eb_gguf_probe(os.fsencode(path), hp, hf, C.byref(n), C.byref(nb)))
+    return dict(E=hp[0], H=hp[1], F=hp[2], V=hp[3], L=hp[4], is_eagle=bool(hp[5]), eps=float(hf[0]), freq_base=float(hf[1]), n_tensors=n.value, bytes=nb.value)
 
 
 def launch_count(reset=False):

@@ -84,6 +84,17 @@ static int alloc_tensor(eb_model *m, int layer, int which, int type, DTensor **o
     *out = t;
     return EB_OK;
 }
+// the loader's entry: allocate the slot and hand back the device pointer (final layout) and its byte count
+int eb_model_alloc_tensor(eb_model *m, int layer, int which, int type, void **d_ptr, size_t *bytes) {
+    DTensor *t; int rc = alloc_tensor(m, layer, which, type, &t); if (rc) return rc;
+    *d_ptr = t->data; *bytes = t->bytes;
+    return EB_OK;
+}
+extern "C" int eb_model_get_hparams(const eb_model *m, int32_t *hp, float *hf) {
+    hp[0] = m->E; hp[1] = m->H; hp[2] = m->F; hp[3] = m->V; hp[4] = m->L; hp[5] = m->is_eagle;
+    hf[0] = m->eps; hf[1] = m->freq_base;
+    return EB_OK;
+}
 extern "C" int eb_model_set_tensor(eb_model *m, int layer, int which, int type, const void *h_data) {
     DTensor *t; int rc = alloc_tensor(m, layer, which, type, &t); if (rc) return rc;
     if (is_planar(type)) {

@@ -19,6 +19,8 @@ struct eb_model {
     std::vector<LayerFuse> fuse; std::vector<void *> fused_bufs; bool finalized = false;
 };
 
+int eb_model_alloc_tensor(eb_model *m, int layer, int which, int type, void **d_ptr, size_t *bytes);
+
 struct KVCache { __half *k = nullptr, *v = nullptr; int64_t layer_stride = 0; int L = 0, E = 0, n_ctx = 0; };
 
 // activation buffers for one forward of up to Tmax rows

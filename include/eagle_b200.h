@@ -200,6 +200,16 @@ EB_API int eb_model_synth_tensor(eb_model *m, int layer, int which, int type, ui
 EB_API int eb_model_get_tensor(const eb_model *m, int layer, int which, void *h_data, size_t bytes);
 EB_API int eb_model_share_lm_head(eb_model *head, const eb_model *target);   /* R/src/llama.cpp:2016 */
 EB_API size_t eb_model_weight_bytes(const eb_model *m);   /* bytes one forward streams */
+/* hp = {E, H, F, V, L, is_eagle}, hf = {rms eps, rope freq base} */
+EB_API int eb_model_get_hparams(const eb_model *m, int32_t *hp, float *hf);
+/* GGUF file -> resident model.  Replaces, for the tensors of this path, gguf_init_from_file (R/ggml/src/gguf.cpp) +
+ * llama_model_loader's per-tensor ggml_backend_tensor_set (R/src/llama-model-loader.cpp): the header is parsed here (GGUF v2 / v3;
+ * arch "llama" = target, "eagle" = draft head, tensor names of R/src/llama-arch.cpp:1301-1326), the data section streams through two
+ * page-locked buffers into the final allocations (plane-layout types through a device staging area + repack on the stream).
+ * An eagle file without output.weight is completed with eb_model_share_lm_head.  seconds / bytes (optional) report the upload.
+ * eb_gguf_probe reads the header only (no device needed): tensors of this path and their bytes. */
+EB_API int eb_model_load_gguf(const char *path, eb_model **out, double *seconds, uint64_t *bytes);
+EB_API int eb_gguf_probe(const char *path, int32_t *hp, float *hf, int32_t *n_tensors_used, uint64_t *bytes_used);
 
 /* ---- tensor parallelism of the target's verify forward (BASELINE config 4).  Replaces the reference's --split-mode row
  * (ggml_backend_cuda_split_buffer_type / ggml_cuda_op_mul_mat, R/ggml/src/ggml-cuda/ggml-cuda.cu:735-748,1359-1668: weight rows

@@ -1,0 +1,85 @@
+"""SURVEY 8f N3 — GGUF file -> resident model (csrc/gguf_load.cu).  The files are written by tests/gguf_fixture.py with the reference's
+vendored gguf-py and are the same ones the reference's own loader accepts (tests/test_ref_round.py, tests/test_dropin.py).
+CPU: the header parser (eb_gguf_probe needs no device) on llama / eagle files with and without a vocabulary section, and its error paths.
+GPU: eb_model_load_gguf streams the data section into HBM; every tensor read back is bit-identical to the fixture's GGUF bytes (plane-layout
+types included) and a forward through the loaded models equals the forward through models filled tensor by tensor."""
+import os
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from __graft_entry__ import load_package  # noqa: E402
+
+import fixtures as fx  # noqa: E402
+import gguf_fixture as gf  # noqa: E402
+import pyoracle as po  # noqa: E402
+
+HP = dict(E=256, H=2, F=512, V=1024, L=2)
+
+
+def _files(tmp_path, vocab):
+    tgt = fx.make_model(**HP, ftype="q4_k_m", seed=81)
+    head = fx.make_model(**{**HP, "L": 1}, ftype=po.Q4_0, seed=82, is_eagle=True)
+    return tgt, head, gf.write_gguf(tgt, str(tmp_path / "t.gguf"), vocab=vocab), gf.write_gguf(head, str(tmp_path / "h.gguf"), vocab=vocab)
+
+
+@pytest.mark.parametrize("vocab", [False, True])
+def test_gguf_probe_reads_the_reference_format(tmp_path, vocab):
+    eb = load_package()
+    tgt, head, pt, ph = _files(tmp_path, vocab)
+    a, b = eb.gguf_probe(pt), eb.gguf_probe(ph)
+    assert (a["E"], a["H"], a["F"], a["V"], a["L"], a["is_eagle"]) == (256, 2, 512, 1024, 2, False)
+    assert (b["E"], b["H"], b["F"], b["V"], b["L"], b["is_eagle"]) == (256, 2, 512, 1024, 1, True)
+    assert abs(a["eps"] - 1e-5) < 1e-12 and a["freq_base"] == 10000.0
+    n_t = len(tgt["globals"]) + sum(len(d) for d in tgt["layers"]); n_h = len(head["globals"]) + sum(len(d) for d in head["layers"])
+    assert a["n_tensors"] == n_t and b["n_tensors"] == n_h
+    assert a["bytes"] == sum(r.nbytes for _, r in tgt["globals"].values()) + sum(r.nbytes for d in tgt["layers"] for _, r in d.values())
+
+
+def test_gguf_probe_rejects_what_it_cannot_load(tmp_path):
+    eb = load_package()
+    _, _, pt, _ = _files(tmp_path, False)
+    raw = open(pt, "rb").read()
+    bad = tmp_path / "bad.gguf"
+    bad.write_bytes(b"GGML" + raw[4:])
+    with pytest.raises(eb.EagleB200Error, match="magic"):
+        eb.gguf_probe(str(bad))
+    bad.write_bytes(raw[:len(raw) // 2])                      # truncated data section
+    with pytest.raises(eb.EagleB200Error, match="past the end"):
+        eb.gguf_probe(str(bad))
+    bad.write_bytes(raw[:64])                                 # truncated header
+    with pytest.raises(eb.EagleB200Error):
+        eb.gguf_probe(str(bad))
+    with pytest.raises(eb.EagleB200Error, match="cannot open"):
+        eb.gguf_probe(str(tmp_path / "missing.gguf"))
+
+
+@pytest.mark.gpu
+def test_load_gguf_bit_exact_and_same_forward(eb, tmp_path):
+    tgt, head, pt, ph = _files(tmp_path, True)
+    mt, mh = eb.Model.from_gguf(pt), eb.Model.from_gguf(ph)
+    assert (mt.E, mt.H, mt.F, mt.V, mt.L, mt.is_eagle) == (256, 2, 512, 1024, 2, False) and mh.is_eagle and mh.L == 1
+    assert mt.load_bytes == eb.gguf_probe(pt)["bytes"] and mt.load_seconds > 0
+    for m, f in ((mt, tgt), (mh, head)):
+        for which, (t, raw) in f["globals"].items():
+            np.testing.assert_array_equal(m.get_tensor(-1, which, raw.nbytes), raw.view(np.uint8).reshape(-1))
+        for l, d in enumerate(f["layers"]):
+            for which, (t, raw) in d.items():
+                np.testing.assert_array_equal(m.get_tensor(l, which, raw.nbytes), raw.view(np.uint8).reshape(-1))
+    mh.share_lm_head(mt)
+    rt = fx.to_gpu_model(eb, tgt); rh = fx.to_gpu_model(eb, head, target=rt)
+    rng = np.random.default_rng(3)
+    prompt = rng.integers(3, HP["V"], 12).astype(np.int32)
+    outs = []
+    for a, b in ((mt, mh), (rt, rh)):
+        s = eb.Session(a, b, n_ctx=128, max_nodes=17, use_graph=False)
+        lg, ft = s.forward(0, prompt, np.arange(12))
+        hid = np.zeros((12, HP["E"]), np.float32); hid[1:] = ft[:-1]
+        lh, _ = s.forward(1, prompt, np.arange(12), hidden=hid)
+        outs.append((lg, lh)); s.free()
+    assert np.array_equal(outs[0][0], outs[1][0]) and np.array_equal(outs[0][1], outs[1][1])
+    for m in (mt, mh, rt, rh):
+        m.free()
