@@ -99,6 +99,7 @@ def lib():
         "eb_model_create_tp": ([i32, i32, i32, i32, i32, i32, f32, f32], vp),
         "eb_tp_create": ([i32, i32, i64], vp), "eb_tp_handle": ([vp, vp], i32), "eb_tp_open_peer": ([vp, i32, vp], i32),
         "eb_tp_free": ([vp], None), "eb_tp_error": ([vp], i32), "eb_tp_allreduce": ([vp, vp, i32, i64, vp, vp], i32),
+        "eb_tp_bench": ([vp, vp, i32, i64, vp, i32, i32, C.POINTER(C.c_float)], i32),
         "eb_session_set_tp": ([vp, vp], i32),
         "eb_session_set_tap": ([vp, vp, sz], i32), "eb_session_tap_state": ([vp, C.POINTER(sz), C.POINTER(i32)], i32),
         "eb_session_prefill": ([vp, vp, i32, vp, vp], i32),

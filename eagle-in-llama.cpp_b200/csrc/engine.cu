@@ -405,7 +405,7 @@ static int forward_dev(const eb_model *m, KVCache &kv, Workspace &w, const int32
         const float *po_planes = w.po;
         // tensor parallel: wo is K-split over the ranks' heads; the partial [T][E] sums (this rank's split-K planes included) are
         // summed over the group by one peer-memory kernel (tp.cu), every rank ends up with the same bits
-        if (tp) { RC(eb_tp_allreduce_planes(tp, w.po, ko_, (int64_t)T * E, tp_buf, st)); po_planes = tp_buf; ko_ = 1; }
+        if (tp) { RC(eb_tp_allreduce_planes(tp, w.po, ko_, (int64_t)T * E, tp_buf, st, 0)); po_planes = tp_buf; ko_ = 1; }      // slot set 0
         // ffn_inp = wo.att + x ; cur = rms_norm(ffn_inp) * ffn_norm -> grid of up/gate
         const int gu = grid_of(t[EB_L_UP]);
         if (grid_of(t[EB_L_GATE]) != gu) return eb_set_err(EB_ERR_UNSUPPORTED, "layer %d: ffn_up/ffn_gate mix formats", l);
@@ -429,7 +429,7 @@ static int forward_dev(const eb_model *m, KVCache &kv, Workspace &w, const int32
         RC(tap_site(tap, ad, st));
         RC(mm_parts(t[EB_L_DOWN], ad, w.pq, &pend_ks, st));       // pq is free again: holds the down planes
         pend = w.pq;
-        if (tp) { RC(eb_tp_allreduce_planes(tp, w.pq, pend_ks, (int64_t)T * E, tp_buf, st)); pend = tp_buf; pend_ks = 1; }   // ffn_down is K-split too
+        if (tp) { RC(eb_tp_allreduce_planes(tp, w.pq, pend_ks, (int64_t)T * E, tp_buf, st, 1)); pend = tp_buf; pend_ks = 1; }   // ffn_down is K-split too: slot set 1
     }
     // x += pending; result_norm = rms_norm(x) * output_norm  (-> feat, and the lm_head's grid)
     const DTensor &o = m->g[EB_T_OUTPUT];

@@ -36,7 +36,7 @@ struct Workspace {
 };
 
 struct eb_tp;      // tp.cu: peer-memory communicator of a tensor-parallel group
-int eb_tp_allreduce_planes(eb_tp *tp, const float *planes, int ks, int64_t n, float *out, cudaStream_t st);
+int eb_tp_allreduce_planes(eb_tp *tp, const float *planes, int ks, int64_t n, float *out, cudaStream_t st, int set);
 
 struct ActTap { int8_t *buf = nullptr; size_t cap = 0, off = 0; int sites = 0; };
 

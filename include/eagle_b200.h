@@ -229,6 +229,9 @@ EB_API void eb_tp_free(eb_tp *tp);
 EB_API int  eb_tp_error(eb_tp *tp);      /* 1 after a wait for a peer timed out */
 /* out[i] = sum over ranks of sum over the ks planes [ks][n] of every rank; identical bits on all ranks; n % 4 == 0 */
 EB_API int  eb_tp_allreduce(eb_tp *tp, const float *d_planes, int ks, int64_t n, float *d_out, void *stream);
+/* device time of one all-reduce, measured over `iters` (even) calls replayed from one CUDA graph (host launch overhead excluded);
+ * engine_sets != 0 alternates the engine's slot sets, else the operator's.  Collective: all ranks call it together. */
+EB_API int  eb_tp_bench(eb_tp *tp, const float *d_planes, int ks, int64_t n, float *d_out, int engine_sets, int iters, float *us_per_call);
 
 typedef struct {
     int n_ctx;          /* KV cells per cache */

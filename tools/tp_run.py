@@ -136,26 +136,23 @@ def check():
 
 
 def bench_allreduce(iters=200):
-    """the collective alone: [65][5120] f32 with 4 split-K planes per rank, back to back on the stream, CUDA events"""
-    import torch
+    """the collective alone: [65][5120] f32 with 4 split-K planes per rank; device time per call from a CUDA-graph replay of `iters` calls
+    (eb_tp_bench), in the engine's form (rank partials left in the slots for the consumer) and in the operator form (rank-order sum included)"""
     E, T, ks = 5120, 65, 4
     tp = eb.TpGroup(rank, world, 128 * E, exchange)
     n = T * E
     planes = eb.DeviceBuffer.from_host(np.random.default_rng(rank).normal(0, 1, (ks, n)).astype(np.float32)); out = eb.DeviceBuffer(n * 4)
     lib = eb.lib()
-    barrier()
-    for _ in range(10):
-        lib.eb_tp_allreduce(tp.h, planes.ptr, ks, n, out.ptr, None)
-    lib.eb_synchronize(None); barrier()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    st = torch.cuda.current_stream()
-    e0.record(st)
-    for _ in range(iters):
-        lib.eb_tp_allreduce(tp.h, planes.ptr, ks, n, out.ptr, C.c_void_p(st.cuda_stream))
-    e1.record(st); e1.synchronize()
-    us = max_over_ranks(e0.elapsed_time(e1) * 1e3 / iters)
+    res = {}
+    for form, eng in (("engine_sets", 1), ("operator_sets", 0)):
+        us = C.c_float()
+        barrier()
+        rc = lib.eb_tp_bench(tp.h, planes.ptr, ks, n, out.ptr, eng, iters, C.byref(us))
+        assert rc == 0, lib.eb_last_error().decode()
+        res[form] = max_over_ranks(float(us.value))
     if rank == 0:
-        print("TP_AR_JSON " + json.dumps({"tp": world, "elems": n, "planes": ks, "us_per_allreduce": us, "tp_error_word": tp.error()}), flush=True)
+        print("TP_AR_JSON " + json.dumps({"tp": world, "elems": n, "planes": ks, "us_per_allreduce": res["engine_sets"],
+                                          "us_per_allreduce_operator_sets": res["operator_sets"], "tp_error_word": tp.error()}), flush=True)
 
 
 def bench(shape, steps, warmup=5, quiet=False):
