@@ -202,7 +202,7 @@ int eb_event_record(void *ev, void *st) { EB_CUDA(cudaEventRecord((cudaEvent_t)e
 int eb_stream_wait_event(void *st, void *ev) { EB_CUDA(cudaStreamWaitEvent(S(st), (cudaEvent_t)ev, 0)); return EB_OK; }
 int eb_event_synchronize(void *ev) { EB_CUDA(cudaEventSynchronize((cudaEvent_t)ev)); return EB_OK; }
 
-int eb_top_k(const float *logits, int rows, int V, int k, int32_t *ids, float *vals, float *probs, void *st) { NEED_DEV(); return eb_top_k_impl(logits, rows, V, k, ids, vals, probs, S(st), 1, 0, rows <= 128 ? eb_top_k_default_scratch() : nullptr); }
+int eb_top_k(const float *logits, int rows, int V, int k, int32_t *ids, float *vals, float *probs, void *st) { NEED_DEV(); return eb_top_k_impl(logits, rows, V, k, ids, vals, probs, S(st), 1, 0, rows <= 128 ? eb_top_k_default_scratch(S(st)) : nullptr); }
 int eb_argmax(const float *logits, int rows, int V, int32_t *ids, void *st) { NEED_DEV(); return eb_argmax_impl(logits, rows, V, ids, S(st)); }
 
 

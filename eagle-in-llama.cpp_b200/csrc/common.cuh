@@ -131,7 +131,16 @@ int eb_mmq_parts(int type, const void *W, int64_t N, int64_t K, const ActQ &a, f
 int eb_fused_init();
 int eb_mmq_tc_init();                                                                  // mmq_tc.cu (tcgen05 path)
 int eb_mmq_tc_supported(int type, int64_t N, int64_t K, int T);
-int eb_mmq_tc_parts(int type, const void *W, int64_t N, int64_t K, const ActQ &a, float *planes, int *ks_out, cudaStream_t st);
+// Tensor-parallel hand-over fused into the GEMM (tp.cu, mmq_tc.cu, fused.cu): the epilogue of a K-split GEMM (wo, ffn_down) mirrors
+// its split-K planes, as 8-byte {value, call number} pairs, straight into every peer's memory while it writes them locally; the
+// consumer kernel (residual add + RMS norm + quantisation) adds the local planes and, rank by rank, the peers' planes as they arrive
+// (an element whose upper word is the current call number has arrived).  No all-reduce kernel, no flag, no fence: the transfer
+// overlaps the GEMM's tail.  seq = this rank's call counter of the slot set (last completed call).  Shards may differ in shape: each
+// pushing rank also writes {its split-K plane count, call number} into a header word behind its planes (EB_TP_HDR elements in).
+constexpr int EB_TP_MAX_PEERS = 7;
+struct TpPush { unsigned long long *peer[EB_TP_MAX_PEERS]; int n_peers; int64_t hdr; const unsigned *seq; };
+struct TpPull { const unsigned long long *src[EB_TP_MAX_PEERS]; int n_peers, my_pos; int64_t hdr, plane; unsigned *seq, *done, *err; };
+int eb_mmq_tc_parts(int type, const void *W, int64_t N, int64_t K, const ActQ &a, float *planes, int *ks_out, cudaStream_t st, const TpPush *push = nullptr);
 int eb_splitk_reduce(const float *partial, float *y, int64_t n, int ksplit, cudaStream_t st);
 int eb_mmq_supported(int type, int64_t N, int64_t K, int T);
 // mmq_small.cu: T <= 8 (draft head)

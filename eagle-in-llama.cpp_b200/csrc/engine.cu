@@ -371,12 +371,18 @@ static int forward_dev(const eb_model *m, KVCache &kv, Workspace &w, const int32
     }
     const bool use_tab = m->L > 1;                          // one layer: the rotation angles are computed where they are used
     if (use_tab) RC(eb_rope_table(pos, D, T, m->freq_base, w.rope_tab, st));
+    // tensor parallel, fused hand-over (common.cuh TpPush / TpPull): when both K-split GEMMs of a layer run on the tcgen05 kernel and all
+    // shards have one shape, their epilogues mirror the planes into the peers' memory and the consumer below adds them; otherwise a
+    // separate all-reduce kernel (tp.cu) sits between the GEMM and its consumer
+    TpPull pend_pull{}; bool have_pend_pull = false;
     for (int l = 0; l < m->L; l++) {
         const std::vector<DTensor> &t = m->layers[l];
         // x += pending; cur = rms_norm(x) * attn_norm -> activation grid of wq
         const int gq = grid_of(t[EB_L_WQ]);
         ActQ a = eb_actq_carve(w.actq, gq, E, T);
-        if (!skip_class("resid")) RC(eb_resid_norm_quant(w.x, pend, pend_ks, (const float *)t[EB_L_ATTN_NORM].data, m->eps, E, T, a, nullptr, st, pend_bias));
+        if (!skip_class("resid")) RC(eb_resid_norm_quant(w.x, pend, pend_ks, (const float *)t[EB_L_ATTN_NORM].data, m->eps, E, T, a, nullptr, st, pend_bias, nullptr, nullptr,
+                                                         have_pend_pull ? &pend_pull : nullptr));
+        have_pend_pull = false;
         pend_bias = nullptr;
         RC(tap_site(tap, a, st));
         if (grid_of(t[EB_L_WK]) != gq || grid_of(t[EB_L_WV]) != gq) return eb_set_err(EB_ERR_UNSUPPORTED, "layer %d: wq/wk/wv mix K-quant and 32-block formats", l);
@@ -401,16 +407,26 @@ static int forward_dev(const eb_model *m, KVCache &kv, Workspace &w, const int32
         if (!att_quantized) RC(eb_quantize_act(w.att, ao, st));
         RC(tap_site(tap, ao, st));
         int ko_;
-        RC(mm_parts(t[EB_L_WO], ao, w.po, &ko_, st));
         const float *po_planes = w.po;
-        // tensor parallel: wo is K-split over the ranks' heads; the partial [T][E] sums (this rank's split-K planes included) are
-        // summed over the group by one peer-memory kernel (tp.cu), every rank ends up with the same bits
-        if (tp) { RC(eb_tp_allreduce_planes(tp, w.po, ko_, (int64_t)T * E, tp_buf, st, 0)); po_planes = tp_buf; ko_ = 1; }      // slot set 0
+        TpPull pull_o{}; bool have_pull_o = false;
+        const bool fuse_tp = tp && !skip_class("gemm") && eb_tp_fused_ok(tp, 8, (int64_t)T * E) && eb_mmq_tc_supported(t[EB_L_WO].type, t[EB_L_WO].rows, t[EB_L_WO].cols, T) &&
+                             eb_mmq_tc_supported(t[EB_L_DOWN].type, t[EB_L_DOWN].rows, t[EB_L_DOWN].cols, T);
+        if (fuse_tp) {
+            const TpPush ph = eb_tp_push(tp, 0);
+            RC(eb_mmq_tc_parts(t[EB_L_WO].type, t[EB_L_WO].data, t[EB_L_WO].rows, t[EB_L_WO].cols, ao, w.po, &ko_, st, &ph));
+            pull_o = eb_tp_pull(tp, 0, (int64_t)T * E); have_pull_o = true;
+        } else {
+            RC(mm_parts(t[EB_L_WO], ao, w.po, &ko_, st));
+            // tensor parallel: wo is K-split over the ranks' heads; the partial [T][E] sums (this rank's split-K planes included) are
+            // summed over the group by one peer-memory kernel (tp.cu), every rank ends up with the same bits
+            if (tp) { RC(eb_tp_allreduce_planes(tp, w.po, ko_, (int64_t)T * E, tp_buf, st, 0)); po_planes = tp_buf; ko_ = 1; }      // slot set 0
+        }
         // ffn_inp = wo.att + x ; cur = rms_norm(ffn_inp) * ffn_norm -> grid of up/gate
         const int gu = grid_of(t[EB_L_UP]);
         if (grid_of(t[EB_L_GATE]) != gu) return eb_set_err(EB_ERR_UNSUPPORTED, "layer %d: ffn_up/ffn_gate mix formats", l);
         ActQ af = eb_actq_carve(w.actq, gu, E, T);
-        if (!skip_class("resid")) RC(eb_resid_norm_quant(w.x, po_planes, ko_, (const float *)t[EB_L_FFN_NORM].data, m->eps, E, T, af, nullptr, st));
+        if (!skip_class("resid")) RC(eb_resid_norm_quant(w.x, po_planes, ko_, (const float *)t[EB_L_FFN_NORM].data, m->eps, E, T, af, nullptr, st, nullptr, nullptr, nullptr,
+                                                         have_pull_o ? &pull_o : nullptr));
         RC(tap_site(tap, af, st));
         PlaneRef rg, ru;
         {
@@ -427,15 +443,21 @@ static int forward_dev(const eb_model *m, KVCache &kv, Workspace &w, const int32
         ActQ ad = eb_actq_carve(w.actq2, grid_of(t[EB_L_DOWN]), F, T);
         if (!skip_class("swiglu")) RC(eb_swiglu_quant(rg, ru, F, T, ad, st));
         RC(tap_site(tap, ad, st));
-        RC(mm_parts(t[EB_L_DOWN], ad, w.pq, &pend_ks, st));       // pq is free again: holds the down planes
-        pend = w.pq;
-        if (tp) { RC(eb_tp_allreduce_planes(tp, w.pq, pend_ks, (int64_t)T * E, tp_buf, st, 1)); pend = tp_buf; pend_ks = 1; }   // ffn_down is K-split too: slot set 1
+        pend = w.pq;                                              // pq is free again: holds the down planes
+        if (fuse_tp) {
+            const TpPush ph = eb_tp_push(tp, 1);
+            RC(eb_mmq_tc_parts(t[EB_L_DOWN].type, t[EB_L_DOWN].data, t[EB_L_DOWN].rows, t[EB_L_DOWN].cols, ad, w.pq, &pend_ks, st, &ph));
+            pend_pull = eb_tp_pull(tp, 1, (int64_t)T * E); have_pend_pull = true;
+        } else {
+            RC(mm_parts(t[EB_L_DOWN], ad, w.pq, &pend_ks, st));
+            if (tp) { RC(eb_tp_allreduce_planes(tp, w.pq, pend_ks, (int64_t)T * E, tp_buf, st, 1)); pend = tp_buf; pend_ks = 1; }   // ffn_down is K-split too: slot set 1
+        }
     }
     // x += pending; result_norm = rms_norm(x) * output_norm  (-> feat, and the lm_head's grid)
     const DTensor &o = m->g[EB_T_OUTPUT];
     ActQ al = eb_actq_carve(w.actq, grid_of(o), E, T);
     if (!want_logits) al.qs = nullptr;
-    RC(eb_resid_norm_quant(w.x, pend, pend_ks, (const float *)m->g[EB_T_OUTPUT_NORM].data, m->eps, E, T, al, w.feat, st, nullptr, spec, node_feat));
+    RC(eb_resid_norm_quant(w.x, pend, pend_ks, (const float *)m->g[EB_T_OUTPUT_NORM].data, m->eps, E, T, al, w.feat, st, nullptr, spec, node_feat, have_pend_pull ? &pend_pull : nullptr));
     RC(tap_site(tap, al, st));
     if (gate_lm) eb_gate_set(gate_lm);
     if (want_logits && logit_ks) {

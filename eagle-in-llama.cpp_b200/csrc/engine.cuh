@@ -37,6 +37,9 @@ struct Workspace {
 
 struct eb_tp;      // tp.cu: peer-memory communicator of a tensor-parallel group
 int eb_tp_allreduce_planes(eb_tp *tp, const float *planes, int ks, int64_t n, float *out, cudaStream_t st, int set);
+int eb_tp_fused_ok(const eb_tp *tp, int ks, int64_t n);
+TpPush eb_tp_push(const eb_tp *tp, int set);
+TpPull eb_tp_pull(const eb_tp *tp, int set, int64_t plane);
 
 struct ActTap { int8_t *buf = nullptr; size_t cap = 0, off = 0; int sites = 0; };
 
@@ -81,7 +84,7 @@ int eb_rope_kv_store_ctl(float *q, const float *k, const float *v, const int32_t
 int eb_flash_attn_ctl(const float *q, const void *k, const void *v, int64_t kv_stride, const uint32_t *tree_bits, const FwdCtl *ctl,
                       int T, int H, int D, int n_ctx, float scale, float *out, void *ws, cudaStream_t st);
 int eb_resid_norm_quant(float *x, const float *part, int ks, const float *w, float eps, int n, int T, const ActQ &aq, float *feat, cudaStream_t st, const float *bias = nullptr,
-                        const SpecState *spec = nullptr, float *node_feat = nullptr);
+                        const SpecState *spec = nullptr, float *node_feat = nullptr, const TpPull *pull = nullptr);
 struct PlaneRef { const float *p; int ks; int64_t ld; };   // split-K planes [ks][T][ld] of a (possibly fused) GEMM, first column of interest at p
 int eb_rope_table(const int32_t *pos, int D, int T, float freq_base, float *tab, cudaStream_t st);
 int eb_rope_kv_store_fused(PlaneRef qp, PlaneRef kp, PlaneRef vp, float *q, void *q16, const float *tab, void *kc, void *vc,

@@ -33,6 +33,42 @@ __device__ __forceinline__ float4 sum_parts(const Parts &s, int64_t off) {
     return a;
 }
 
+// tensor parallel (common.cuh TpPull): eight consecutive elements of the planes one peer pushed into this rank's memory, summed in
+// plane order; an element has arrived when its upper word is the call number (the spin gives up after ~2 s and raises the error word)
+__device__ __forceinline__ void pull_sum8(const unsigned long long *src, int64_t hdr, int64_t plane, int64_t off, unsigned call, unsigned *err, float4 &s0, float4 &s1) {
+    float v[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    int ks = 0;
+    {                                                   // the peer's plane count of this call
+        const long long t0 = clock64();
+        for (;;) {
+            unsigned long long h; asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(h) : "l"(src + hdr) : "memory");
+            if ((unsigned)(h >> 32) == call) { ks = (int)(unsigned)h; break; }
+            if (clock64() - t0 > 4000000000ll) { atomicExch(err, 1u); break; }
+        }
+    }
+    for (int k = 0; k < ks; k++) {
+        const unsigned long long *q = src + (int64_t)k * plane + off;
+        uint4 u[4];
+        long long t0 = 0; bool timing = false;
+        for (;;) {
+#pragma unroll
+            for (int i = 0; i < 4; i++) asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(u[i].x), "=r"(u[i].y), "=r"(u[i].z), "=r"(u[i].w) : "l"(q + 2 * i) : "memory");
+            bool ok = true;
+#pragma unroll
+            for (int i = 0; i < 4; i++) ok = ok && u[i].y == call && u[i].w == call;
+            if (ok) break;
+            if (!timing) { timing = true; t0 = clock64(); }
+            else if (clock64() - t0 > 4000000000ll) { atomicExch(err, 1u); break; }
+        }
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            const float a = __uint_as_float(u[i].x), b = __uint_as_float(u[i].z);
+            if (k == 0) { v[2 * i] = a; v[2 * i + 1] = b; } else { v[2 * i] += a; v[2 * i + 1] += b; }
+        }
+    }
+    s0 = make_float4(v[0], v[1], v[2], v[3]); s1 = make_float4(v[4], v[5], v[6], v[7]);
+}
+
 // one CTA (256 threads) per token row
 // bias != null: x = relu(sum_s part[s] + bias) instead of x += sum_s part[s]  (the EAGLE head's fc + bias + ReLU, R/src/llama.cpp:1886-1890)
 __global__ void __launch_bounds__(256) resid_norm_quant_kernel(float *__restrict__ x, Parts add, const float *__restrict__ w, float eps,
@@ -84,7 +120,7 @@ __global__ void __launch_bounds__(256) resid_norm_quant_kernel(float *__restrict
 template <int MAXT>
 __global__ void __launch_bounds__(MAXT) resid_norm_quant_regs_kernel(float *__restrict__ x, Parts add, const float *__restrict__ w, float eps,
                                                                     int n, ActQ a, float *__restrict__ feat, const float *__restrict__ bias,
-                                                                    const SpecState *__restrict__ spec, float *__restrict__ node_feat, const int *__restrict__ gate) {
+                                                                    const SpecState *__restrict__ spec, float *__restrict__ node_feat, const int *__restrict__ gate, TpPull pull) {
     __shared__ double red[32];
     pdl_trigger(); pdl_wait();
     if (gate_closed(gate)) return;
@@ -93,7 +129,22 @@ __global__ void __launch_bounds__(MAXT) resid_norm_quant_regs_kernel(float *__re
     float4 v0 = make_float4(0.f, 0.f, 0.f, 0.f), v1 = v0;
     if (!bias) { v0 = *(const float4 *)(x + off); v1 = *(const float4 *)(x + off + 4); }
     if (add.p) {
-        const float4 c0 = sum_parts(add, off), c1 = sum_parts(add, off + 4);
+        float4 c0 = sum_parts(add, off), c1 = sum_parts(add, off + 4);
+        if (pull.n_peers) {
+            // tensor parallel: this rank's planes (above) and every peer's, added IN RANK ORDER so that all ranks produce the same bits
+            const unsigned call = *(volatile const unsigned *)pull.seq + 1u;
+            float4 t0 = c0, t1 = c1;
+            for (int rr = 0; rr <= pull.n_peers; rr++) {
+                float4 s0 = c0, s1 = c1;
+                if (rr != pull.my_pos) pull_sum8(pull.src[rr < pull.my_pos ? rr : rr - 1], pull.hdr, pull.plane, off, call, pull.err, s0, s1);
+                if (rr == 0) { t0 = s0; t1 = s1; }
+                else { t0.x += s0.x; t0.y += s0.y; t0.z += s0.z; t0.w += s0.w; t1.x += s1.x; t1.y += s1.y; t1.z += s1.z; t1.w += s1.w; }
+            }
+            c0 = t0; c1 = t1;
+            // the last CTA to get here closes the call (the next GEMM on this slot set is a whole layer away)
+            __syncthreads();
+            if (tid == 0 && atomicAdd(pull.done, 1u) == gridDim.x - 1) { *pull.done = 0u; *(volatile unsigned *)pull.seq = call; }
+        }
         if (bias) {
             const float4 b0 = *(const float4 *)(bias + tid * 8), b1 = *(const float4 *)(bias + tid * 8 + 4);
             v0 = make_float4(fmaxf(__fadd_rn(c0.x, b0.x), 0.f), fmaxf(__fadd_rn(c0.y, b0.y), 0.f), fmaxf(__fadd_rn(c0.z, b0.z), 0.f), fmaxf(__fadd_rn(c0.w, b0.w), 0.f));
@@ -210,15 +261,17 @@ __global__ void __launch_bounds__(256) swiglu_quant_kernel(Parts gate, Parts up,
 
 // plain row quantisation of an f32 [T][K] tensor that is already final (attention output)
 int eb_resid_norm_quant(float *x, const float *part, int ks, const float *w, float eps, int n, int T, const ActQ &aq, float *feat, cudaStream_t st, const float *bias,
-                        const SpecState *spec, float *node_feat) {
+                        const SpecState *spec, float *node_feat, const TpPull *pull) {
+    TpPull pl{}; if (pull) pl = *pull;
     if (bias && !part) return eb_set_err(EB_ERR_ARG, "resid_norm_quant: bias without planes");
     if (n % 4 || n > 16384) return eb_set_err(EB_ERR_ARG, "resid_norm_quant: n=%d", n);
     if (T == 0) return EB_OK;
     Parts p{part, ks, (int64_t)T * n, n};
     if (n % 256 == 0 && n <= 8192 && (!aq.qs || (aq.kq && aq.K == n)))
-        if (n <= 4096) eb_launch_pdl_c(EB_PDL_RESID, resid_norm_quant_regs_kernel<512>, dim3(T), dim3(n / 8), 0, st, x, p, w, eps, n, aq, feat, bias, spec, node_feat, eb_gate());
-        else eb_launch_pdl_c(EB_PDL_RESID, resid_norm_quant_regs_kernel<1024>, dim3(T), dim3(n / 8), 0, st, x, p, w, eps, n, aq, feat, bias, spec, node_feat, eb_gate());
+        if (n <= 4096) eb_launch_pdl_c(EB_PDL_RESID, resid_norm_quant_regs_kernel<512>, dim3(T), dim3(n / 8), 0, st, x, p, w, eps, n, aq, feat, bias, spec, node_feat, eb_gate(), pl);
+        else eb_launch_pdl_c(EB_PDL_RESID, resid_norm_quant_regs_kernel<1024>, dim3(T), dim3(n / 8), 0, st, x, p, w, eps, n, aq, feat, bias, spec, node_feat, eb_gate(), pl);
     else {
+        if (pl.n_peers) return eb_set_err(EB_ERR_UNSUPPORTED, "resid_norm_quant: the tensor-parallel hand-over needs the register kernel");
         if (spec) return eb_set_err(EB_ERR_UNSUPPORTED, "resid_norm_quant: node-feature scatter needs the register kernel (n %% 256 == 0, n <= 8192, K-quant grid)");
         resid_norm_quant_kernel<<<T, 256, (size_t)n * 4, st>>>(x, p, w, eps, n, aq, feat, bias);
     }

@@ -60,6 +60,7 @@ struct TcArgs {
     uint32_t k_lo, k_hi, k_magic;    // 0x000f000f, 0x00f000f0, 0x64006400 passed as data: kept in registers so that (x & m) | c is ONE LOP3
     uint32_t k_q2;                   // 0x03000300
     const __half *w_d;               // Q6_K: per-block d plane [N][nbr]
+    TpPush tp;                       // tensor parallel: mirror the planes into the peers' memory (n_peers = 0: off)
 };
 
 // optional in-kernel profile (EB_TC_PROF=1): cycles each role of CTA 0 spends waiting on its barriers
@@ -392,7 +393,27 @@ __device__ __forceinline__ void epilogue_role(const TcArgs &p, uint8_t *smem, ui
                 }
             }
         }
+        // tensor parallel (common.cuh TpPush): the same values again, as {value, call number} pairs, into every peer's memory — posted
+        // NVLink stores; the peers' consumer kernels take an element as arrived when its upper word is the call number
+        if (p.tp.n_peers && grow < p.N) {
+            const unsigned long long tag = (unsigned long long)(*(volatile const unsigned *)p.tp.seq + 1u) << 32;
+            const int nc = min(40, p.T - c_base);
+            for (int j = 0; j < p.tp.n_peers; j++) {
+                unsigned long long *o = p.tp.peer[j] + ((int64_t)ks * p.T + c_base) * p.N + grow;
+                const int64_t ld = p.N;
+#pragma unroll
+                for (int c = 0; c < 20; c++) {
+                    if (2 * c < nc) asm volatile("st.volatile.global.u64 [%0], %1;" ::"l"(o), "l"(tag | (acc2[c] & 0xffffffffull)) : "memory");
+                    if (2 * c + 1 < nc) asm volatile("st.volatile.global.u64 [%0], %1;" ::"l"(o + ld), "l"(tag | (acc2[c] >> 32)) : "memory");
+                    o += 2 * ld;
+                }
+            }
+        }
         if (PROF && blockIdx.x == 0 && warp == 12 && lane == 0) p.prof[89] += clock64() - tst_;
+    }
+    if (p.tp.n_peers && blockIdx.x == 0 && warp == 12 && lane == 0) {       // header: how many planes this rank pushes in this call
+        const unsigned long long tag = (unsigned long long)(*(volatile const unsigned *)p.tp.seq + 1u) << 32;
+        for (int j = 0; j < p.tp.n_peers; j++) asm volatile("st.volatile.global.u64 [%0], %1;" ::"l"(p.tp.peer[j] + p.tp.hdr), "l"(tag | (unsigned)(p.n_items / p.n_rb)) : "memory");
     }
     if (PROF && blockIdx.x == 0 && warp == 12 && lane == 0) p.prof[64 + 7] = clock64();
     if (PROF && blockIdx.x == 0 && warp == 12 && lane == 0) { long long *o = p.prof + 32; o[0] = clock64() - pt0; o[1] = pw[0]; o[2] = pw[1]; o[3] = pw[2]; for (int k = 0; k < 9; k++) p.prof[80 + k] = sec[k]; }
@@ -638,7 +659,7 @@ static int tc_pick_ksplit(int64_t N, int nbr) {
 }
 
 // planes [ks][T][N] (unreduced split-K partials; ks returned)
-int eb_mmq_tc_parts(int type, const void *W, int64_t N, int64_t K, const ActQ &a, float *planes, int *ks_out, cudaStream_t st) {
+int eb_mmq_tc_parts(int type, const void *W, int64_t N, int64_t K, const ActQ &a, float *planes, int *ks_out, cudaStream_t st, const TpPush *push) {
     if (!eb_mmq_tc_supported(type, N, K, a.T)) return eb_set_err(EB_ERR_UNSUPPORTED, "mmq_tc: type %d N %lld K %lld T %d", type, (long long)N, (long long)K, a.T);
     if (!a.h16 || !a.dT || !a.bsum) return eb_set_err(EB_ERR_ARG, "mmq_tc: activations lack the f16 planes");
     const int nbr = (int)(K / 256);
@@ -646,6 +667,7 @@ int eb_mmq_tc_parts(int type, const void *W, int64_t N, int64_t K, const ActQ &a
     TcArgs p;
     p.dT = a.dT; p.out = planes; p.N = N; p.nbr = nbr; p.T = a.T; p.npad = (a.T + 15) / 16 * 16;
     p.k_lo = 0x000f000fu; p.k_hi = 0x00f000f0u; p.k_magic = 0x64006400u; p.k_q2 = 0x03000300u; p.w_d = nullptr;
+    if (push) p.tp = *push; else { p.tp = TpPush{}; }
     p.n_rb = (int)cdiv(N, 128); p.spp = (int)cdiv(nbr, ks); p.n_items = p.n_rb * ks;
     static const int early = getenv("EB_TC_LATE_TRIGGER") ? 0 : 1;
     p.early_trigger = early;

@@ -3,6 +3,8 @@
 // Nothing here returns to the host inside a round (the reference does a 32000-float D2H and a
 // host partial_sort per node: R/src/llama.cpp:9637, R/src/llama-sampling.cpp:228-302).
 #include "common.cuh"
+#include <map>
+#include <mutex>
 #include "spec.cuh"
 
 // ------------------------------------------------------------------ top-k / argmax
@@ -457,8 +459,21 @@ int eb_spec_round_end(SpecState *s, const float *tgt_feat, float *root_feat, int
     return EB_OK;
 }
 
-static void *g_topk_scr = nullptr;      // scratch of the operator-layer eb_top_k (sessions own theirs)
-void *eb_top_k_default_scratch() { return g_topk_scr; }
+// scratch of the operator-layer eb_top_k (sessions own theirs): one per stream, so that calls on different streams do not share the
+// slice lists and arrival counters (they used to: ADVICE round 1).  Created on first use, kept until the process exits.
+static void *g_topk_scr = nullptr;      // the NULL stream's
+static std::mutex g_topk_mu;
+static std::map<cudaStream_t, void *> g_topk_by_stream;
+void *eb_top_k_default_scratch(cudaStream_t st) {
+    if (!st) return g_topk_scr;
+    std::lock_guard<std::mutex> lk(g_topk_mu);
+    auto it = g_topk_by_stream.find(st);
+    if (it != g_topk_by_stream.end()) return it->second;
+    void *p = nullptr;
+    if (cudaMalloc(&p, eb_top_k_scratch_bytes(128)) != cudaSuccess || cudaMemset(p, 0, eb_top_k_scratch_bytes(128)) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    g_topk_by_stream[st] = p;
+    return p;
+}
 
 // ---- eb_top_k_noalloc: the 16-slice top-k with its scratch in a file-scope device array, for callers that cannot allocate
 // (CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc); no

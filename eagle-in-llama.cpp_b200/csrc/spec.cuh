@@ -34,5 +34,5 @@ int eb_spec_compact(SpecState *s, void *kc, void *vc, void *stage, int64_t layer
 int eb_spec_round_end(SpecState *s, const float *tgt_feat, float *root_feat, int E, eb_round_result *res, cudaStream_t st);
 int eb_top_k_impl(const float *logits, int rows, int V, int k, int32_t *ids, float *vals, float *probs, cudaStream_t st, int ks = 1, int64_t plane = 0, void *scratch = nullptr);
 size_t eb_top_k_scratch_bytes(int rows);
-void *eb_top_k_default_scratch();
+void *eb_top_k_default_scratch(cudaStream_t st);
 int eb_argmax_impl(const float *logits, int rows, int V, int32_t *ids, cudaStream_t st, int ks = 1, int64_t plane = 0);

@@ -130,21 +130,27 @@ struct eb_tp {
     uint4 *ll = nullptr; unsigned *seq = nullptr, *err = nullptr;
     TpPeers peers{}; void *opened[TP_MAX_RANKS] = {};
     unsigned op_calls = 0;                                  // operator-form calls (host side): slot sets 2 and 3 alternate
+    uint8_t *peer_base[TP_MAX_RANKS] = {};                  // fused hand-over (TpPush / TpPull): every rank's buffer
 };
 static size_t tp_data_bytes(int64_t cap, int size) { return (size_t)TP_SETS * size * cap * 8; }      // LL: 8 bytes per float (the flag form uses half)
 static size_t tp_flag_bytes() { return (size_t)TP_SETS * TP_MAX_RANKS * TP_CTAS * 4; }
+// fused hand-over: [2 sets][size - 1 source ranks][8 planes][cap] 8-byte elements, then 2 x (seq, done) words
+constexpr int TP_PLANES = 8;
+static size_t tp_push_region(int64_t cap) { return (size_t)TP_PLANES * cap * 8 + 256; }      // planes + the header word
+static size_t tp_push_bytes(int64_t cap, int size) { return (size_t)2 * (size - 1) * tp_push_region(cap); }
 
 // max_elems: largest [T][E] result that will be reduced (floats, a multiple of 4)
 extern "C" eb_tp *eb_tp_create(int rank, int size, int64_t max_elems) {
     if (size < 1 || size > TP_MAX_RANKS || rank < 0 || rank >= size || max_elems < 4 || (max_elems & 3)) { eb_set_err(EB_ERR_ARG, "tp_create: rank %d of %d, %lld elems", rank, size, (long long)max_elems); return nullptr; }
     eb_tp *t = new eb_tp(); t->rank = rank; t->size = size; t->cap = max_elems;
-    t->bytes = tp_data_bytes(max_elems, size) + tp_flag_bytes() + TP_CTAS * 4 + 256;
+    t->bytes = tp_data_bytes(max_elems, size) + tp_flag_bytes() + TP_CTAS * 4 + 256 + tp_push_bytes(max_elems, size) + 256;
     if (cudaMalloc((void **)&t->base, t->bytes) != cudaSuccess || cudaMemset(t->base, 0, t->bytes) != cudaSuccess || cudaDeviceSynchronize() != cudaSuccess) {
         eb_set_err(EB_ERR_OOM, "tp_create: %s", cudaGetErrorString(cudaGetLastError())); delete t; return nullptr;
     }
     t->ll = (uint4 *)t->base;
     t->seq = (unsigned *)(t->base + tp_data_bytes(max_elems, size) + tp_flag_bytes()); t->err = t->seq + TP_CTAS;
     t->peers.ll[rank] = t->ll; t->peers.flags[rank] = (unsigned *)(t->base + tp_data_bytes(max_elems, size));
+    t->peer_base[rank] = t->base;
     return t;
 }
 // 64-byte IPC handle of this rank's buffer (cudaIpcMemHandle_t), to be carried to the peers by the host program
@@ -160,6 +166,7 @@ extern "C" int eb_tp_open_peer(eb_tp *t, int peer_rank, const void *handle64) {
     EB_CUDA(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
     t->opened[peer_rank] = p;
     t->peers.ll[peer_rank] = (uint4 *)p; t->peers.flags[peer_rank] = (unsigned *)((uint8_t *)p + tp_data_bytes(t->cap, t->size));
+    t->peer_base[peer_rank] = (uint8_t *)p;
     return EB_OK;
 }
 extern "C" void eb_tp_free(eb_tp *t) {
@@ -219,4 +226,41 @@ extern "C" int eb_tp_bench(eb_tp *t, const float *d_planes, int ks, int64_t n, f
     if (g) cudaGraphDestroy(g);
     cudaEventDestroy(e0); cudaEventDestroy(e1); cudaStreamDestroy(st);
     return rc;
+}
+
+// ---- fused hand-over (see common.cuh TpPush / TpPull)
+static size_t tp_push_off(const eb_tp *t) { return tp_data_bytes(t->cap, t->size) + tp_flag_bytes() + TP_CTAS * 4 + 256; }
+static int src_index(int src_rank, int dst_rank) { return src_rank < dst_rank ? src_rank : src_rank - 1; }      // position of src among dst's peers
+// Off by default.  Measured on the 13B verify step (bench.py --config 4, same box, back to back): the hand-over fused into the GEMM
+// epilogue 4889 us vs 4823 us with the separate all-reduce kernel at 2 ranks, 6755 vs 4568 us at 4 ranks.  The 8-byte remote stores
+// (one per element per peer, 40-120 per lane per item) sit on the GEMM's critical path — its epilogue is already the role with the
+// least slack — while the all-reduce kernel moves the same data with 16-byte coalesced stores from 65 536 threads
+// that have nothing else to do; and either way every layer waits for the slowest rank twice.  EB_TP_FUSE=1 selects this path.
+int eb_tp_fused_ok(const eb_tp *t, int ks, int64_t n) {
+    static const int on = getenv("EB_TP_FUSE") ? 1 : 0;
+    return on && t->size > 1 && ks <= TP_PLANES && n <= t->cap;
+}
+// where this rank's GEMM epilogue mirrors its planes (set 0 = after wo, 1 = after ffn_down)
+TpPush eb_tp_push(const eb_tp *t, int set) {
+    TpPush p{}; p.n_peers = t->size - 1; p.hdr = (int64_t)TP_PLANES * t->cap;
+    unsigned *words = (unsigned *)(t->base + tp_push_off(t) + tp_push_bytes(t->cap, t->size));
+    p.seq = words + 2 * set;
+    int j = 0;
+    for (int q = 0; q < t->size; q++) {
+        if (q == t->rank) continue;
+        p.peer[j++] = (unsigned long long *)(t->peer_base[q] + tp_push_off(t) + ((size_t)set * (t->size - 1) + src_index(t->rank, q)) * tp_push_region(t->cap));
+    }
+    return p;
+}
+// where the peers' planes arrive in this rank's memory; ks = planes per rank, plane = elements between planes
+TpPull eb_tp_pull(const eb_tp *t, int set, int64_t plane) {
+    TpPull p{}; p.n_peers = t->size - 1; p.my_pos = t->rank; p.hdr = (int64_t)TP_PLANES * t->cap; p.plane = plane;
+    unsigned *words = (unsigned *)(t->base + tp_push_off(t) + tp_push_bytes(t->cap, t->size));
+    p.seq = words + 2 * set; p.done = words + 2 * set + 1; p.err = t->err;
+    int j = 0;
+    for (int r = 0; r < t->size; r++) {
+        if (r == t->rank) continue;
+        p.src[j++] = (const unsigned long long *)(t->base + tp_push_off(t) + ((size_t)set * (t->size - 1) + src_index(r, t->rank)) * tp_push_region(t->cap));
+    }
+    return p;
 }

@@ -165,8 +165,8 @@ EB_API int eb_flash_attn_bits(const float *d_q, const void *d_k, const void *d_v
 
 /* GGML_OP_ARGMAX / top-k (R/ggml/src/ggml-cuda/argmax.cu:8, argsort.cu:11; host sampler
  * R/src/llama-sampling.cpp:228-302): per row top-k by logit, ties to the lower id; probs =
- * softmax over the k kept logits. k <= 16.  eb_top_k uses one process-wide scratch list: calls on different streams
- * must not overlap in time (sessions own their scratch). */
+ * softmax over the k kept logits. k <= 16.  eb_top_k keeps one scratch list per stream (created on first use): calls on
+ * different streams may overlap, calls on one stream are ordered anyway (sessions own their scratch). */
 EB_API int eb_top_k(const float *d_logits, int rows, int V, int k, int32_t *d_ids, float *d_vals, float *d_probs, void *stream);
 EB_API int eb_argmax(const float *d_logits, int rows, int V, int32_t *d_ids, void *stream);
 /* eb_top_k without any allocation.  NO COUNTERPART IN THE REFERENCE: added for callers that

@@ -218,6 +218,31 @@ def test_flash_attn_bit_mask_form_vs_oracle(eb, T, n_kv, H):
     assert eb.flash_attn_ext_bits(q, k, v, 1 / np.sqrt(D), mask2) == (None, True)
 
 
+def test_top_k_on_two_streams_does_not_share_scratch(eb):
+    """eb_top_k keeps one scratch list per stream: calls issued back to back on two streams (they may overlap on the device) give the
+    answers of the same calls made alone"""
+    import ctypes as C
+    lib = eb.lib()
+    rng = np.random.default_rng(21)
+    xs = [rng.normal(0, 2, (16, 32000)).astype(np.float32) for _ in range(2)]
+    want = [eb.top_k(x, 10) for x in xs]
+    sts = [C.c_void_p(), C.c_void_p()]
+    for s_ in sts:
+        assert lib.eb_stream_create(C.byref(s_)) == 0
+    bufs = []
+    for x in xs:
+        bufs.append((eb.DeviceBuffer.from_host(x), eb.DeviceBuffer(16 * 10 * 4), eb.DeviceBuffer(16 * 10 * 4), eb.DeviceBuffer(16 * 10 * 4)))
+    for rep in range(20):
+        for (dl, di, dv, dp), s_ in zip(bufs, sts):
+            assert lib.eb_top_k(dl.ptr, 16, 32000, 10, di.ptr, dv.ptr, dp.ptr, s_) == 0
+    for s_ in sts:
+        assert lib.eb_synchronize(s_) == 0
+    for (dl, di, dv, dp), w in zip(bufs, want):
+        assert np.array_equal(di.to_host(np.int32, (16, 10)), w[0]) and np.array_equal(dv.to_host(np.float32, (16, 10)), w[1])
+    for s_ in sts:
+        assert lib.eb_stream_destroy(s_) == 0
+
+
 def test_mul_mat_shared_activation_and_rope_out_of_place(eb):
     """eb_mul_mat_ex: three weight matrices on ONE activation tensor (wq / wk / wv in a ggml graph) with the quantisation done once — bit-identical
     to three independent eb_mul_mat calls; eb_rope_norm_to out of place == eb_rope_norm in place, source untouched"""
