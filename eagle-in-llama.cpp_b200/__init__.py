@@ -109,6 +109,7 @@ def lib():
         "eb_session_synth_kv": ([vp, i32, C.c_uint64], i32), "eb_session_set_root": ([vp, C.c_int32, vp], i32),
         "eb_session_round": ([vp, C.POINTER(RoundResult)], i32),
         "eb_session_verify_only": ([vp, i32, C.POINTER(f32)], i32),
+        "eb_session_gen_draft": ([vp, vp, vp, i32, C.POINTER(i32)], i32),
         "eb_bench_mul_mat_kernel": ([i32, i64, i64, i32, i32, i32, C.POINTER(f32)], i32),
         "eb_bench_flash_attn": ([i32, i32, i32, i32, i32, i32, C.POINTER(f32)], i32),
         "eb_launch_count": ([i32], C.c_long),
@@ -629,6 +630,12 @@ class Session:
         r = RoundResult()
         _ck(lib().eb_session_round(self.h, C.byref(r)))
         return r
+
+    def gen_draft(self):
+        """the draft half alone (common_speculative_gen_draft): -> (tokens, parent) of the drafted tree, node 0 = the root"""
+        tok, par, n = np.zeros(128, np.int32), np.zeros(128, np.int32), C.c_int32()
+        _ck(lib().eb_session_gen_draft(self.h, _hp(tok), _hp(par), 128, C.byref(n)))
+        return tok[:n.value].copy(), par[:n.value].copy()
 
     def verify_only(self, T):
         ms = C.c_float()

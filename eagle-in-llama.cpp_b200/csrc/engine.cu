@@ -695,7 +695,9 @@ static int verify_dev(eb_session *s, int T, cudaStream_t st) {
     if (rc) return rc;
     return eb_argmax_impl(s->ws_t.partial, T, s->tgt->V, s->best, st, ks, (int64_t)T * s->tgt->V);
 }
-static int round_dev(eb_session *s, cudaStream_t st) {
+// the draft half of a round: head forwards + top-k + expansion, level by level (speculative-eagle.cpp:505-642; with one branch it is the
+// chain of common_speculative_gen_draft, R/common/speculative.cpp:137-299, p_min stop included)
+static int draft_dev(eb_session *s, cudaStream_t st) {
     SpecState *d = s->state; const SpecCfg &c = s->cfg; const int E = s->tgt->E, V = s->tgt->V;
     int rc;
 #define RC(x) do { rc = (x); if (rc) return rc; } while (0)
@@ -719,6 +721,14 @@ static int round_dev(eb_session *s, cudaStream_t st) {
         if (rc) return rc;
         RC(eb_spec_expand(d, c, s->cand_ids, s->cand_p, st));
     }
+#undef RC
+    return EB_OK;
+}
+static int round_dev(eb_session *s, cudaStream_t st) {
+    SpecState *d = s->state; const SpecCfg &c = s->cfg; const int E = s->tgt->E;
+    int rc;
+#define RC(x) do { rc = (x); if (rc) return rc; } while (0)
+    RC(draft_dev(s, st));
     RC(verify_dev(s, c.max_nodes, st));
     RC(eb_spec_accept(d, c, s->best, st));
     RC(eb_spec_compact(d, s->kv_t.k, s->kv_t.v, s->stage, s->kv_t.layer_stride, E, s->tgt->L, s->max_acc, st));
@@ -764,6 +774,26 @@ extern "C" int eb_session_round(eb_session *s, eb_round_result *h_out) {
     s->h_res->gpu_ms = ms;
     s->n_past_h += s->h_res->n_accept;                          // round_end commits the accepted path: n_past += n_accept
     if (h_out) *h_out = *s->h_res;
+    return EB_OK;
+}
+
+// Draft only: what common_speculative_gen_draft returns to its caller (R/common/speculative.cpp:137-299: the drafted tokens) — here the
+// whole drafted tree of the session's configuration (one branch = the reference's chain, p_min included), node 0 = the root / id_last.
+// Nothing is committed: a following eb_session_round() drafts again from the same state.
+extern "C" int eb_session_gen_draft(eb_session *s, int32_t *h_tokens, int32_t *h_parent, int cap, int *n_nodes) {
+    if (!s->head) return eb_set_err(EB_ERR_ARG, "gen_draft: session has no draft head");
+    int rc = check_model(s->head); if (rc) return rc;
+    const int n_past = eb_session_n_past(s, 0);
+    if (n_past + s->p.max_nodes + s->p.n_branch > s->p.n_ctx) return eb_set_err(EB_ERR_ARG, "gen_draft: KV cache full (n_past=%d)", n_past);
+    rc = draft_dev(s, s->st); if (rc) return rc;
+    int n = 0;
+    EB_CUDA(cudaMemcpyAsync(&n, &s->state->n_nodes, 4, cudaMemcpyDeviceToHost, s->st));
+    EB_CUDA(cudaStreamSynchronize(s->st));
+    if (n < 1 || n > 128) return eb_set_err(EB_ERR_CUDA, "gen_draft: tree of %d nodes", n);
+    if (n > cap) return eb_set_err(EB_ERR_ARG, "gen_draft: %d nodes, room for %d", n, cap);
+    if (h_tokens) EB_CUDA(cudaMemcpy(h_tokens, s->state->tokens, (size_t)n * 4, cudaMemcpyDeviceToHost));
+    if (h_parent) EB_CUDA(cudaMemcpy(h_parent, s->state->parent, (size_t)n * 4, cudaMemcpyDeviceToHost));
+    if (n_nodes) *n_nodes = n;
     return EB_OK;
 }
 

@@ -307,6 +307,11 @@ typedef struct {
  * hand-off.  Only h_out crosses the bus (one small D2H). */
 EB_API int eb_session_round(eb_session *s, eb_round_result *h_out);
 /* verify forward alone on the current tree (micro-bench: device time in *gpu_ms) */
+/* The draft half alone: what common_speculative_gen_draft hands to its caller (R/common/speculative.cpp:137-299).  Runs the head
+ * forwards, top-k and expansion of the session's configuration from the current root and returns the drafted tree (node 0 = the root
+ * token id_last, h_parent[0] = -1); with n_branch = 1 this is the reference's chain draft, p_min stop included.  Nothing is
+ * committed; a following eb_session_round() drafts again from the same state. */
+EB_API int eb_session_gen_draft(eb_session *s, int32_t *h_tokens, int32_t *h_parent, int cap, int *n_nodes);
 EB_API int eb_session_verify_only(eb_session *s, int T, float *gpu_ms);
 /* micro-bench of one hot kernel class (GEMM for T > 8, matvec for T <= 8): average device ms per
  * launch over `iters` launches cycling through n_bufs distinct weight buffers (HBM-resident,

@@ -238,6 +238,42 @@ def test_spec_round_p_min_stops_branches(eb):
     assert sizes[(4, 0.9999)] < sizes[(4, 0.0)] and sizes[(1, 0.9999)] < sizes[(1, 0.0)]
 
 
+def test_gen_draft_chain_is_the_reference_chain_drafter(eb):
+    """eb_session_gen_draft with ONE branch = common_speculative_gen_draft (R/common/speculative.cpp:137-299): top-k 10, take the best, stop
+    below p_min or at n_draft; the drafted chain equals the oracle composition's, nothing is committed, and the round that follows drafts
+    the same chain again and verifies it"""
+    hp = dict(E=256, H=2, F=512, V=1024, L=2)
+    tgt = fx.make_model(**hp, ftype="q4_k_m", seed=41)
+    head = fx.make_model(**{**hp, "L": 1}, ftype="q4_k_m", seed=42, is_eagle=True)
+    mt = fx.to_gpu_model(eb, tgt); mh = fx.to_gpu_model(eb, head, target=mt)
+    po.set_fattn_acc_f32(1)
+    ok = 0
+    for seed, p_min in ((1, 0.0), (2, 0.0), (3, 0.05), (4, 0.05)):
+        cfg = dict(n_branch=1, n_draft=8, max_depth=8, top_k=10, p_split=0.1, max_nodes=9, p_min=p_min)
+        cpu = CpuStream(po.oracle(), tgt, head, 128)
+        s = eb.Session(mt, mh, n_ctx=128, use_graph=False, **cfg)
+        prompt = np.random.default_rng(seed).integers(3, hp["V"], 12).astype(np.int32)
+        cpu.prefill(prompt)
+        lg, ft = s.forward(0, prompt, np.arange(12))
+        hid = np.zeros((12, hp["E"]), np.float32); hid[1:] = ft[:-1]
+        s.forward(1, prompt, np.arange(12), hidden=hid); s.commit(0, 12); s.set_root(cpu.root_token, ft[-1])
+        n_past0 = s.n_past()
+        tok, par = s.gen_draft()
+        assert s.n_past() == n_past0 and tok[0] == cpu.root_token and par[0] == -1
+        assert np.array_equal(par[1:], np.arange(len(tok) - 1)), par            # a chain
+        want = cpu.round(**cfg)
+        same = len(tok) == len(want["tokens"]) and np.array_equal(tok, want["tokens"])
+        if not same:                                                            # only a near-tie in a candidate list may explain it
+            assert pa.round_margin(want, cfg["p_split"]) <= pa.NORTH_STAR_REL, (seed, tok.tolist(), want["tokens"].tolist())
+        else:
+            ok += 1
+            got = s.round()                                                     # drafts the same chain again, then verifies it
+            assert list(got.tokens[:got.n_nodes]) == tok.tolist()
+        s.free()
+    po.set_fattn_acc_f32(0)
+    assert ok >= 2
+
+
 def test_fixed_accept_round_properties(eb):
     """bench mode: accept exactly `a` draft nodes per round; n_past advances by a+1, trees stay
     well-formed, and re-running from the same state is deterministic."""
