@@ -60,22 +60,34 @@ static void b200_buf_memset_tensor(ggml_backend_buffer_t, ggml_tensor *t, uint8_
     B200_OK(eb_memset((char *)t->data + off, v, size, nullptr)); B200_OK(eb_synchronize(nullptr));
 }
 // host -> device, blocking (ggml_backend_cuda_buffer_set_tensor, ggml-cuda.cu:571)
+// GGUF-layout staging area of the plane-layout types: one grow-only device allocation for the process (a model load is ~100
+// set_tensor calls of such tensors; a cudaMalloc / cudaFree pair per call synchronises the device twice each time)
+static std::mutex g_stage_mu;
+static void *g_stage = nullptr; static size_t g_stage_size = 0;
+static void *b200_stage(size_t need) {
+    if (need > g_stage_size) { if (g_stage) eb_free(g_stage); g_stage = nullptr; g_stage_size = 0; if (eb_malloc(&g_stage, need) != EB_OK) return nullptr; g_stage_size = need; }
+    return g_stage;
+}
 static void b200_buf_set_tensor(ggml_backend_buffer_t, ggml_tensor *t, const void *data, size_t off, size_t size) {
     B200_OK(eb_device_synchronize());
     if (!b200_repacked(t->type)) { B200_OK(eb_upload((char *)t->data + off, data, size, nullptr)); return; }
     const size_t total = ggml_nbytes(t);
-    void *stage = nullptr; B200_OK(eb_malloc(&stage, total));
+    std::lock_guard<std::mutex> lk(g_stage_mu);
+    void *stage = b200_stage(total);
+    if (!stage) { b200_log_err("set_tensor: staging"); GGML_ABORT("ggml-b200: out of device memory"); }
     if (off != 0 || size != total) B200_OK(eb_unpack((int)t->type, t->data, stage, ggml_nelements(t), nullptr));   // read-modify-write
     B200_OK(eb_upload((char *)stage + off, data, size, nullptr));
     B200_OK(eb_repack((int)t->type, stage, t->data, ggml_nelements(t), nullptr));
-    B200_OK(eb_synchronize(nullptr)); B200_OK(eb_free(stage));
+    B200_OK(eb_synchronize(nullptr));
 }
 static void b200_buf_get_tensor(ggml_backend_buffer_t, const ggml_tensor *t, void *data, size_t off, size_t size) {
     B200_OK(eb_device_synchronize());
     if (!b200_repacked(t->type)) { B200_OK(eb_download(data, (const char *)t->data + off, size, nullptr)); return; }
-    void *stage = nullptr; B200_OK(eb_malloc(&stage, ggml_nbytes(t)));
+    std::lock_guard<std::mutex> lk(g_stage_mu);
+    void *stage = b200_stage(ggml_nbytes(t));
+    if (!stage) { b200_log_err("get_tensor: staging"); GGML_ABORT("ggml-b200: out of device memory"); }
     B200_OK(eb_unpack((int)t->type, t->data, stage, ggml_nelements(t), nullptr));
-    B200_OK(eb_download(data, (const char *)stage + off, size, nullptr)); B200_OK(eb_free(stage));
+    B200_OK(eb_download(data, (const char *)stage + off, size, nullptr));
 }
 static ggml_backend_buffer_type_t b200_buffer_type();
 static bool b200_buf_cpy_tensor(ggml_backend_buffer_t, const ggml_tensor *src, ggml_tensor *dst) {
