@@ -82,7 +82,7 @@ def lib():
         "eb_upload_async": ([vp, vp, sz, vp], i32), "eb_download_async": ([vp, vp, sz, vp], i32),
         "eb_event_create": ([C.POINTER(vp)], i32), "eb_event_destroy": ([vp], i32), "eb_event_record": ([vp, vp], i32),
         "eb_stream_wait_event": ([vp, vp], i32), "eb_event_synchronize": ([vp], i32),
-        "eb_top_k": ([vp, i32, i32, i32, vp, vp, vp, vp], i32), "eb_argmax": ([vp, i32, i32, vp, vp], i32),
+        "eb_top_k": ([vp, i32, i32, i32, vp, vp, vp, vp], i32), "eb_argmax": ([vp, i32, i32, vp, vp], i32), "eb_argsort": ([vp, i32, i32, i32, vp, vp], i32),
         "eb_top_k_noalloc": ([vp, i32, i32, i32, vp, vp, vp, vp], i32),
         "eb_model_create": ([i32, i32, i32, i32, i32, f32, f32, i32], vp), "eb_model_free": ([vp], None),
         "eb_model_set_tensor": ([vp, i32, i32, i32, vp], i32),

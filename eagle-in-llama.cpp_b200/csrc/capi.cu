@@ -203,6 +203,7 @@ int eb_stream_wait_event(void *st, void *ev) { EB_CUDA(cudaStreamWaitEvent(S(st)
 int eb_event_synchronize(void *ev) { EB_CUDA(cudaEventSynchronize((cudaEvent_t)ev)); return EB_OK; }
 
 int eb_top_k(const float *logits, int rows, int V, int k, int32_t *ids, float *vals, float *probs, void *st) { NEED_DEV(); return eb_top_k_impl(logits, rows, V, k, ids, vals, probs, S(st), 1, 0, rows <= 128 ? eb_top_k_default_scratch(S(st)) : nullptr); }
+int eb_argsort(const float *x, int rows, int n, int descending, int32_t *ids, void *st) { NEED_DEV(); return eb_argsort_impl(x, rows, n, descending, ids, S(st)); }
 int eb_argmax(const float *logits, int rows, int V, int32_t *ids, void *st) { NEED_DEV(); return eb_argmax_impl(logits, rows, V, ids, S(st)); }
 
 

@@ -244,6 +244,44 @@ __global__ void __launch_bounds__(1024) argmax_kernel(const float *__restrict__ 
         if (lane == 0) ids[r] = bi == 0x7fffffff ? 0 : bi;
     }
 }
+// GGML_OP_ARGSORT (ggml_argsort / ggml_top_k, R/ggml/include/ggml.h:1761-1776; CUDA: R/ggml/src/ggml-cuda/argsort.cu): per row the
+// indices that sort the row, ascending or descending.  One CTA per row, bitonic network over the next power of two (<= 1024) in shared
+// memory; padding sorts last; equal values keep index order (the comparison falls back to the index), so the result is deterministic.
+__global__ void argsort_kernel(const float *__restrict__ x, int n, int n_pad, int desc, int32_t *__restrict__ ids) {
+    extern __shared__ int32_t idx[];
+    const float *row = x + (int64_t)blockIdx.x * n;
+    const int t = threadIdx.x;
+    idx[t] = t;
+    __syncthreads();
+    // a sorts before b ?
+    auto before = [&](int a, int b) {
+        if (a >= n) return false;
+        if (b >= n) return true;
+        const float va = row[a], vb = row[b];
+        if (va != vb) return desc ? va > vb : va < vb;
+        return a < b;
+    };
+    for (int k = 2; k <= n_pad; k <<= 1) {
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            const int p = t ^ j;
+            if (p > t) {
+                const int a = idx[t], b = idx[p];
+                const bool up = (t & k) == 0;                 // this pair sorts "forward"
+                if (up ? before(b, a) : before(a, b)) { idx[t] = b; idx[p] = a; }
+            }
+            __syncthreads();
+        }
+    }
+    if (t < n) ids[(int64_t)blockIdx.x * n + t] = idx[t];
+}
+int eb_argsort_impl(const float *x, int rows, int n, int descending, int32_t *ids, cudaStream_t st) {
+    if (rows == 0) return EB_OK;
+    if (n < 1 || n > 1024) return eb_set_err(EB_ERR_UNSUPPORTED, "argsort: row length %d (1..1024)", n);
+    int n_pad = 1; while (n_pad < n) n_pad <<= 1;
+    argsort_kernel<<<rows, n_pad, (size_t)n_pad * 4, st>>>(x, n, n_pad, descending, ids);
+    EB_CHECK_LAUNCH();
+    return EB_OK;
+}
 int eb_argmax_impl(const float *logits, int rows, int V, int32_t *ids, cudaStream_t st, int ks, int64_t plane) {
     if (rows == 0) return EB_OK;
     argmax_kernel<<<rows, 1024, 0, st>>>(logits, ks, plane, V, ids);

@@ -35,4 +35,5 @@ int eb_spec_round_end(SpecState *s, const float *tgt_feat, float *root_feat, int
 int eb_top_k_impl(const float *logits, int rows, int V, int k, int32_t *ids, float *vals, float *probs, cudaStream_t st, int ks = 1, int64_t plane = 0, void *scratch = nullptr);
 size_t eb_top_k_scratch_bytes(int rows);
 void *eb_top_k_default_scratch(cudaStream_t st);
+int eb_argsort_impl(const float *x, int rows, int n, int descending, int32_t *ids, cudaStream_t st);
 int eb_argmax_impl(const float *logits, int rows, int V, int32_t *ids, cudaStream_t st, int ks = 1, int64_t plane = 0);

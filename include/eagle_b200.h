@@ -169,6 +169,9 @@ EB_API int eb_flash_attn_bits(const float *d_q, const void *d_k, const void *d_v
  * different streams may overlap, calls on one stream are ordered anyway (sessions own their scratch). */
 EB_API int eb_top_k(const float *d_logits, int rows, int V, int k, int32_t *d_ids, float *d_vals, float *d_probs, void *stream);
 EB_API int eb_argmax(const float *d_logits, int rows, int V, int32_t *d_ids, void *stream);
+/* GGML_OP_ARGSORT (ggml_argsort, and ggml_top_k = its first k columns; R/ggml/src/ggml-cuda/argsort.cu:11): per row of n <= 1024 values
+ * the indices in ascending (descending != 0: descending) order of value; equal values keep index order. */
+EB_API int eb_argsort(const float *d_x, int rows, int n, int descending, int32_t *d_ids, void *stream);
 /* eb_top_k without any allocation.  NO COUNTERPART IN THE REFERENCE: added for callers that
  * cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same results as
  * eb_top_k (the 16-slice kernel); its scratch is a file-scope `static __device__` array of EB_TOP_K_NOALLOC_MAX_ROWS rows

@@ -25,7 +25,7 @@ from golden_io import nmse
 pytestmark = pytest.mark.gpu
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 PLUGIN = os.path.join(ROOT, "eagle-in-llama.cpp_b200", "ggml_backend", "libggml-b200.so")
-OPS = ["MUL_MAT", "FLASH_ATTN_EXT", "RMS_NORM", "ROPE", "GET_ROWS", "CONCAT", "CPY", "CONT", "DUP", "SOFT_MAX", "ARGMAX", "ADD", "MUL", "SILU", "RELU"]
+OPS = ["MUL_MAT", "FLASH_ATTN_EXT", "RMS_NORM", "ROPE", "GET_ROWS", "CONCAT", "CPY", "CONT", "DUP", "SOFT_MAX", "ARGMAX", "ARGSORT", "ADD", "MUL", "SILU", "RELU"]
 
 
 def _need_ref():
@@ -48,7 +48,7 @@ def test_backend_ops_reference_harness(eb, op):
     print(f"[dropin] test-backend-ops {op}: {m.group(0) if m else 'no summary'}; ran on plug-in {ran}, not supported {unsupported}")
     assert r.returncode == 0 and m and m.group(1) == m.group(2), "\n".join(fails[:20]) + "\n" + clean[-1500:]
     assert "Backend B200: OK" in clean
-    if op in ("MUL_MAT", "FLASH_ATTN_EXT", "RMS_NORM", "ROPE", "GET_ROWS", "CPY", "SOFT_MAX", "ADD", "MUL"):
+    if op in ("MUL_MAT", "FLASH_ATTN_EXT", "RMS_NORM", "ROPE", "GET_ROWS", "CPY", "SOFT_MAX", "ADD", "MUL", "ARGSORT"):
         assert ran > 0, f"no {op} case ran on the plug-in:\n{clean[-1500:]}"
 
 

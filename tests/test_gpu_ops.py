@@ -218,6 +218,22 @@ def test_flash_attn_bit_mask_form_vs_oracle(eb, T, n_kv, H):
     assert eb.flash_attn_ext_bits(q, k, v, 1 / np.sqrt(D), mask2) == (None, True)
 
 
+@pytest.mark.parametrize("n", [1, 8, 60, 1000, 1024])
+def test_argsort_vs_numpy(eb, n):
+    """GGML_OP_ARGSORT: ascending and descending, ties keep index order (a stable sort of the row, like numpy's with kind='stable')"""
+    lib = eb.lib()
+    rng = np.random.default_rng(n)
+    x = rng.integers(-20, 20, (7, n)).astype(np.float32)              # plenty of ties
+    dx, di = eb.DeviceBuffer.from_host(x), eb.DeviceBuffer(x.size * 4)
+    for desc in (0, 1):
+        assert lib.eb_argsort(dx.ptr, 7, n, desc, di.ptr, None) == 0, lib.eb_last_error().decode()
+        assert lib.eb_synchronize(None) == 0
+        got = di.to_host(np.int32, (7, n))
+        want = np.argsort(-x if desc else x, axis=1, kind="stable")
+        assert np.array_equal(got, want)
+    assert lib.eb_argsort(dx.ptr, 1, 2000, 0, di.ptr, None) != 0       # beyond one CTA's network: refused, not mis-sorted
+
+
 def test_top_k_on_two_streams_does_not_share_scratch(eb):
     """eb_top_k keeps one scratch list per stream: calls issued back to back on two streams (they may overlap on the device) give the
     answers of the same calls made alone"""
