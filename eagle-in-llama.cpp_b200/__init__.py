@@ -70,7 +70,7 @@ def lib():
         "eb_rope_norm": ([vp, vp, i32, i32, i32, f32, vp], i32),
         "eb_get_rows_n": ([i32, vp, i64, i64, vp, i32, vp, vp], i32),
         "eb_add": ([vp, vp, vp, i64, i64, vp], i32), "eb_mul": ([vp, vp, vp, i64, i64, vp], i32),
-        "eb_silu": ([vp, vp, i64, vp], i32), "eb_relu": ([vp, vp, i64, vp], i32),
+        "eb_silu": ([vp, vp, i64, vp], i32), "eb_scale": ([vp, vp, i64, f32, vp], i32), "eb_relu": ([vp, vp, i64, vp], i32),
         "eb_cpy_f32_f16": ([vp, vp, i64, vp], i32),
         "eb_flash_attn_ws_size": ([i32, i32, i32, i32], sz),
         "eb_flash_attn": ([vp, vp, vp, i64, vp, i64, vp, i32, i32, i32, i32, i32, f32, vp, vp, vp], i32),

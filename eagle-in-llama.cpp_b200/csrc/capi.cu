@@ -134,6 +134,7 @@ int eb_rope_norm_to(const float *src, float *dst, const int32_t *pos, int D, int
 int eb_get_rows_n(int type, const void *W, int64_t n_rows, int64_t K, const int32_t *ids, int n, float *out, void *st) { NEED_DEV(); return eb_get_rows_dev(type, W, n_rows, K, ids, n, out, S(st)); }
 int eb_add(const float *a, const float *b, float *y, int64_t n, int64_t nb, void *st) { NEED_DEV(); return eb_add_impl(a, b, y, n, nb, S(st)); }
 int eb_mul(const float *a, const float *b, float *y, int64_t n, int64_t nb, void *st) { NEED_DEV(); return eb_mul_impl(a, b, y, n, nb, S(st)); }
+int eb_scale(const float *x, float *y, int64_t n, float s, void *st) { NEED_DEV(); return eb_scale_impl(x, y, n, s, S(st)); }
 int eb_silu(const float *x, float *y, int64_t n, void *st) { NEED_DEV(); return eb_silu_impl(x, y, n, S(st)); }
 int eb_relu(const float *x, float *y, int64_t n, void *st) { NEED_DEV(); return eb_relu_impl(x, y, n, S(st)); }
 int eb_copy_strided(int src_type, int dst_type, const void *src, void *dst, const int64_t *ne, const int64_t *nb_src, const int64_t *dne, const int64_t *nb_dst, void *st) {

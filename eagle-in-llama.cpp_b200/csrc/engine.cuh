@@ -65,6 +65,7 @@ int eb_rope_norm_impl(const float *src, float *dst, const int32_t *pos, int D, i
 int eb_add_impl(const float *a, const float *b, float *y, int64_t n, int64_t nb, cudaStream_t st);
 int eb_mul_impl(const float *a, const float *b, float *y, int64_t n, int64_t nb, cudaStream_t st);
 int eb_silu_impl(const float *x, float *y, int64_t n, cudaStream_t st);
+int eb_scale_impl(const float *x, float *y, int64_t n, float s, cudaStream_t st);
 int eb_relu_impl(const float *x, float *y, int64_t n, cudaStream_t st);
 int eb_bias_relu_impl(const float *x, const float *b, float *y, int64_t n, int nb, cudaStream_t st);
 int eb_cpy_f32_f16_impl(const float *x, void *y, int64_t n, cudaStream_t st);

@@ -142,6 +142,10 @@ __global__ void silu_kernel(const float *x, float *y, int64_t n) {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) y[i] = silu_f(x[i]);
 }
+__global__ void scale_kernel(const float *x, float *y, int64_t n, float s) {      // GGML_OP_SCALE: ggml_vec_scale_f32, R/ggml/src/ggml-cpu/ggml-cpu.c
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) y[i] = __fmul_rn(x[i], s);
+}
 __global__ void relu_kernel(const float *x, float *y, int64_t n) {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) y[i] = x[i] > 0.f ? x[i] : 0.f;
@@ -176,6 +180,7 @@ __global__ void concat2_kernel(const float *__restrict__ a, const float *__restr
 int eb_add_impl(const float *a, const float *b, float *y, int64_t n, int64_t nb, cudaStream_t st) { EW_LAUNCH(add_kernel, n, a, b, y, n, nb); }
 int eb_mul_impl(const float *a, const float *b, float *y, int64_t n, int64_t nb, cudaStream_t st) { EW_LAUNCH(mul_kernel, n, a, b, y, n, nb); }
 int eb_silu_impl(const float *x, float *y, int64_t n, cudaStream_t st) { EW_LAUNCH(silu_kernel, n, x, y, n); }
+int eb_scale_impl(const float *x, float *y, int64_t n, float s, cudaStream_t st) { EW_LAUNCH(scale_kernel, n, x, y, n, s); }
 int eb_relu_impl(const float *x, float *y, int64_t n, cudaStream_t st) { EW_LAUNCH(relu_kernel, n, x, y, n); }
 int eb_bias_relu_impl(const float *x, const float *b, float *y, int64_t n, int nb, cudaStream_t st) { EW_LAUNCH(bias_relu_kernel, n, x, b, y, n, nb); }
 int eb_cpy_f32_f16_impl(const float *x, void *y, int64_t n, cudaStream_t st) { EW_LAUNCH(cpy_f32_f16_kernel, n, x, (__half *)y, n); }

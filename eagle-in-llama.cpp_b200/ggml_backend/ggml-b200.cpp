@@ -255,6 +255,7 @@ static bool b200_dev_supports_op(ggml_backend_dev_t, const ggml_tensor *op) {
     }
     case GGML_OP_ARGMAX: return a->type == GGML_TYPE_F32 && ggml_is_contiguous(a);
     case GGML_OP_ARGSORT: return a->type == GGML_TYPE_F32 && ggml_is_contiguous(a) && a->ne[0] <= 1024;     // ggml_top_k = argsort + view
+    case GGML_OP_SCALE: return a->type == GGML_TYPE_F32 && ggml_is_contiguous(a) && op->type == GGML_TYPE_F32;
     default: return false;
     }
 }
@@ -332,6 +333,7 @@ static int b200_compute_node(b200_backend_ctx *ctx, ggml_tensor *d) {
                                (float *)d->data, a->ne[0], ggml_nrows(a), a->ne[1], op_f32(d, 0), st);
     }
     case GGML_OP_ARGMAX: return eb_argmax((const float *)a->data, (int)ggml_nrows(a), (int)a->ne[0], (int32_t *)d->data, st);
+    case GGML_OP_SCALE: return eb_scale((const float *)a->data, (float *)d->data, ggml_nelements(d), op_f32(d, 0), st);
     case GGML_OP_ARGSORT: return eb_argsort((const float *)a->data, (int)ggml_nrows(a), (int)a->ne[0], ((const int32_t *)d->op_params)[0] == GGML_SORT_ORDER_DESC, (int32_t *)d->data, st);
     default: return EB_ERR_UNSUPPORTED;
     }

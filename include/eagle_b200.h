@@ -115,6 +115,8 @@ EB_API int eb_get_rows_n(int type, const void *d_W, int64_t n_rows, int64_t K, c
 EB_API int eb_add(const float *d_a, const float *d_b, float *d_y, int64_t n, int64_t nb, void *stream);
 EB_API int eb_mul(const float *d_a, const float *d_b, float *d_y, int64_t n, int64_t nb, void *stream);
 EB_API int eb_silu(const float *d_x, float *d_y, int64_t n, void *stream);
+/* GGML_OP_SCALE: y = x * s (R/ggml/src/ggml-cuda/scale.cu) */
+EB_API int eb_scale(const float *d_x, float *d_y, int64_t n, float s, void *stream);
 EB_API int eb_relu(const float *d_x, float *d_y, int64_t n, void *stream);
 /* GGML_OP_CONCAT along dim 0 of two f32 [E][T] tensors -> [2E][T] (build_eagle's [embd | hidden],
  * R/src/llama.cpp:1893; R/ggml/src/ggml-cuda/concat.cu:4) */

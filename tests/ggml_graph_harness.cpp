@@ -176,9 +176,9 @@ GH_API int gh_forward(int which, const GModel *m, uint16_t *kv_k, uint16_t *kv_v
         inpL = ggml_add(c, cur, ffn_inp);
     }
     b.res_norm = norm(c, inpL, out_norm, m->eps);
-    // use_sched: an op the plugin does not claim (SCALE) sits between the norm and the lm_head, so ggml_backend_sched has to cut the graph
+    // use_sched: an op the plugin does not claim (NEG, twice: exact identity, and not an in-place view like ggml_clamp) sits between the norm and the lm_head, so ggml_backend_sched has to cut the graph
     // into plugin | CPU | plugin splits and move tensors across the backends in both directions
-    if (use_sched) b.res_norm = ggml_scale(c, b.res_norm, 1.0f);
+    if (use_sched) b.res_norm = ggml_neg(c, ggml_neg(c, b.res_norm));
     ggml_set_output(b.res_norm);
     ggml_build_forward_expand(gf, b.res_norm);
     if (logits) { b.logits = ggml_mul_mat(c, output, b.res_norm); ggml_set_output(b.logits); ggml_build_forward_expand(gf, b.logits); }
@@ -218,12 +218,12 @@ GH_API int gh_forward(int which, const GModel *m, uint16_t *kv_k, uint16_t *kv_v
             const ggml_status st = ggml_backend_sched_graph_compute(sched, gf);
             if (st != GGML_STATUS_SUCCESS) { snprintf(g_err, sizeof g_err, "sched_graph_compute -> %s", ggml_status_to_string(st)); rc = -5; }
             if (n_splits_out) *n_splits_out = ggml_backend_sched_get_n_splits(sched);
-            // every MUL_MAT and the attention must have been placed on the plugin, the SCALE on the CPU
+            // every MUL_MAT and the attention must have been placed on the plugin, the NEGs on the CPU
             for (int i = 0; i < ggml_graph_n_nodes(gf) && !rc && which == 1; i++) {
                 ggml_tensor *nd = ggml_graph_node(gf, i);
                 const bool on_plugin = ggml_backend_sched_get_tensor_backend(sched, nd) == be;
                 if ((nd->op == GGML_OP_MUL_MAT || nd->op == GGML_OP_FLASH_ATTN_EXT) && !on_plugin) { snprintf(g_err, sizeof g_err, "node %d (%s) was not given to the plugin", i, ggml_op_name(nd->op)); rc = -6; }
-                if (nd->op == GGML_OP_SCALE && on_plugin) { snprintf(g_err, sizeof g_err, "SCALE was given to the plugin"); rc = -6; }
+                if (nd->op == GGML_OP_UNARY && ggml_get_unary_op(nd) == GGML_UNARY_OP_NEG && on_plugin) { snprintf(g_err, sizeof g_err, "NEG was given to the plugin"); rc = -6; }
             }
         }
     }

@@ -25,7 +25,7 @@ from golden_io import nmse
 pytestmark = pytest.mark.gpu
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 PLUGIN = os.path.join(ROOT, "eagle-in-llama.cpp_b200", "ggml_backend", "libggml-b200.so")
-OPS = ["MUL_MAT", "FLASH_ATTN_EXT", "RMS_NORM", "ROPE", "GET_ROWS", "CONCAT", "CPY", "CONT", "DUP", "SOFT_MAX", "ARGMAX", "ARGSORT", "ADD", "MUL", "SILU", "RELU"]
+OPS = ["MUL_MAT", "FLASH_ATTN_EXT", "RMS_NORM", "ROPE", "GET_ROWS", "CONCAT", "CPY", "CONT", "DUP", "SOFT_MAX", "ARGMAX", "ARGSORT", "ADD", "MUL", "SCALE", "SILU", "RELU"]
 
 
 def _need_ref():

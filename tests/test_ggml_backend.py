@@ -253,7 +253,7 @@ def test_plugin_graph_7b_width_layer(plugin):
 @pytest.mark.gpu
 @pytest.mark.parametrize("ftype,is_eagle", [("q4_k_m", False), (po.Q4_0, True)])
 def test_plugin_under_ggml_backend_sched(plugin, ftype, is_eagle):
-    """the way libllama drives a backend: ggml_backend_sched over {plugin, CPU} (R/ggml/src/ggml-backend.cpp:1353,1448).  A SCALE node
+    """the way libllama drives a backend: ggml_backend_sched over {plugin, CPU} (R/ggml/src/ggml-backend.cpp:1353,1448).  A pair of NEG nodes
     the plugin does not claim forces plugin | CPU | plugin splits, so tensors cross the backends in both directions; every
     MUL_MAT / FLASH_ATTN_EXT must have been assigned to the plugin (checked inside the harness)."""
     h = plugin
