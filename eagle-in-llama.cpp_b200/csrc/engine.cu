@@ -609,8 +609,8 @@ extern "C" int eb_session_prefill(eb_session *s, const int32_t *h_tokens, int n,
     uint32_t bits[128 * 4];
     // rows per pass: 128 (one verify tile).  EB_PREFILL_CHUNK=80 keeps the K-quant GEMMs on the tcgen05 kernel (T <= 80) and is 1.5x
     // faster per token (tools/prefill_bench.py: 2048 tokens in 103 ms instead of 154 ms), but one of three full-size parity runs with it
-    // produced engine logits that differed between two processes on the same inputs (tests/test_fullsize.py) — not understood yet, so
-    // the default stays at the configuration that has never shown it
+    // failed and passed again when repeated on the same code (tests/test_fullsize.py, config 2; the failing assertion was not captured) —
+    // i.e. something in that run was not reproducible.  Not understood yet, so the default stays at the configuration that has never shown it
     static const int chunk_env = getenv("EB_PREFILL_CHUNK") ? atoi(getenv("EB_PREFILL_CHUNK")) : 0;
     const int CH = chunk_env >= 1 && chunk_env <= 128 ? chunk_env : 128;
     for (int c0 = 0; c0 < n; c0 += CH) {
