@@ -57,6 +57,35 @@ def test_gguf_probe_rejects_what_it_cannot_load(tmp_path):
         eb.gguf_probe(str(tmp_path / "missing.gguf"))
 
 
+def test_gguf_probe_survives_truncation_and_corruption(tmp_path):
+    """every prefix of a valid file and a few hundred single-byte corruptions of its header must end in an error code or a clean answer,
+    never in a crash (the parser bounds every read: lengths, counts and offsets come from the file)"""
+    eb = load_package()
+    _, _, pt, _ = _files(tmp_path, True)
+    raw = open(pt, "rb").read()
+    hdr = raw.index(b"token_embd.weight") + 4096 if b"token_embd.weight" in raw else 8192
+    hdr = min(hdr, len(raw))
+    f = tmp_path / "cut.gguf"
+    outcomes = {"error": 0, "ok": 0}
+    for cut in list(range(0, 200, 7)) + list(range(200, hdr, 97)) + [len(raw) - 1]:
+        f.write_bytes(raw[:cut])
+        try:
+            eb.gguf_probe(str(f)); outcomes["ok"] += 1
+        except eb.EagleB200Error:
+            outcomes["error"] += 1
+    assert outcomes["error"] > 0 and outcomes["ok"] == 0                  # no prefix of the file is a whole file
+    rng = np.random.default_rng(0)
+    for _ in range(300):
+        b = bytearray(raw[:hdr + 64])
+        i = int(rng.integers(4, hdr)); b[i] = int(rng.integers(0, 256))
+        f.write_bytes(bytes(b) + raw[hdr + 64:])
+        try:
+            eb.gguf_probe(str(f)); outcomes["ok"] += 1
+        except eb.EagleB200Error:
+            outcomes["error"] += 1
+    assert outcomes["ok"] + outcomes["error"] >= 300
+
+
 @pytest.mark.gpu
 def test_load_gguf_bit_exact_and_same_forward(eb, tmp_path):
     tgt, head, pt, ph = _files(tmp_path, True)
