@@ -96,3 +96,22 @@ def test_reference_tree_driver_on_the_plugin_generates_the_cpu_text(eb, models):
     assert same >= 4, (g, c)
     if same < min(len(g), len(c)):
         print(f"[drivers] texts agree on the first {same} generated tokens, then diverge")
+
+
+@pytest.mark.gpu
+def test_reference_chain_driver_on_the_plugin(eb, models):
+    """the chain driver (llama_decode_initial / _eagle / _draft: the fork's own graph builders and hidden-state plumbing) with target and
+    head on the plug-in.  Its head input is not well defined in the fork itself, so only the target-decided text is compared"""
+    rc, out_cpu, err, st_cpu = _run("llama-speculative-eagle", models, patched=True)
+    assert rc == 0, err[-2000:]
+    rc, out_gpu, err, st_gpu = _run("llama-speculative-eagle", models, ("-ngl", "99", "-ngld", "99"), {"GGML_BACKEND_PATH": PLUGIN}, patched=True)
+    assert rc == 0, err[-3000:]
+    off = re.findall(r"offloaded (\d+)/(\d+) layers", err)
+    g, c = _generated(out_gpu), _generated(out_cpu)
+    print(f"[drivers] chain driver on the plug-in: offloaded {off}, {st_gpu}; generated {g} (ggml-cpu: {c})")
+    assert "B2000" in err and off and all(a == b for a, b in off), off
+    assert st_gpu["decoded"] >= 16 and st_gpu["n_drafted"] > 0
+    same = 0
+    while same < min(len(g), len(c)) and g[same] == c[same]:
+        same += 1
+    assert same >= 2, (g, c)
