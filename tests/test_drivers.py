@@ -115,3 +115,34 @@ def test_reference_chain_driver_on_the_plugin(eb, models):
     while same < min(len(g), len(c)) and g[same] == c[same]:
         same += 1
     assert same >= 2, (g, c)
+
+
+def _run_self_draft(models, extra=(), env_extra=None):
+    """the tree driver with the TARGET as its own draft model: every drafted token is the target's greedy token, so the accept walk takes
+    whole draft paths and the KV sequence operations of accepted branches run (seq_keep / seq_cp / seq_rm on target and draft caches)"""
+    return _run("llama-speculative-eagle-tree", (models[0], models[0]), ("-np", "4", *extra), env_extra)
+
+
+def test_reference_tree_driver_accepts_whole_drafts_on_ggml_cpu(models):
+    rc, out, err, st = _run_self_draft(models)
+    assert rc == 0, err[-2000:]
+    print(f"[drivers] tree driver, target as its own draft, ggml-cpu: {st}; generated {_generated(out)}")
+    assert st["n_drafted"] > 0 and st["n_accept"] == st["n_drafted"] and st["decoded"] >= 16
+
+
+@pytest.mark.gpu
+def test_reference_tree_driver_accepts_whole_drafts_on_the_plugin(eb, models):
+    rc, out_cpu, err, st_cpu = _run_self_draft(models)
+    assert rc == 0, err[-2000:]
+    rc, out_gpu, err, st_gpu = _run_self_draft(models, ("-ngl", "99", "-ngld", "99"), {"GGML_BACKEND_PATH": PLUGIN})
+    assert rc == 0, err[-3000:]
+    g, c = _generated(out_gpu), _generated(out_cpu)
+    print(f"[drivers] tree driver, target as its own draft, plug-in: {st_gpu}; generated {g} (ggml-cpu: {st_cpu}, {c})")
+    assert "B2000" in err and st_gpu["n_drafted"] > 0 and st_gpu["decoded"] >= 16
+    same = 0
+    while same < min(len(g), len(c)) and g[same] == c[same]:
+        same += 1
+    assert same >= 4, (g, c)
+    # draft and target are the same weights but different batch shapes (1 row vs tree rows): on either backend a near-tie may reject a draft,
+    # so the acceptance rate is high rather than exactly 100 %
+    assert st_gpu["n_accept"] >= 0.75 * st_gpu["n_drafted"], st_gpu
