@@ -63,32 +63,8 @@ class CpuStream:
                 node_feat[n] = ft[r]
             if d == max_depth or done:
                 break
-            new = []
-            skip = [False] * n_branch
-            for b in range(n_branch):
-                if not drafting[b] or skip[b]:
-                    continue
-                ids, vals, pr = po.top_k(lg[row[b]], top_k)
-                sa = [b]; checked = []
-                for f in range(1, min(8, top_k)):
-                    if n_seq < n_branch:
-                        checked.append(f)                 # a p_split comparison that was actually evaluated
-                    if n_seq < n_branch and pr[f] > p_split:
-                        nb = n_seq; n_seq += 1
-                        drafting[nb] = True; skip[nb] = True; last_node[nb] = last_node[b]; row[nb] = row[b]
-                        sa.append(nb)
-                    else:
-                        break
-                cand_log.append((ids.copy(), vals.copy(), len(sa), checked))
-                for i, br in enumerate(sa):
-                    if len(tokens) + len(new) >= max_nodes:
-                        drafting[br] = False
-                        continue
-                    new.append((int(ids[i]), last_node[br], br))
-                    if len(tokens) + len(new) > n_draft:
-                        drafting[br] = False
-                if p_min > 0 and pr[0] < p_min:               # R/common/speculative.cpp:283
-                    drafting[b] = False
+            new, n_seq = expand_level(drafting, last_node, row, n_seq, len(tokens), lambda b: po.top_k(lg[row[b]], top_k), n_branch, n_draft, top_k,
+                                      p_split, max_nodes, p_min, cand_log)
             first = len(tokens)
             for i, (tok, par, br) in enumerate(new):
                 tokens.append(tok); parent.append(par); depth.append(depth[par] + 1)
@@ -115,6 +91,43 @@ class CpuStream:
         self.root_feat = ft[path[-1]].copy()
         self.n_past += len(path); self.root_token = bonus
         return dict(tokens=np.array(tokens, np.int32), parent=par, path=path, bonus=bonus, logits=lg, cand=cand_log)
+
+
+def expand_level(drafting, last_node, row, n_seq, n_tokens, cands_of, n_branch, n_draft, top_k, p_split, max_nodes, p_min=0.0, cand_log=None):
+    """One level of the tree expansion (R/examples/speculative/speculative-eagle.cpp:527-600): every drafting branch looks at its candidate
+    list (ids, values, probabilities, best first: cands_of(b)), splits off a new branch for each further candidate above p_split while
+    branches are left, and every branch of the split takes one candidate as its next token.  Mutates drafting / last_node / row of the new
+    branches; -> ([(token, parent node, branch)] in batch order, n_seq).  max_nodes / p_min are this repo's additions (caps that do not bind
+    in the reference's configuration; R/common/speculative.cpp:283).  Pinned against the reference driver's own log in
+    tests/test_drivers.py::test_tree_expansion_replays_the_reference_drivers_log."""
+    new = []
+    skip = [False] * n_branch
+    for b in range(n_branch):
+        if not drafting[b] or skip[b]:
+            continue
+        ids, vals, pr = cands_of(b)
+        sa = [b]; checked = []
+        for f in range(1, min(8, top_k)):
+            if n_seq < n_branch:
+                checked.append(f)                 # a p_split comparison that was actually evaluated
+            if n_seq < n_branch and pr[f] > p_split:
+                nb = n_seq; n_seq += 1
+                drafting[nb] = True; skip[nb] = True; last_node[nb] = last_node[b]; row[nb] = row[b]
+                sa.append(nb)
+            else:
+                break
+        if cand_log is not None:
+            cand_log.append((np.array(ids).copy(), np.array(vals).copy(), len(sa), checked))
+        for i, br in enumerate(sa):
+            if n_tokens + len(new) >= max_nodes:
+                drafting[br] = False
+                continue
+            new.append((int(ids[i]), last_node[br], br))
+            if n_tokens + len(new) > n_draft:
+                drafting[br] = False
+        if p_min > 0 and pr[0] < p_min:               # R/common/speculative.cpp:283
+            drafting[b] = False
+    return new, n_seq
 
 
 def _compact_ref(stream, kv, path):

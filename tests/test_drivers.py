@@ -146,3 +146,88 @@ def test_reference_tree_driver_accepts_whole_drafts_on_the_plugin(eb, models):
     # draft and target are the same weights but different batch shapes (1 row vs tree rows): on either backend a near-tie may reject a draft,
     # so the acceptance rate is high rather than exactly 100 %
     assert st_gpu["n_accept"] >= 0.75 * st_gpu["n_drafted"], st_gpu
+
+
+def _parse_tree_log(err):
+    """-lv 5 log of the tree driver -> one dict per drafting round: cands[(seq, level)] = ([ids], [p]) as printed by
+    R/examples/speculative/speculative-eagle.cpp:543-546, splits = [(from, into)] (:556), drafts[seq] = [token ids] (:669)"""
+    rounds, cur = [], None
+    for line in err.splitlines():
+        if "keeping sequence" in line:
+            cur = dict(cands={}, splits=[], drafts={})
+            rounds.append(cur)
+            continue
+        if cur is None:
+            continue
+        m = re.search(r"- draft candidate\s+(\d+) for seq\s+(\d+), pos\s+(\d+):\s+(\d+) \(\s*([0-9.]+)\)", line)
+        if m:
+            k, s, lvl, tok, p = int(m.group(1)), int(m.group(2)), int(m.group(3)), int(m.group(4)), float(m.group(5))
+            ids, pr = cur["cands"].setdefault((s, lvl), ([], []))
+            assert k == len(ids)
+            ids.append(tok); pr.append(p)
+            continue
+        m = re.search(r"splitting seq\s+(\d+) into\s+(\d+)", line)
+        if m:
+            cur["splits"].append((int(m.group(1)), int(m.group(2))))
+            continue
+        m = re.match(r"draft (\d+): \[(.*)\]\s*$", line)
+        if m:
+            cur["drafts"][int(m.group(1))] = [int(t) for t in re.findall(r"':(\d+)(?=,| |$)", m.group(2))]
+    return [r for r in rounds if r["cands"]]
+
+
+@pytest.mark.parametrize("NB,n_draft,p_split", [(5, 8, 0.0305), (6, 8, 0.0325), (8, 8, 0.0315), (6, 16, 0.0305), (8, 24, 0.0325), (10, 16, 0.0265)])
+def test_tree_expansion_replays_the_reference_drivers_log(models, NB, n_draft, p_split):
+    """SURVEY row a13: the tree-expansion rule the GPU engine is checked against (tests/oracle_round.py::expand_level, the rule of
+    eb_session_round) is pinned here to the reference BINARY: the unmodified tree driver runs with a temperature (so that the draft
+    probabilities are not one-hot and branches do split) and logs, per level and branch, the candidate list it saw, every split it made and
+    the final token list of every branch.  expand_level is replayed on the logged candidate lists and must ask for exactly the lists the
+    driver logged, make the driver's splits and end with the driver's per-branch token lists.  p_split sits on a x.xxx5 boundary so that
+    the three printed decimals decide every comparison."""
+    import numpy as np
+    from oracle_round import expand_level
+    # -np >= 5: the driver prints min(np + 3, n) >= 8 candidates per list, all that the rule reads
+    rc, out, err, st = _run("llama-speculative-eagle-tree", models, ("-np", str(NB), "--temp", "1.0", "--seed", "3", "--draft-max", str(n_draft),
+                                                                      "--draft-p-split", repr(p_split), "-lv", "5"))
+    rounds = _parse_tree_log(err)
+    if rc != 0:
+        # the reference's stochastic accept walk (temp > 0) dies on some trees (seen: one unsplit branch of full length); everything it
+        # logged up to the last complete drafting round still counts
+        print(f"[drivers] the reference driver exited with {rc} after {len(rounds)} drafting rounds")
+        rounds = rounds[:-1] if rounds and not rounds[-1]["drafts"] else rounds
+    assert len(rounds) >= (8 if rc == 0 else 1), (rc, len(rounds), err[-2000:])
+    n_split = n_multi = 0
+    shapes = set()
+    for ri, r in enumerate(rounds):
+        asked = []
+
+        def cands_of(b, level=None):
+            raise AssertionError
+        drafting, last_node, row = [True] + [False] * (NB - 1), [0] * NB, [0] * NB
+        n_seq, tokens, parent = 1, [-1], [-1]
+        for level in range(n_draft):
+            def cands_of(b, level=level):
+                asked.append((b, level))
+                assert (b, level) in r["cands"], f"round {ri}: the rule reads branch {b} at level {level}, the driver did not"
+                ids, pr = r["cands"][(b, level)]
+                return np.array(ids[:8]), np.array(pr[:8], np.float32), np.array(pr[:8], np.float64)
+            before = n_seq
+            new, n_seq = expand_level(drafting, last_node, row, n_seq, len(tokens), cands_of, NB, n_draft, 8, p_split, 10 ** 6)
+            for tok, par, br in new:
+                tokens.append(tok); parent.append(par); last_node[br] = len(tokens) - 1
+            n_split += n_seq - before
+            if not new or not any(drafting) or len(tokens) > n_draft:
+                break
+        assert sorted(asked) == sorted(r["cands"]), f"round {ri}: candidate lists read {sorted(asked)} vs logged {sorted(r['cands'])}"
+        assert [into for _, into in r["splits"]] == list(range(1, n_seq)), (ri, r["splits"], n_seq)
+        for b in range(n_seq):
+            path, n = [], last_node[b]
+            while n > 0:
+                path.append(tokens[n]); n = parent[n]
+            assert path[::-1] == r["drafts"][b], f"round {ri} branch {b}: {path[::-1]} vs the driver's {r['drafts'][b]}"
+        assert set(r["drafts"]) == set(range(n_seq))
+        n_multi += n_seq > 1
+        shapes.add(tuple(len(r["drafts"][b]) for b in range(n_seq)))
+    print(f"[drivers] tree expansion replayed over {len(rounds)} rounds of the reference driver (draft-max {n_draft}, p_split {p_split}): "
+          f"{n_split} splits, {n_multi} rounds with more than one branch, branch lengths seen {sorted(shapes)}")
+    assert n_split >= len(rounds) // 2
