@@ -716,7 +716,9 @@ static int draft_dev(eb_session *s, cudaStream_t st) {
         if (!fused_io) RC(eb_spec_gather_hidden(d, s->root_feat, s->node_feat, s->ws_h.hidden, E, c.n_branch, st));
         // idle levels (tree full / no branch drafting: the reference leaves its draft loop, speculative-eagle.cpp:627-641) switch themselves off
         static const bool no_gate = getenv("EB_NO_GATE") != nullptr;
-        const bool gated = fused_io && !no_gate;
+        // (every kernel that streams weights or writes the cache takes the gate: the fused glue, the tcgen05 / mma GEMMs of T <= 8, the 32-block GEMM and
+        // the matvec; what stays ungated on a Q4_0 / Q8_0 head — the generic norm kernel, the feature gather / scatter — works on dead rows)
+        const bool gated = !no_gate;
         rc = forward_dev(s->head, s->kv_h, s->ws_h, d->dft_tokens, d->dft_pos, d->dft_bits, s->ws_h.hidden, &d->ctl_head, c.n_branch, !last, st, &ks_h,
                        fused_io ? d : nullptr, s->root_feat, s->node_feat, gated ? &d->gate_fwd : nullptr, gated ? &d->gate_lm : nullptr);
         if (rc) { eb_gate_set(nullptr); return rc; }

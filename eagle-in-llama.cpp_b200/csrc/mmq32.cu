@@ -70,7 +70,8 @@ __device__ __forceinline__ float scale_of(const uint4 &v, int bb) {
 }
 
 template <int FMT, int NT>
-__global__ void __launch_bounds__(128) mmq32_kernel(WPlanes wp, int64_t N, int nbr, ActQ a, float *__restrict__ out, int chunks_per_split) {
+__global__ void __launch_bounds__(128) mmq32_kernel(WPlanes wp, int64_t N, int nbr, ActQ a, float *__restrict__ out, int chunks_per_split, const int *gate) {
+    if (gate_closed(gate)) return;                       // idle draft level (common.cuh "launch gate"): the planes are not read either
     constexpr int TP = NT * 8, PITCH = L32<FMT>::PITCH, STAGE = TP * PITCH + TP * KC * 4;
     extern __shared__ __align__(16) uint8_t smem[];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, t = lane & 3;
@@ -143,7 +144,7 @@ template <int FMT, int NT> size_t smem32() { return 2 * ((size_t)NT * 8 * L32<FM
 
 template <int FMT, int NT>
 int launch32(const WPlanes &wp, int64_t N, int nbr, const ActQ &a, float *planes, int ks, int cps, cudaStream_t st) {
-    mmq32_kernel<FMT, NT><<<dim3((unsigned)cdiv(N, 64), ks), 128, smem32<FMT, NT>(), st>>>(wp, N, nbr, a, planes, cps);
+    mmq32_kernel<FMT, NT><<<dim3((unsigned)cdiv(N, 64), ks), 128, smem32<FMT, NT>(), st>>>(wp, N, nbr, a, planes, cps, eb_gate());
     EB_CHECK_LAUNCH();
     return EB_OK;
 }

@@ -18,7 +18,8 @@ __device__ __forceinline__ int dot16(const int4 &w, const int4 &a, int acc) {
 #define SHR4(v, s) make_int4((int)((uint32_t)(v).x >> (s)), (int)((uint32_t)(v).y >> (s)), (int)((uint32_t)(v).z >> (s)), (int)((uint32_t)(v).w >> (s)))
 
 template <int NC>
-__global__ void __launch_bounds__(128) mmvq_q4_K(const block_q4_K *__restrict__ W, int64_t N, int nbr, ActQ a, int t0, float *__restrict__ y) {
+__global__ void __launch_bounds__(128) mmvq_q4_K(const block_q4_K *__restrict__ W, int64_t N, int nbr, ActQ a, int t0, float *__restrict__ y, const int *gate) {
+    if (gate_closed(gate)) return;
     const int lane = threadIdx.x & 31;
     const int64_t row = (int64_t)blockIdx.x * 4 + (threadIdx.x >> 5);
     if (row >= N) return;
@@ -56,7 +57,8 @@ __global__ void __launch_bounds__(128) mmvq_q4_K(const block_q4_K *__restrict__ 
 }
 
 template <int NC>
-__global__ void __launch_bounds__(128) mmvq_q6_K(WPlanes w, int64_t N, int nbr, ActQ a, int t0, float *__restrict__ y) {
+__global__ void __launch_bounds__(128) mmvq_q6_K(WPlanes w, int64_t N, int nbr, ActQ a, int t0, float *__restrict__ y, const int *gate) {
+    if (gate_closed(gate)) return;
     const int lane = threadIdx.x & 31;
     const int64_t row = (int64_t)blockIdx.x * 4 + (threadIdx.x >> 5);
     if (row >= N) return;
@@ -93,7 +95,8 @@ __global__ void __launch_bounds__(128) mmvq_q6_K(WPlanes w, int64_t N, int nbr, 
 }
 
 template <int NC>
-__global__ void __launch_bounds__(128) mmvq_q4_0(WPlanes w, int64_t N, int nbr, ActQ a, int t0, float *__restrict__ y) {
+__global__ void __launch_bounds__(128) mmvq_q4_0(WPlanes w, int64_t N, int nbr, ActQ a, int t0, float *__restrict__ y, const int *gate) {
+    if (gate_closed(gate)) return;
     const int lane = threadIdx.x & 31;
     const int64_t row = (int64_t)blockIdx.x * 4 + (threadIdx.x >> 5);
     if (row >= N) return;
@@ -119,7 +122,8 @@ __global__ void __launch_bounds__(128) mmvq_q4_0(WPlanes w, int64_t N, int nbr, 
 }
 
 template <int NC>
-__global__ void __launch_bounds__(128) mmvq_q8_0(WPlanes w, int64_t N, int nbr, ActQ a, int t0, float *__restrict__ y) {
+__global__ void __launch_bounds__(128) mmvq_q8_0(WPlanes w, int64_t N, int nbr, ActQ a, int t0, float *__restrict__ y, const int *gate) {
+    if (gate_closed(gate)) return;
     const int lane = threadIdx.x & 31;
     const int64_t row = (int64_t)blockIdx.x * 4 + (threadIdx.x >> 5);
     if (row >= N) return;
@@ -148,10 +152,10 @@ static void launch_nc(int type, const void *W, int64_t N, int64_t K, const ActQ 
     const int nbr = (int)(K / be);
     WPlanes w{(const uint8_t *)W, N * nbr};
     switch (type) {
-        case EB_Q4_K: mmvq_q4_K<NC><<<grid, block, 0, st>>>((const block_q4_K *)W, N, nbr, a, t0, y); break;
-        case EB_Q6_K: mmvq_q6_K<NC><<<grid, block, 0, st>>>(w, N, nbr, a, t0, y); break;
-        case EB_Q4_0: mmvq_q4_0<NC><<<grid, block, 0, st>>>(w, N, nbr, a, t0, y); break;
-        case EB_Q8_0: mmvq_q8_0<NC><<<grid, block, 0, st>>>(w, N, nbr, a, t0, y); break;
+        case EB_Q4_K: mmvq_q4_K<NC><<<grid, block, 0, st>>>((const block_q4_K *)W, N, nbr, a, t0, y, eb_gate()); break;
+        case EB_Q6_K: mmvq_q6_K<NC><<<grid, block, 0, st>>>(w, N, nbr, a, t0, y, eb_gate()); break;
+        case EB_Q4_0: mmvq_q4_0<NC><<<grid, block, 0, st>>>(w, N, nbr, a, t0, y, eb_gate()); break;
+        case EB_Q8_0: mmvq_q8_0<NC><<<grid, block, 0, st>>>(w, N, nbr, a, t0, y, eb_gate()); break;
     }
 }
 
