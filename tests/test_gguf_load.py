@@ -112,3 +112,65 @@ def test_load_gguf_bit_exact_and_same_forward(eb, tmp_path):
     assert np.array_equal(outs[0][0], outs[1][0]) and np.array_equal(outs[0][1], outs[1][1])
     for m in (mt, mh, rt, rh):
         m.free()
+
+
+def _llama_quantize(tmp_path, L=4, seed=83):
+    """an f16 fixture through the reference's OWN llama-quantize (C++ gguf writer, Q4_K_M mixture): the file a user of the reference has"""
+    import subprocess
+    import refround as rr
+    exe = os.path.join(rr.REF, "llama-quantize")
+    if not os.path.exists(exe):
+        pytest.fail("oracle/_ref/llama-quantize is missing: run __graft_entry__.build() where /root/reference is present")
+    src = fx.make_model(**{**HP, "L": L}, ftype=po.F16, seed=seed)
+    f16 = gf.write_gguf(src, str(tmp_path / "f16.gguf"))
+    out = str(tmp_path / "q4km.gguf")
+    r = subprocess.run([exe, f16, out, "Q4_K_M", "2"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    return src, out
+
+
+def test_gguf_probe_reads_llama_quantize_output(tmp_path):
+    """the header parser on a file written by the reference's C++ gguf writer (R/ggml/src/gguf.cpp via llama-quantize), not by gguf-py"""
+    import refround as rr
+    eb = load_package()
+    L = 4
+    src, out = _llama_quantize(tmp_path, L)
+    p = eb.gguf_probe(out)
+    assert (p["E"], p["H"], p["F"], p["V"], p["L"], p["is_eagle"]) == (256, 2, 512, 1024, L, False)
+    assert p["n_tensors"] == len(src["globals"]) + sum(len(d) for d in src["layers"])
+    m = rr.Model(out)
+    want = 0
+    for which, name in gf.GLOBAL_NAMES.items():
+        if which in src["globals"]:
+            shape = gf._shape(src["hparams"], -1, which)
+            want += int(np.prod(shape[:-1], dtype=np.int64)) * po.row_size(m.tensor_type(name), shape[-1])
+    for l in range(L):
+        for which, name in gf.LAYER_NAMES.items():
+            shape = gf._shape(src["hparams"], l, which)
+            want += int(np.prod(shape[:-1], dtype=np.int64)) * po.row_size(m.tensor_type(f"blk.{l}.{name}.weight"), shape[-1])
+    m.free()
+    assert p["bytes"] == want, (p["bytes"], want)
+
+
+@pytest.mark.gpu
+def test_llama_quantize_output_through_own_loader_matches_the_reference_decode(eb, tmp_path):
+    """file on disk written by the reference's own tool -> eb_model_load_gguf -> engine forward, against the reference's loader ->
+    llama_decode on ggml-cpu of the same file: nothing of this repo's fixture code between the file and either side"""
+    import parity as pa
+    import refround as rr
+    from golden_io import nmse
+    _, out = _llama_quantize(tmp_path, 4)
+    rng = np.random.default_rng(11)
+    prompt = rng.integers(3, HP["V"], 24).astype(np.int32)
+    mt = eb.Model.from_gguf(out)
+    s = eb.Session(mt, n_ctx=128, max_nodes=17, use_graph=False)
+    lg, _ = s.forward(0, prompt, np.arange(24))
+    s.free(); mt.free()
+    m = rr.Model(out)
+    c = rr.Context(m, 128)
+    lr = c.decode(prompt, np.arange(24))
+    c.free(); m.free()
+    rel = pa.row_rel(lg, lr)
+    agree = int((lg.argmax(1) == lr.argmax(1)).sum())
+    print(f"[gguf] llama-quantize file, own loader + engine vs reference loader + llama_decode: max rel {rel.max():.2e}, NMSE {nmse(lg, lr):.2e}, greedy ids {agree}/24")
+    assert nmse(lg, lr) <= 2e-3 and rel.max() <= pa.FLIP_REL
