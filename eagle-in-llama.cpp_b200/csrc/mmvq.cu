@@ -17,6 +17,17 @@ __device__ __forceinline__ int dot16(const int4 &w, const int4 &a, int acc) {
 #define AND4(v, m) make_int4((v).x & (m), (v).y & (m), (v).z & (m), (v).w & (m))
 #define SHR4(v, s) make_int4((int)((uint32_t)(v).x >> (s)), (int)((uint32_t)(v).y >> (s)), (int)((uint32_t)(v).z >> (s)), (int)((uint32_t)(v).w >> (s)))
 
+// 6-bit scale / min of sub-block j from the three scale words of a Q4_K header held in registers (q4k_scale_min on bytes would put
+// the header into local memory for the dynamic index)
+__device__ __forceinline__ void q4k_scale_min_reg(int j, uint32_t w0, uint32_t w1, uint32_t w2, int &sc, int &m) {
+    const int sh = 8 * (j & 3);
+    const uint32_t b0 = (w0 >> sh) & 0xFFu, b1 = (w1 >> sh) & 0xFFu, b2 = (w2 >> sh) & 0xFFu;
+    if (j < 4) { sc = (int)(b0 & 63u); m = (int)(b1 & 63u); }
+    else { sc = (int)((b2 & 0xFu) | ((b0 >> 6) << 4)); m = (int)((b2 >> 4) | ((b1 >> 6) << 4)); }
+}
+
+// K-quant rows: 8 lanes per super-block, 4 super-blocks per warp step, and 4 steps (16 super-blocks = one 4096-wide row) requested
+// before the first is used, so every lane has eight 16-byte weight loads in flight instead of two
 template <int NC>
 __global__ void __launch_bounds__(128) mmvq_q4_K(const block_q4_K *__restrict__ W, int64_t N, int nbr, ActQ a, int t0, float *__restrict__ y, const int *gate) {
     if (gate_closed(gate)) return;
@@ -28,27 +39,49 @@ __global__ void __launch_bounds__(128) mmvq_q4_K(const block_q4_K *__restrict__ 
     float acc[NC];
 #pragma unroll
     for (int t = 0; t < NC; t++) acc[t] = 0.f;
-    for (int sb0 = 0; sb0 < nbr; sb0 += 4) {
-        const int sb = sb0 + g;
-        if (sb < nbr) {
-            const int4 hdr = ldg_stream(&wr[sb]);
-            const int4 q = ldg_stream((const uint8_t *)&wr[sb] + 16 + 16 * c);
-            const __half2 dm = *(const __half2 *)&hdr.x;
-            const float dw = __low2float(dm), dmin = __high2float(dm);
-            const uint8_t *sc8 = (const uint8_t *)&hdr.y;
-            int sc_lo, m_lo, sc_hi, m_hi, sc_c, m_c;
-            q4k_scale_min(2 * j, sc8, sc_lo, m_lo); q4k_scale_min(2 * j + 1, sc8, sc_hi, m_hi);
-            q4k_scale_min(c, sc8, sc_c, m_c);
-            const int4 qlo = AND4(q, 0x0F0F0F0F), qhi = AND4(SHR4(q, 4), 0x0F0F0F0F);
+    for (int sbb = 0; sbb < nbr; sbb += 16) {
+        int4 hdr[4], q[4];
+        int4 alo1[4], ahi1[4]; float dx1[4]; __half2 bs1[4];          // NC == 1: the column's operands, requested with the weights
 #pragma unroll
-            for (int t = 0; t < NC; t++) {
-                const int8_t *ap = a.qs + (int64_t)(t0 + t) * a.K + sb * 256 + j * 64 + (c & 1) * 16;
-                const int4 alo = *(const int4 *)ap, ahi = *(const int4 *)(ap + 32);
-                const int isum = dot16(qlo, alo, 0) * sc_lo + dot16(qhi, ahi, 0) * sc_hi;
-                const float dx = a.d[(int64_t)(t0 + t) * nbr + sb];
-                const __half2 bs = *(const __half2 *)(a.bsum + ((int64_t)(t0 + t) * nbr + sb) * 16 + 2 * c);
-                const float bsum = __low2float(bs) + __high2float(bs);
-                acc[t] += (dw * dx) * (float)isum - (dmin * dx) * ((float)m_c * bsum);
+        for (int u = 0; u < 4; u++) {
+            const int sb = sbb + 4 * u + g;
+            hdr[u] = make_int4(0, 0, 0, 0); q[u] = make_int4(0, 0, 0, 0);
+            if (sb < nbr) { hdr[u] = ldg_stream(&wr[sb]); q[u] = ldg_stream((const uint8_t *)&wr[sb] + 16 + 16 * c); }
+            if constexpr (NC == 1) {
+                const int sbc = min(sb, nbr - 1);                      // clamped: the loads need no predicate and can issue at once
+                const int8_t *ap = a.qs + (int64_t)t0 * a.K + sbc * 256 + j * 64 + (c & 1) * 16;
+                alo1[u] = *(const int4 *)ap; ahi1[u] = *(const int4 *)(ap + 32);
+                dx1[u] = a.d[(int64_t)t0 * nbr + sbc];
+                bs1[u] = *(const __half2 *)(a.bsum + ((int64_t)t0 * nbr + sbc) * 16 + 2 * c);
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const int sb = sbb + 4 * u + g;
+            if (sb < nbr) {
+                const __half2 dm = *(const __half2 *)&hdr[u].x;
+                const float dw = __low2float(dm), dmin = __high2float(dm);
+                int sc_lo, m_lo, sc_hi, m_hi, sc_c, m_c;
+                q4k_scale_min_reg(2 * j, (uint32_t)hdr[u].y, (uint32_t)hdr[u].z, (uint32_t)hdr[u].w, sc_lo, m_lo);
+                q4k_scale_min_reg(2 * j + 1, (uint32_t)hdr[u].y, (uint32_t)hdr[u].z, (uint32_t)hdr[u].w, sc_hi, m_hi);
+                q4k_scale_min_reg(c, (uint32_t)hdr[u].y, (uint32_t)hdr[u].z, (uint32_t)hdr[u].w, sc_c, m_c);
+                const int4 qlo = AND4(q[u], 0x0F0F0F0F), qhi = AND4(SHR4(q[u], 4), 0x0F0F0F0F);
+                if constexpr (NC == 1) {
+                    const int isum = dot16(qlo, alo1[u], 0) * sc_lo + dot16(qhi, ahi1[u], 0) * sc_hi;
+                    const float bsum = __low2float(bs1[u]) + __high2float(bs1[u]);
+                    acc[0] += (dw * dx1[u]) * (float)isum - (dmin * dx1[u]) * ((float)m_c * bsum);
+                } else {
+#pragma unroll
+                    for (int t = 0; t < NC; t++) {
+                        const int8_t *ap = a.qs + (int64_t)(t0 + t) * a.K + sb * 256 + j * 64 + (c & 1) * 16;
+                        const int4 alo = *(const int4 *)ap, ahi = *(const int4 *)(ap + 32);
+                        const int isum = dot16(qlo, alo, 0) * sc_lo + dot16(qhi, ahi, 0) * sc_hi;
+                        const float dx = a.d[(int64_t)(t0 + t) * nbr + sb];
+                        const __half2 bs = *(const __half2 *)(a.bsum + ((int64_t)(t0 + t) * nbr + sb) * 16 + 2 * c);
+                        const float bsum = __low2float(bs) + __high2float(bs);
+                        acc[t] += (dw * dx) * (float)isum - (dmin * dx) * ((float)m_c * bsum);
+                    }
+                }
             }
         }
     }
@@ -67,26 +100,49 @@ __global__ void __launch_bounds__(128) mmvq_q6_K(WPlanes w, int64_t N, int nbr, 
     float acc[NC];
 #pragma unroll
     for (int t = 0; t < NC; t++) acc[t] = 0.f;
-    for (int sb0 = 0; sb0 < nbr; sb0 += 4) {
-        const int sb = sb0 + g;
-        if (sb < nbr) {
-            const int64_t blk = row * nbr + sb;
-            const int4 ql = ldg_stream(w.q6k_ql() + blk * 128 + 16 * c);
-            const int4 qh = ldg_stream(w.q6k_qh() + blk * 64 + n * 32 + 16 * (cc & 1));
-            const int8_t *sc = w.q6k_sc() + blk * 16 + 8 * n;
-            const int sc_lo = sc[cc], sc_hi = sc[4 + cc];
-            const float dw = __half2float(w.q6k_d()[blk]);
-            int4 qlo, qhi;
-#define Q6(dst, lw, hw, sh, hsh) dst = __vsubss4((((uint32_t)(lw) >> (sh)) & 0x0F0F0F0Fu) | ((((uint32_t)(hw) >> (hsh)) & 0x03030303u) << 4), 0x20202020u)
-            Q6(qlo.x, ql.x, qh.x, 0, shift); Q6(qlo.y, ql.y, qh.y, 0, shift); Q6(qlo.z, ql.z, qh.z, 0, shift); Q6(qlo.w, ql.w, qh.w, 0, shift);
-            Q6(qhi.x, ql.x, qh.x, 4, shift + 4); Q6(qhi.y, ql.y, qh.y, 4, shift + 4); Q6(qhi.z, ql.z, qh.z, 4, shift + 4); Q6(qhi.w, ql.w, qh.w, 4, shift + 4);
-#undef Q6
+    for (int sbb = 0; sbb < nbr; sbb += 16) {
+        int4 ql[4], qh[4]; int sc_lo[4], sc_hi[4]; float dw[4];
+        int4 alo1[4], ahi1[4]; float dx1[4];                          // NC == 1: the column's operands, requested with the weights
 #pragma unroll
-            for (int t = 0; t < NC; t++) {
-                const int8_t *ap = a.qs + (int64_t)(t0 + t) * a.K + sb * 256 + n * 128 + 16 * cc;
-                const int4 alo = *(const int4 *)ap, ahi = *(const int4 *)(ap + 64);
-                const int isum = dot16(qlo, alo, 0) * sc_lo + dot16(qhi, ahi, 0) * sc_hi;
-                acc[t] += (dw * a.d[(int64_t)(t0 + t) * nbr + sb]) * (float)isum;
+        for (int u = 0; u < 4; u++) {
+            const int sb = sbb + 4 * u + g;
+            ql[u] = make_int4(0, 0, 0, 0); qh[u] = make_int4(0, 0, 0, 0); sc_lo[u] = sc_hi[u] = 0; dw[u] = 0.f;
+            if constexpr (NC == 1) {
+                const int sbc = min(sb, nbr - 1);
+                const int8_t *ap = a.qs + (int64_t)t0 * a.K + sbc * 256 + n * 128 + 16 * cc;
+                alo1[u] = *(const int4 *)ap; ahi1[u] = *(const int4 *)(ap + 64);
+                dx1[u] = a.d[(int64_t)t0 * nbr + sbc];
+            }
+            if (sb < nbr) {
+                const int64_t blk = row * nbr + sb;
+                ql[u] = ldg_stream(w.q6k_ql() + blk * 128 + 16 * c);
+                qh[u] = ldg_stream(w.q6k_qh() + blk * 64 + n * 32 + 16 * (cc & 1));
+                const int8_t *sc = w.q6k_sc() + blk * 16 + 8 * n;
+                sc_lo[u] = sc[cc]; sc_hi[u] = sc[4 + cc];
+                dw[u] = __half2float(w.q6k_d()[blk]);
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const int sb = sbb + 4 * u + g;
+            if (sb < nbr) {
+                int4 qlo, qhi;
+#define Q6(dst, lw, hw, sh, hsh) dst = __vsubss4((((uint32_t)(lw) >> (sh)) & 0x0F0F0F0Fu) | ((((uint32_t)(hw) >> (hsh)) & 0x03030303u) << 4), 0x20202020u)
+                Q6(qlo.x, ql[u].x, qh[u].x, 0, shift); Q6(qlo.y, ql[u].y, qh[u].y, 0, shift); Q6(qlo.z, ql[u].z, qh[u].z, 0, shift); Q6(qlo.w, ql[u].w, qh[u].w, 0, shift);
+                Q6(qhi.x, ql[u].x, qh[u].x, 4, shift + 4); Q6(qhi.y, ql[u].y, qh[u].y, 4, shift + 4); Q6(qhi.z, ql[u].z, qh[u].z, 4, shift + 4); Q6(qhi.w, ql[u].w, qh[u].w, 4, shift + 4);
+#undef Q6
+                if constexpr (NC == 1) {
+                    const int isum = dot16(qlo, alo1[u], 0) * sc_lo[u] + dot16(qhi, ahi1[u], 0) * sc_hi[u];
+                    acc[0] += (dw[u] * dx1[u]) * (float)isum;
+                } else {
+#pragma unroll
+                    for (int t = 0; t < NC; t++) {
+                        const int8_t *ap = a.qs + (int64_t)(t0 + t) * a.K + sb * 256 + n * 128 + 16 * cc;
+                        const int4 alo = *(const int4 *)ap, ahi = *(const int4 *)(ap + 64);
+                        const int isum = dot16(qlo, alo, 0) * sc_lo[u] + dot16(qhi, ahi, 0) * sc_hi[u];
+                        acc[t] += (dw[u] * a.d[(int64_t)(t0 + t) * nbr + sb]) * (float)isum;
+                    }
+                }
             }
         }
     }
@@ -103,6 +159,7 @@ __global__ void __launch_bounds__(128) mmvq_q4_0(WPlanes w, int64_t N, int nbr, 
     float acc[NC];
 #pragma unroll
     for (int t = 0; t < NC; t++) acc[t] = 0.f;
+#pragma unroll 4
     for (int b = lane; b < nbr; b += 32) {
         const int64_t blk = row * nbr + b;
         const int4 q = ldg_stream(w.q40_qs() + blk * 16);
@@ -130,6 +187,7 @@ __global__ void __launch_bounds__(128) mmvq_q8_0(WPlanes w, int64_t N, int nbr, 
     float acc[NC];
 #pragma unroll
     for (int t = 0; t < NC; t++) acc[t] = 0.f;
+#pragma unroll 4
     for (int hb = lane; hb < nbr * 2; hb += 32) {          // half blocks of 16 quants
         const int b = hb >> 1;
         const int64_t blk = row * nbr + b;

@@ -104,6 +104,24 @@ def test_mul_mat_draft_shapes(eb, t, N, K, T):
     assert rel_max(got, want) < 2e-5
 
 
+@pytest.mark.parametrize("t", [po.Q4_K, po.Q6_K])
+@pytest.mark.parametrize("T", [1, 2, 3, 4, 7, 8])
+@pytest.mark.parametrize("K", [2816, 4096, 11008])
+def test_mul_mat_kquant_matvec_ragged(eb, t, T, K):
+    """the dequant-dot matvec of the K-quants (mmvq.cu) at every column count it is instantiated for: a row count that no GEMM kernel
+    takes (not a multiple of 16), K of 11 / 16 / 43 super-blocks (partial 16-super-block steps, a last step of 3 groups), random block
+    bytes, a zero activation super-block"""
+    rng = np.random.default_rng(11 * t + T + K)
+    N = 203
+    raw = fx.random_blocks(t, N * K, rng)
+    X = rng.normal(0, 1, (T, K)).astype(np.float32)
+    X[T - 1, 256:512] = 0
+    got = eb.mul_mat(eb.Weights(t, raw, N, K), X)
+    want = po.oracle().mul_mat(t, raw, N, K, X)
+    assert got.shape == want.shape
+    assert rel_max(got, want) < 2e-5
+
+
 @pytest.mark.parametrize("t", [po.Q4_0, po.Q8_0])
 @pytest.mark.parametrize("T", [2, 17, 40, 65, 72, 128])
 def test_mul_mat_32block_gemm_ragged(eb, t, T):
